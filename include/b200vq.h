@@ -1,0 +1,243 @@
+/* b200vq.h — C ABI of the B200-native quantize-and-search hot path.
+ *
+ * This is the drop-in boundary below the reference's Python quantizer classes.
+ * Every entry point replaces one arithmetic provider call the reference makes
+ * (faiss via SWIG, numpy, or the `saq` pybind module); the reference file:line
+ * each one stands in for is cited beside it (paths relative to the reference
+ * repository root, Human-Augment-Analytics/vector-quantization).
+ *
+ * Conventions
+ *   - All data pointers are DEVICE pointers unless the name ends in `_host`.
+ *   - Matrices are row-major, C-contiguous. `n` counts rows (vectors).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *     Calls are asynchronous with respect to the host; no hidden allocation,
+ *     no hidden synchronisation. Scratch buffers are caller-owned; their
+ *     required sizes come from the matching *_scratch_bytes() function.
+ *   - Return value: B200VQ_OK (0) or a negative status; on error
+ *     b200vq_last_error() returns a thread-local, NUL-terminated message.
+ *   - Top-k results are ordered by (value ascending, id ascending) for L2 and
+ *     by (value descending, id ascending) for inner product; ids are uint32
+ *     row indices local to the scanned shard (callers add the shard offset).
+ */
+#ifndef B200VQ_H
+#define B200VQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200VQ_OK 0
+#define B200VQ_ERR_INVALID (-1)     /* bad argument / unsupported shape */
+#define B200VQ_ERR_CUDA (-2)        /* a CUDA runtime call failed        */
+#define B200VQ_ERR_UNSUPPORTED (-3) /* valid request the build cannot serve */
+
+#define B200VQ_METRIC_L2 0
+#define B200VQ_METRIC_IP 1
+
+const char* b200vq_last_error(void);
+/* ABI version: bumped whenever a signature below changes. */
+int b200vq_abi_version(void);
+/* Compute capability of the current device as major*10+minor (100 on B200), <0 on error. */
+int b200vq_device_cc(void);
+
+/* ------------------------------------------------------------------ PQ ---
+ * centroids: (M, ksub, dsub) fp32, the layout of faiss ProductQuantizer.centroids
+ * (reference: src/haag_vq/methods/product_quantization.py:70-73). D = M*dsub.
+ * cnorm: (M, ksub) fp32 squared norms of the centroids (b200vq_pq_centroid_norms).
+ */
+
+/* ||c_{m,k}||^2 for every centroid. */
+int b200vq_pq_centroid_norms(const float* centroids, int M, int ksub, int dsub,
+                             float* cnorm, void* stream);
+
+/* Nearest-centroid assignment, exact fp32 SIMT path (any dsub, ksub <= 256).
+ * Replaces faiss ProductQuantizer.compute_codes as called at
+ * src/haag_vq/methods/product_quantization.py:76-80 and
+ * src/haag_vq/methods/optimized_product_quantization.py:30-31.
+ * x: (n, ldx) fp32 with ldx >= D (row stride in floats); codes: (n, M) uint8.
+ * Distance = (||x_m||^2 + ||c||^2) - 2 x_m.c in fp32, ties -> lowest index.
+ * If sqdist != NULL it receives (n, M) fp32 winning distances. */
+int b200vq_pq_assign_f32(const float* x, int64_t n, int64_t ldx, const float* centroids,
+                         const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
+                         float* sqdist, void* stream);
+
+/* Tensor-core assignment (tcgen05 kind::tf32 screen + exact fp32 re-rank of the
+ * candidates inside the TF32 error margin). Same contract and results as
+ * b200vq_pq_assign_f32. Requires ksub == 256, dsub % 8 == 0, x 16-byte aligned,
+ * ldx % 4 == 0. scratch: b200vq_pq_assign_tc_scratch_bytes(n, M) bytes.
+ * stats (optional, 2 x uint64 device): [0] += pairs re-ranked, [1] += candidates. */
+size_t b200vq_pq_assign_tc_scratch_bytes(int64_t n, int M);
+int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const float* centroids,
+                        const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
+                        void* scratch, size_t scratch_bytes, unsigned long long* stats,
+                        void* stream);
+
+/* Decode: out[i, m*dsub:(m+1)*dsub] = centroids[m, codes[i,m], :].
+ * Replaces faiss ProductQuantizer.decode (product_quantization.py:82-86). */
+int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* centroids, int M, int ksub,
+                     int dsub, float* out, int64_t ldo, void* stream);
+
+/* Decode selected rows: out[j] = decode(codes[ids[j]]) — the adapter's
+ * reconstruct(ids) (src/haag_vq/benchmarks/quantizer_adapters.py:48-54). */
+int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, int64_t n_ids,
+                         const float* centroids, int M, int ksub, int dsub, float* out,
+                         int64_t ldo, void* stream);
+
+/* One Lloyd accumulation pass for all M sub-quantizers (k-means inside
+ * faiss ProductQuantizer.train, product_quantization.py:67-68):
+ * sums (M,ksub,dsub) fp32 and counts (M,ksub) int32 must be zeroed by the
+ * caller; codes are the assignments of x under the current centroids. */
+int b200vq_pq_kmeans_accumulate(const float* x, int64_t n, int64_t ldx, const uint8_t* codes,
+                                int M, int ksub, int dsub, float* sums, int* counts,
+                                void* stream);
+/* centroids = sums / counts; empty clusters are re-seeded by splitting the
+ * currently largest cluster with the +-1/1024 perturbation faiss uses.
+ * n_split (device int, optional) receives the number of re-seeded clusters. */
+int b200vq_pq_kmeans_finalize(const float* sums, int* counts, int M, int ksub, int dsub,
+                              float* centroids, int* n_split, void* stream);
+
+/* Sum over rows and sub-quantizers of the squared distance to the assigned
+ * centroid (the k-means objective / reconstruction SSE). out: 1 x double, +=. */
+int b200vq_pq_sse(const float* x, int64_t n, int64_t ldx, const uint8_t* codes,
+                  const float* centroids, int M, int ksub, int dsub, double* out,
+                  void* stream);
+
+/* ----------------------------------------------------------------- ADC ---
+ * Per-query look-up tables: lut[q, m, k] = ||q_m - c_{m,k}||^2 (L2) or q_m.c_{m,k} (IP).
+ * This is the code-domain equivalent of the reference's decompress-then-distance
+ * search (src/haag_vq/methods/search/flat_quantized_index.py:57-68) and of the ADC
+ * inner loop of bench/ffd_speed.cpp:87-127. */
+int b200vq_adc_lut(const float* queries, int nq, int64_t ldq, const float* centroids, int M,
+                   int ksub, int dsub, int metric, float* lut, void* stream);
+
+/* Scan (n, M) uint8 codes against nq LUTs and keep the best k per query.
+ * score(q, i) = sum_m lut[q, m, codes[i, m]] (+ bias[i] if bias != NULL).
+ * out_vals (nq, k) fp32, out_ids (nq, k) uint32; rows with fewer than k hits
+ * are padded with +inf/-inf and id 0xffffffff. k <= 128.
+ * scratch: b200vq_adc_scan_scratch_bytes(n, nq, k). */
+size_t b200vq_adc_scan_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_adc_scan_topk(const uint8_t* codes, int64_t n, int M, int ksub, const float* lut,
+                         int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                         void* scratch, size_t scratch_bytes, void* stream);
+
+/* Same scan over the conflict-free "scan layout" produced by
+ * b200vq_pq_codes_to_scan_layout (blocks of 32 rows, byte s of lane i holds
+ * sub-quantizer (i+s) mod 32 of the 32-wide group). Requires M % 32 == 0. */
+int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, int M, uint8_t* out,
+                                   void* stream);
+int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksub,
+                             const float* lut, int nq, int metric, int k, float* out_vals,
+                             uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                             void* stream);
+
+/* ---------------------------------------------------- exact flat search ---
+ * Exact top-k of queries against raw fp32 rows (faiss IndexFlatL2/IndexFlatIP.search:
+ * src/haag_vq/benchmarks/exact_search.py:44-51,72-77, search_bench.py:42-56).
+ * L2: ||q||^2 + ||x||^2 - 2 q.x (fp32); IP: q.x. xnorm (n) may be NULL for IP.
+ * row_scale (n, optional): x rows are multiplied by row_scale[i] before the
+ * product (the 1/||x|| pre-scaling of build_scaled_ip_index). */
+size_t b200vq_flat_topk_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_flat_topk(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                     const float* row_scale, const float* queries, int nq, int64_t ldq,
+                     int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
+                     size_t scratch_bytes, void* stream);
+
+/* Row squared norms (compute_exact_norms, exact_search.py:20-24, before the sqrt). */
+int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out, void* stream);
+
+/* Merge P sorted partial lists per query into the final top-k.
+ * in_vals (nq, P, k) fp32 ascending-better after sign handling by `metric`,
+ * in_ids (nq, P, k) int64 global ids (-1 = empty). Used for the per-shard
+ * merge after the NCCL all-gather. out_ids int64. */
+int b200vq_topk_merge(const float* in_vals, const int64_t* in_ids, int nq, int P, int k,
+                      int metric, float* out_vals, int64_t* out_ids, void* stream);
+
+/* ------------------------------------------------------------------ SQ ---
+ * Reference: src/haag_vq/methods/scalar_quantization.py:37-90. */
+/* Column-wise min / max; vmin/vmax (D) must be pre-filled with +inf/-inf
+ * (so that several calls accumulate over row batches / shards). */
+int b200vq_sq_minmax(const float* x, int64_t n, int64_t ldx, int D, float* vmin, float* vmax,
+                     void* stream);
+/* bits in {4, 8, 16}. codes: (n, D) u8 | (n, ceil(D/2)) u8 (even dim in the high
+ * nibble) | (n, D) u16. q = rint((x-min)/(max-min+1e-8f) * (2^bits-1)), fp32,
+ * each operation rounded separately like numpy; out-of-range values saturate. */
+int b200vq_sq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
+                     const float* vmax, int bits, void* codes, void* stream);
+int b200vq_sq_decode(const void* codes, int64_t n, int D, const float* vmin, const float* vmax,
+                     int bits, float* out, int64_t ldo, void* stream);
+
+/* Segmented variable-bit scalar quantiser (the `SAQ(num_bits|total_bits,
+ * allowed_bits, n_segments)` CLI contract, src/haag_vq/benchmarks/sweep.py:418-430).
+ * dim_bits (D) int32 in [0, 8]: bits of every dimension (constant inside a
+ * segment). bit_offset (D+1) int32: exclusive prefix sum of dim_bits. Codes are an
+ * MSB-first bit string of bit_offset[D] bits per row, padded to code_bytes. */
+int b200vq_saq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
+                      const float* vmax, const int* dim_bits, const int* bit_offset,
+                      int code_bytes, uint8_t* codes, void* stream);
+int b200vq_saq_decode(const uint8_t* codes, int64_t n, int D, const float* vmin,
+                      const float* vmax, const int* dim_bits, const int* bit_offset,
+                      int code_bytes, float* out, int64_t ldo, void* stream);
+
+/* ------------------------------------------------------ Extended RaBitQ ---
+ * Reference: src/haag_vq/methods/extended_rabitq.py:125-198 (fp64 numpy).
+ * s = ((x-c)/||x-c||) P sqrt(D) is produced by the caller (rotation GEMM);
+ * these kernels do the per-row tail. `srot` (n, D) fp64 rotated+scaled rows,
+ * `nrm` (n) fp64 residual norms, levels (2^B) fp64 sorted, bounds (2^B-1) fp64
+ * mid-points. codes (n, ceil(D*B/8)+8) u8: MSB-first B-bit indices, then
+ * float32 nrm, float32 t. */
+int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_t n, int D, int B,
+                        const double* levels, const double* bounds, uint8_t* codes,
+                        void* stream);
+/* Unpack: shat (n, D) fp64 = levels[idx]/sqrt(D)*t ; nrm_out (n) fp64. The caller
+ * applies P^T, the norm and the centroid. */
+int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B, const double* levels,
+                          double* shat, double* nrm_out, void* stream);
+/* Code-domain estimator scan: <s_hat, qrot> per (query, code) with a per-query
+ * level LUT, score = ||q-c||^2 + nrm^2 - 2 nrm t/sqrt(D) <levels[idx], qrot>  (L2)
+ * or the inner-product analogue. qrot (nq, D) fp32 = (q-c) P. */
+size_t b200vq_erabitq_scan_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
+                             const float* qrot, const float* qconst, int nq, int metric, int k,
+                             float* out_vals, uint32_t* out_ids, void* scratch,
+                             size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------- 1-bit RaBitQ ---
+ * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
+ * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):
+ * code = ceil(D/8) sign bytes of (x - centroid), LSB-first, + {float
+ * or_minus_c_l2sqr, float dp_multiplier}. */
+int b200vq_rabitq1_encode(const float* x, int64_t n, int64_t ldx, int D, const float* centroid,
+                          int metric, uint8_t* codes, void* stream);
+int b200vq_rabitq1_decode(const uint8_t* codes, int64_t n, int D, const float* centroid,
+                          float* out, int64_t ldo, void* stream);
+/* Query preparation: residual, qb-bit scalar quantisation, bit-plane transpose.
+ * planes (nq, qb, W) uint32 with W = ceil(D/32); qfac (nq, 8) fp32:
+ * {c1, c2, c34, qr_to_c_l2sqr, qr_norm_l2sqr, 0, 0, 0}. qb in [1, 8]. */
+int b200vq_rabitq1_prepare_queries(const float* queries, int nq, int64_t ldq, int D,
+                                   const float* centroid, int qb, uint32_t* planes, float* qfac,
+                                   void* stream);
+/* AND+popcount estimator scan with top-k. */
+size_t b200vq_rabitq1_scan_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
+                             const float* qfac, int nq, int qb, int metric, int k,
+                             float* out_vals, uint32_t* out_ids, void* scratch,
+                             size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------ utilities ---
+ * Deterministic synthetic rows for throughput runs (Philox-4x32-10 keyed by
+ * (seed, global row, column/4); anisotropic N(0,1)*scale[col], optional row
+ * L2-normalisation). Used so 53M x 1024 never crosses PCIe. */
+int b200vq_synth_rows(float* out, int64_t n, int64_t ldo, int D, int64_t row0, uint64_t seed,
+                      const float* col_scale, int normalize, void* stream);
+
+/* Per-element squared error sum between two (n, D) matrices: out (1 double) +=. */
+int b200vq_sq_err_sum(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t n, int D,
+                      double* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VQ_H */

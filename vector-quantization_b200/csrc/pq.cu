@@ -1,0 +1,413 @@
+// Product-quantizer kernels (exact fp32 SIMT paths): centroid norms, nearest-
+// centroid assignment, decode, Lloyd accumulation/finalisation, SSE, ADC LUTs.
+//
+// Reference semantics being reproduced (faiss ProductQuantizer as driven by
+// src/haag_vq/methods/product_quantization.py:58-86 of the reference):
+//   compute_codes : argmin_k (||x_m||^2 + ||c_mk||^2) - 2 x_m.c_mk  in fp32,
+//                   negative distances clamped to 0, first index wins ties
+//   decode        : concatenation of the selected centroids
+//   train         : per-sub-quantizer Lloyd iterations
+#include "common.cuh"
+
+namespace b200vq {
+
+// ------------------------------------------------------- centroid norms ---
+__global__ void pq_centroid_norms_kernel(const float* __restrict__ c, int total, int dsub,
+                                         float* __restrict__ out) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const float* p = c + (size_t)idx * dsub;
+    float acc = 0.f;
+    for (int i = 0; i < dsub; ++i) acc = __fmaf_rn(p[i], p[i], acc);
+    out[idx] = acc;
+}
+
+// ----------------------------------------------------- exact assignment ---
+// One CTA = R rows x one sub-quantizer. Thread r owns row r and walks the
+// centroids in blocks of KB, accumulating KB dot products in registers with a
+// sequential fp32 FMA chain over the sub-vector (deterministic order).
+template <int KB>
+__global__ void pq_assign_simt_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
+                                      const float* __restrict__ centroids,
+                                      const float* __restrict__ cnorm, int M, int ksub, int dsub,
+                                      uint8_t* __restrict__ codes, float* __restrict__ sqdist) {
+    extern __shared__ float smem[];
+    const int R = blockDim.x;
+    const int tid = threadIdx.x;
+    const int m = blockIdx.y;
+    const int64_t row0 = (int64_t)blockIdx.x * R;
+    float* xs = smem;                          // [dsub][R+1]
+    float* cs = xs + (size_t)dsub * (R + 1);   // [dsub][KB]
+
+    for (int idx = tid; idx < R * dsub; idx += R) {
+        int r = idx / dsub, i = idx - r * dsub;
+        int64_t row = row0 + r;
+        float v = 0.f;
+        if (row < n) v = x[row * ldx + (int64_t)m * dsub + i];
+        xs[i * (R + 1) + r] = v;
+    }
+    __syncthreads();
+
+    float xn = 0.f;
+    for (int i = 0; i < dsub; ++i) {
+        float v = xs[i * (R + 1) + tid];
+        xn = __fmaf_rn(v, v, xn);
+    }
+
+    float best = __int_as_float(0x7f800000);
+    int bestk = 0;
+    const float* cm = centroids + (size_t)m * ksub * dsub;
+    const float* cnm = cnorm + (size_t)m * ksub;
+
+    for (int k0 = 0; k0 < ksub; k0 += KB) {
+        __syncthreads();
+        for (int idx = tid; idx < KB * dsub; idx += R) {
+            int kk = idx / dsub, i = idx - kk * dsub;
+            float v = 0.f;
+            if (k0 + kk < ksub) v = cm[(size_t)(k0 + kk) * dsub + i];
+            cs[i * KB + kk] = v;
+        }
+        __syncthreads();
+
+        float acc[KB];
+#pragma unroll
+        for (int j = 0; j < KB; ++j) acc[j] = 0.f;
+        for (int i = 0; i < dsub; ++i) {
+            float xv = xs[i * (R + 1) + tid];
+            const float4* c4 = reinterpret_cast<const float4*>(cs + i * KB);
+#pragma unroll
+            for (int j4 = 0; j4 < KB / 4; ++j4) {
+                float4 c = c4[j4];
+                acc[4 * j4 + 0] = __fmaf_rn(xv, c.x, acc[4 * j4 + 0]);
+                acc[4 * j4 + 1] = __fmaf_rn(xv, c.y, acc[4 * j4 + 1]);
+                acc[4 * j4 + 2] = __fmaf_rn(xv, c.z, acc[4 * j4 + 2]);
+                acc[4 * j4 + 3] = __fmaf_rn(xv, c.w, acc[4 * j4 + 3]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+            if (k0 + j < ksub) {
+                float d = __fmaf_rn(-2.f, acc[j], __fadd_rn(xn, cnm[k0 + j]));
+                d = fmaxf(d, 0.f);
+                if (d < best) {
+                    best = d;
+                    bestk = k0 + j;
+                }
+            }
+        }
+    }
+    int64_t row = row0 + tid;
+    if (row < n) {
+        codes[row * M + m] = (uint8_t)bestk;
+        if (sqdist) sqdist[row * M + m] = best;
+    }
+}
+
+// ---------------------------------------------------------------- decode ---
+template <bool BY_ID>
+__global__ void pq_decode_kernel(const uint8_t* __restrict__ codes, const int64_t* __restrict__ ids,
+                                 int64_t n, const float* __restrict__ centroids, int M, int ksub,
+                                 int dsub, float* __restrict__ out, int64_t ldo) {
+    const int D = M * dsub;
+    const int64_t total = n * (int64_t)D;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int col = (int)(e - row * D);
+        int m = col / dsub, i = col - m * dsub;
+        int64_t src = BY_ID ? ids[row] : row;
+        int code = codes[src * M + m];
+        out[row * ldo + col] = centroids[((size_t)m * ksub + code) * dsub + i];
+    }
+}
+
+// 128-bit variant: one thread moves 4 consecutive floats of one sub-vector.
+template <bool BY_ID>
+__global__ void pq_decode_v4_kernel(const uint8_t* __restrict__ codes,
+                                    const int64_t* __restrict__ ids, int64_t n,
+                                    const float* __restrict__ centroids, int M, int ksub, int dsub,
+                                    float* __restrict__ out, int64_t ldo) {
+    const int D4 = (M * dsub) >> 2;
+    const int dsub4 = dsub >> 2;
+    const int64_t total = n * (int64_t)D4;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D4;
+        int c4 = (int)(e - row * D4);
+        int m = c4 / dsub4, i4 = c4 - m * dsub4;
+        int64_t src = BY_ID ? ids[row] : row;
+        int code = codes[src * M + m];
+        const float4* cp =
+            reinterpret_cast<const float4*>(centroids + ((size_t)m * ksub + code) * dsub) + i4;
+        reinterpret_cast<float4*>(out + row * ldo)[c4] = __ldg(cp);
+    }
+}
+
+// --------------------------------------------------------------- k-means ---
+__global__ void pq_kmeans_accumulate_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
+                                            const uint8_t* __restrict__ codes, int M, int ksub,
+                                            int dsub, float* __restrict__ sums,
+                                            int* __restrict__ counts) {
+    const int D = M * dsub;
+    const int64_t total = n * (int64_t)D;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int col = (int)(e - row * D);
+        int m = col / dsub, i = col - m * dsub;
+        int code = codes[row * M + m];
+        size_t cidx = (size_t)m * ksub + code;
+        atomicAdd(&sums[cidx * dsub + i], x[row * ldx + col]);
+        if (i == 0) atomicAdd(&counts[cidx], 1);
+    }
+}
+
+// One CTA per sub-quantizer. Empty clusters are re-seeded by splitting the
+// largest cluster (deterministic restatement of faiss' split_clusters, which
+// draws the donor at random: Clustering.cpp, EPS = 1/1024).
+__global__ void pq_kmeans_finalize_kernel(const float* __restrict__ sums, int* __restrict__ counts,
+                                          int ksub, int dsub, float* __restrict__ centroids,
+                                          int* __restrict__ n_split) {
+    const int m = blockIdx.x;
+    const float* s = sums + (size_t)m * ksub * dsub;
+    int* cnt = counts + (size_t)m * ksub;
+    float* c = centroids + (size_t)m * ksub * dsub;
+    for (int idx = threadIdx.x; idx < ksub * dsub; idx += blockDim.x) {
+        int k = idx / dsub;
+        int h = cnt[k];
+        if (h > 0) c[idx] = s[idx] * (1.0f / (float)h);
+    }
+    __syncthreads();
+    __shared__ int s_donor;
+    int nsplit = 0;
+    for (int ci = 0; ci < ksub; ++ci) {
+        if (cnt[ci] != 0) continue;  // uniform: everybody reads the same global value
+        if (threadIdx.x == 0) {
+            int best = 0, bi = 0;
+            for (int k = 0; k < ksub; ++k)
+                if (cnt[k] > best) {
+                    best = cnt[k];
+                    bi = k;
+                }
+            s_donor = bi;
+        }
+        __syncthreads();
+        const int cj = s_donor;
+        const float EPS = 1.f / 1024.f;
+        for (int j = threadIdx.x; j < dsub; j += blockDim.x) {
+            float v = c[(size_t)cj * dsub + j];
+            if ((j & 1) == 0) {
+                c[(size_t)ci * dsub + j] = v * (1.f + EPS);
+                c[(size_t)cj * dsub + j] = v * (1.f - EPS);
+            } else {
+                c[(size_t)ci * dsub + j] = v * (1.f - EPS);
+                c[(size_t)cj * dsub + j] = v * (1.f + EPS);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int h = cnt[cj];
+            cnt[ci] = h / 2;
+            cnt[cj] = h - h / 2;
+            __threadfence_block();
+        }
+        __syncthreads();
+        ++nsplit;
+    }
+    if (threadIdx.x == 0 && n_split && nsplit) atomicAdd(n_split, nsplit);
+}
+
+__global__ void pq_sse_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
+                              const uint8_t* __restrict__ codes,
+                              const float* __restrict__ centroids, int M, int ksub, int dsub,
+                              double* __restrict__ out) {
+    const int D = M * dsub;
+    const int64_t total = n * (int64_t)D;
+    double acc = 0.0;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int col = (int)(e - row * D);
+        int m = col / dsub, i = col - m * dsub;
+        int code = codes[row * M + m];
+        float d = x[row * ldx + col] - centroids[((size_t)m * ksub + code) * dsub + i];
+        acc += (double)d * (double)d;
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
+    __shared__ double part[32];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) part[w] = acc;
+    __syncthreads();
+    if (w == 0) {
+        double v = (lane < (blockDim.x >> 5)) ? part[lane] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+        if (lane == 0) atomicAdd(out, v);
+    }
+}
+
+// --------------------------------------------------------------- ADC LUT ---
+// grid (nq, M); thread k computes lut[q, m, k] with a sequential fp32 chain.
+__global__ void adc_lut_kernel(const float* __restrict__ queries, int64_t ldq,
+                               const float* __restrict__ centroids, int M, int ksub, int dsub,
+                               int metric, float* __restrict__ lut) {
+    extern __shared__ float qs[];
+    const int q = blockIdx.x, m = blockIdx.y;
+    for (int i = threadIdx.x; i < dsub; i += blockDim.x)
+        qs[i] = queries[(int64_t)q * ldq + (int64_t)m * dsub + i];
+    __syncthreads();
+    for (int k = threadIdx.x; k < ksub; k += blockDim.x) {
+        const float* c = centroids + ((size_t)m * ksub + k) * dsub;
+        float acc = 0.f;
+        if (metric == B200VQ_METRIC_L2) {
+            for (int i = 0; i < dsub; ++i) {
+                float d = __fsub_rn(qs[i], c[i]);
+                acc = __fmaf_rn(d, d, acc);
+            }
+        } else {
+            for (int i = 0; i < dsub; ++i) acc = __fmaf_rn(qs[i], c[i], acc);
+        }
+        lut[((size_t)q * M + m) * ksub + k] = acc;
+    }
+}
+
+}  // namespace b200vq
+
+using namespace b200vq;
+
+extern "C" int b200vq_pq_centroid_norms(const float* centroids, int M, int ksub, int dsub,
+                                        float* cnorm, void* stream) {
+    VQ_CHECK_ARG(centroids && cnorm && M > 0 && ksub > 0 && dsub > 0, "pq_centroid_norms: bad args");
+    int total = M * ksub;
+    pq_centroid_norms_kernel<<<(total + 255) / 256, 256, 0, as_stream(stream)>>>(centroids, total,
+                                                                                 dsub, cnorm);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_pq_assign_f32(const float* x, int64_t n, int64_t ldx, const float* centroids,
+                                    const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
+                                    float* sqdist, void* stream) {
+    VQ_CHECK_ARG(x && centroids && cnorm && codes, "pq_assign_f32: null pointer");
+    VQ_CHECK_ARG(n >= 0 && M > 0 && dsub > 0 && ksub > 0 && ksub <= 256,
+                 "pq_assign_f32: need n>=0, M>0, dsub>0, 0<ksub<=256 (got n=%lld M=%d ksub=%d dsub=%d)",
+                 (long long)n, M, ksub, dsub);
+    VQ_CHECK_ARG(ldx >= (int64_t)M * dsub, "pq_assign_f32: ldx < D");
+    VQ_CHECK_ARG(M <= 65535, "pq_assign_f32: M > 65535");
+    if (n == 0) return B200VQ_OK;
+    constexpr int KB = 16;
+    int R = 128;
+    auto need = [&](int r) { return ((size_t)dsub * (r + 1) + (size_t)dsub * KB) * sizeof(float); };
+    while (R > 32 && need(R) > 200 * 1024) R >>= 1;
+    VQ_CHECK_ARG(need(R) <= 200 * 1024, "pq_assign_f32: dsub=%d too large for the SIMT path", dsub);
+    size_t smem = need(R);
+    VQ_CUDA(cudaFuncSetAttribute(pq_assign_simt_kernel<KB>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((n + R - 1) / R), (unsigned)M);
+    pq_assign_simt_kernel<KB><<<grid, R, smem, as_stream(stream)>>>(x, n, ldx, centroids, cnorm, M,
+                                                                    ksub, dsub, codes, sqdist);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+static inline int grid_for(int64_t work, int block, int waves = 8) {
+    int64_t g = (work + block - 1) / block;
+    int64_t cap = (int64_t)device_sm_count() * waves;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+extern "C" int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* centroids, int M,
+                                int ksub, int dsub, float* out, int64_t ldo, void* stream) {
+    VQ_CHECK_ARG(codes && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+                 "pq_decode: bad args");
+    VQ_CHECK_ARG(ldo >= (int64_t)M * dsub, "pq_decode: ldo < D");
+    if (n == 0) return B200VQ_OK;
+    bool v4 = (dsub % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
+              (((uintptr_t)centroids & 15) == 0);
+    if (v4) {
+        int64_t work = n * (int64_t)(M * dsub / 4);
+        pq_decode_v4_kernel<false><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
+            codes, nullptr, n, centroids, M, ksub, dsub, out, ldo);
+    } else {
+        int64_t work = n * (int64_t)(M * dsub);
+        pq_decode_kernel<false><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
+            codes, nullptr, n, centroids, M, ksub, dsub, out, ldo);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, int64_t n_ids,
+                                    const float* centroids, int M, int ksub, int dsub, float* out,
+                                    int64_t ldo, void* stream) {
+    VQ_CHECK_ARG(codes && ids && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n_ids >= 0,
+                 "pq_decode_ids: bad args");
+    VQ_CHECK_ARG(ldo >= (int64_t)M * dsub, "pq_decode_ids: ldo < D");
+    if (n_ids == 0) return B200VQ_OK;
+    bool v4 = (dsub % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
+              (((uintptr_t)centroids & 15) == 0);
+    if (v4) {
+        int64_t work = n_ids * (int64_t)(M * dsub / 4);
+        pq_decode_v4_kernel<true><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
+            codes, ids, n_ids, centroids, M, ksub, dsub, out, ldo);
+    } else {
+        int64_t work = n_ids * (int64_t)(M * dsub);
+        pq_decode_kernel<true><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
+            codes, ids, n_ids, centroids, M, ksub, dsub, out, ldo);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_pq_kmeans_accumulate(const float* x, int64_t n, int64_t ldx,
+                                           const uint8_t* codes, int M, int ksub, int dsub,
+                                           float* sums, int* counts, void* stream) {
+    VQ_CHECK_ARG(x && codes && sums && counts && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+                 "pq_kmeans_accumulate: bad args");
+    if (n == 0) return B200VQ_OK;
+    int64_t work = n * (int64_t)(M * dsub);
+    pq_kmeans_accumulate_kernel<<<grid_for(work, 256, 16), 256, 0, as_stream(stream)>>>(
+        x, n, ldx, codes, M, ksub, dsub, sums, counts);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_pq_kmeans_finalize(const float* sums, int* counts, int M, int ksub, int dsub,
+                                         float* centroids, int* n_split, void* stream) {
+    VQ_CHECK_ARG(sums && counts && centroids && M > 0 && ksub > 0 && dsub > 0,
+                 "pq_kmeans_finalize: bad args");
+    pq_kmeans_finalize_kernel<<<M, 256, 0, as_stream(stream)>>>(sums, counts, ksub, dsub, centroids,
+                                                               n_split);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_pq_sse(const float* x, int64_t n, int64_t ldx, const uint8_t* codes,
+                             const float* centroids, int M, int ksub, int dsub, double* out,
+                             void* stream) {
+    VQ_CHECK_ARG(x && codes && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+                 "pq_sse: bad args");
+    if (n == 0) return B200VQ_OK;
+    int64_t work = n * (int64_t)(M * dsub);
+    pq_sse_kernel<<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(x, n, ldx, codes, centroids,
+                                                                      M, ksub, dsub, out);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_adc_lut(const float* queries, int nq, int64_t ldq, const float* centroids,
+                              int M, int ksub, int dsub, int metric, float* lut, void* stream) {
+    VQ_CHECK_ARG(queries && centroids && lut && nq >= 0 && M > 0 && ksub > 0 && dsub > 0,
+                 "adc_lut: bad args");
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "adc_lut: bad metric");
+    VQ_CHECK_ARG(M <= 65535, "adc_lut: M > 65535");
+    VQ_CHECK_ARG((size_t)dsub * sizeof(float) <= 48 * 1024, "adc_lut: dsub too large");
+    if (nq == 0) return B200VQ_OK;
+    dim3 grid((unsigned)nq, (unsigned)M);
+    int block = ksub >= 256 ? 256 : ((ksub + 31) / 32) * 32;
+    adc_lut_kernel<<<grid, block, dsub * sizeof(float), as_stream(stream)>>>(
+        queries, ldq, centroids, M, ksub, dsub, metric, lut);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}

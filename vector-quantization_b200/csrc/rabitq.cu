@@ -1,0 +1,652 @@
+// RaBitQ kernels.
+//
+// (1) 1-bit RaBitQ with faiss RaBitQuantizer / IndexRaBitQ semantics, as driven
+//     by src/haag_vq/methods/rabit_quantization.py:20-29 and
+//     src/haag_vq/methods/search/rabitq_index.py:42-70 of the reference.
+//     faiss is a third-party dependency that is not vendored in the reference
+//     tree; the arithmetic is restated from faiss >= 1.11
+//     (faiss/impl/RaBitQuantizer.cpp: compute_codes_core, decode_core,
+//     RaBitDistanceComputerQ::{set_query,distance_to_code}) and Gao & Long 2024.
+//       code  = ceil(D/8) sign bytes of (x - c), bit j%8 of byte j/8,
+//               then float or_minus_c_l2sqr (minus ||x||^2 for IP), float dp_multiplier
+//       query = (q - c) scalar-quantised to qb bits, bit-plane transposed
+//       est   = ||o-c||^2 + ||q-c||^2 - 2 dp_multiplier (c1 <q~,o> + c2 popc(o) - c34)
+// (2) Extended (multi-bit) RaBitQ row tail for
+//     src/haag_vq/methods/extended_rabitq.py:125-198 (fp64): level search,
+//     rescale factor t, MSB-first B-bit packing with float32 (nrm, t) trailer.
+#include "common.cuh"
+#include "topk.cuh"
+
+namespace b200vq {
+
+// ============================================================ 1-bit =======
+// One warp per row. Lane l owns dimensions j0 + l; the sign bits of 32
+// consecutive dimensions are gathered with one __ballot_sync.
+__global__ void rabitq1_encode_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                      const float* __restrict__ centroid, int metric,
+                                      uint8_t* __restrict__ codes) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int nbytes = (D + 7) >> 3;
+    const int code_size = nbytes + 8;
+    const float inv_d_sqrt = 1.0f / sqrtf((float)D);
+    for (int64_t row = wid; row < n; row += nw) {
+        const float* xr = x + row * ldx;
+        uint8_t* code = codes + row * (int64_t)code_size;
+        float norm = 0.f, orl2 = 0.f, dp = 0.f;
+        for (int j0 = 0; j0 < D; j0 += 32) {
+            int j = j0 + lane;
+            float v = 0.f, omc = 0.f;
+            if (j < D) {
+                v = xr[j];
+                omc = v - (centroid ? centroid[j] : 0.f);
+            }
+            norm = __fmaf_rn(omc, omc, norm);
+            orl2 = __fmaf_rn(v, v, orl2);
+            bool xb = omc > 0.f;
+            dp += fabsf(omc);
+            unsigned word = __ballot_sync(FULL_MASK, xb);
+            if (lane < 4) {
+                int byte = (j0 >> 3) + lane;
+                if (byte < nbytes) code[byte] = (uint8_t)(word >> (8 * lane));
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            norm += __shfl_xor_sync(FULL_MASK, norm, o);
+            orl2 += __shfl_xor_sync(FULL_MASK, orl2, o);
+            dp += __shfl_xor_sync(FULL_MASK, dp, o);
+        }
+        if (lane == 0) {
+            const float eps = 1.1920929e-07f;  // std::numeric_limits<float>::epsilon()
+            float sq = sqrtf(norm);
+            float inv_norm = (fabsf(norm) < eps) ? 1.0f : (1.0f / sq);
+            float dpn = dp * inv_norm;
+            dpn *= inv_d_sqrt;
+            float inv_dp = (fabsf(dpn) < eps) ? 1.0f : (1.0f / dpn);
+            float f0 = norm;
+            if (metric == B200VQ_METRIC_IP) f0 -= orl2;
+            float f1 = inv_dp * sq;
+            uint32_t u0 = __float_as_uint(f0), u1 = __float_as_uint(f1);
+            uint8_t* f = code + nbytes;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                f[b] = (uint8_t)(u0 >> (8 * b));
+                f[4 + b] = (uint8_t)(u1 >> (8 * b));
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ float load_f32_unaligned(const uint8_t* p) {
+    uint32_t u = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) |
+                 ((uint32_t)p[3] << 24);
+    return __uint_as_float(u);
+}
+
+__global__ void rabitq1_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
+                                      const float* __restrict__ centroid, float* __restrict__ out,
+                                      int64_t ldo) {
+    const int nbytes = (D + 7) >> 3;
+    const int code_size = nbytes + 8;
+    const float inv_d_sqrt = 1.0f / sqrtf((float)D);
+    const int64_t total = n * (int64_t)D;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int j = (int)(e - row * D);
+        const uint8_t* code = codes + row * (int64_t)code_size;
+        float dpm = load_f32_unaligned(code + nbytes + 4);
+        float bit = ((code[j >> 3] >> (j & 7)) & 1) ? 1.f : 0.f;
+        // (bit - 0.5f) * dp_multiplier * 2 * inv_d_sqrt + c[j], left to right like faiss
+        float v = __fmul_rn(__fmul_rn(__fmul_rn(bit - 0.5f, dpm), 2.f), inv_d_sqrt);
+        out[row * ldo + j] = __fadd_rn(v, centroid ? centroid[j] : 0.f);
+    }
+}
+
+// One CTA (256 threads) per query.
+__global__ void rabitq1_prepare_queries_kernel(const float* __restrict__ queries, int64_t ldq, int D,
+                                               const float* __restrict__ centroid, int qb,
+                                               uint32_t* __restrict__ planes,
+                                               float* __restrict__ qfac) {
+    extern __shared__ float rq[];  // D residuals, then D quantised ints (as int)
+    int* qq = reinterpret_cast<int*>(rq + D);
+    __shared__ float red[4][32];
+    __shared__ unsigned long long s_sum;
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int nwarp = blockDim.x >> 5;
+    const float* qr = queries + (int64_t)q * ldq;
+    float l2 = 0.f, nrm = 0.f;
+    float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
+    for (int j = tid; j < D; j += blockDim.x) {
+        float v = qr[j];
+        float r = v - (centroid ? centroid[j] : 0.f);
+        rq[j] = r;
+        l2 = __fmaf_rn(r, r, l2);
+        nrm = __fmaf_rn(v, v, nrm);
+        mn = fminf(mn, r);
+        mx = fmaxf(mx, r);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        l2 += __shfl_xor_sync(FULL_MASK, l2, o);
+        nrm += __shfl_xor_sync(FULL_MASK, nrm, o);
+        mn = fminf(mn, __shfl_xor_sync(FULL_MASK, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(FULL_MASK, mx, o));
+    }
+    if (lane == 0) {
+        red[0][w] = l2;
+        red[1][w] = nrm;
+        red[2][w] = mn;
+        red[3][w] = mx;
+    }
+    if (tid == 0) s_sum = 0ull;
+    __syncthreads();
+    l2 = 0.f;
+    nrm = 0.f;
+    mn = __int_as_float(0x7f800000);
+    mx = __int_as_float(0xff800000);
+    for (int i = 0; i < nwarp; ++i) {
+        l2 += red[0][i];
+        nrm += red[1][i];
+        mn = fminf(mn, red[2][i]);
+        mx = fmaxf(mx, red[3][i]);
+    }
+    const float pow2 = (float)(1 << qb);
+    const float delta = (mx - mn) / (pow2 - 1.f);
+    const float inv_delta = 1.0f / delta;
+    unsigned long long local = 0;
+    for (int j = tid; j < D; j += blockDim.x) {
+        float vq = (rq[j] - mn) * inv_delta;
+        int v = (int)roundf(vq);  // std::round: half away from zero
+        local += (unsigned long long)(long long)v;
+        qq[j] = min(255, max(0, v));
+    }
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(FULL_MASK, local, o);
+    if (lane == 0) atomicAdd(&s_sum, local);
+    __syncthreads();
+    // bit-plane transpose with ballots: warp w handles words w, w+nwarp, ...
+    const int W = (D + 31) >> 5;
+    for (int wd = w; wd < W; wd += nwarp) {
+        int j = wd * 32 + lane;
+        int v = (j < D) ? qq[j] : 0;
+        for (int b = 0; b < qb; ++b) {
+            unsigned word = __ballot_sync(FULL_MASK, (v >> b) & 1);
+            if (lane == 0) planes[((size_t)q * qb + b) * W + wd] = word;
+        }
+    }
+    if (tid == 0) {
+        const float inv_d = 1.0f / sqrtf((float)D);
+        float* f = qfac + (size_t)q * 8;
+        f[0] = 2.f * delta * inv_d;                                    // c1
+        f[1] = 2.f * mn * inv_d;                                       // c2
+        f[2] = inv_d * (delta * (float)s_sum + (float)D * mn);         // c34
+        f[3] = l2;                                                     // ||q - c||^2
+        f[4] = nrm;                                                    // ||q||^2
+        f[5] = 0.f;
+        f[6] = 0.f;
+        f[7] = 0.f;
+    }
+}
+
+// Scan: grid (nq, nchunks), 256 threads. A warp stages 32 code rows into shared
+// memory with coalesced loads (row pitch padded to an odd number of words so
+// the per-lane row walk is bank-conflict free), then lane = row.
+template <int CAP>
+__global__ void __launch_bounds__(256)
+    rabitq1_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
+                        const uint32_t* __restrict__ planes, const float* __restrict__ qfac, int qb,
+                        int metric, int k, int64_t chunk_rows, uint64_t* __restrict__ part) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int W = (D + 31) >> 5;
+    const int nbytes = (D + 7) >> 3;
+    const int code_size = nbytes + 8;
+    const int pitch_w = ((code_size + 3) >> 2) | 1;  // words per staged row, odd
+    uint32_t* qpl = reinterpret_cast<uint32_t*>(smem_raw);                  // [qb][W]
+    uint32_t* stage = qpl + ((qb * W + 3) & ~3);                            // [8 warps][32][pitch_w]
+    uint64_t* wbuf = reinterpret_cast<uint64_t*>(
+        (reinterpret_cast<uintptr_t>(stage + 8 * 32 * pitch_w) + 15) & ~(uintptr_t)15);
+    const int n2 = next_pow2(8 * k);
+    uint64_t* mbuf = wbuf + 8 * CAP;
+
+    for (int i = threadIdx.x; i < qb * W; i += blockDim.x) qpl[i] = planes[(size_t)q * qb * W + i];
+    const float c1 = qfac[(size_t)q * 8 + 0], c2 = qfac[(size_t)q * 8 + 1],
+                c34 = qfac[(size_t)q * 8 + 2], qc2 = qfac[(size_t)q * 8 + 3],
+                qn2 = qfac[(size_t)q * 8 + 4];
+    __syncthreads();
+
+    WarpTopK<CAP> tk;
+    tk.init(wbuf + w * CAP, k);
+    uint32_t* st = stage + (size_t)w * 32 * pitch_w;
+    uint8_t* st8 = reinterpret_cast<uint8_t*>(st);
+
+    const int64_t r0 = (int64_t)chunk * chunk_rows;
+    int64_t r1 = r0 + chunk_rows;
+    if (r1 > n) r1 = n;
+    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += 256) {
+        int rows = (int)((r1 - base) < 32 ? (r1 - base) : 32);
+        // coalesced byte-range copy of `rows` code rows
+        const uint8_t* src = codes + base * (int64_t)code_size;
+        const int64_t nb = (int64_t)rows * code_size;
+        __syncwarp();
+        if ((((uintptr_t)src) & 3) == 0 && (code_size & 3) == 0) {
+            const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src);
+            const int wpr = code_size >> 2;
+            for (int i = lane; i < rows * wpr; i += 32) {
+                int r = i / wpr, c = i - r * wpr;
+                st[r * pitch_w + c] = __ldg(s4 + i);
+            }
+        } else {
+            for (int64_t i = lane; i < nb; i += 32) {
+                int r = (int)(i / code_size), c = (int)(i - (int64_t)r * code_size);
+                st8[(size_t)r * pitch_w * 4 + c] = src[i];
+            }
+        }
+        __syncwarp();
+        const bool valid = lane < rows;
+        float est = 0.f;
+        if (valid) {
+            const uint32_t* cw = st + lane * pitch_w;
+            const uint8_t* cb = reinterpret_cast<const uint8_t*>(cw);
+            uint32_t dot = 0, sumq = 0;
+            for (int wd = 0; wd < W; ++wd) {
+                uint32_t c = cw[wd];
+                if (wd == W - 1 && (D & 31)) c &= (1u << (D & 31)) - 1u;  // drop factor bytes
+                sumq += __popc(c);
+                for (int b = 0; b < qb; ++b) dot += (uint32_t)__popc(c & qpl[b * W + wd]) << b;
+            }
+            float f0 = load_f32_unaligned(cb + nbytes);
+            float f1 = load_f32_unaligned(cb + nbytes + 4);
+            float final_dot = c1 * (float)dot;
+            final_dot += c2 * (float)sumq;
+            final_dot -= c34;
+            float pre = f0 + qc2 - 2.f * f1 * final_dot;
+            est = (metric == B200VQ_METRIC_L2) ? pre : 0.5f * (pre - qn2);  // IP: key = -ip
+        }
+        tk.offer(valid, est, (uint32_t)(base + lane));
+    }
+    // emit
+    tk.finish();
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) mbuf[i] = KEY_INF;
+    __syncthreads();
+    for (int i = lane; i < tk.count; i += 32) mbuf[w * k + i] = tk.buf[i];
+    block_bitonic_sort(mbuf, n2);
+    uint64_t* dst = part + ((size_t)q * nchunks + chunk) * k;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) dst[j] = mbuf[j];
+}
+
+// ======================================================= extended =========
+// One CTA per row (grid-stride). levels/bounds in shared memory.
+__global__ void erabitq_pack_kernel(const double* __restrict__ srot, const double* __restrict__ nrm,
+                                    int64_t n, int D, int B, const double* __restrict__ levels,
+                                    const double* __restrict__ bounds, uint8_t* __restrict__ codes) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* lv = reinterpret_cast<double*>(smem_raw);        // [2^B]
+    double* bd = lv + (1 << B);                              // [2^B - 1] (padded to 2^B)
+    uint8_t* idx = reinterpret_cast<uint8_t*>(bd + (1 << B));  // [D]
+    __shared__ double red[2][32];
+    const int L = 1 << B;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nwarp = blockDim.x >> 5;
+    for (int i = tid; i < L; i += blockDim.x) lv[i] = levels[i];
+    for (int i = tid; i < L - 1; i += blockDim.x) bd[i] = bounds[i];
+    __syncthreads();
+    const int ibytes = (D * B + 7) >> 3;
+    const int code_size = ibytes + 8;
+    for (int64_t row = blockIdx.x; row < n; row += gridDim.x) {
+        const double* s = srot + row * (int64_t)D;
+        double num = 0.0, den = 0.0;
+        for (int d = tid; d < D; d += blockDim.x) {
+            double v = s[d];
+            // np.searchsorted(bounds, v) (side='left'): number of bounds < v
+            int lo = 0, hi = L - 1;
+            while (lo < hi) {
+                int mid = (lo + hi) >> 1;
+                if (bd[mid] < v) lo = mid + 1;
+                else hi = mid;
+            }
+            idx[d] = (uint8_t)lo;
+            double sh = lv[lo];
+            num += v * sh;
+            den += sh * sh;
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            num += __shfl_xor_sync(FULL_MASK, num, o);
+            den += __shfl_xor_sync(FULL_MASK, den, o);
+        }
+        if (lane == 0) {
+            red[0][w] = num;
+            red[1][w] = den;
+        }
+        __syncthreads();
+        uint8_t* code = codes + row * (int64_t)code_size;
+        // MSB-first B-bit packing, one thread per output byte
+        for (int byte = tid; byte < ibytes; byte += blockDim.x) {
+            int b0 = byte * 8, b1 = b0 + 8;
+            uint32_t acc = 0;
+            for (int d = b0 / B; d < D && d * B < b1; ++d) {
+                int off = d * B;
+                int shift = b1 - (off + B);
+                uint32_t qv = idx[d];
+                acc |= ((shift >= 0) ? (qv << shift) : (qv >> (-shift))) & 0xffu;
+            }
+            code[byte] = (uint8_t)acc;
+        }
+        if (tid == 0) {
+            double nsum = 0.0, dsum = 0.0;
+            for (int i = 0; i < nwarp; ++i) {
+                nsum += red[0][i];
+                dsum += red[1][i];
+            }
+            double t = (dsum > 1e-12) ? (nsum / dsum) : 1.0;
+            uint32_t u0 = __float_as_uint((float)nrm[row]);
+            uint32_t u1 = __float_as_uint((float)t);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                code[ibytes + b] = (uint8_t)(u0 >> (8 * b));
+                code[ibytes + 4 + b] = (uint8_t)(u1 >> (8 * b));
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ uint32_t erabitq_index(const uint8_t* code, int d, int B, int ibytes) {
+    int off = d * B;
+    int byte = off >> 3;
+    uint32_t wv = ((uint32_t)code[byte] << 8) | (byte + 1 < ibytes ? code[byte + 1] : 0u);
+    int shift = 16 - ((off & 7) + B);
+    return (wv >> shift) & ((1u << B) - 1u);
+}
+
+__global__ void erabitq_unpack_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
+                                      const double* __restrict__ levels, double* __restrict__ shat,
+                                      double* __restrict__ nrm_out) {
+    const int ibytes = (D * B + 7) >> 3;
+    const int code_size = ibytes + 8;
+    const double sqrt_d = sqrt((double)D);
+    const int64_t total = n * (int64_t)D;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int d = (int)(e - row * D);
+        const uint8_t* code = codes + row * (int64_t)code_size;
+        uint32_t iv = erabitq_index(code, d, B, ibytes);
+        double t = (double)load_f32_unaligned(code + ibytes + 4);
+        shat[e] = (levels[iv] / sqrt_d) * t;
+        if (d == 0) nrm_out[row] = (double)load_f32_unaligned(code + ibytes);
+    }
+}
+
+// Code-domain scan: thread = row, levels (fp32) and the rotated query in shared
+// memory. est = qconst + nrm^2 t^2 sum(l^2)/D - 2 nrm t/sqrt(D) <l[idx], qrot>  (L2)
+//        ip  = qc_dot + nrm t/sqrt(D) <l[idx], qrot>                         (IP; qconst = q.c)
+template <int CAP>
+__global__ void __launch_bounds__(256)
+    erabitq_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
+                        const float* __restrict__ levels, const float* __restrict__ qrot,
+                        const float* __restrict__ qconst, int metric, int k, int64_t chunk_rows,
+                        uint64_t* __restrict__ part) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int L = 1 << B;
+    float* qs = reinterpret_cast<float*>(smem_raw);   // [D]
+    float* lv = qs + ((D + 3) & ~3);                  // [L]
+    uint64_t* wbuf = reinterpret_cast<uint64_t*>(
+        (reinterpret_cast<uintptr_t>(lv + L) + 15) & ~(uintptr_t)15);
+    const int n2 = next_pow2(8 * k);
+    uint64_t* mbuf = wbuf + 8 * CAP;
+    for (int i = threadIdx.x; i < D; i += blockDim.x) qs[i] = qrot[(size_t)q * D + i];
+    for (int i = threadIdx.x; i < L; i += blockDim.x) lv[i] = levels[i];
+    const float qc = qconst[q];
+    __syncthreads();
+    const int ibytes = (D * B + 7) >> 3;
+    const int code_size = ibytes + 8;
+    const float inv_sqrt_d = 1.0f / sqrtf((float)D);
+
+    WarpTopK<CAP> tk;
+    tk.init(wbuf + w * CAP, k);
+    const int64_t r0 = (int64_t)chunk * chunk_rows;
+    int64_t r1 = r0 + chunk_rows;
+    if (r1 > n) r1 = n;
+    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += 256) {
+        const int64_t row = base + lane;
+        const bool valid = row < r1;
+        float est = 0.f;
+        if (valid) {
+            const uint8_t* code = codes + row * (int64_t)code_size;
+            float dot = 0.f, l2 = 0.f;
+            for (int d = 0; d < D; ++d) {
+                float lvl = lv[erabitq_index(code, d, B, ibytes)];
+                dot = __fmaf_rn(lvl, qs[d], dot);
+                l2 = __fmaf_rn(lvl, lvl, l2);
+            }
+            float nrm = load_f32_unaligned(code + ibytes);
+            float t = load_f32_unaligned(code + ibytes + 4);
+            float a = nrm * t * inv_sqrt_d;
+            if (metric == B200VQ_METRIC_L2) est = qc + a * a * l2 - 2.f * a * dot;
+            else est = -(qc + a * dot);
+        }
+        tk.offer(valid, est, (uint32_t)row);
+    }
+    tk.finish();
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) mbuf[i] = KEY_INF;
+    __syncthreads();
+    for (int i = lane; i < tk.count; i += 32) mbuf[w * k + i] = tk.buf[i];
+    block_bitonic_sort(mbuf, n2);
+    uint64_t* dst = part + ((size_t)q * nchunks + chunk) * k;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) dst[j] = mbuf[j];
+}
+
+// Chunk planning identical to scan.cu (kept local: 2048-row units).
+struct RPlan {
+    int64_t chunk_rows;
+    int nchunks;
+};
+static RPlan rplan(int64_t n, int nq) {
+    const int64_t unit = 2048;
+    int64_t target = (int64_t)device_sm_count() * 8;
+    int64_t want = (target + nq - 1) / (nq > 0 ? nq : 1);
+    if (want < 1) want = 1;
+    int64_t maxc = (n + unit - 1) / unit;
+    if (maxc < 1) maxc = 1;
+    int64_t minc = (n + 262143) / 262144;
+    if (minc < 1) minc = 1;
+    int64_t nch = want;
+    if (nch > maxc) nch = maxc;
+    if (nch < minc) nch = minc;
+    if (nch > 65535) nch = 65535;
+    int64_t rows = (n + nch - 1) / nch;
+    rows = ((rows + unit - 1) / unit) * unit;
+    if (rows < unit) rows = unit;
+    RPlan p;
+    p.chunk_rows = rows;
+    p.nchunks = (int)((n + rows - 1) / rows);
+    if (p.nchunks < 1) p.nchunks = 1;
+    return p;
+}
+
+}  // namespace b200vq
+
+using namespace b200vq;
+
+extern "C" int b200vq_rabitq1_encode(const float* x, int64_t n, int64_t ldx, int D,
+                                     const float* centroid, int metric, uint8_t* codes,
+                                     void* stream) {
+    VQ_CHECK_ARG(x && codes && n >= 0 && D > 0 && ldx >= D, "rabitq1_encode: bad args");
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "rabitq1_encode: bad metric");
+    if (n == 0) return B200VQ_OK;
+    int64_t g = (n * 32 + 255) / 256;
+    int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    rabitq1_encode_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, ldx, D, centroid, metric,
+                                                                 codes);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_rabitq1_decode(const uint8_t* codes, int64_t n, int D, const float* centroid,
+                                     float* out, int64_t ldo, void* stream) {
+    VQ_CHECK_ARG(codes && out && n >= 0 && D > 0 && ldo >= D, "rabitq1_decode: bad args");
+    if (n == 0) return B200VQ_OK;
+    int64_t g = (n * (int64_t)D + 255) / 256;
+    int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    rabitq1_decode_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, centroid, out, ldo);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_rabitq1_prepare_queries(const float* queries, int nq, int64_t ldq, int D,
+                                              const float* centroid, int qb, uint32_t* planes,
+                                              float* qfac, void* stream) {
+    VQ_CHECK_ARG(queries && planes && qfac && nq >= 0 && D > 0 && ldq >= D,
+                 "rabitq1_prepare_queries: bad args");
+    VQ_CHECK_ARG(qb >= 1 && qb <= 8, "rabitq1_prepare_queries: qb must be in [1,8], got %d", qb);
+    VQ_CHECK_ARG((size_t)D * 8 <= 160 * 1024, "rabitq1_prepare_queries: D too large");
+    if (nq == 0) return B200VQ_OK;
+    size_t smem = (size_t)D * 8;
+    VQ_CUDA(cudaFuncSetAttribute(rabitq1_prepare_queries_kernel,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    rabitq1_prepare_queries_kernel<<<nq, 256, smem, as_stream(stream)>>>(queries, ldq, D, centroid,
+                                                                         qb, planes, qfac);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" size_t b200vq_rabitq1_scan_scratch_bytes(int64_t n, int nq, int k) {
+    if (n < 0 || nq <= 0 || k <= 0) return 0;
+    RPlan p = rplan(n, nq);
+    return (size_t)nq * p.nchunks * k * sizeof(uint64_t);
+}
+
+template <int CAP>
+static int rabitq1_scan_launch(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
+                               const float* qfac, int nq, int qb, int metric, int k, uint64_t* part,
+                               const RPlan& p, cudaStream_t st) {
+    const int W = (D + 31) >> 5;
+    const int code_size = ((D + 7) >> 3) + 8;
+    const int pitch_w = ((code_size + 3) >> 2) | 1;
+    const int n2 = next_pow2(8 * k);
+    size_t smem = (size_t)((qb * W + 3) & ~3) * 4 + (size_t)8 * 32 * pitch_w * 4 + 16 +
+                  (size_t)(8 * CAP + n2) * sizeof(uint64_t);
+    VQ_CHECK_ARG(smem <= 227 * 1024, "rabitq1_scan: D=%d needs %zu B of shared memory", D, smem);
+    VQ_CUDA(cudaFuncSetAttribute(rabitq1_scan_kernel<CAP>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)nq, (unsigned)p.nchunks);
+    rabitq1_scan_kernel<CAP><<<grid, 256, smem, st>>>(codes, n, D, planes, qfac, qb, metric, k,
+                                                      p.chunk_rows, part);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D,
+                                        const uint32_t* planes, const float* qfac, int nq, int qb,
+                                        int metric, int k, float* out_vals, uint32_t* out_ids,
+                                        void* scratch, size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(codes && planes && qfac && out_vals && out_ids, "rabitq1_scan_topk: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && nq >= 0, "rabitq1_scan_topk: bad shape");
+    VQ_CHECK_ARG(qb >= 1 && qb <= 8, "rabitq1_scan_topk: qb must be in [1,8]");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "rabitq1_scan_topk: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "rabitq1_scan_topk: bad metric");
+    if (nq == 0) return B200VQ_OK;
+    RPlan p = rplan(n, nq);
+    size_t need = (size_t)nq * p.nchunks * k * sizeof(uint64_t);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "rabitq1_scan_topk: scratch too small");
+    cudaStream_t st = as_stream(stream);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32)
+                 ? rabitq1_scan_launch<128>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st)
+                 : rabitq1_scan_launch<256>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st);
+    if (rc != B200VQ_OK) return rc;
+    merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, p.nchunks, k, metric == B200VQ_METRIC_IP,
+                                                    out_vals, out_ids);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_t n, int D, int B,
+                                   const double* levels, const double* bounds, uint8_t* codes,
+                                   void* stream) {
+    VQ_CHECK_ARG(srot && nrm && levels && bounds && codes && n >= 0 && D > 0,
+                 "erabitq_pack: bad args");
+    VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_pack: B must be in [1,8], got %d", B);
+    if (n == 0) return B200VQ_OK;
+    size_t smem = (size_t)(2 << B) * sizeof(double) + (size_t)D + 16;
+    VQ_CHECK_ARG(smem <= 200 * 1024, "erabitq_pack: D too large");
+    VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
+    int64_t g = n;
+    int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    erabitq_pack_kernel<<<(int)g, 128, smem, as_stream(stream)>>>(srot, nrm, n, D, B, levels, bounds,
+                                                                 codes);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B,
+                                     const double* levels, double* shat, double* nrm_out,
+                                     void* stream) {
+    VQ_CHECK_ARG(codes && levels && shat && nrm_out && n >= 0 && D > 0, "erabitq_unpack: bad args");
+    VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_unpack: B must be in [1,8], got %d", B);
+    if (n == 0) return B200VQ_OK;
+    int64_t g = (n * (int64_t)D + 255) / 256;
+    int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    erabitq_unpack_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, B, levels, shat,
+                                                                 nrm_out);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" size_t b200vq_erabitq_scan_scratch_bytes(int64_t n, int nq, int k) {
+    if (n < 0 || nq <= 0 || k <= 0) return 0;
+    RPlan p = rplan(n, nq);
+    return (size_t)nq * p.nchunks * k * sizeof(uint64_t);
+}
+
+template <int CAP>
+static int erabitq_scan_launch(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
+                               const float* qrot, const float* qconst, int nq, int metric, int k,
+                               uint64_t* part, const RPlan& p, cudaStream_t st) {
+    const int n2 = next_pow2(8 * k);
+    size_t smem = (size_t)(((D + 3) & ~3) + (1 << B)) * 4 + 16 + (size_t)(8 * CAP + n2) * 8;
+    VQ_CHECK_ARG(smem <= 227 * 1024, "erabitq_scan: D too large");
+    VQ_CUDA(cudaFuncSetAttribute(erabitq_scan_kernel<CAP>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)nq, (unsigned)p.nchunks);
+    erabitq_scan_kernel<CAP><<<grid, 256, smem, st>>>(codes, n, D, B, levels, qrot, qconst, metric,
+                                                      k, p.chunk_rows, part);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B,
+                                        const float* levels, const float* qrot, const float* qconst,
+                                        int nq, int metric, int k, float* out_vals,
+                                        uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                                        void* stream) {
+    VQ_CHECK_ARG(codes && levels && qrot && qconst && out_vals && out_ids,
+                 "erabitq_scan_topk: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && nq >= 0 && B >= 1 && B <= 8,
+                 "erabitq_scan_topk: bad shape");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "erabitq_scan_topk: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "erabitq_scan_topk: bad metric");
+    if (nq == 0) return B200VQ_OK;
+    RPlan p = rplan(n, nq);
+    size_t need = (size_t)nq * p.nchunks * k * sizeof(uint64_t);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "erabitq_scan_topk: scratch too small");
+    cudaStream_t st = as_stream(stream);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32) ? erabitq_scan_launch<128>(codes, n, D, B, levels, qrot, qconst, nq, metric,
+                                                  k, part, p, st)
+                       : erabitq_scan_launch<256>(codes, n, D, B, levels, qrot, qconst, nq, metric,
+                                                  k, part, p, st);
+    if (rc != B200VQ_OK) return rc;
+    merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, p.nchunks, k, metric == B200VQ_METRIC_IP,
+                                                    out_vals, out_ids);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}

@@ -1,0 +1,357 @@
+// Scalar-quantiser kernels: per-dimension min/max, uniform 4/8/16-bit
+// encode/decode, and the segmented variable-bit (SAQ CLI contract) bit-string
+// encode/decode.
+//
+// Reference: src/haag_vq/methods/scalar_quantization.py:37-90 (numpy, fp32).
+//   scaled = (X - min) / (max - min + 1e-8)          each op rounded to fp32
+//   q      = np.round(scaled * (L - 1)).astype(u8)   rint = half-to-even
+//   4-bit  : (q[:,0::2] << 4) | q[:,1::2], odd D zero-padded
+//   decode : q / (L - 1) * (max - min + 1e-8) + min
+// The intrinsics below (__fsub_rn, __fdiv_rn, ...) forbid FMA contraction so
+// the results are bit-identical to numpy's. Divergence (documented in
+// DESIGN.md): out-of-range inputs saturate instead of wrapping.
+#include "common.cuh"
+
+namespace b200vq {
+
+__device__ __forceinline__ void atomic_min_f32(float* addr, float v) {
+    if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f32(float* addr, float v) {
+    if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+
+// block (32, 8): 32 consecutive columns x 8 row lanes; grid (ceil(D/32), row CTAs)
+__global__ void sq_minmax_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                 float* __restrict__ vmin, float* __restrict__ vmax) {
+    __shared__ float smin[8][33], smax[8][33];
+    const int col = blockIdx.x * 32 + threadIdx.x;
+    float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
+    if (col < D) {
+        for (int64_t r = (int64_t)blockIdx.y * 8 + threadIdx.y; r < n; r += (int64_t)gridDim.y * 8) {
+            float v = x[r * ldx + col];
+            mn = fminf(mn, v);
+            mx = fmaxf(mx, v);
+        }
+    }
+    smin[threadIdx.y][threadIdx.x] = mn;
+    smax[threadIdx.y][threadIdx.x] = mx;
+    __syncthreads();
+    if (threadIdx.y == 0 && col < D) {
+        for (int j = 1; j < 8; ++j) {
+            mn = fminf(mn, smin[j][threadIdx.x]);
+            mx = fmaxf(mx, smax[j][threadIdx.x]);
+        }
+        if (mn <= mx) {  // skip when no row was seen
+            atomic_min_f32(vmin + col, mn);
+            atomic_max_f32(vmax + col, mx);
+        }
+    }
+}
+
+__device__ __forceinline__ float sq_range(float mn, float mx) {
+    return __fadd_rn(__fsub_rn(mx, mn), 1e-8f);
+}
+// q in [0, lm1]
+__device__ __forceinline__ uint32_t sq_quant(float x, float mn, float range, float lm1) {
+    float scaled = __fdiv_rn(__fsub_rn(x, mn), range);
+    float q = rintf(__fmul_rn(scaled, lm1));
+    q = fminf(fmaxf(q, 0.f), lm1);  // NaN -> 0 via fmaxf
+    return (uint32_t)q;
+}
+__device__ __forceinline__ float sq_dequant(uint32_t q, float mn, float range, float lm1) {
+    float scaled = __fdiv_rn((float)q, lm1);
+    return __fadd_rn(__fmul_rn(scaled, range), mn);
+}
+
+// Generic scalar kernels (any D / alignment). One thread per output element.
+template <int BITS>
+__global__ void sq_encode_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                 const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                 void* __restrict__ codes) {
+    const float lm1 = (float)((1 << BITS) - 1);
+    if (BITS == 4) {
+        const int W = (D + 1) >> 1;
+        const int64_t total = n * (int64_t)W;
+        uint8_t* out = reinterpret_cast<uint8_t*>(codes);
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+             e += (int64_t)gridDim.x * blockDim.x) {
+            int64_t row = e / W;
+            int j = (int)(e - row * W);
+            int d0 = 2 * j, d1 = 2 * j + 1;
+            uint32_t hi = sq_quant(x[row * ldx + d0], vmin[d0], sq_range(vmin[d0], vmax[d0]), lm1);
+            uint32_t lo = 0;
+            if (d1 < D) lo = sq_quant(x[row * ldx + d1], vmin[d1], sq_range(vmin[d1], vmax[d1]), lm1);
+            out[e] = (uint8_t)((hi << 4) | lo);
+        }
+    } else {
+        const int64_t total = n * (int64_t)D;
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+             e += (int64_t)gridDim.x * blockDim.x) {
+            int64_t row = e / D;
+            int d = (int)(e - row * D);
+            uint32_t q = sq_quant(x[row * ldx + d], vmin[d], sq_range(vmin[d], vmax[d]), lm1);
+            if (BITS == 8) reinterpret_cast<uint8_t*>(codes)[e] = (uint8_t)q;
+            else reinterpret_cast<uint16_t*>(codes)[e] = (uint16_t)q;
+        }
+    }
+}
+
+// Vector 8-bit encode: 4 dims per thread, 128-bit load, 32-bit store.
+// grid.y strides rows so that the per-column parameters stay in registers.
+__global__ void sq_encode8_v4_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                     const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                     uint8_t* __restrict__ codes) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;  // group of 4 columns
+    if (c4 * 4 >= D) return;
+    const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
+    const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
+    const float r0 = sq_range(mn.x, mx.x), r1 = sq_range(mn.y, mx.y), r2 = sq_range(mn.z, mx.z),
+                r3 = sq_range(mn.w, mx.w);
+    for (int64_t row = blockIdx.y; row < n; row += gridDim.y) {
+        float4 v = ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4);
+        uint32_t q = sq_quant(v.x, mn.x, r0, 255.f) | (sq_quant(v.y, mn.y, r1, 255.f) << 8) |
+                     (sq_quant(v.z, mn.z, r2, 255.f) << 16) | (sq_quant(v.w, mn.w, r3, 255.f) << 24);
+        reinterpret_cast<uint32_t*>(codes + row * (int64_t)D)[c4] = q;
+    }
+}
+
+template <int BITS>
+__global__ void sq_decode_kernel(const void* __restrict__ codes, int64_t n, int D,
+                                 const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                 float* __restrict__ out, int64_t ldo) {
+    const float lm1 = (float)((1 << BITS) - 1);
+    const int64_t total = n * (int64_t)D;
+    const int W = (D + 1) >> 1;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int d = (int)(e - row * D);
+        uint32_t q;
+        if (BITS == 4) {
+            uint8_t b = reinterpret_cast<const uint8_t*>(codes)[row * W + (d >> 1)];
+            q = (d & 1) ? (b & 0xf) : (b >> 4);
+        } else if (BITS == 8) {
+            q = reinterpret_cast<const uint8_t*>(codes)[e];
+        } else {
+            q = reinterpret_cast<const uint16_t*>(codes)[e];
+        }
+        out[row * ldo + d] = sq_dequant(q, vmin[d], sq_range(vmin[d], vmax[d]), lm1);
+    }
+}
+
+__global__ void sq_decode8_v4_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
+                                     const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                     float* __restrict__ out, int64_t ldo) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c4 * 4 >= D) return;
+    const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
+    const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
+    const float r0 = sq_range(mn.x, mx.x), r1 = sq_range(mn.y, mx.y), r2 = sq_range(mn.z, mx.z),
+                r3 = sq_range(mn.w, mx.w);
+    for (int64_t row = blockIdx.y; row < n; row += gridDim.y) {
+        uint32_t q = __ldg(reinterpret_cast<const uint32_t*>(codes + row * (int64_t)D) + c4);
+        float4 o;
+        o.x = sq_dequant(q & 0xff, mn.x, r0, 255.f);
+        o.y = sq_dequant((q >> 8) & 0xff, mn.y, r1, 255.f);
+        o.z = sq_dequant((q >> 16) & 0xff, mn.z, r2, 255.f);
+        o.w = sq_dequant(q >> 24, mn.w, r3, 255.f);
+        reinterpret_cast<float4*>(out + row * ldo)[c4] = o;
+    }
+}
+
+// ----------------------------------------------- segmented variable-bit ---
+// Codes are an MSB-first bit string: dimension d occupies bits
+// [bit_offset[d], bit_offset[d]+dim_bits[d]) counted from the MSB of byte 0.
+// Gather formulation: one thread builds one output byte from the (at most 8)
+// dimensions overlapping it, so there are no atomics and no write conflicts.
+__device__ __forceinline__ int first_dim_at_bit(const int* __restrict__ bit_offset, int D, int bit) {
+    // largest d with bit_offset[d] <= bit  (bit_offset is non-decreasing, [D] = total)
+    int lo = 0, hi = D;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (bit_offset[mid] <= bit) lo = mid;
+        else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void saq_encode_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                  const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                  const int* __restrict__ dim_bits,
+                                  const int* __restrict__ bit_offset, int code_bytes,
+                                  uint8_t* __restrict__ codes) {
+    const int total_bits = bit_offset[D];
+    const int64_t total = n * (int64_t)code_bytes;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / code_bytes;
+        int byte = (int)(e - row * code_bytes);
+        int b0 = byte * 8, b1 = b0 + 8;
+        uint32_t acc = 0;
+        if (b0 < total_bits) {
+            int d = first_dim_at_bit(bit_offset, D, b0);
+            for (; d < D && bit_offset[d] < b1; ++d) {
+                int nb = dim_bits[d];
+                if (nb == 0) continue;
+                int off = bit_offset[d];
+                if (off + nb <= b0) continue;
+                float lm1 = (float)((1 << nb) - 1);
+                uint32_t q = sq_quant(x[row * ldx + d], vmin[d], sq_range(vmin[d], vmax[d]), lm1);
+                // place q so that its MSB sits at absolute bit `off` (MSB-first)
+                int shift = b1 - (off + nb);  // >0: left shift inside the byte; <0: spill right
+                uint32_t piece = (shift >= 0) ? (q << shift) : (q >> (-shift));
+                acc |= piece & 0xffu;
+            }
+        }
+        codes[e] = (uint8_t)acc;
+    }
+}
+
+__global__ void saq_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
+                                  const float* __restrict__ vmin, const float* __restrict__ vmax,
+                                  const int* __restrict__ dim_bits,
+                                  const int* __restrict__ bit_offset, int code_bytes,
+                                  float* __restrict__ out, int64_t ldo) {
+    const int64_t total = n * (int64_t)D;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t row = e / D;
+        int d = (int)(e - row * D);
+        int nb = dim_bits[d];
+        float v;
+        if (nb == 0) {
+            v = vmin[d];  // 0-bit dimensions decode to the fill value the host put in vmin
+        } else {
+            int off = bit_offset[d];
+            const uint8_t* c = codes + row * (int64_t)code_bytes;
+            int byte = off >> 3;
+            uint32_t w = ((uint32_t)c[byte] << 8) | (byte + 1 < code_bytes ? c[byte + 1] : 0u);
+            int shift = 16 - ((off & 7) + nb);
+            uint32_t q = (w >> shift) & ((1u << nb) - 1u);
+            v = sq_dequant(q, vmin[d], sq_range(vmin[d], vmax[d]), (float)((1 << nb) - 1));
+        }
+        out[row * ldo + d] = v;
+    }
+}
+
+static inline int sq_grid(int64_t work, int block) {
+    int64_t g = (work + block - 1) / block;
+    int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+}  // namespace b200vq
+
+using namespace b200vq;
+
+extern "C" int b200vq_sq_minmax(const float* x, int64_t n, int64_t ldx, int D, float* vmin,
+                                float* vmax, void* stream) {
+    VQ_CHECK_ARG(x && vmin && vmax && n >= 0 && D > 0 && ldx >= D, "sq_minmax: bad args");
+    if (n == 0) return B200VQ_OK;
+    int gx = (D + 31) / 32;
+    int64_t gy = (n + 7) / 8;
+    int64_t cap = ((int64_t)device_sm_count() * 8 + gx - 1) / gx;
+    if (cap < 1) cap = 1;
+    if (gy > cap) gy = cap;
+    if (gy > 65535) gy = 65535;
+    sq_minmax_kernel<<<dim3(gx, (unsigned)gy), dim3(32, 8), 0, as_stream(stream)>>>(x, n, ldx, D,
+                                                                                    vmin, vmax);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_sq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
+                                const float* vmax, int bits, void* codes, void* stream) {
+    VQ_CHECK_ARG(x && vmin && vmax && codes && n >= 0 && D > 0 && ldx >= D, "sq_encode: bad args");
+    VQ_CHECK_ARG(bits == 4 || bits == 8 || bits == 16, "sq_encode: bits must be 4, 8 or 16, got %d",
+                 bits);
+    if (n == 0) return B200VQ_OK;
+    cudaStream_t st = as_stream(stream);
+    if (bits == 8) {
+        bool v4 = (D % 4 == 0) && (ldx % 4 == 0) && (((uintptr_t)x & 15) == 0) &&
+                  (((uintptr_t)vmin & 15) == 0) && (((uintptr_t)vmax & 15) == 0) &&
+                  (((uintptr_t)codes & 3) == 0);
+        if (v4) {
+            int gx = (D / 4 + 127) / 128;
+            int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+            if (gy > n) gy = n;
+            if (gy > 65535) gy = 65535;
+            sq_encode8_v4_kernel<<<dim3(gx, (unsigned)gy), 128, 0, st>>>(
+                x, n, ldx, D, vmin, vmax, reinterpret_cast<uint8_t*>(codes));
+        } else {
+            sq_encode_kernel<8><<<sq_grid(n * (int64_t)D, 256), 256, 0, st>>>(x, n, ldx, D, vmin,
+                                                                              vmax, codes);
+        }
+    } else if (bits == 4) {
+        sq_encode_kernel<4><<<sq_grid(n * (int64_t)((D + 1) / 2), 256), 256, 0, st>>>(
+            x, n, ldx, D, vmin, vmax, codes);
+    } else {
+        sq_encode_kernel<16><<<sq_grid(n * (int64_t)D, 256), 256, 0, st>>>(x, n, ldx, D, vmin, vmax,
+                                                                           codes);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_sq_decode(const void* codes, int64_t n, int D, const float* vmin,
+                                const float* vmax, int bits, float* out, int64_t ldo,
+                                void* stream) {
+    VQ_CHECK_ARG(codes && vmin && vmax && out && n >= 0 && D > 0 && ldo >= D, "sq_decode: bad args");
+    VQ_CHECK_ARG(bits == 4 || bits == 8 || bits == 16, "sq_decode: bits must be 4, 8 or 16, got %d",
+                 bits);
+    if (n == 0) return B200VQ_OK;
+    cudaStream_t st = as_stream(stream);
+    int g = sq_grid(n * (int64_t)D, 256);
+    if (bits == 8) {
+        bool v4 = (D % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
+                  (((uintptr_t)vmin & 15) == 0) && (((uintptr_t)vmax & 15) == 0) &&
+                  (((uintptr_t)codes & 3) == 0);
+        if (v4) {
+            int gx = (D / 4 + 127) / 128;
+            int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+            if (gy > n) gy = n;
+            if (gy > 65535) gy = 65535;
+            sq_decode8_v4_kernel<<<dim3(gx, (unsigned)gy), 128, 0, st>>>(
+                reinterpret_cast<const uint8_t*>(codes), n, D, vmin, vmax, out, ldo);
+        } else {
+            sq_decode_kernel<8><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
+        }
+    } else if (bits == 4) {
+        sq_decode_kernel<4><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
+    } else {
+        sq_decode_kernel<16><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_saq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
+                                 const float* vmax, const int* dim_bits, const int* bit_offset,
+                                 int code_bytes, uint8_t* codes, void* stream) {
+    VQ_CHECK_ARG(x && vmin && vmax && dim_bits && bit_offset && codes && n >= 0 && D > 0 &&
+                     ldx >= D && code_bytes > 0,
+                 "saq_encode: bad args");
+    if (n == 0) return B200VQ_OK;
+    saq_encode_kernel<<<sq_grid(n * (int64_t)code_bytes, 256), 256, 0, as_stream(stream)>>>(
+        x, n, ldx, D, vmin, vmax, dim_bits, bit_offset, code_bytes, codes);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_saq_decode(const uint8_t* codes, int64_t n, int D, const float* vmin,
+                                 const float* vmax, const int* dim_bits, const int* bit_offset,
+                                 int code_bytes, float* out, int64_t ldo, void* stream) {
+    VQ_CHECK_ARG(codes && vmin && vmax && dim_bits && bit_offset && out && n >= 0 && D > 0 &&
+                     ldo >= D && code_bytes > 0,
+                 "saq_decode: bad args");
+    if (n == 0) return B200VQ_OK;
+    saq_decode_kernel<<<sq_grid(n * (int64_t)D, 256), 256, 0, as_stream(stream)>>>(
+        codes, n, D, vmin, vmax, dim_bits, bit_offset, code_bytes, out, ldo);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}

@@ -1,0 +1,82 @@
+// Block-level helpers shared by the scan kernels: bitonic sort of composite
+// (value,id) keys in shared memory, partial-list emission and the cross-chunk
+// merge kernel.
+#pragma once
+#include "common.cuh"
+
+namespace b200vq {
+
+#ifdef __CUDACC__
+
+__host__ __device__ __forceinline__ int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// Sort keys[0..n2) ascending with the whole CTA. n2 must be a power of two.
+// Ends with a __syncthreads().
+__device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, int n2) {
+    for (int size = 2; size <= n2; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
+                int lo = 2 * t - (t & (stride - 1));
+                int hi = lo + stride;
+                bool up = ((lo & size) == 0);
+                uint64_t a = keys[lo], b = keys[hi];
+                if ((a > b) == up) {
+                    keys[lo] = b;
+                    keys[hi] = a;
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// Partial results layout: part[(q * nparts + p) * k + j], u64 keys ascending,
+// KEY_INF padded.
+//
+// Merge kernel: one CTA per query, streams nparts*k keys through a 2*TILE-key
+// shared buffer, keeping the best k after every sort. `negate` un-does the
+// sign flip applied to inner-product scores.
+template <int TILE>
+__global__ void merge_partials_kernel(const uint64_t* __restrict__ part, int nparts, int k,
+                                      int negate, float* __restrict__ out_vals,
+                                      uint32_t* __restrict__ out_ids) {
+    __shared__ uint64_t keys[TILE];
+    const int q = blockIdx.x;
+    const int total = nparts * k;
+    const uint64_t* src = part + (size_t)q * total;
+    const int kpad = k;  // the best k live in keys[0..k)
+    for (int i = threadIdx.x; i < TILE; i += blockDim.x) keys[i] = KEY_INF;
+    __syncthreads();
+    const int step = TILE - kpad;
+    for (int base = 0; base < total; base += step) {
+        for (int i = threadIdx.x; i < step; i += blockDim.x) {
+            int s = base + i;
+            keys[kpad + i] = (s < total) ? src[s] : KEY_INF;
+        }
+        block_bitonic_sort(keys, TILE);
+    }
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        uint64_t key = keys[j];
+        float v;
+        uint32_t id;
+        if (key == KEY_INF) {
+            v = __int_as_float(0x7f800000);
+            id = 0xffffffffu;
+        } else {
+            v = key_value(key);
+            id = key_id(key);
+        }
+        if (negate) v = -v;
+        out_vals[(size_t)q * k + j] = v;
+        out_ids[(size_t)q * k + j] = id;
+    }
+}
+
+#endif
+
+}  // namespace b200vq
