@@ -197,7 +197,8 @@ int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B, const d
                           double* shat, double* nrm_out, void* stream);
 /* Code-domain estimator scan: <s_hat, qrot> per (query, code) with a per-query
  * level LUT, score = ||q-c||^2 + nrm^2 - 2 nrm t/sqrt(D) <levels[idx], qrot>  (L2)
- * or the inner-product analogue. qrot (nq, D) fp32 = (q-c) P. */
+ * with qrot = (q-c) P and qconst = ||q-c||^2; inner product: score = qconst +
+ * nrm t/sqrt(D) <levels[idx], qrot> with qrot = q P and qconst = q.c. */
 size_t b200vq_erabitq_scan_scratch_bytes(int64_t n, int nq, int k);
 int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
                              const float* qrot, const float* qconst, int nq, int metric, int k,

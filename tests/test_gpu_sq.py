@@ -1,0 +1,99 @@
+"""GPU parity tests: scalar quantizer (bit-exact vs the reference's golden vectors) and SAQ."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import sq as osq
+from parity import make_data
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def T():
+    import torch
+    import b200vq
+    from b200vq import ops_sq
+    b200vq.load()
+    class NS:
+        pass
+    ns = NS()
+    ns.torch, ns.ops_sq = torch, ops_sq
+    ns.dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    return ns
+
+
+@pytest.mark.parametrize("name", ["sq_D48.npz", "sq_D33.npz"])
+def test_sq_bit_exact_vs_reference_golden(T, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name))
+    vmin, vmax = T.ops_sq.sq_minmax(T.dev(g["X"]))
+    assert np.array_equal(vmin.cpu().numpy(), g["vmin"]) and np.array_equal(vmax.cpu().numpy(), g["vmax"])
+    D = g["X"].shape[1]
+    for bits in (4, 8, 16):
+        codes = T.ops_sq.sq_encode(T.dev(g["Xq"]), vmin, vmax, bits)
+        got = codes.cpu().numpy()
+        if bits == 16:
+            got = got.view(np.uint16)
+        assert np.array_equal(got, g[f"codes{bits}"]), f"SQ{bits} codes"
+        rec = T.ops_sq.sq_decode(codes, vmin, vmax, bits, D).cpu().numpy()
+        assert np.array_equal(rec, g[f"recon{bits}"]), f"SQ{bits} reconstruction"
+
+
+@pytest.mark.parametrize("n,D", [(20000, 3072), (1001, 100), (5, 7)])
+def test_sq_bit_exact_vs_oracle_at_size(T, n, D):
+    X = make_data(n, D, seed=D, normalize=False, aniso=False) * np.linspace(0.1, 5, D, dtype=np.float32)
+    vmin, vmax = osq.sq_fit(X)
+    xd = T.dev(X)
+    gmin, gmax = T.ops_sq.sq_minmax(xd)
+    assert np.array_equal(gmin.cpu().numpy(), vmin) and np.array_equal(gmax.cpu().numpy(), vmax)
+    for bits in (4, 8, 16):
+        ref = osq.sq_compress(X, vmin, vmax, bits)
+        codes = T.ops_sq.sq_encode(xd, gmin, gmax, bits)
+        got = codes.cpu().numpy()
+        got = got.view(np.uint16) if bits == 16 else got
+        assert np.array_equal(got, ref)
+        rec = T.ops_sq.sq_decode(codes, gmin, gmax, bits, D).cpu().numpy()
+        assert np.array_equal(rec, osq.sq_decompress(ref, vmin, vmax, bits))
+
+
+def test_sq_minmax_accumulates_over_batches_and_saturates(T):
+    X = make_data(3000, 64, 3, normalize=False)
+    a = T.ops_sq.sq_minmax(T.dev(X[:1000]))
+    a = T.ops_sq.sq_minmax(T.dev(X[1000:]), *a)
+    assert np.array_equal(a[0].cpu().numpy(), X.min(0)) and np.array_equal(a[1].cpu().numpy(), X.max(0))
+    out_of_range = T.dev(X * 10)
+    codes = T.ops_sq.sq_encode(out_of_range, a[0], a[1], 8).cpu().numpy()
+    assert codes.min() == 0 and codes.max() == 255  # documented divergence: saturate, never wrap
+    empty = T.torch.empty((0, 64), dtype=T.torch.float32, device="cuda")
+    assert T.ops_sq.sq_encode(empty, a[0], a[1], 8).shape == (0, 64)
+
+
+@pytest.mark.parametrize("D,total,nseg", [(64, 256, 8), (3072, 3072 * 4, 8), (100, 333, 7), (48, 48 * 8, 3)])
+def test_saq_bit_exact_vs_oracle(T, D, total, nseg):
+    X = (make_data(1500, D, seed=D, normalize=False, aniso=False) * np.linspace(3, 0.05, D, dtype=np.float32))
+    plan = osq.saq_plan(X, total_bits=total, allowed_bits=(0, 2, 4, 6, 8), n_segments=nseg)
+    ref = osq.saq_compress(X[:300], plan)
+    fill = np.where(plan["dim_bits"] == 0, plan["mean"], plan["vmin"]).astype(np.float32)
+    bits, off = T.dev(plan["dim_bits"]), T.dev(plan["bit_offset"])
+    codes = T.ops_sq.saq_encode(T.dev(X[:300]), T.dev(plan["vmin"]), T.dev(plan["vmax"]), bits, off,
+                                plan["code_bytes"])
+    assert np.array_equal(codes.cpu().numpy(), ref)
+    rec = T.ops_sq.saq_decode(codes, T.dev(fill), T.dev(plan["vmax"]), bits, off, D).cpu().numpy()
+    assert np.array_equal(rec, osq.saq_decompress(ref, plan))
+
+
+def test_saq_odd_widths_and_uniform_mode(T):
+    """Bit widths outside the CLI default set (1,3,5,7) exercise every byte-straddling case."""
+    D = 40
+    X = make_data(200, D, seed=1, normalize=False)
+    for allowed, total in (((1, 3, 5, 7), D * 4), ((0, 8), D * 3), ((3,), D * 3)):
+        plan = osq.saq_plan(X, total_bits=total, allowed_bits=allowed, n_segments=5)
+        ref = osq.saq_compress(X, plan)
+        bits, off = T.dev(plan["dim_bits"]), T.dev(plan["bit_offset"])
+        codes = T.ops_sq.saq_encode(T.dev(X), T.dev(plan["vmin"]), T.dev(plan["vmax"]), bits, off,
+                                    plan["code_bytes"])
+        assert np.array_equal(codes.cpu().numpy(), ref), allowed
+        fill = np.where(plan["dim_bits"] == 0, plan["mean"], plan["vmin"]).astype(np.float32)
+        rec = T.ops_sq.saq_decode(codes, T.dev(fill), T.dev(plan["vmax"]), bits, off, D).cpu().numpy()
+        assert np.array_equal(rec, osq.saq_decompress(ref, plan)), allowed

@@ -1,0 +1,258 @@
+"""Tensor-level wrappers over the C ABI: torch CUDA tensors in, torch CUDA tensors out.
+
+torch is used for device memory, streams and (elsewhere) torch.distributed only;
+all arithmetic below runs in the hand-written sm_100a kernels of libb200vq.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import METRIC_IP, METRIC_L2, B200VQError, check
+
+_scratch_cache: dict = {}
+
+
+def require_cuda() -> None:
+    if not torch.cuda.is_available():
+        raise B200VQError("b200vq needs a CUDA device (sm_100a); there is no CPU fallback")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise B200VQError(f"{name}: expected a CUDA tensor")
+    if t.dtype != dtype:
+        raise B200VQError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+    return t
+
+
+def _rows(t: torch.Tensor, name: str):
+    """(n, D) tensor with unit column stride -> (ptr, n, ld, D)."""
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+        raise B200VQError(f"{name}: expected a row-major 2-D tensor")
+    ld = t.stride(0) if t.shape[0] > 1 else max(t.shape[1], t.stride(0))
+    return t.data_ptr(), t.shape[0], ld, t.shape[1]
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def scratch(nbytes: int, device, key: str = "default") -> torch.Tensor:
+    """Grow-only per-device scratch buffers (caller-owned from the ABI's point of view)."""
+    k = (key, torch.device(device).index)
+    buf = _scratch_cache.get(k)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _scratch_cache[k] = buf
+    return buf
+
+
+def metric_id(metric) -> int:
+    if metric in ("l2", "L2", METRIC_L2):
+        return METRIC_L2
+    if metric in ("ip", "IP", METRIC_IP):
+        return METRIC_IP
+    raise ValueError(f"unknown metric {metric!r}")
+
+
+# ------------------------------------------------------------------ PQ
+def pq_centroid_norms(centroids: torch.Tensor) -> torch.Tensor:
+    _chk(centroids, torch.float32, "centroids")
+    M, ksub, dsub = centroids.shape
+    out = torch.empty((M, ksub), dtype=torch.float32, device=centroids.device)
+    check(_lib.load().b200vq_pq_centroid_norms(centroids.data_ptr(), M, ksub, dsub, out.data_ptr(), _stream()),
+          "pq_centroid_norms")
+    return out
+
+
+def pq_assign(x: torch.Tensor, centroids: torch.Tensor, cnorm: torch.Tensor | None = None,
+              out: torch.Tensor | None = None, want_dist: bool = False, impl: str = "auto"):
+    """codes (n, M) uint8 = nearest centroid per sub-quantizer.
+
+    impl: "simt" exact fp32 kernel, "tc" tcgen05 screen + exact re-rank, "auto" picks
+    "tc" when the shape qualifies (ksub == 256, dsub % 8 == 0, 16-byte aligned rows).
+    """
+    _chk(x, torch.float32, "x")
+    _chk(centroids, torch.float32, "centroids")
+    M, ksub, dsub = centroids.shape
+    ptr, n, ld, D = _rows(x, "x")
+    if D != M * dsub:
+        raise B200VQError(f"pq_assign: D={D} != M*dsub={M * dsub}")
+    centroids = centroids.contiguous()
+    if cnorm is None:
+        cnorm = pq_centroid_norms(centroids)
+    if out is None:
+        out = torch.empty((n, M), dtype=torch.uint8, device=x.device)
+    lib = _lib.load()
+    tc_ok = (ksub == 256 and dsub % 8 == 0 and ld % 4 == 0 and ptr % 16 == 0 and not want_dist
+             and tc_available())
+    if impl == "tc" and not tc_ok:
+        raise B200VQError("pq_assign(impl='tc'): shape/alignment not supported by the tcgen05 path")
+    if impl == "tc" or (impl == "auto" and tc_ok):
+        nbytes = lib.b200vq_pq_assign_tc_scratch_bytes(n, M)
+        sc = scratch(nbytes, x.device, "assign_tc")
+        check(lib.b200vq_pq_assign_tc(ptr, n, ld, centroids.data_ptr(), cnorm.data_ptr(), M, ksub, dsub,
+                                      out.data_ptr(), sc.data_ptr(), sc.numel(), None, _stream()),
+              "pq_assign_tc")
+        return out
+    dist = torch.empty((n, M), dtype=torch.float32, device=x.device) if want_dist else None
+    check(lib.b200vq_pq_assign_f32(ptr, n, ld, centroids.data_ptr(), cnorm.data_ptr(), M, ksub, dsub,
+                                   out.data_ptr(), _p(dist), _stream()), "pq_assign_f32")
+    return (out, dist) if want_dist else out
+
+
+_tc_state = {"checked": False, "ok": False}
+
+
+def tc_available() -> bool:
+    """True when the tcgen05 assign kernel is compiled in (probe with n = 0)."""
+    if not _tc_state["checked"]:
+        lib = _lib.load()
+        rc = lib.b200vq_pq_assign_tc(None, 0, 0, None, None, 1, 256, 8, None, None, 0, None, None)
+        _tc_state["ok"] = rc != -3  # B200VQ_ERR_UNSUPPORTED
+        _tc_state["checked"] = True
+    return _tc_state["ok"]
+
+
+def pq_decode(codes: torch.Tensor, centroids: torch.Tensor, ids: torch.Tensor | None = None,
+              out: torch.Tensor | None = None) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    _chk(centroids, torch.float32, "centroids")
+    M, ksub, dsub = centroids.shape
+    codes = codes.contiguous()
+    if codes.dim() != 2 or codes.shape[1] != M:
+        raise B200VQError(f"pq_decode: codes must be (n, {M})")
+    n = codes.shape[0] if ids is None else ids.shape[0]
+    if out is None:
+        out = torch.empty((n, M * dsub), dtype=torch.float32, device=codes.device)
+    lib = _lib.load()
+    if ids is None:
+        check(lib.b200vq_pq_decode(codes.data_ptr(), n, centroids.data_ptr(), M, ksub, dsub, out.data_ptr(),
+                                   out.stride(0), _stream()), "pq_decode")
+    else:
+        _chk(ids, torch.int64, "ids")
+        check(lib.b200vq_pq_decode_ids(codes.data_ptr(), ids.contiguous().data_ptr(), n, centroids.data_ptr(),
+                                       M, ksub, dsub, out.data_ptr(), out.stride(0), _stream()),
+              "pq_decode_ids")
+    return out
+
+
+def pq_kmeans_step(x: torch.Tensor, centroids: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor,
+                   codes: torch.Tensor, nsplit: torch.Tensor, impl: str = "simt") -> None:
+    """One Lloyd iteration in place: assign, accumulate, finalize."""
+    M, ksub, dsub = centroids.shape
+    ptr, n, ld, D = _rows(x, "x")
+    lib = _lib.load()
+    pq_assign(x, centroids, out=codes, impl=impl)
+    sums.zero_()
+    counts.zero_()
+    check(lib.b200vq_pq_kmeans_accumulate(ptr, n, ld, codes.data_ptr(), M, ksub, dsub, sums.data_ptr(),
+                                          counts.data_ptr(), _stream()), "pq_kmeans_accumulate")
+    check(lib.b200vq_pq_kmeans_finalize(sums.data_ptr(), counts.data_ptr(), M, ksub, dsub,
+                                        centroids.data_ptr(), nsplit.data_ptr(), _stream()),
+          "pq_kmeans_finalize")
+
+
+def pq_sse(x: torch.Tensor, codes: torch.Tensor, centroids: torch.Tensor) -> torch.Tensor:
+    M, ksub, dsub = centroids.shape
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.zeros(1, dtype=torch.float64, device=x.device)
+    check(_lib.load().b200vq_pq_sse(ptr, n, ld, codes.data_ptr(), centroids.data_ptr(), M, ksub, dsub,
+                                    out.data_ptr(), _stream()), "pq_sse")
+    return out
+
+
+# ------------------------------------------------------------------ ADC / search
+def adc_lut(queries: torch.Tensor, centroids: torch.Tensor, metric) -> torch.Tensor:
+    _chk(queries, torch.float32, "queries")
+    M, ksub, dsub = centroids.shape
+    ptr, nq, ld, D = _rows(queries, "queries")
+    if D != M * dsub:
+        raise B200VQError(f"adc_lut: D={D} != M*dsub={M * dsub}")
+    lut = torch.empty((nq, M, ksub), dtype=torch.float32, device=queries.device)
+    check(_lib.load().b200vq_adc_lut(ptr, nq, ld, centroids.data_ptr(), M, ksub, dsub, metric_id(metric),
+                                     lut.data_ptr(), _stream()), "adc_lut")
+    return lut
+
+
+def _topk_out(nq, k, device):
+    return (torch.empty((nq, k), dtype=torch.float32, device=device),
+            torch.empty((nq, k), dtype=torch.int32, device=device))
+
+
+def adc_scan_topk(codes: torch.Tensor, lut: torch.Tensor, k: int, metric, n: int | None = None,
+                  rot: bool = False):
+    """Top-k of sum_m lut[q, m, codes[i, m]]. codes: (n, M) uint8 row-major, or the
+    scan layout (rot=True, n must then be given). Returns (vals fp32, ids int32 view of uint32)."""
+    _chk(codes, torch.uint8, "codes")
+    _chk(lut, torch.float32, "lut")
+    nq, M, ksub = lut.shape
+    if n is None:
+        n = codes.shape[0]
+    lib = _lib.load()
+    vals, ids = _topk_out(nq, k, codes.device)
+    nbytes = lib.b200vq_adc_scan_scratch_bytes(n, nq, k)
+    sc = scratch(nbytes, codes.device, "scan")
+    fn = lib.b200vq_adc_scan_topk_rot if rot else lib.b200vq_adc_scan_topk
+    check(fn(codes.data_ptr(), n, M, ksub, lut.data_ptr(), nq, metric_id(metric), k, vals.data_ptr(),
+             ids.data_ptr(), sc.data_ptr(), sc.numel(), _stream()),
+          "adc_scan_topk_rot" if rot else "adc_scan_topk")
+    return vals, ids
+
+
+def pq_codes_to_scan_layout(codes: torch.Tensor) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    n, M = codes.shape
+    out = torch.empty((((n + 31) // 32) * 32 * M,), dtype=torch.uint8, device=codes.device)
+    check(_lib.load().b200vq_pq_codes_to_scan_layout(codes.contiguous().data_ptr(), n, M, out.data_ptr(),
+                                                     _stream()), "pq_codes_to_scan_layout")
+    return out
+
+
+def row_sqnorms(x: torch.Tensor) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.empty((n,), dtype=torch.float32, device=x.device)
+    check(_lib.load().b200vq_row_sqnorms(ptr, n, ld, D, out.data_ptr(), _stream()), "row_sqnorms")
+    return out
+
+
+def flat_topk(x: torch.Tensor, queries: torch.Tensor, k: int, metric, xnorm: torch.Tensor | None = None,
+              row_scale: torch.Tensor | None = None):
+    _chk(x, torch.float32, "x")
+    _chk(queries, torch.float32, "queries")
+    ptr, n, ld, D = _rows(x, "x")
+    qptr, nq, ldq, Dq = _rows(queries, "queries")
+    if D != Dq:
+        raise B200VQError(f"flat_topk: dimension mismatch {D} vs {Dq}")
+    mid = metric_id(metric)
+    if mid == METRIC_L2 and xnorm is None:
+        xnorm = row_sqnorms(x)
+    lib = _lib.load()
+    vals, ids = _topk_out(nq, k, x.device)
+    nbytes = lib.b200vq_flat_topk_scratch_bytes(n, nq, k)
+    sc = scratch(nbytes, x.device, "scan")
+    check(lib.b200vq_flat_topk(ptr, n, ld, D, _p(xnorm), _p(row_scale), qptr, nq, ldq, mid, k,
+                               vals.data_ptr(), ids.data_ptr(), sc.data_ptr(), sc.numel(), _stream()),
+          "flat_topk")
+    return vals, ids
+
+
+def topk_merge(vals: torch.Tensor, ids: torch.Tensor, k: int, metric):
+    """vals (nq, P, k) fp32, ids (nq, P, k) int64 -> merged (nq, k)."""
+    _chk(vals, torch.float32, "vals")
+    _chk(ids, torch.int64, "ids")
+    nq, P, kk = vals.shape
+    out_v = torch.empty((nq, k), dtype=torch.float32, device=vals.device)
+    out_i = torch.empty((nq, k), dtype=torch.int64, device=vals.device)
+    if kk != k:
+        raise B200VQError("topk_merge: partial lists must have k entries")
+    check(_lib.load().b200vq_topk_merge(vals.contiguous().data_ptr(), ids.contiguous().data_ptr(), nq, P, k,
+                                        metric_id(metric), out_v.data_ptr(), out_i.data_ptr(), _stream()),
+          "topk_merge")
+    return out_v, out_i

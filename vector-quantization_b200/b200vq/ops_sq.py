@@ -1,0 +1,186 @@
+"""Tensor-level wrappers: scalar quantizers, RaBitQ family, utilities."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import B200VQError, check
+from .ops import _chk, _p, _rows, _stream, _topk_out, metric_id, scratch
+
+
+# ------------------------------------------------------------------ SQ
+def sq_minmax(x: torch.Tensor, vmin: torch.Tensor | None = None, vmax: torch.Tensor | None = None):
+    """Column-wise min/max; pass the previous (vmin, vmax) to accumulate over batches."""
+    _chk(x, torch.float32, "x")
+    ptr, n, ld, D = _rows(x, "x")
+    if vmin is None:
+        vmin = torch.full((D,), float("inf"), dtype=torch.float32, device=x.device)
+        vmax = torch.full((D,), float("-inf"), dtype=torch.float32, device=x.device)
+    check(_lib.load().b200vq_sq_minmax(ptr, n, ld, D, vmin.data_ptr(), vmax.data_ptr(), _stream()),
+          "sq_minmax")
+    return vmin, vmax
+
+
+def sq_code_shape(n: int, D: int, bits: int):
+    if bits == 4:
+        return (n, (D + 1) // 2), torch.uint8
+    if bits == 8:
+        return (n, D), torch.uint8
+    if bits == 16:
+        return (n, D), torch.int16  # bit pattern of uint16
+    raise ValueError(f"num_bits must be 4, 8, or 16, got {bits}")
+
+
+def sq_encode(x: torch.Tensor, vmin: torch.Tensor, vmax: torch.Tensor, bits: int,
+              out: torch.Tensor | None = None) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    ptr, n, ld, D = _rows(x, "x")
+    shape, dt = sq_code_shape(n, D, bits)
+    if out is None:
+        out = torch.empty(shape, dtype=dt, device=x.device)
+    check(_lib.load().b200vq_sq_encode(ptr, n, ld, D, vmin.data_ptr(), vmax.data_ptr(), bits, out.data_ptr(),
+                                       _stream()), "sq_encode")
+    return out
+
+
+def sq_decode(codes: torch.Tensor, vmin: torch.Tensor, vmax: torch.Tensor, bits: int, D: int,
+              out: torch.Tensor | None = None) -> torch.Tensor:
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    if out is None:
+        out = torch.empty((n, D), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_sq_decode(codes.data_ptr(), n, D, vmin.data_ptr(), vmax.data_ptr(), bits,
+                                       out.data_ptr(), out.stride(0), _stream()), "sq_decode")
+    return out
+
+
+def saq_encode(x: torch.Tensor, vmin, vmax, dim_bits: torch.Tensor, bit_offset: torch.Tensor,
+               code_bytes: int) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    _chk(dim_bits, torch.int32, "dim_bits")
+    _chk(bit_offset, torch.int32, "bit_offset")
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.empty((n, code_bytes), dtype=torch.uint8, device=x.device)
+    check(_lib.load().b200vq_saq_encode(ptr, n, ld, D, vmin.data_ptr(), vmax.data_ptr(), dim_bits.data_ptr(),
+                                        bit_offset.data_ptr(), code_bytes, out.data_ptr(), _stream()),
+          "saq_encode")
+    return out
+
+
+def saq_decode(codes: torch.Tensor, vmin_fill, vmax, dim_bits, bit_offset, D: int) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n, code_bytes = codes.shape
+    out = torch.empty((n, D), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_saq_decode(codes.data_ptr(), n, D, vmin_fill.data_ptr(), vmax.data_ptr(),
+                                        dim_bits.data_ptr(), bit_offset.data_ptr(), code_bytes,
+                                        out.data_ptr(), out.stride(0), _stream()), "saq_decode")
+    return out
+
+
+# ------------------------------------------------------------------ extended RaBitQ
+def erabitq_pack(srot: torch.Tensor, nrm: torch.Tensor, B: int, levels: torch.Tensor,
+                 bounds: torch.Tensor) -> torch.Tensor:
+    _chk(srot, torch.float64, "srot")
+    _chk(nrm, torch.float64, "nrm")
+    srot = srot.contiguous()
+    n, D = srot.shape
+    out = torch.empty((n, (D * B + 7) // 8 + 8), dtype=torch.uint8, device=srot.device)
+    check(_lib.load().b200vq_erabitq_pack(srot.data_ptr(), nrm.data_ptr(), n, D, B, levels.data_ptr(),
+                                          bounds.data_ptr(), out.data_ptr(), _stream()), "erabitq_pack")
+    return out
+
+
+def erabitq_unpack(codes: torch.Tensor, D: int, B: int, levels: torch.Tensor):
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    shat = torch.empty((n, D), dtype=torch.float64, device=codes.device)
+    nrm = torch.empty((n,), dtype=torch.float64, device=codes.device)
+    check(_lib.load().b200vq_erabitq_unpack(codes.data_ptr(), n, D, B, levels.data_ptr(), shat.data_ptr(),
+                                            nrm.data_ptr(), _stream()), "erabitq_unpack")
+    return shat, nrm
+
+
+def erabitq_scan_topk(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Tensor, qrot: torch.Tensor,
+                      qconst: torch.Tensor, k: int, metric):
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    nq = qrot.shape[0]
+    lib = _lib.load()
+    vals, ids = _topk_out(nq, k, codes.device)
+    sc = scratch(lib.b200vq_erabitq_scan_scratch_bytes(n, nq, k), codes.device, "scan")
+    check(lib.b200vq_erabitq_scan_topk(codes.data_ptr(), n, D, B, levels_f32.data_ptr(),
+                                       qrot.contiguous().data_ptr(), qconst.data_ptr(), nq, metric_id(metric),
+                                       k, vals.data_ptr(), ids.data_ptr(), sc.data_ptr(), sc.numel(),
+                                       _stream()), "erabitq_scan_topk")
+    return vals, ids
+
+
+# ------------------------------------------------------------------ 1-bit RaBitQ
+def rabitq1_encode(x: torch.Tensor, centroid: torch.Tensor | None, metric) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.empty((n, (D + 7) // 8 + 8), dtype=torch.uint8, device=x.device)
+    check(_lib.load().b200vq_rabitq1_encode(ptr, n, ld, D, _p(centroid), metric_id(metric), out.data_ptr(),
+                                            _stream()), "rabitq1_encode")
+    return out
+
+
+def rabitq1_decode(codes: torch.Tensor, D: int, centroid: torch.Tensor | None) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    out = torch.empty((n, D), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_rabitq1_decode(codes.data_ptr(), n, D, _p(centroid), out.data_ptr(),
+                                            out.stride(0), _stream()), "rabitq1_decode")
+    return out
+
+
+def rabitq1_prepare_queries(queries: torch.Tensor, centroid: torch.Tensor | None, qb: int):
+    _chk(queries, torch.float32, "queries")
+    ptr, nq, ld, D = _rows(queries, "queries")
+    W = (D + 31) // 32
+    planes = torch.empty((nq, qb, W), dtype=torch.int32, device=queries.device)
+    qfac = torch.empty((nq, 8), dtype=torch.float32, device=queries.device)
+    check(_lib.load().b200vq_rabitq1_prepare_queries(ptr, nq, ld, D, _p(centroid), qb, planes.data_ptr(),
+                                                     qfac.data_ptr(), _stream()), "rabitq1_prepare_queries")
+    return planes, qfac
+
+
+def rabitq1_scan_topk(codes: torch.Tensor, D: int, planes: torch.Tensor, qfac: torch.Tensor, qb: int,
+                      k: int, metric):
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    nq = planes.shape[0]
+    lib = _lib.load()
+    vals, ids = _topk_out(nq, k, codes.device)
+    sc = scratch(lib.b200vq_rabitq1_scan_scratch_bytes(n, nq, k), codes.device, "scan")
+    check(lib.b200vq_rabitq1_scan_topk(codes.data_ptr(), n, D, planes.data_ptr(), qfac.data_ptr(), nq, qb,
+                                       metric_id(metric), k, vals.data_ptr(), ids.data_ptr(), sc.data_ptr(),
+                                       sc.numel(), _stream()), "rabitq1_scan_topk")
+    return vals, ids
+
+
+# ------------------------------------------------------------------ utilities
+def synth_rows(n: int, D: int, row0: int, seed: int, col_scale: torch.Tensor | None = None,
+               normalize: bool = False, out: torch.Tensor | None = None, device="cuda") -> torch.Tensor:
+    if out is None:
+        out = torch.empty((n, D), dtype=torch.float32, device=device)
+    check(_lib.load().b200vq_synth_rows(out.data_ptr(), n, out.stride(0), D, row0, seed, _p(col_scale),
+                                        int(normalize), _stream()), "synth_rows")
+    return out
+
+
+def sq_err_sum(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    _chk(a, torch.float32, "a")
+    _chk(b, torch.float32, "b")
+    pa, n, lda, D = _rows(a, "a")
+    pb, nb, ldb, Db = _rows(b, "b")
+    if (n, D) != (nb, Db):
+        raise B200VQError("sq_err_sum: shape mismatch")
+    out = torch.zeros(1, dtype=torch.float64, device=a.device)
+    check(_lib.load().b200vq_sq_err_sum(pa, lda, pb, ldb, n, D, out.data_ptr(), _stream()), "sq_err_sum")
+    return out

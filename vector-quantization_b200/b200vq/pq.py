@@ -1,0 +1,149 @@
+"""Device-resident product quantizer / OPQ (train, encode, decode, ADC search).
+
+Host orchestration only; the arithmetic is in libb200vq.so. Mirrors the faiss
+objects the reference drives (ProductQuantizer, OPQMatrix): reference call
+sites src/haag_vq/methods/product_quantization.py:58-86 and
+src/haag_vq/methods/optimized_product_quantization.py:21-34. All randomness
+(training subset, seeds, OPQ start rotation) follows the same seeded numpy
+recipe as the CPU oracle so both share trained state.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops
+
+MAX_POINTS_PER_CENTROID = 256
+KMEANS_NITER = 25
+
+
+def subsample_ids(n: int, nmax: int, seed: int) -> np.ndarray:
+    if n <= nmax:
+        return np.arange(n, dtype=np.int64)
+    return np.random.default_rng(seed).permutation(n)[:nmax].astype(np.int64)
+
+
+def _take_rows(x: torch.Tensor, ids: np.ndarray) -> torch.Tensor:
+    if ids.size == x.shape[0]:
+        return x
+    return x.index_select(0, torch.from_numpy(ids).to(x.device))
+
+
+def pq_init_centroids(xt: torch.Tensor, M: int, ksub: int, seed: int) -> torch.Tensor:
+    n, D = xt.shape
+    dsub = D // M
+    if n < ksub:
+        raise RuntimeError(
+            f"Number of training points ({n}) should be at least as large as number of clusters ({ksub})")
+    C = torch.empty((M, ksub, dsub), dtype=torch.float32, device=xt.device)
+    for m in range(M):
+        ids = np.random.default_rng(seed + m).permutation(n)[:ksub]
+        C[m] = xt.index_select(0, torch.from_numpy(ids).to(xt.device))[:, m * dsub:(m + 1) * dsub]
+    return C
+
+
+def pq_train(x: torch.Tensor, M: int, nbits: int = 8, niter: int = KMEANS_NITER, seed: int = 1234,
+             centroids0: torch.Tensor | None = None, impl: str = "auto") -> torch.Tensor:
+    """M independent Lloyd k-means on the device. Returns centroids (M, ksub, dsub)."""
+    n, D = x.shape
+    if D % M != 0:
+        raise AssertionError("D must be divisible by M (number of subquantizers)")
+    if nbits < 1 or nbits > 8:
+        raise ValueError("b200vq supports 1 <= B <= 8 bits per sub-quantizer index")
+    ksub = 1 << nbits
+    xt = _take_rows(x, subsample_ids(n, MAX_POINTS_PER_CENTROID * ksub, seed))
+    if centroids0 is None:
+        C = pq_init_centroids(xt, M, ksub, seed)
+        if xt.shape[0] == ksub:
+            return C
+    else:
+        C = centroids0.to(torch.float32).clone().contiguous()
+    dsub = D // M
+    nt = xt.shape[0]
+    sums = torch.empty((M, ksub, dsub), dtype=torch.float32, device=x.device)
+    counts = torch.empty((M, ksub), dtype=torch.int32, device=x.device)
+    codes = torch.empty((nt, M), dtype=torch.uint8, device=x.device)
+    nsplit = torch.zeros(1, dtype=torch.int32, device=x.device)
+    for _ in range(niter):
+        ops.pq_kmeans_step(xt, C, sums, counts, codes, nsplit, impl=impl)
+    return C
+
+
+def random_rotation(D: int, seed: int) -> np.ndarray:
+    A = np.random.default_rng(seed).standard_normal((D, D))
+    Qm, _ = np.linalg.qr(A)
+    return np.ascontiguousarray(Qm.astype(np.float32))
+
+
+def rotate(x: torch.Tensor, A: torch.Tensor, transpose: bool = True) -> torch.Tensor:
+    """y = x A^T (OPQMatrix.apply) or y = x A (reverse_transform). Plain library GEMM in
+    strict fp32 (TF32 off) so the rotated values match an fp32 sgemm."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        return torch.matmul(x, A.t() if transpose else A)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+def opq_train(x: torch.Tensor, M: int, nbits: int = 8, niter: int = 50, niter_pq: int = 4,
+              niter_pq_0: int = 40, seed: int = 123, A0: np.ndarray | None = None) -> torch.Tensor:
+    """OPQMatrix.train: alternate PQ training on rotated data with the Procrustes update."""
+    n, D = x.shape
+    xt = _take_rows(x, subsample_ids(n, MAX_POINTS_PER_CENTROID * 256, seed))
+    A = torch.from_numpy(random_rotation(D, seed) if A0 is None else np.asarray(A0, dtype=np.float32)).to(x.device)
+    C = None
+    xt64 = None
+    for it in range(niter):
+        y = rotate(xt, A)
+        if it == 0:
+            C = pq_train(y, M, nbits, niter=niter_pq_0, seed=seed)
+        else:
+            C = pq_train(y, M, nbits, niter=niter_pq, seed=seed, centroids0=C)
+        r = ops.pq_decode(ops.pq_assign(y, C), C)
+        if xt64 is None:
+            xt64 = xt.to(torch.float64)
+        U, _, Vt = torch.linalg.svd(xt64.t() @ r.to(torch.float64))
+        A = (U @ Vt).t().to(torch.float32).contiguous()
+    return A
+
+
+class PQCodec:
+    """Trained PQ state on one device + encode/decode/search helpers."""
+
+    def __init__(self, centroids: torch.Tensor, rotation: torch.Tensor | None = None):
+        self.centroids = centroids.contiguous()
+        self.M, self.ksub, self.dsub = centroids.shape
+        self.D = self.M * self.dsub
+        self.cnorm = ops.pq_centroid_norms(self.centroids)
+        self.rotation = rotation  # (D, D) A of OPQ, or None
+
+    def encode(self, x: torch.Tensor, out: torch.Tensor | None = None, impl: str = "auto") -> torch.Tensor:
+        if self.rotation is not None:
+            x = rotate(x, self.rotation)
+        return ops.pq_assign(x, self.centroids, self.cnorm, out=out, impl=impl)
+
+    def decode(self, codes: torch.Tensor, ids: torch.Tensor | None = None) -> torch.Tensor:
+        r = ops.pq_decode(codes, self.centroids, ids=ids)
+        if self.rotation is not None:
+            r = rotate(r, self.rotation, transpose=False)
+        return r
+
+    def luts(self, queries: torch.Tensor, metric) -> torch.Tensor:
+        if self.rotation is not None:
+            queries = rotate(queries, self.rotation)  # orthonormal: distances are preserved
+        return ops.adc_lut(queries, self.centroids, metric)
+
+    def search(self, codes: torch.Tensor, queries: torch.Tensor, k: int, metric, n: int | None = None,
+               rot: bool = False, q_batch: int = 4096):
+        """ADC top-k over (n, M) codes. Returns (vals (nq,k) fp32, ids (nq,k) int32-as-uint32)."""
+        nq = queries.shape[0]
+        vals = torch.empty((nq, k), dtype=torch.float32, device=queries.device)
+        ids = torch.empty((nq, k), dtype=torch.int32, device=queries.device)
+        for s in range(0, nq, q_batch):
+            e = min(nq, s + q_batch)
+            lut = self.luts(queries[s:e], metric)
+            v, i = ops.adc_scan_topk(codes, lut, k, metric, n=n, rot=rot)
+            vals[s:e], ids[s:e] = v, i
+        return vals, ids

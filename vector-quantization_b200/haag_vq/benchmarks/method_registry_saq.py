@@ -1,0 +1,25 @@
+"""Registry for the SAQ-study methods outside the faiss family.
+
+Mirrors src/haag_vq/benchmarks/method_registry_saq.py:17-74 for the methods on
+the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)). The
+other names of SAQ_METHODS are the reference's C++-engine / per-dimension
+codebook studies (saq_paper, ours*, lvq, rankaware*, perdim_mse*), which
+SURVEY.md §8(f) ranks as "next"; they raise NotImplementedError here instead of
+silently falling back to anything.
+"""
+from __future__ import annotations
+
+SAQ_METHODS = ("saq_paper", "ours", "ours_exact", "rabitq", "lvq",
+               "rankaware", "perdim_mse", "rankaware_exact", "perdim_mse_exact")
+
+
+def build_saq_quantizer(method: str, bpd: float, D: int):
+    b = int(round(bpd))
+    if method == "rabitq":
+        from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
+        from haag_vq.methods.extended_rabitq import ExtendedRaBitQuantizer
+        return FaissQuantizerAdapter(ExtendedRaBitQuantizer(num_bits=b))
+    if method in SAQ_METHODS:
+        raise NotImplementedError(
+            f"method {method!r} is not built on the B200 path yet (SURVEY.md §8f); no fallback is provided")
+    raise ValueError(f"Unknown SAQ-study method: {method!r}")
