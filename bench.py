@@ -1,0 +1,483 @@
+#!/usr/bin/env python
+"""bench.py — PQ streaming encode + ADC top-10 scan on the MS MARCO shape (BASELINE config 5).
+
+Workload (weak scaling): every GPU owns a shard of 6 625 000 x 1024 fp32 rows (8 shards =
+53 M rows), PQ M=32 nbits=8. One step = encode one batch of 2^20 synthetic rows that are
+already resident in HBM (b200vq_pq_assign*) + scan the shard's (n, 32) uint8 codes with
+1000 per-query LUTs for the top-10 (b200vq_adc_lut, b200vq_adc_scan_topk*), followed, when
+N > 1, by the NCCL all-gather + k-way merge of the per-shard lists.
+
+  value            vectors/s encoded, whole job (all ranks), device-timed, inputs in HBM
+  adc.value        ADC codes/s scanned = total rows x queries / scan time
+  e2e              same two numbers through the reference-facing haag_vq objects with HOST
+                   (pinned) buffers: ProductQuantizer.compress(X) and
+                   FlatQuantizedIndex.search_with_scores(Q, 10), copies inside the timed region
+  roofline         ADC scan kernel vs the measured HBM copy bandwidth (algorithmic bytes =
+                   rows x M per query pass)
+  roofline_assign  PQ assign kernel vs the tensor pipe (TF32 = measured bf16 peak / 2)
+  cpu_baseline     the CPU oracle timed on a bounded sample on this box's host cores
+
+`--impl reference` times the reference's CPU path for the same step (faiss-semantics
+numpy/BLAS nearest-centroid assign + the ADC loop of bench/ffd_speed.cpp restated in C with
+OpenMP, all host threads) on a bounded sample and prints the same line.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "vector-quantization_b200")
+for _p in (PKG, ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+D, M, KSUB, K = 1024, 32, 256, 10
+SHARD_ROWS = 6_625_000          # 53 M / 8
+BATCH_ROWS = 1 << 20
+NQ = 1000
+E2E_ROWS = 1 << 18              # host batch of the e2e encode leg (1 GiB pinned)
+TRAIN_ROWS = 65_536             # 256 * ksub, faiss' training subset size
+METRIC = "vectors/s encoded + ADC codes/s scanned at 1/2/4/8 B200, % of HBM roofline"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows-per-gpu", type=int, default=SHARD_ROWS)
+    ap.add_argument("--batch-rows", type=int, default=BATCH_ROWS)
+    ap.add_argument("--nq", type=int, default=NQ)
+    ap.add_argument("--assign-impl", default="auto", choices=["auto", "simt", "tc"])
+    ap.add_argument("--scan-layout", default="auto", choices=["auto", "rows", "rot"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]),
+                "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                "source": "measured"}
+    # fallback stated in the profiling recipe
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": (sm[len(sm) // 2] if sm else None), "sm_max_mhz": mx,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------- CPU legs ---
+def synth_host(n: int, seed: int) -> np.ndarray:
+    """Host twin of the device generator's distribution (anisotropic Gaussian, unit rows)."""
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((n, D), dtype=np.float32) * np.linspace(4.0, 0.2, D, dtype=np.float32)
+    X /= np.maximum(np.linalg.norm(X, axis=1, keepdims=True), 1e-12)
+    return np.ascontiguousarray(X, dtype=np.float32)
+
+
+def _load_oracle_adc():
+    path = os.path.join(ROOT, "oracle", "_ref", "liboracle_adc.so")
+    if not os.path.exists(path):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "_ref/liboracle_adc.so"], check=True)
+    lib = ctypes.CDLL(path)
+    lib.oracle_adc_scores.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                      ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    lib.oracle_adc_scores.restype = None
+    return lib
+
+
+def cpu_step(X, C, codes_db, Q, adc_lib, scores_buf):
+    """One pass of the reference CPU path on a bounded sample: numpy/BLAS nearest-centroid
+    assign (oracle.pq.pq_assign) + ADC scores (C loop, OpenMP) + argpartition top-k."""
+    from oracle import pq as opq
+    t0 = time.perf_counter()
+    opq.pq_assign(X, C)
+    t1 = time.perf_counter()
+    lut = opq.adc_lut(Q, C, opq.L2)
+    n = codes_db.shape[0]
+    adc_lib.oracle_adc_scores(codes_db.ctypes.data, n, M, KSUB, lut.ctypes.data, Q.shape[0],
+                              scores_buf.ctypes.data)
+    sc = scores_buf.reshape(-1)[:Q.shape[0] * n].reshape(Q.shape[0], n)
+    for q in range(Q.shape[0]):
+        part = np.argpartition(sc[q], K - 1)[:K]
+        part[np.argsort(sc[q][part], kind="stable")]
+    t2 = time.perf_counter()
+    return t1 - t0, t2 - t1
+
+
+def cpu_setup(enc_rows: int, db_rows: int, nq: int):
+    from oracle import pq as opq
+    X = synth_host(enc_rows, 11)
+    C = opq.pq_init_centroids(synth_host(4096, 12), M, KSUB, seed=1)
+    rng = np.random.default_rng(13)
+    codes_db = rng.integers(0, 256, size=(db_rows, M), dtype=np.uint8)
+    Q = synth_host(nq, 14)
+    scores = np.empty((nq, db_rows), dtype=np.float32)
+    return X, C, codes_db, Q, _load_oracle_adc(), scores
+
+
+CPU_SAMPLE = dict(enc_rows=131_072, db_rows=1_000_000, nq=64)
+
+
+def cpu_baseline_leg(reps: int = 2):
+    cores = os.cpu_count() or 1
+    X, C, codes_db, Q, lib, scores = cpu_setup(**CPU_SAMPLE)
+    cpu_step(X[:2048], C, codes_db[:65536], Q[:2], lib, scores)  # warm BLAS / OpenMP pools
+    te = ts = 0.0
+    for _ in range(reps):
+        a, b = cpu_step(X, C, codes_db, Q, lib, scores)
+        te += a
+        ts += b
+    return {"value": CPU_SAMPLE["enc_rows"] * reps / te, "unit": "vectors/s", "cores": cores, "kind": "port",
+            "adc": {"value": CPU_SAMPLE["db_rows"] * CPU_SAMPLE["nq"] * reps / ts, "unit": "codes/s"},
+            "sample": (f"oracle port (faiss is not vendored in the reference): numpy/BLAS pq_assign of "
+                       f"{CPU_SAMPLE['enc_rows']}x{D} rows + C/OpenMP ADC scan of {CPU_SAMPLE['db_rows']} codes x "
+                       f"{CPU_SAMPLE['nq']} queries with argpartition top-{K}, {reps} reps")}
+
+
+def run_reference(args):
+    """--impl reference: the CPU path, rank 0 only, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    X, C, codes_db, Q, lib, scores = cpu_setup(**CPU_SAMPLE)
+    for _ in range(max(1, min(args.warmup, 3))):
+        cpu_step(X[:4096], C, codes_db[:131072], Q[:2], lib, scores)
+    te = ts = 0.0
+    for _ in range(args.steps):
+        a, b = cpu_step(X, C, codes_db, Q, lib, scores)
+        te += a
+        ts += b
+    enc = CPU_SAMPLE["enc_rows"] * args.steps / te
+    adc = CPU_SAMPLE["db_rows"] * CPU_SAMPLE["nq"] * args.steps / ts
+    sample = (f"per step: pq_assign of {CPU_SAMPLE['enc_rows']}x{D} rows (numpy/BLAS, faiss semantics) + ADC scan of "
+              f"{CPU_SAMPLE['db_rows']} codes x {CPU_SAMPLE['nq']} queries (C/OpenMP restatement of bench/ffd_speed.cpp)")
+    line = {"impl": "reference", "metric": METRIC, "value": enc, "unit": "vectors/s",
+            "adc": {"value": adc, "unit": "codes/s"}, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": (te + ts) / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args),
+            "cpu_baseline": {"value": enc, "unit": "vectors/s", "cores": cores, "kind": "port",
+                             "adc": {"value": adc, "unit": "codes/s"}, "sample": sample},
+            "e2e": {"value": enc, "unit": "vectors/s", "adc": {"value": adc, "unit": "codes/s"},
+                    "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args):
+    return {"workload": f"PQ M={M} nbits=8 streaming encode + ADC top-{K}, synthetic {args.rows_per_gpu * args.gpus}x{D} "
+                        f"(MS MARCO shape, BASELINE config 5), {args.rows_per_gpu} rows per GPU",
+            "rows_per_gpu": args.rows_per_gpu, "batch_rows": args.batch_rows, "D": D, "M": M, "ksub": KSUB,
+            "queries": args.nq, "k": K, "parallelism": f"row-shard x{args.gpus}",
+            "l2": "inputs larger than L2 (4 GiB row batches rotate; 212 MB of codes per scan)"}
+
+
+# ----------------------------------------------------------------- GPU arm ---
+def run_b200(args):
+    import torch
+    import torch.distributed as tdist
+
+    import b200vq
+    from b200vq import _lib, dist as vdist, ops, ops_sq
+    from b200vq import pq as dpq
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        tdist.init_process_group("nccl", device_id=dev)
+    if world != args.gpus and rank == 0:
+        print(f"bench.py: WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE", file=sys.stderr)
+    b200vq.load()
+    peaks = measured_peaks()
+
+    n, B, nq = args.rows_per_gpu, min(args.batch_rows, args.rows_per_gpu), args.nq
+    row_offset = rank * n
+    col_scale = torch.linspace(4.0, 0.2, D, device=dev)
+
+    # trained state: identical on every rank (same seed, same generator rows)
+    xt = ops_sq.synth_rows(TRAIN_ROWS, D, 1 << 40, 1234, col_scale, True, device=dev)
+    C = dpq.pq_train(xt, M, 8, niter=8, seed=1234)
+    del xt
+    codec = dpq.PQCodec(C)
+    impl = args.assign_impl
+    if impl == "auto":
+        impl = "tc" if ops.tc_available() else "simt"
+
+    # streaming encode of the whole shard (untimed): generator batch -> codes
+    codes = torch.empty((n, M), dtype=torch.uint8, device=dev)
+    xbuf = [torch.empty((B, D), dtype=torch.float32, device=dev) for _ in range(2)]
+    starts = list(range(0, n, B))
+    for i, s in enumerate(starts):
+        e = min(n, s + B)
+        ops_sq.synth_rows(e - s, D, row_offset + s, 1234, col_scale, True, out=xbuf[i & 1][:e - s])
+        codec.encode(xbuf[i & 1][:e - s], out=codes[s:e], impl=impl)
+    # the two timed batches are the first two full batches of the shard
+    full = [s for s in starts if s + B <= n][:2] or [0]
+    for j, s in enumerate(full):
+        ops_sq.synth_rows(B, D, row_offset + s, 1234, col_scale, True, out=xbuf[j])
+    Qd = ops_sq.synth_rows(nq, D, 1 << 41, 4321, col_scale, True, device=dev)
+    torch.cuda.synchronize()
+
+    def time_ms(fn, reps=2):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    lut0 = codec.luts(Qd[:min(nq, 64)], "l2")
+    layout = args.scan_layout
+    codes_rot = None
+    if layout in ("auto", "rot") and M % 32 == 0:
+        codes_rot = ops.pq_codes_to_scan_layout(codes)
+        if layout == "auto":
+            t_rows = time_ms(lambda: ops.adc_scan_topk(codes, lut0, K, "l2"))
+            t_rot = time_ms(lambda: ops.adc_scan_topk(codes_rot, lut0, K, "l2", n=n, rot=True))
+            layout = "rot" if t_rot < t_rows else "rows"
+            if layout == "rows":
+                codes_rot = None
+    else:
+        layout = "rows"
+    del lut0
+
+    def scan(lut):
+        if layout == "rot":
+            return ops.adc_scan_topk(codes_rot, lut, K, "l2", n=n, rot=True)
+        return ops.adc_scan_topk(codes, lut, K, "l2")
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    marks = []
+
+    def step(i, record):
+        j = i % len(full)
+        s = full[j]
+        e0, e1, e2, e3, e4 = ev(), ev(), ev(), ev(), ev()
+        e0.record()
+        codec.encode(xbuf[j], out=codes[s:s + B], impl=impl)
+        e1.record()
+        lut = codec.luts(Qd, "l2")
+        e2.record()
+        vals, ids = scan(lut)
+        e3.record()
+        if world > 1:
+            vals, ids = vdist.sharded_topk(vals, ids, row_offset, K, "l2")
+        e4.record()
+        if record:
+            marks.append((e0, e1, e2, e3, e4))
+        return vals, ids
+
+    def barrier():
+        if world > 1:
+            tdist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(3, args.warmup)):
+        step(i, False)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    calls0 = _lib.abi_calls
+    t0, t1 = ev(), ev()
+    barrier()
+    t0.record()
+    for i in range(args.steps):
+        step(i, True)
+    t1.record()
+    barrier()
+    n_calls = _lib.abi_calls - calls0
+    clocks = sampler.stop() if sampler else None
+    tot = t0.elapsed_time(t1)
+    enc = sum(a.elapsed_time(b) for a, b, _, _, _ in marks)
+    scn = sum(b.elapsed_time(e) for _, b, _, _, e in marks)
+    knl = sum(c.elapsed_time(d) for _, _, c, d, _ in marks)
+    t = torch.tensor([tot, enc, scn, knl], dtype=torch.float64, device=dev)
+    if world > 1:
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    tot, enc, scn, knl = (float(v) for v in t.tolist())
+    steps = args.steps
+    enc_vps = B * world * steps / (enc * 1e-3)
+    adc_cps = float(n) * world * nq * steps / (scn * 1e-3)
+
+    # roofline: algorithmic bytes per launch / average launch duration (per GPU)
+    scan_bytes = float(n) * M * nq                     # rows x M bytes per query pass, Q_tile = 1
+    scan_gbs = scan_bytes / (knl / steps * 1e-3) / 1e9
+    assign_tflops = 2.0 * D * KSUB * B / (enc / steps * 1e-3) / 1e12
+    tf32_peak = peaks["bf16_tflops_sustained"] / 2.0
+    line = {
+        "metric": METRIC, "value": enc_vps, "unit": "vectors/s",
+        "adc": {"value": adc_cps, "unit": "codes/s"},
+        "n_gpus": world, "steps": steps, "warmup": max(3, args.warmup), "ms_per_step": tot / steps,
+        "ms_encode_per_step": enc / steps, "ms_scan_per_step": scn / steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": dict(workload_config(args), assign_impl=impl, scan_layout=layout),
+        "roofline": {"kernel": "adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel", "bound": "hbm",
+                     "achieved": scan_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": scan_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
+                     "algorithmic_bytes_per_launch": scan_bytes},
+        "roofline_assign": {"kernel": "pq_assign_tc_kernel" if impl == "tc" else "pq_assign_simt_kernel",
+                            "bound": "tensor", "achieved": assign_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
+                            "frac": assign_tflops / tf32_peak,
+                            "peak_source": peaks["source"] + " (bf16 sustained / 2 = dense TF32)",
+                            "hbm_gbs": (4.0 * D + M) * B / (enc / steps * 1e-3) / 1e9},
+        "gpu_launches": int(n_calls + steps),  # every ABI call is >= 1 kernel; the scan call adds its merge kernel
+        "clocks": clocks,
+    }
+    return line, dict(torch=torch, tdist=tdist, codec=codec, codes=codes, C=C, Qd=Qd, world=world, rank=rank,
+                      dev=dev, n=n, nq=nq, row_offset=row_offset, col_scale=col_scale, xbuf=xbuf)
+
+
+def run_e2e(args, ctx):
+    """Same step through the reference-facing objects with host buffers (pinned numpy in,
+    numpy out): ProductQuantizer.compress + FlatQuantizedIndex.search_with_scores."""
+    torch, tdist = ctx["torch"], ctx["tdist"]
+    from b200vq import dist as vdist, host, ops_sq
+    from haag_vq.methods.product_quantization import ProductQuantizer
+    from haag_vq.methods.search.flat_quantized_index import FlatQuantizedIndex
+
+    world, dev, nq = ctx["world"], ctx["dev"], ctx["nq"]
+    rows = min(E2E_ROWS, args.rows_per_gpu)
+    pq = ProductQuantizer._from_state({"type": "ProductQuantizer", "M": M, "B": 8, "D": D,
+                                       "flat_centroids": ctx["C"].cpu().numpy().reshape(-1)})
+    index = FlatQuantizedIndex(pq)
+    index.attach_device_codes(ctx["codes"], D, "l2")
+    xh = torch.empty((rows, D), dtype=torch.float32, pin_memory=True)
+    xh.copy_(ctx["xbuf"][0][:rows])
+    qh = torch.empty((nq, D), dtype=torch.float32, pin_memory=True)
+    qh.copy_(ctx["Qd"])
+    torch.cuda.synchronize()
+    Xh, Qh = xh.numpy(), qh.numpy()
+
+    def one():
+        torch.cuda.synchronize()
+        a = time.perf_counter()
+        codes_h = pq.compress(Xh)
+        torch.cuda.synchronize()
+        b = time.perf_counter()
+        ids, sc = index.search_with_scores(Qh, K)
+        if world > 1:
+            v, i = vdist.sharded_topk(host.to_device(sc), host.to_device(ids.view(np.int32)),
+                                      ctx["row_offset"], K, "l2")
+            sc, ids = host.to_host(v), host.to_host(i)
+        torch.cuda.synchronize()
+        c = time.perf_counter()
+        assert codes_h.shape == (rows, M) and ids.shape == (nq, K)
+        return b - a, c - b
+
+    one()
+    reps = max(1, min(args.steps, 3))
+    if world > 1:
+        tdist.barrier()
+    te = ts = 0.0
+    for _ in range(reps):
+        a, b = one()
+        te += a
+        ts += b
+    t = torch.tensor([te, ts], dtype=torch.float64, device=dev)
+    if world > 1:
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    te, ts = (float(v) for v in t.tolist())
+    return {"value": rows * world * reps / te, "unit": "vectors/s",
+            "adc": {"value": float(ctx["n"]) * world * nq * reps / ts, "unit": "codes/s"},
+            "h2d_bytes_per_step": rows * D * 4 + nq * D * 4, "d2h_bytes_per_step": rows * M + nq * K * 8,
+            "api": "haag_vq ProductQuantizer.compress(X) + FlatQuantizedIndex.search_with_scores(Q, 10); "
+                   f"pinned host X ({rows}x{D}) and Q, numpy results; codes of the shard resident in HBM",
+            "timing": "host perf_counter around the call, device synchronised both sides, max over ranks"}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    line, ctx = run_b200(args)
+    if not args.no_e2e:
+        line["e2e"] = run_e2e(args, ctx)
+    if ctx["rank"] == 0:
+        if ctx["world"] == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline_leg()
+        print(json.dumps(line), flush=True)
+    if ctx["world"] > 1:
+        ctx["tdist"].barrier()
+        ctx["tdist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

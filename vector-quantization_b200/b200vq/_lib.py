@@ -85,7 +85,14 @@ def load() -> C.CDLL:
     return lib
 
 
+# number of compute entry points called (bench.py's gpu_launches claim; every call launches
+# at least one kernel of libb200vq.so)
+abi_calls = 0
+
+
 def check(status: int, what: str) -> None:
+    global abi_calls
+    abi_calls += 1
     if status != OK:
         msg = load().b200vq_last_error()
         raise B200VQError(f"{what} failed (status {status}): {msg.decode(errors='replace') if msg else ''}")

@@ -37,7 +37,7 @@ __global__ void pq_assign_simt_kernel(const float* __restrict__ x, int64_t n, in
     const int m = blockIdx.y;
     const int64_t row0 = (int64_t)blockIdx.x * R;
     float* xs = smem;                          // [dsub][R+1]
-    float* cs = xs + (size_t)dsub * (R + 1);   // [dsub][KB]
+    float* cs = xs + (((size_t)dsub * (R + 1) + 3) & ~(size_t)3);   // [dsub][KB], 16-byte aligned
 
     for (int idx = tid; idx < R * dsub; idx += R) {
         int r = idx / dsub, i = idx - r * dsub;
@@ -296,7 +296,9 @@ extern "C" int b200vq_pq_assign_f32(const float* x, int64_t n, int64_t ldx, cons
     if (n == 0) return B200VQ_OK;
     constexpr int KB = 16;
     int R = 128;
-    auto need = [&](int r) { return ((size_t)dsub * (r + 1) + (size_t)dsub * KB) * sizeof(float); };
+    auto need = [&](int r) {
+        return ((((size_t)dsub * (r + 1) + 3) & ~(size_t)3) + (size_t)dsub * KB) * sizeof(float);
+    };
     while (R > 32 && need(R) > 200 * 1024) R >>= 1;
     VQ_CHECK_ARG(need(R) <= 200 * 1024, "pq_assign_f32: dsub=%d too large for the SIMT path", dsub);
     size_t smem = need(R);

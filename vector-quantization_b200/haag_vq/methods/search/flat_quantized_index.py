@@ -48,6 +48,19 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes_dev = None
         self._recon_dev = None
 
+    def attach_device_codes(self, codes_dev: torch.Tensor, D: int,
+                            metric: Literal['l2', 'ip'] = 'l2') -> None:
+        """Streaming build hook (the shape of benchmarks/streaming_sweep.py:153-185): adopt
+        (N, M) uint8 PQ codes that were encoded batch by batch on the device by the already
+        fitted quantizer, without a host round trip. Not part of the reference surface."""
+        if self._pq_codec() is None:
+            raise RuntimeError("attach_device_codes needs a fitted ProductQuantizer / OPQ")
+        self._metric = metric
+        self._N, self._D = int(codes_dev.shape[0]), int(D)
+        self._codes = None
+        self._codes_dev = codes_dev
+        self._recon_dev = None
+
     def search(self, Q: np.ndarray, k: int) -> np.ndarray:
         ids, _ = self.search_with_scores(Q, k)
         return ids
@@ -88,7 +101,9 @@ class FlatQuantizedIndex(BaseSearchIndex):
         return host.to_host(ids).view(np.uint32), host.to_host(vals)
 
     def memory_footprint(self) -> int:
-        return int(self._codes.nbytes) if self._codes is not None else 0
+        if self._codes is not None:
+            return int(self._codes.nbytes)
+        return int(self._codes_dev.numel()) if self._codes_dev is not None else 0
 
     def reconstruction_mse(self, X: np.ndarray, sample_ids: Optional[np.ndarray] = None) -> Optional[float]:
         if self._codes is None:
