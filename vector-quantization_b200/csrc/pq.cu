@@ -321,7 +321,7 @@ static inline int grid_for(int64_t work, int block, int waves = 8) {
 
 extern "C" int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* centroids, int M,
                                 int ksub, int dsub, float* out, int64_t ldo, void* stream) {
-    VQ_CHECK_ARG(codes && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+    VQ_CHECK_ARG((codes || n == 0) && centroids && (out || n == 0) && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
                  "pq_decode: bad args");
     VQ_CHECK_ARG(ldo >= (int64_t)M * dsub, "pq_decode: ldo < D");
     if (n == 0) return B200VQ_OK;
@@ -343,7 +343,7 @@ extern "C" int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* ce
 extern "C" int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, int64_t n_ids,
                                     const float* centroids, int M, int ksub, int dsub, float* out,
                                     int64_t ldo, void* stream) {
-    VQ_CHECK_ARG(codes && ids && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n_ids >= 0,
+    VQ_CHECK_ARG(codes && (ids || n_ids == 0) && centroids && (out || n_ids == 0) && M > 0 && ksub > 0 && dsub > 0 && n_ids >= 0,
                  "pq_decode_ids: bad args");
     VQ_CHECK_ARG(ldo >= (int64_t)M * dsub, "pq_decode_ids: ldo < D");
     if (n_ids == 0) return B200VQ_OK;
@@ -365,7 +365,7 @@ extern "C" int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, in
 extern "C" int b200vq_pq_kmeans_accumulate(const float* x, int64_t n, int64_t ldx,
                                            const uint8_t* codes, int M, int ksub, int dsub,
                                            float* sums, int* counts, void* stream) {
-    VQ_CHECK_ARG(x && codes && sums && counts && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+    VQ_CHECK_ARG((x || n == 0) && (codes || n == 0) && sums && counts && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
                  "pq_kmeans_accumulate: bad args");
     if (n == 0) return B200VQ_OK;
     int64_t work = n * (int64_t)(M * dsub);
@@ -388,7 +388,7 @@ extern "C" int b200vq_pq_kmeans_finalize(const float* sums, int* counts, int M, 
 extern "C" int b200vq_pq_sse(const float* x, int64_t n, int64_t ldx, const uint8_t* codes,
                              const float* centroids, int M, int ksub, int dsub, double* out,
                              void* stream) {
-    VQ_CHECK_ARG(x && codes && centroids && out && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
+    VQ_CHECK_ARG((x || n == 0) && (codes || n == 0) && centroids && (out || n == 0) && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
                  "pq_sse: bad args");
     if (n == 0) return B200VQ_OK;
     int64_t work = n * (int64_t)(M * dsub);

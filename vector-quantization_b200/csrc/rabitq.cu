@@ -474,7 +474,7 @@ using namespace b200vq;
 extern "C" int b200vq_rabitq1_encode(const float* x, int64_t n, int64_t ldx, int D,
                                      const float* centroid, int metric, uint8_t* codes,
                                      void* stream) {
-    VQ_CHECK_ARG(x && codes && n >= 0 && D > 0 && ldx >= D, "rabitq1_encode: bad args");
+    VQ_CHECK_ARG((x || n == 0) && (codes || n == 0) && n >= 0 && D > 0 && ldx >= D, "rabitq1_encode: bad args");
     VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "rabitq1_encode: bad metric");
     if (n == 0) return B200VQ_OK;
     int64_t g = (n * 32 + 255) / 256;
@@ -488,7 +488,7 @@ extern "C" int b200vq_rabitq1_encode(const float* x, int64_t n, int64_t ldx, int
 
 extern "C" int b200vq_rabitq1_decode(const uint8_t* codes, int64_t n, int D, const float* centroid,
                                      float* out, int64_t ldo, void* stream) {
-    VQ_CHECK_ARG(codes && out && n >= 0 && D > 0 && ldo >= D, "rabitq1_decode: bad args");
+    VQ_CHECK_ARG((codes || n == 0) && (out || n == 0) && n >= 0 && D > 0 && ldo >= D, "rabitq1_decode: bad args");
     if (n == 0) return B200VQ_OK;
     int64_t g = (n * (int64_t)D + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;
@@ -569,7 +569,7 @@ extern "C" int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D,
 extern "C" int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_t n, int D, int B,
                                    const double* levels, const double* bounds, uint8_t* codes,
                                    void* stream) {
-    VQ_CHECK_ARG(srot && nrm && levels && bounds && codes && n >= 0 && D > 0,
+    VQ_CHECK_ARG((srot || n == 0) && (nrm || n == 0) && levels && bounds && (codes || n == 0) && n >= 0 && D > 0,
                  "erabitq_pack: bad args");
     VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_pack: B must be in [1,8], got %d", B);
     if (n == 0) return B200VQ_OK;
@@ -589,7 +589,7 @@ extern "C" int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_
 extern "C" int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B,
                                      const double* levels, double* shat, double* nrm_out,
                                      void* stream) {
-    VQ_CHECK_ARG(codes && levels && shat && nrm_out && n >= 0 && D > 0, "erabitq_unpack: bad args");
+    VQ_CHECK_ARG((codes || n == 0) && levels && (shat || n == 0) && (nrm_out || n == 0) && n >= 0 && D > 0, "erabitq_unpack: bad args");
     VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_unpack: B must be in [1,8], got %d", B);
     if (n == 0) return B200VQ_OK;
     int64_t g = (n * (int64_t)D + 255) / 256;

@@ -162,7 +162,7 @@ extern "C" int b200vq_synth_rows(float* out, int64_t n, int64_t ldo, int D, int6
 
 extern "C" int b200vq_sq_err_sum(const float* a, int64_t lda, const float* b, int64_t ldb, int64_t n,
                                  int D, double* out, void* stream) {
-    VQ_CHECK_ARG(a && b && out && n >= 0 && D > 0 && lda >= D && ldb >= D, "sq_err_sum: bad args");
+    VQ_CHECK_ARG((a || n == 0) && (b || n == 0) && (out || n == 0) && n >= 0 && D > 0 && lda >= D && ldb >= D, "sq_err_sum: bad args");
     if (n == 0) return B200VQ_OK;
     int64_t g = (n * (int64_t)D + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 8;

@@ -514,7 +514,7 @@ extern "C" int b200vq_adc_scan_topk(const uint8_t* codes, int64_t n, int M, int 
 
 extern "C" int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, int M, uint8_t* out,
                                               void* stream) {
-    VQ_CHECK_ARG(codes && out && n >= 0 && M > 0 && M % 32 == 0,
+    VQ_CHECK_ARG((codes || n == 0) && (out || n == 0) && n >= 0 && M > 0 && M % 32 == 0,
                  "pq_codes_to_scan_layout: need M %% 32 == 0 (M=%d)", M);
     if (n == 0) return B200VQ_OK;
     int64_t total = ((n + 31) / 32) * 32 * (int64_t)M;
@@ -567,7 +567,7 @@ extern "C" int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int
 
 extern "C" int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out,
                                   void* stream) {
-    VQ_CHECK_ARG(x && out && n >= 0 && D > 0 && ldx >= D, "row_sqnorms: bad args");
+    VQ_CHECK_ARG((x || n == 0) && (out || n == 0) && n >= 0 && D > 0 && ldx >= D, "row_sqnorms: bad args");
     if (n == 0) return B200VQ_OK;
     int64_t g = (n * 32 + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;

@@ -251,7 +251,7 @@ using namespace b200vq;
 
 extern "C" int b200vq_sq_minmax(const float* x, int64_t n, int64_t ldx, int D, float* vmin,
                                 float* vmax, void* stream) {
-    VQ_CHECK_ARG(x && vmin && vmax && n >= 0 && D > 0 && ldx >= D, "sq_minmax: bad args");
+    VQ_CHECK_ARG((x || n == 0) && vmin && vmax && n >= 0 && D > 0 && ldx >= D, "sq_minmax: bad args");
     if (n == 0) return B200VQ_OK;
     int gx = (D + 31) / 32;
     int64_t gy = (n + 7) / 8;
@@ -267,7 +267,7 @@ extern "C" int b200vq_sq_minmax(const float* x, int64_t n, int64_t ldx, int D, f
 
 extern "C" int b200vq_sq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
                                 const float* vmax, int bits, void* codes, void* stream) {
-    VQ_CHECK_ARG(x && vmin && vmax && codes && n >= 0 && D > 0 && ldx >= D, "sq_encode: bad args");
+    VQ_CHECK_ARG((x || n == 0) && vmin && vmax && (codes || n == 0) && n >= 0 && D > 0 && ldx >= D, "sq_encode: bad args");
     VQ_CHECK_ARG(bits == 4 || bits == 8 || bits == 16, "sq_encode: bits must be 4, 8 or 16, got %d",
                  bits);
     if (n == 0) return B200VQ_OK;
@@ -301,7 +301,7 @@ extern "C" int b200vq_sq_encode(const float* x, int64_t n, int64_t ldx, int D, c
 extern "C" int b200vq_sq_decode(const void* codes, int64_t n, int D, const float* vmin,
                                 const float* vmax, int bits, float* out, int64_t ldo,
                                 void* stream) {
-    VQ_CHECK_ARG(codes && vmin && vmax && out && n >= 0 && D > 0 && ldo >= D, "sq_decode: bad args");
+    VQ_CHECK_ARG((codes || n == 0) && vmin && vmax && (out || n == 0) && n >= 0 && D > 0 && ldo >= D, "sq_decode: bad args");
     VQ_CHECK_ARG(bits == 4 || bits == 8 || bits == 16, "sq_decode: bits must be 4, 8 or 16, got %d",
                  bits);
     if (n == 0) return B200VQ_OK;
@@ -333,7 +333,7 @@ extern "C" int b200vq_sq_decode(const void* codes, int64_t n, int D, const float
 extern "C" int b200vq_saq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* vmin,
                                  const float* vmax, const int* dim_bits, const int* bit_offset,
                                  int code_bytes, uint8_t* codes, void* stream) {
-    VQ_CHECK_ARG(x && vmin && vmax && dim_bits && bit_offset && codes && n >= 0 && D > 0 &&
+    VQ_CHECK_ARG((x || n == 0) && vmin && vmax && dim_bits && bit_offset && (codes || n == 0) && n >= 0 && D > 0 &&
                      ldx >= D && code_bytes > 0,
                  "saq_encode: bad args");
     if (n == 0) return B200VQ_OK;
@@ -346,7 +346,7 @@ extern "C" int b200vq_saq_encode(const float* x, int64_t n, int64_t ldx, int D, 
 extern "C" int b200vq_saq_decode(const uint8_t* codes, int64_t n, int D, const float* vmin,
                                  const float* vmax, const int* dim_bits, const int* bit_offset,
                                  int code_bytes, float* out, int64_t ldo, void* stream) {
-    VQ_CHECK_ARG(codes && vmin && vmax && dim_bits && bit_offset && out && n >= 0 && D > 0 &&
+    VQ_CHECK_ARG((codes || n == 0) && vmin && vmax && dim_bits && bit_offset && (out || n == 0) && n >= 0 && D > 0 &&
                      ldo >= D && code_bytes > 0,
                  "saq_decode: bad args");
     if (n == 0) return B200VQ_OK;
