@@ -64,12 +64,17 @@ int b200vq_pq_assign_f32(const float* x, int64_t n, int64_t ldx, const float* ce
                          const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
                          float* sqdist, void* stream);
 
-/* Tensor-core assignment (tcgen05 kind::tf32 screen + exact fp32 re-rank of the
- * candidates inside the TF32 error margin). Same contract and results as
- * b200vq_pq_assign_f32. Requires ksub == 256, dsub % 8 == 0, x 16-byte aligned,
- * ldx % 4 == 0. scratch: b200vq_pq_assign_tc_scratch_bytes(n, M) bytes.
- * stats (optional, 2 x uint64 device): [0] += pairs re-ranked, [1] += candidates. */
+/* Tensor-core assignment: tcgen05 kind::tf32 screen (128 x 256 TMEM accumulators, TMA-staged
+ * swizzled tiles, ||c||^2 folded in as an extra K slice) + exact fp32 re-evaluation of every
+ * (row, sub-quantizer) whose screen leaves more than one candidate inside the TF32 error
+ * margin. Same contract and bit-identical codes to b200vq_pq_assign_f32. Requires
+ * ksub == 256, dsub % 8 == 0, 8 <= dsub <= 128, x 16-byte aligned, ldx % 4 == 0
+ * (B200VQ_ERR_UNSUPPORTED / B200VQ_ERR_INVALID otherwise). scratch: 256-byte aligned,
+ * b200vq_pq_assign_tc_scratch_bytes2(n, M, dsub) bytes (the two-argument form sizes for the
+ * largest dsub). stats (optional, 2 x uint64 device): [0] += pairs re-evaluated exactly,
+ * [1] += candidates they held. */
 size_t b200vq_pq_assign_tc_scratch_bytes(int64_t n, int M);
+size_t b200vq_pq_assign_tc_scratch_bytes2(int64_t n, int M, int dsub);
 int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const float* centroids,
                         const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
                         void* scratch, size_t scratch_bytes, unsigned long long* stats,

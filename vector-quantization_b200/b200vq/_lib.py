@@ -31,6 +31,7 @@ SIGNATURES = {
     "b200vq_pq_centroid_norms": (_i, [_p, _i, _i, _i, _p, _p]),
     "b200vq_pq_assign_f32": (_i, [_p, _i64, _i64, _p, _p, _i, _i, _i, _p, _p, _p]),
     "b200vq_pq_assign_tc_scratch_bytes": (_sz, [_i64, _i]),
+    "b200vq_pq_assign_tc_scratch_bytes2": (_sz, [_i64, _i, _i]),
     "b200vq_pq_assign_tc": (_i, [_p, _i64, _i64, _p, _p, _i, _i, _i, _p, _p, _sz, _p, _p]),
     "b200vq_pq_decode": (_i, [_p, _i64, _p, _i, _i, _i, _p, _i64, _p]),
     "b200vq_pq_decode_ids": (_i, [_p, _p, _i64, _p, _i, _i, _i, _p, _i64, _p]),

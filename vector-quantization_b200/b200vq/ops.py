@@ -71,7 +71,8 @@ def pq_centroid_norms(centroids: torch.Tensor) -> torch.Tensor:
 
 
 def pq_assign(x: torch.Tensor, centroids: torch.Tensor, cnorm: torch.Tensor | None = None,
-              out: torch.Tensor | None = None, want_dist: bool = False, impl: str = "auto"):
+              out: torch.Tensor | None = None, want_dist: bool = False, impl: str = "auto",
+              stats: torch.Tensor | None = None):
     """codes (n, M) uint8 = nearest centroid per sub-quantizer.
 
     impl: "simt" exact fp32 kernel, "tc" tcgen05 screen + exact re-rank, "auto" picks
@@ -89,15 +90,15 @@ def pq_assign(x: torch.Tensor, centroids: torch.Tensor, cnorm: torch.Tensor | No
     if out is None:
         out = torch.empty((n, M), dtype=torch.uint8, device=x.device)
     lib = _lib.load()
-    tc_ok = (ksub == 256 and dsub % 8 == 0 and ld % 4 == 0 and ptr % 16 == 0 and not want_dist
-             and tc_available())
+    tc_ok = (ksub == 256 and dsub % 8 == 0 and 8 <= dsub <= 128 and ld % 4 == 0 and ptr % 16 == 0
+             and not want_dist and tc_available())
     if impl == "tc" and not tc_ok:
         raise B200VQError("pq_assign(impl='tc'): shape/alignment not supported by the tcgen05 path")
     if impl == "tc" or (impl == "auto" and tc_ok):
-        nbytes = lib.b200vq_pq_assign_tc_scratch_bytes(n, M)
+        nbytes = lib.b200vq_pq_assign_tc_scratch_bytes2(n, M, dsub)
         sc = scratch(nbytes, x.device, "assign_tc")
         check(lib.b200vq_pq_assign_tc(ptr, n, ld, centroids.data_ptr(), cnorm.data_ptr(), M, ksub, dsub,
-                                      out.data_ptr(), sc.data_ptr(), sc.numel(), None, _stream()),
+                                      out.data_ptr(), sc.data_ptr(), sc.numel(), _p(stats), _stream()),
               "pq_assign_tc")
         return out
     dist = torch.empty((n, M), dtype=torch.float32, device=x.device) if want_dist else None

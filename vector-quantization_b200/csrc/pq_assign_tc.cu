@@ -1,12 +1,773 @@
-// placeholder until the tcgen05 kernel lands (replaced in a later commit)
+// PQ / OPQ nearest-centroid assignment on the sm_100a tensor cores.
+//
+// Replaces faiss ProductQuantizer.compute_codes as driven by the reference at
+// src/haag_vq/methods/product_quantization.py:76-80 and
+// src/haag_vq/methods/optimized_product_quantization.py:30-31; same contract and
+// the same codes as the exact SIMT kernel b200vq_pq_assign_f32 (pq.cu).
+//
+// Per (128-row tile, sub-quantizer m) one tcgen05.mma chain computes
+//     v[r][j] = x_m[r] . (-2 c_mj)  +  ||c_mj||^2          (kind::tf32, fp32 accumulate)
+// into a 128 x 256 TMEM accumulator (||c||^2 enters through one extra K=8 slice:
+// A = [1 1 1 0..], B = three-way TF32 split of the fp32 norm, so the epilogue needs
+// no per-value add). v differs from the true distance by the row constant ||x_m||^2.
+//
+// TF32 truncates both operands to 10 mantissa bits, so the argmin of v is only a
+// SCREEN: |v - v_true| <= E with E = 2^-8 * 1.02 * |x_m| * max_j|c_mj| + slack.
+// The epilogue (one TMEM lane = one row) makes two passes over the accumulator:
+//   pass 1   row minimum m1 with 3-input FMNMX              (0.5 ALU op / value)
+//   pass 2   f = (v <= m1 + 2E); acc1 += f*(4096+j); acc2 += f*j*j
+//            (FSET.BF on the ALU pipe, two FFMA-immediates on the FMA pipe)
+// which yields the candidate count and, for 1 or 2 candidates, their indices with
+// no branch per value. One candidate: it IS the exact argmin. Two: both are
+// re-evaluated with the SIMT kernel's exact fp32 arithmetic (sequential FMA chain,
+// (||x||^2 + ||c||^2) - 2 x.c, clamp at 0, lower index wins ties). Three or more
+// (< 1 % of pairs on the benchmark data): the pair is appended to a fix-up list and a
+// second small kernel runs the exact 256-way scan for it. The result is therefore
+// bit-identical to b200vq_pq_assign_f32 whenever E bounds the screen error.
+//
+// Data movement: persistent CTAs, one per SM. A CTA keeps the (-2 c) tiles of KS
+// consecutive sub-quantizers resident in shared memory (TMA, hardware swizzle) and
+// streams 128-row slices of x (only the KS*dsub columns it needs) through an
+// NST-deep TMA ring, so x is read from HBM exactly once and the centroids are not
+// re-read per tile. Warp roles: 0 = TMA producer, 1 = MMA issuer (owns TMEM),
+// 2..5 = epilogue (TMEM lanes 32*(warp%4)..). The two 256-column accumulators
+// double-buffer MMA against the epilogue.
+#include <cuda.h>
+
 #include "common.cuh"
-using namespace b200vq;
-extern "C" size_t b200vq_pq_assign_tc_scratch_bytes(int64_t n, int M) {
-    if (n <= 0 || M <= 0) return 0;
-    return (size_t)n * M * 4;
+
+namespace b200vq {
+namespace tc {
+
+constexpr int TILE_ROWS = 128;
+constexpr int KSUB = 256;
+constexpr int THREADS = 192;
+constexpr int MAX_STAGES = 4;
+constexpr uint32_t SMEM_BUDGET = 220 * 1024;
+
+// ------------------------------------------------------------ PTX helpers ---
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
-extern "C" int b200vq_pq_assign_tc(const float*, int64_t, int64_t, const float*, const float*, int, int,
-                                   int, uint8_t*, void*, size_t, unsigned long long*, void*) {
-    set_error("pq_assign_tc: not built yet");
-    return B200VQ_ERR_UNSUPPORTED;
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
+                                            int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, M=128, N=256, K=8 (tf32), both operands K-major.
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Arrive on an mbarrier once every MMA issued so far by this thread has completed.
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                 : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (lane = TMEM lane).
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+          "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+          "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+          "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+    float m;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(a), "f"(b), "f"(c));
+    return m;
+}
+__device__ __forceinline__ float fset_le(float a, float b) {  // 1.0f if a <= b else 0.0f
+    float f;
+    asm("set.le.f32.f32 %0, %1, %2;" : "=f"(f) : "f"(a), "f"(b));
+    return f;
+}
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) swizzle mode.
+__device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout_type) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(sbo_bytes >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)layout_type << 61;
+    return d;
+}
+// kind::tf32, fp32 accumulate, A and B K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor).
+constexpr uint32_t IDESC_TF32_128x256 = (1u << 4) | (2u << 7) | (2u << 10) | ((256u >> 3) << 17) | ((128u >> 4) << 24);
+
+// ------------------------------------------------------------- parameters ---
+struct Params {
+    const float* x;          // (n, ldx)
+    int64_t n, ldx;
+    const float* centroids;  // (M, 256, dsub) original fp32 centroids (exact re-evaluation)
+    const float* cnorm;      // (M, 256)
+    const float* cmax;       // (M) max_j |c_mj|
+    uint8_t* codes;          // (n, M)
+    unsigned long long* fix_count;  // entries appended to fix_list (may exceed fix_cap)
+    unsigned long long* fix_list;   // row * M + m
+    unsigned long long fix_cap;
+    unsigned long long* stats;      // optional: [0] += pairs re-ranked, [1] += candidates
+    int M, dsub;
+    int KS;        // sub-quantizers resident per CTA
+    int CH;        // floats per K chunk (= swizzle span / 4): 32, 16 or 8
+    int nchunk;    // dsub / CH
+    int nstages;   // A ring depth
+    int groups;    // M / KS
+    int64_t ntiles;          // ceil(n / 128)
+    int64_t tiles_per_item;  // row tiles per work item
+    int64_t nitems;          // groups * ceil(ntiles / tiles_per_item)
+};
+
+__device__ __forceinline__ uint32_t swizzle_mask(int CH) { return (uint32_t)(CH >> 2) - 1u; }  // 7, 3, 1
+__device__ __forceinline__ uint32_t layout_type_of(int CH) { return CH == 32 ? 2u : (CH == 16 ? 4u : 6u); }
+
+// --------------------------------------------------------- prepare kernel ---
+// grid M, block 256: thread j prepares centroid j of sub-quantizer m.
+//   bprep  (M*256, dsub)  = -2 c           (exact scaling)
+//   bextra (M*256, 8)     = {hi, mid, lo, 0...} TF32-truncation split of ||c||^2
+//   cmax   (M)            = max_j |c_mj|
+//   ones   (128, 8)       = {1,1,1,0,0,0,0,0} per row; counter zeroed.
+__global__ void prepare_kernel(const float* __restrict__ centroids, const float* __restrict__ cnorm, int dsub,
+                               float* __restrict__ bprep, float* __restrict__ bextra,
+                               float* __restrict__ cmax, float* __restrict__ ones,
+                               unsigned long long* __restrict__ fix_count) {
+    const int m = blockIdx.x, j = threadIdx.x;
+    const size_t row = (size_t)m * KSUB + j;
+    const float* c = centroids + row * dsub;
+    float* b = bprep + row * dsub;
+    for (int i = 0; i < dsub; ++i) b[i] = -2.0f * c[i];
+    const float cn = cnorm[row];
+    const float hi = __uint_as_float(__float_as_uint(cn) & 0xFFFFE000u);
+    const float r1 = cn - hi;
+    const float mid = __uint_as_float(__float_as_uint(r1) & 0xFFFFE000u);
+    const float r2 = r1 - mid;
+    const float lo = __uint_as_float(__float_as_uint(r2) & 0xFFFFE000u);
+    float* e = bextra + row * 8;
+    e[0] = hi;
+    e[1] = mid;
+    e[2] = lo;
+    e[3] = e[4] = e[5] = e[6] = e[7] = 0.f;
+    __shared__ float red[KSUB / 32];
+    float v = sqrtf(fmaxf(cn, 0.f)) * 1.0000005f;
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(FULL_MASK, v, o));
+    if ((j & 31) == 0) red[j >> 5] = v;
+    __syncthreads();
+    if (j == 0) {
+        float mx = red[0];
+        for (int w = 1; w < KSUB / 32; ++w) mx = fmaxf(mx, red[w]);
+        cmax[m] = mx;
+    }
+    if (m == 0) {
+        if (j < TILE_ROWS) {
+            float* o = ones + j * 8;
+            o[0] = o[1] = o[2] = 1.f;
+            o[3] = o[4] = o[5] = o[6] = o[7] = 0.f;
+        }
+        if (j == 0) *fix_count = 0ull;
+    }
+}
+
+// Exact distance of the SIMT kernel (pq.cu: pq_assign_simt_kernel): sequential fp32 FMA chain
+// over the sub-vector, (xn + cn) - 2 acc, clamped at 0. x is read from global memory.
+__device__ __forceinline__ float exact_dist(const float* __restrict__ xr, const float* __restrict__ c, int dsub,
+                                            float xn, float cn) {
+    float acc = 0.f;
+    for (int i = 0; i < dsub; ++i) acc = __fmaf_rn(xr[i], c[i], acc);
+    float d = __fmaf_rn(-2.f, acc, __fadd_rn(xn, cn));
+    return fmaxf(d, 0.f);
+}
+
+// Exact 256-way scan by one thread (used when the fix-up list is full; practically never).
+__device__ __noinline__ int exact_scan_thread(const float* xr, const float* cm, const float* cnm, int dsub,
+                                              float xn) {
+    float best = __int_as_float(0x7f800000);
+    int bk = 0;
+    for (int j = 0; j < KSUB; ++j) {
+        float d = exact_dist(xr, cm + (size_t)j * dsub, dsub, xn, cnm[j]);
+        if (d < best) {
+            best = d;
+            bk = j;
+        }
+    }
+    return bk;
+}
+
+// ---------------------------------------------------------- fix-up kernel ---
+// One warp per listed (row, m): exact scan of all 256 centroids, identical arithmetic
+// and tie-breaking (lowest index) to pq_assign_simt_kernel.
+__global__ void fixup_kernel(Params p) {
+    const int lane = threadIdx.x & 31;
+    const unsigned long long wid = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nw = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    unsigned long long cnt = *p.fix_count;
+    if (cnt > p.fix_cap) cnt = p.fix_cap;
+    for (unsigned long long e = wid; e < cnt; e += nw) {
+        const unsigned long long key = p.fix_list[e];
+        const int64_t row = (int64_t)(key / (unsigned)p.M);
+        const int m = (int)(key % (unsigned)p.M);
+        const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
+        const float* cm = p.centroids + (size_t)m * KSUB * p.dsub;
+        const float* cnm = p.cnorm + (size_t)m * KSUB;
+        float xn = 0.f;
+        for (int i = 0; i < p.dsub; ++i) xn = __fmaf_rn(xr[i], xr[i], xn);
+        float best = __int_as_float(0x7f800000);
+        int bk = 0x7fffffff;
+        for (int j = lane; j < KSUB; j += 32) {
+            float d = exact_dist(xr, cm + (size_t)j * p.dsub, p.dsub, xn, cnm[j]);
+            if (d < best) {
+                best = d;
+                bk = j;
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            float ob = __shfl_xor_sync(FULL_MASK, best, o);
+            int ok = __shfl_xor_sync(FULL_MASK, bk, o);
+            if (ob < best || (ob == best && ok < bk)) {
+                best = ob;
+                bk = ok;
+            }
+        }
+        if (bk == 0x7fffffff) bk = 0;  // all distances NaN: the SIMT kernel keeps index 0
+        if (lane == 0) p.codes[row * p.M + m] = (uint8_t)bk;
+    }
+}
+
+// ------------------------------------------------------------ main kernel ---
+struct SmemPlan {
+    uint32_t b_off, bx_off, ax_off, a_off, bar_off, total;
+    uint32_t a_chunk_bytes, b_chunk_bytes, a_stage_bytes;
+};
+__host__ __device__ inline SmemPlan make_plan(int KS, int CH, int nchunk, int nstages) {
+    SmemPlan s;
+    s.a_chunk_bytes = TILE_ROWS * CH * 4;
+    s.b_chunk_bytes = KSUB * CH * 4;
+    s.a_stage_bytes = (uint32_t)KS * nchunk * s.a_chunk_bytes;
+    s.b_off = 0;
+    s.bx_off = s.b_off + (uint32_t)KS * nchunk * s.b_chunk_bytes;
+    s.ax_off = s.bx_off + (uint32_t)KS * 8192;
+    s.a_off = s.ax_off + 4096;
+    s.bar_off = s.a_off + (uint32_t)nstages * s.a_stage_bytes;
+    s.total = s.bar_off + 256;
+    return s;
+}
+
+// barrier slots (8 bytes each) inside the bar region
+enum { BAR_B_FULL = 0, BAR_B_EMPTY = 1, BAR_AX_FULL = 2, BAR_A_FULL = 3, BAR_A_EMPTY = 7, BAR_T_FULL = 11,
+       BAR_T_EMPTY = 13, BAR_TMEM_PTR = 15 };
+
+__global__ void __launch_bounds__(THREADS, 1)
+    assign_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ CUtensorMap map_bx, const __grid_constant__ CUtensorMap map_ax,
+                     const Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // dynamic shared memory is only guaranteed 16-byte aligned: round up to 1024 for the swizzle atoms
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - raw);
+    const SmemPlan sp = make_plan(p.KS, p.CH, p.nchunk, p.nstages);
+    const uint32_t bar0 = base + sp.bar_off;
+    auto bar = [&](int slot) { return bar0 + 8u * (uint32_t)slot; };
+    volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(gbase + sp.bar_off + 8 * BAR_TMEM_PTR);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int KS = p.KS, CH = p.CH, nchunk = p.nchunk, NST = p.nstages;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_b);
+        tma_prefetch_desc(&map_bx);
+        tma_prefetch_desc(&map_ax);
+        mbar_init(bar(BAR_B_FULL), 1);
+        mbar_init(bar(BAR_B_EMPTY), 1);
+        mbar_init(bar(BAR_AX_FULL), 1);
+        for (int i = 0; i < MAX_STAGES; ++i) {
+            mbar_init(bar(BAR_A_FULL + i), 1);
+            mbar_init(bar(BAR_A_EMPTY + i), 1 + 4);  // MMA commit + 4 epilogue warps
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar(BAR_T_FULL + i), 1);
+            mbar_init(bar(BAR_T_EMPTY + i), 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(bar(BAR_TMEM_PTR), 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer ===
+        if (lane == 0) {
+            mbar_expect_tx(bar(BAR_AX_FULL), 4096);
+            tma_load_2d(base + sp.ax_off, &map_ax, bar(BAR_AX_FULL), 0, 0);
+            uint32_t st = 0, a_phase = 0, b_phase = 0;
+            for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+                const int g = (int)(item % p.groups);
+                const int64_t rc = item / p.groups;
+                const int64_t t0 = rc * p.tiles_per_item;
+                int64_t t1 = t0 + p.tiles_per_item;
+                if (t1 > p.ntiles) t1 = p.ntiles;
+                mbar_wait(bar(BAR_B_EMPTY), b_phase ^ 1);
+                mbar_expect_tx(bar(BAR_B_FULL), (uint32_t)KS * (nchunk * sp.b_chunk_bytes + 8192));
+                for (int s = 0; s < KS; ++s) {
+                    const int m = g * KS + s;
+                    for (int c = 0; c < nchunk; ++c)
+                        tma_load_2d(base + sp.b_off + (uint32_t)(s * nchunk + c) * sp.b_chunk_bytes, &map_b,
+                                    bar(BAR_B_FULL), c * CH, m * KSUB);
+                    tma_load_2d(base + sp.bx_off + (uint32_t)s * 8192, &map_bx, bar(BAR_B_FULL), 0, m * KSUB);
+                }
+                b_phase ^= 1;
+                for (int64_t t = t0; t < t1; ++t) {
+                    mbar_wait(bar(BAR_A_EMPTY + st), a_phase ^ 1);
+                    mbar_expect_tx(bar(BAR_A_FULL + st), sp.a_stage_bytes);
+                    for (int s = 0; s < KS; ++s)
+                        for (int c = 0; c < nchunk; ++c)
+                            tma_load_2d(base + sp.a_off + st * sp.a_stage_bytes +
+                                            (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes,
+                                        &map_x, bar(BAR_A_FULL + st), (g * KS + s) * p.dsub + c * CH,
+                                        (int)(t * TILE_ROWS));
+                    if (++st == (uint32_t)NST) {
+                        st = 0;
+                        a_phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================================================= MMA issuer ===
+        if (lane == 0) {
+            const uint32_t lt = layout_type_of(CH);
+            const uint32_t sbo = 32u * (uint32_t)CH;
+            const int kper = CH / 8;
+            uint32_t st = 0, a_phase = 0, b_phase = 0, acc = 0, t_phase = 0;
+            mbar_wait(bar(BAR_AX_FULL), 0);
+            const uint64_t ax_desc = make_kmajor_desc(base + sp.ax_off, 256, 6);
+            for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+                const int64_t rc = item / p.groups;
+                const int64_t t0 = rc * p.tiles_per_item;
+                int64_t t1 = t0 + p.tiles_per_item;
+                if (t1 > p.ntiles) t1 = p.ntiles;
+                mbar_wait(bar(BAR_B_FULL), b_phase);
+                b_phase ^= 1;
+                for (int64_t t = t0; t < t1; ++t) {
+                    mbar_wait(bar(BAR_A_FULL + st), a_phase);
+                    for (int s = 0; s < KS; ++s) {
+                        mbar_wait(bar(BAR_T_EMPTY + acc), t_phase ^ 1);
+                        tc_fence_after();
+                        const uint32_t d = tmem_base + acc * 256u;
+                        uint32_t accum = 0;
+                        for (int c = 0; c < nchunk; ++c) {
+                            const uint32_t a_addr = base + sp.a_off + st * sp.a_stage_bytes +
+                                                    (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes;
+                            const uint32_t b_addr = base + sp.b_off + (uint32_t)(s * nchunk + c) * sp.b_chunk_bytes;
+                            for (int kk = 0; kk < kper; ++kk) {
+                                umma_tf32(d, make_kmajor_desc(a_addr + kk * 32, sbo, lt),
+                                          make_kmajor_desc(b_addr + kk * 32, sbo, lt), IDESC_TF32_128x256, accum);
+                                accum = 1;
+                            }
+                        }
+                        umma_tf32(d, ax_desc, make_kmajor_desc(base + sp.bx_off + (uint32_t)s * 8192, 256, 6),
+                                  IDESC_TF32_128x256, 1);
+                        umma_commit(bar(BAR_T_FULL + acc));
+                        if (++acc == 2) {
+                            acc = 0;
+                            t_phase ^= 1;
+                        }
+                    }
+                    umma_commit(bar(BAR_A_EMPTY + st));
+                    if (++st == (uint32_t)NST) {
+                        st = 0;
+                        a_phase ^= 1;
+                    }
+                }
+                umma_commit(bar(BAR_B_EMPTY));
+            }
+        }
+    } else {
+        // ========================================================= epilogue ===
+        const int q = warp & 3;                 // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;            // row inside the tile
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t pitch = (uint32_t)CH * 4u, swz = swizzle_mask(CH);
+        const int units = CH / 4;
+        uint32_t st = 0, a_phase = 0, acc = 0, t_phase = 0;
+        for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+            const int g = (int)(item % p.groups);
+            const int64_t rc = item / p.groups;
+            const int64_t t0 = rc * p.tiles_per_item;
+            int64_t t1 = t0 + p.tiles_per_item;
+            if (t1 > p.ntiles) t1 = p.ntiles;
+            for (int64_t t = t0; t < t1; ++t) {
+                const int64_t row = t * TILE_ROWS + r;
+                const bool live = row < p.n;
+                mbar_wait(bar(BAR_A_FULL + st), a_phase);
+                for (int s = 0; s < KS; ++s) {
+                    const int m = g * KS + s;
+                    // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
+                    float xn = 0.f;
+                    for (int c = 0; c < nchunk; ++c) {
+                        const uint8_t* tile = gbase + sp.a_off + st * sp.a_stage_bytes +
+                                              (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes;
+                        for (int u = 0; u < units; ++u) {
+                            uint32_t off = (uint32_t)r * pitch + (uint32_t)u * 16u;
+                            off ^= ((off >> 7) & swz) << 4;
+                            const float4 w = *reinterpret_cast<const float4*>(tile + off);
+                            xn = __fmaf_rn(w.x, w.x, xn);
+                            xn = __fmaf_rn(w.y, w.y, xn);
+                            xn = __fmaf_rn(w.z, w.z, xn);
+                            xn = __fmaf_rn(w.w, w.w, xn);
+                        }
+                    }
+                    mbar_wait(bar(BAR_T_FULL + acc), t_phase);
+                    tc_fence_after();
+                    const uint32_t taddr = lane_addr + acc * 256u;
+                    float v[32];
+                    // pass 1: row minimum
+                    float mn = __int_as_float(0x7f800000);
+#pragma unroll 1
+                    for (int cb = 0; cb < 8; ++cb) {
+                        tmem_ld32(taddr + cb * 32, v);
+                        float a0 = fmin3(v[0], v[1], v[2]), a1 = fmin3(v[3], v[4], v[5]);
+                        float a2 = fmin3(v[6], v[7], v[8]), a3 = fmin3(v[9], v[10], v[11]);
+                        float a4 = fmin3(v[12], v[13], v[14]), a5 = fmin3(v[15], v[16], v[17]);
+                        float a6 = fmin3(v[18], v[19], v[20]), a7 = fmin3(v[21], v[22], v[23]);
+                        float a8 = fmin3(v[24], v[25], v[26]), a9 = fmin3(v[27], v[28], v[29]);
+                        float b0 = fmin3(a0, a1, a2), b1 = fmin3(a3, a4, a5), b2 = fmin3(a6, a7, a8);
+                        float b3 = fmin3(a9, v[30], v[31]);
+                        mn = fmin3(mn, fmin3(b0, b1, b2), b3);
+                    }
+                    // screen error bound: TF32 truncation of both operands (2^-9 |x||c| on x.c, doubled by
+                    // the -2 factor), widened by 2 %, plus slack for fp32 accumulation and the norm split
+                    const float xl = sqrtf(xn) * 1.0000005f;
+                    const float cm = p.cmax[m];
+                    const float E = __fmaf_rn(0.00390625f * 1.02f, xl * cm,
+                                              3.8147e-6f * __fmaf_rn(2.f * xl, cm, cm * cm));
+                    const float thr = mn + 2.f * E;
+                    // pass 2: candidate count and index moments
+                    float m1a = 0.f, m1b = 0.f, m2a = 0.f, m2b = 0.f;
+#pragma unroll
+                    for (int cb = 0; cb < 8; ++cb) {
+                        tmem_ld32(taddr + cb * 32, v);
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {
+                            const int j0 = cb * 32 + i, j1 = j0 + 1;
+                            const float f0 = fset_le(v[i], thr), f1 = fset_le(v[i + 1], thr);
+                            m1a = __fmaf_rn(f0, (float)(4096 + j0), m1a);
+                            m1b = __fmaf_rn(f1, (float)(4096 + j1), m1b);
+                            m2a = __fmaf_rn(f0, (float)(j0 * j0), m2a);
+                            m2b = __fmaf_rn(f1, (float)(j1 * j1), m2b);
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar(BAR_T_EMPTY + acc));
+                    if (++acc == 2) {
+                        acc = 0;
+                        t_phase ^= 1;
+                    }
+                    // resolve
+                    const float m1 = m1a + m1b, m2 = m2a + m2b;      // exact: all sums < 2^24
+                    const int cnt = (int)(m1 * (1.f / 4096.f));
+                    const int s1 = (int)m1 - cnt * 4096;
+                    int code = 0;
+                    bool multi = false;
+                    if (live) {
+                        if (cnt == 1) {
+                            code = s1;
+                        } else {
+                            multi = true;
+                            const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
+                            const float* cmx = p.centroids + (size_t)m * KSUB * p.dsub;
+                            const float* cnm = p.cnorm + (size_t)m * KSUB;
+                            if (cnt == 2) {
+                                const int s2 = (int)m2;
+                                const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
+                                const int ja = (s1 - df) >> 1, jb = (s1 + df) >> 1;
+                                const float da = exact_dist(xr, cmx + (size_t)ja * p.dsub, p.dsub, xn, cnm[ja]);
+                                const float db = exact_dist(xr, cmx + (size_t)jb * p.dsub, p.dsub, xn, cnm[jb]);
+                                code = (db < da) ? jb : ja;
+                            } else {
+                                // 0 (NaN input) or >= 3 candidates: exact scan later, or here if the list is full
+                                const unsigned long long slot = atomicAdd(p.fix_count, 1ull);
+                                if (slot < p.fix_cap) p.fix_list[slot] = (unsigned long long)row * (unsigned)p.M + m;
+                                else code = exact_scan_thread(xr, cmx, cnm, p.dsub, xn);
+                            }
+                        }
+                        p.codes[row * p.M + m] = (uint8_t)code;
+                    }
+                    if (p.stats) {
+                        const unsigned mm = __ballot_sync(FULL_MASK, multi);
+                        if (lane == 0 && mm) atomicAdd(p.stats, (unsigned long long)__popc(mm));
+                        unsigned long long cc = multi ? (unsigned long long)(cnt > 0 ? cnt : KSUB) : 0ull;
+                        for (int o = 16; o > 0; o >>= 1) cc += __shfl_xor_sync(FULL_MASK, cc, o);
+                        if (lane == 0 && cc) atomicAdd(p.stats + 1, cc);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(BAR_A_EMPTY + st));
+                if (++st == (uint32_t)NST) {
+                    st = 0;
+                    a_phase ^= 1;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace tc
+}  // namespace b200vq
+
+using namespace b200vq;
+using namespace b200vq::tc;
+
+// ------------------------------------------------------------- host side ---
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// 2-D fp32 row-major tensor (rows, cols) with row stride ld (floats); box = (box_rows, box_cols).
+static int encode_2d(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                     uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("pq_assign_tc: cuTensorMapEncodeTiled is not available from the driver");
+        return B200VQ_ERR_CUDA;
+    }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * sizeof(float)};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("pq_assign_tc: cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r,
+                  (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
+        return B200VQ_ERR_CUDA;
+    }
+    return B200VQ_OK;
+}
+
+struct TcShape {
+    int KS, CH, nchunk, nstages;
+    SmemPlan sp;
+    bool ok;
+};
+
+static TcShape plan_shape(int M, int dsub) {
+    TcShape t{};
+    t.ok = false;
+    if (dsub % 8 != 0 || dsub < 8 || dsub > 128) return t;
+    t.CH = (dsub % 32 == 0) ? 32 : (dsub % 16 == 0 ? 16 : 8);
+    t.nchunk = dsub / t.CH;
+    int ks = 64 / dsub;
+    if (ks < 1) ks = 1;
+    while (ks > 1 && M % ks != 0) --ks;
+    t.KS = ks;
+    for (int nst = MAX_STAGES; nst >= 1; --nst) {
+        SmemPlan sp = make_plan(t.KS, t.CH, t.nchunk, nst);
+        if (sp.total + 1024 <= SMEM_BUDGET) {
+            t.nstages = nst;
+            t.sp = sp;
+            t.ok = true;
+            break;
+        }
+    }
+    return t;
+}
+
+// scratch layout (all offsets 256-byte aligned)
+struct ScratchPlan {
+    size_t bprep, bextra, ones, cmax, counter, list, total;
+    unsigned long long cap;
+};
+static ScratchPlan plan_scratch(int64_t n, int M, int dsub) {
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    ScratchPlan s;
+    s.bprep = 0;
+    s.bextra = al(s.bprep + (size_t)M * KSUB * dsub * 4);
+    s.ones = al(s.bextra + (size_t)M * KSUB * 8 * 4);
+    s.cmax = al(s.ones + TILE_ROWS * 8 * 4);
+    s.counter = al(s.cmax + (size_t)M * 4);
+    s.list = al(s.counter + 16);
+    unsigned long long cap = (unsigned long long)((n * (int64_t)M) / 8);
+    if (cap < 4096) cap = 4096;
+    s.cap = cap;
+    s.total = al(s.list + cap * 8);
+    return s;
+}
+
+extern "C" size_t b200vq_pq_assign_tc_scratch_bytes2(int64_t n, int M, int dsub) {
+    if (n < 0 || M <= 0 || dsub <= 0) return 0;
+    return plan_scratch(n, M, dsub).total;
+}
+
+// Kept for ABI v1 callers that do not know dsub: sized for the largest supported dsub.
+extern "C" size_t b200vq_pq_assign_tc_scratch_bytes(int64_t n, int M) {
+    return b200vq_pq_assign_tc_scratch_bytes2(n, M, 128);
+}
+
+extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const float* centroids,
+                                   const float* cnorm, int M, int ksub, int dsub, uint8_t* codes,
+                                   void* scratch, size_t scratch_bytes, unsigned long long* stats,
+                                   void* stream) {
+    VQ_CHECK_ARG(n >= 0 && M > 0 && dsub > 0, "pq_assign_tc: bad shape");
+    VQ_CHECK_ARG(ksub == KSUB, "pq_assign_tc: needs ksub == 256 (got %d)", ksub);
+    TcShape ts = plan_shape(M, dsub);
+    if (!ts.ok) {
+        set_error("pq_assign_tc: dsub=%d unsupported (needs dsub %% 8 == 0 and 8 <= dsub <= 128)", dsub);
+        return B200VQ_ERR_UNSUPPORTED;
+    }
+    if (n == 0) return B200VQ_OK;
+    VQ_CHECK_ARG(x && centroids && cnorm && codes, "pq_assign_tc: null pointer");
+    VQ_CHECK_ARG(ldx >= (int64_t)M * dsub && ldx % 4 == 0 && ((uintptr_t)x & 15) == 0,
+                 "pq_assign_tc: x must be 16-byte aligned with ldx %% 4 == 0 and ldx >= D");
+    VQ_CHECK_ARG(n < (1ll << 31) * TILE_ROWS, "pq_assign_tc: n too large for one call");
+    ScratchPlan sc = plan_scratch(n, M, dsub);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= sc.total && ((uintptr_t)scratch & 255) == 0,
+                 "pq_assign_tc: scratch too small or not 256-byte aligned (%zu < %zu)", scratch_bytes, sc.total);
+    cudaStream_t st = as_stream(stream);
+    uint8_t* sb = reinterpret_cast<uint8_t*>(scratch);
+    float* bprep = reinterpret_cast<float*>(sb + sc.bprep);
+    float* bextra = reinterpret_cast<float*>(sb + sc.bextra);
+    float* ones = reinterpret_cast<float*>(sb + sc.ones);
+    float* cmax = reinterpret_cast<float*>(sb + sc.cmax);
+    unsigned long long* counter = reinterpret_cast<unsigned long long*>(sb + sc.counter);
+    unsigned long long* list = reinterpret_cast<unsigned long long*>(sb + sc.list);
+
+    prepare_kernel<<<M, KSUB, 0, st>>>(centroids, cnorm, dsub, bprep, bextra, cmax, ones, counter);
+    VQ_LAUNCH_CHECK();
+
+    const CUtensorMapSwizzle swz = ts.CH == 32 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                   : ts.CH == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+    CUtensorMap map_x, map_b, map_bx, map_ax;
+    int rc;
+    if ((rc = encode_2d(&map_x, x, (uint64_t)n, (uint64_t)M * dsub, (uint64_t)ldx, TILE_ROWS, ts.CH, swz))) return rc;
+    if ((rc = encode_2d(&map_b, bprep, (uint64_t)M * KSUB, dsub, dsub, KSUB, ts.CH, swz))) return rc;
+    if ((rc = encode_2d(&map_bx, bextra, (uint64_t)M * KSUB, 8, 8, KSUB, 8, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+    if ((rc = encode_2d(&map_ax, ones, TILE_ROWS, 8, 8, TILE_ROWS, 8, CU_TENSOR_MAP_SWIZZLE_32B))) return rc;
+
+    Params p{};
+    p.x = x;
+    p.n = n;
+    p.ldx = ldx;
+    p.centroids = centroids;
+    p.cnorm = cnorm;
+    p.cmax = cmax;
+    p.codes = codes;
+    p.fix_count = counter;
+    p.fix_list = list;
+    p.fix_cap = sc.cap;
+    p.stats = stats;
+    p.M = M;
+    p.dsub = dsub;
+    p.KS = ts.KS;
+    p.CH = ts.CH;
+    p.nchunk = ts.nchunk;
+    p.nstages = ts.nstages;
+    p.groups = M / ts.KS;
+    p.ntiles = (n + TILE_ROWS - 1) / TILE_ROWS;
+    const int sms = device_sm_count();
+    // ~4 work items per CTA when the problem allows, at most 64 row tiles per item
+    int64_t tpi = (p.ntiles * p.groups) / ((int64_t)sms * 4);
+    if (tpi < 1) tpi = 1;
+    if (tpi > 64) tpi = 64;
+    p.tiles_per_item = tpi;
+    p.nitems = (int64_t)p.groups * ((p.ntiles + tpi - 1) / tpi);
+    int grid = (int)(p.nitems < sms ? p.nitems : sms);
+    const size_t smem = ts.sp.total + 1024;
+    VQ_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    assign_tc_kernel<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
+    VQ_LAUNCH_CHECK();
+    fixup_kernel<<<sms * 2, 256, 0, st>>>(p);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
 }
