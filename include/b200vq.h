@@ -71,8 +71,8 @@ int b200vq_pq_assign_f32(const float* x, int64_t n, int64_t ldx, const float* ce
  * ksub == 256, dsub % 8 == 0, 8 <= dsub <= 128, x 16-byte aligned, ldx % 4 == 0
  * (B200VQ_ERR_UNSUPPORTED / B200VQ_ERR_INVALID otherwise). scratch: 256-byte aligned,
  * b200vq_pq_assign_tc_scratch_bytes2(n, M, dsub) bytes (the two-argument form sizes for the
- * largest dsub). stats (optional, 2 x uint64 device): [0] += pairs re-evaluated exactly,
- * [1] += candidates they held. */
+ * largest dsub). stats (optional, 3 x uint64 device): [0] += pairs re-evaluated exactly,
+ * [1] += candidates they held, [2] += pairs sent to the exact 256-way fix-up scan. */
 size_t b200vq_pq_assign_tc_scratch_bytes(int64_t n, int M);
 size_t b200vq_pq_assign_tc_scratch_bytes2(int64_t n, int M, int dsub);
 int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const float* centroids,

@@ -48,7 +48,7 @@ def test_tc_equals_simt_and_oracle(T, n, D, M):
     C = _centroids(D, M, seed=5)
     xd, cd = T.dev(X), T.dev(C)
     simt = T.ops.pq_assign(xd, cd, impl="simt").cpu().numpy()
-    stats = T.torch.zeros(2, dtype=T.torch.int64, device="cuda")
+    stats = T.torch.zeros(3, dtype=T.torch.int64, device="cuda")
     tc = T.ops.pq_assign(xd, cd, impl="tc", stats=stats).cpu().numpy()
     ndiff = int((tc != simt).sum())
     assert ndiff == 0, f"tc vs simt: {ndiff} of {tc.size} codes differ (first rows {np.nonzero((tc != simt).any(1))[0][:5]})"
@@ -73,7 +73,7 @@ def test_tc_near_duplicate_centroids_and_strided_rows(T):
     view = wd[:, D:]
     cd = T.dev(C)
     simt = T.ops.pq_assign(view, cd, impl="simt").cpu().numpy()
-    stats = T.torch.zeros(2, dtype=T.torch.int64, device="cuda")
+    stats = T.torch.zeros(3, dtype=T.torch.int64, device="cuda")
     tc = T.ops.pq_assign(view, cd, impl="tc", stats=stats).cpu().numpy()
     assert np.array_equal(tc, simt)
     assert not np.any(tc[:, 1] == 200)

@@ -173,7 +173,7 @@ struct Params {
     unsigned long long* fix_count;  // entries appended to fix_list (may exceed fix_cap)
     unsigned long long* fix_list;   // row * M + m
     unsigned long long fix_cap;
-    unsigned long long* stats;      // optional: [0] += pairs re-ranked, [1] += candidates
+    unsigned long long* stats;      // optional: [0] += pairs re-ranked, [1] += candidates, [2] += fix-up entries
     int M, dsub;
     int KS;        // sub-quantizers resident per CTA
     int CH;        // floats per K chunk (= swizzle span / 4): 32, 16 or 8
@@ -261,26 +261,53 @@ __device__ __noinline__ int exact_scan_thread(const float* xr, const float* cm, 
 
 // ---------------------------------------------------------- fix-up kernel ---
 // One warp per listed (row, m): exact scan of all 256 centroids, identical arithmetic
-// and tie-breaking (lowest index) to pq_assign_simt_kernel.
-__global__ void fixup_kernel(Params p) {
-    const int lane = threadIdx.x & 31;
-    const unsigned long long wid = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const unsigned long long nw = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+// and tie-breaking (lowest index) to pq_assign_simt_kernel. The sub-vector is staged in
+// shared memory; lane l evaluates centroids l, l+32, ... (the 32 rows a warp touches per
+// step are contiguous in memory), each with its own sequential FMA chain.
+constexpr int FIX_WARPS = 8;
+__global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
+    __shared__ __align__(16) float xs_all[FIX_WARPS][128];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* xs = xs_all[w];
+    const unsigned long long wid = (unsigned long long)blockIdx.x * FIX_WARPS + w;
+    const unsigned long long nw = (unsigned long long)gridDim.x * FIX_WARPS;
     unsigned long long cnt = *p.fix_count;
+    if (p.stats && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(p.stats + 2, cnt);
     if (cnt > p.fix_cap) cnt = p.fix_cap;
+    const int dsub = p.dsub, units = dsub >> 2;
     for (unsigned long long e = wid; e < cnt; e += nw) {
         const unsigned long long key = p.fix_list[e];
         const int64_t row = (int64_t)(key / (unsigned)p.M);
         const int m = (int)(key % (unsigned)p.M);
-        const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
-        const float* cm = p.centroids + (size_t)m * KSUB * p.dsub;
+        const float* xr = p.x + row * p.ldx + (int64_t)m * dsub;
+        const float* cm = p.centroids + (size_t)m * KSUB * dsub;
         const float* cnm = p.cnorm + (size_t)m * KSUB;
+        __syncwarp();
+        for (int i = lane; i < dsub; i += 32) xs[i] = xr[i];
+        __syncwarp();
         float xn = 0.f;
-        for (int i = 0; i < p.dsub; ++i) xn = __fmaf_rn(xr[i], xr[i], xn);
+        for (int i = 0; i < dsub; ++i) xn = __fmaf_rn(xs[i], xs[i], xn);
         float best = __int_as_float(0x7f800000);
         int bk = 0x7fffffff;
         for (int j = lane; j < KSUB; j += 32) {
-            float d = exact_dist(xr, cm + (size_t)j * p.dsub, p.dsub, xn, cnm[j]);
+            const float4* c4 = reinterpret_cast<const float4*>(cm + (size_t)j * dsub);
+            float acc = 0.f;
+            for (int u0 = 0; u0 < units; u0 += 8) {
+                float4 cw[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (u0 + u < units) cw[u] = __ldg(c4 + u0 + u);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (u0 + u < units) {
+                        const float4 xw = *reinterpret_cast<const float4*>(xs + 4 * (u0 + u));
+                        acc = __fmaf_rn(xw.x, cw[u].x, acc);
+                        acc = __fmaf_rn(xw.y, cw[u].y, acc);
+                        acc = __fmaf_rn(xw.z, cw[u].z, acc);
+                        acc = __fmaf_rn(xw.w, cw[u].w, acc);
+                    }
+            }
+            float d = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(xn, cnm[j])), 0.f);
             if (d < best) {
                 best = d;
                 bk = j;
@@ -345,7 +372,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         tma_prefetch_desc(&map_bx);
         tma_prefetch_desc(&map_ax);
         mbar_init(bar(BAR_B_FULL), 1);
-        mbar_init(bar(BAR_B_EMPTY), 1);
+        mbar_init(bar(BAR_B_EMPTY), 1 + 4);  // MMA commit + 4 epilogue warps (they read B for the exact path)
         mbar_init(bar(BAR_AX_FULL), 1);
         for (int i = 0; i < MAX_STAGES; ++i) {
             mbar_init(bar(BAR_A_FULL + i), 1);
@@ -551,8 +578,35 @@ __global__ void __launch_bounds__(THREADS, 1)
                                 const int s2 = (int)m2;
                                 const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
                                 const int ja = (s1 - df) >> 1, jb = (s1 + df) >> 1;
-                                const float da = exact_dist(xr, cmx + (size_t)ja * p.dsub, p.dsub, xn, cnm[ja]);
-                                const float db = exact_dist(xr, cmx + (size_t)jb * p.dsub, p.dsub, xn, cnm[jb]);
+                                // both candidates with the SIMT kernel's arithmetic, operands from the
+                                // swizzled tiles already in shared memory (c = -0.5 * (-2c), exact)
+                                float acca = 0.f, accb = 0.f;
+                                for (int c = 0; c < nchunk; ++c) {
+                                    const uint8_t* at = gbase + sp.a_off + st * sp.a_stage_bytes +
+                                                        (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes;
+                                    const uint8_t* bt = gbase + sp.b_off + (uint32_t)(s * nchunk + c) * sp.b_chunk_bytes;
+                                    for (int u = 0; u < units; ++u) {
+                                        uint32_t ox = (uint32_t)r * pitch + (uint32_t)u * 16u;
+                                        uint32_t oa = (uint32_t)ja * pitch + (uint32_t)u * 16u;
+                                        uint32_t ob = (uint32_t)jb * pitch + (uint32_t)u * 16u;
+                                        ox ^= ((ox >> 7) & swz) << 4;
+                                        oa ^= ((oa >> 7) & swz) << 4;
+                                        ob ^= ((ob >> 7) & swz) << 4;
+                                        const float4 xw = *reinterpret_cast<const float4*>(at + ox);
+                                        const float4 ca = *reinterpret_cast<const float4*>(bt + oa);
+                                        const float4 cb4 = *reinterpret_cast<const float4*>(bt + ob);
+                                        acca = __fmaf_rn(xw.x, -0.5f * ca.x, acca);
+                                        acca = __fmaf_rn(xw.y, -0.5f * ca.y, acca);
+                                        acca = __fmaf_rn(xw.z, -0.5f * ca.z, acca);
+                                        acca = __fmaf_rn(xw.w, -0.5f * ca.w, acca);
+                                        accb = __fmaf_rn(xw.x, -0.5f * cb4.x, accb);
+                                        accb = __fmaf_rn(xw.y, -0.5f * cb4.y, accb);
+                                        accb = __fmaf_rn(xw.z, -0.5f * cb4.z, accb);
+                                        accb = __fmaf_rn(xw.w, -0.5f * cb4.w, accb);
+                                    }
+                                }
+                                const float da = fmaxf(__fmaf_rn(-2.f, acca, __fadd_rn(xn, cnm[ja])), 0.f);
+                                const float db = fmaxf(__fmaf_rn(-2.f, accb, __fadd_rn(xn, cnm[jb])), 0.f);
                                 code = (db < da) ? jb : ja;
                             } else {
                                 // 0 (NaN input) or >= 3 candidates: exact scan later, or here if the list is full
@@ -578,6 +632,8 @@ __global__ void __launch_bounds__(THREADS, 1)
                     a_phase ^= 1;
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(BAR_B_EMPTY));
         }
     }
     tc_fence_before();
@@ -767,7 +823,7 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     VQ_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     assign_tc_kernel<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
     VQ_LAUNCH_CHECK();
-    fixup_kernel<<<sms * 2, 256, 0, st>>>(p);
+    fixup_kernel<<<sms * 8, FIX_WARPS * 32, 0, st>>>(p);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
