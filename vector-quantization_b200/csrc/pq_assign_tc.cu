@@ -41,7 +41,8 @@ namespace tc {
 
 constexpr int TILE_ROWS = 128;
 constexpr int KSUB = 256;
-constexpr int THREADS = 192;
+constexpr int EPI_WARPS = 16;   // 2 accumulator stages x 4 TMEM lane quarters x 2 column halves
+constexpr int THREADS = 64 + 32 * EPI_WARPS;
 constexpr int MAX_STAGES = 4;
 constexpr uint32_t SMEM_BUDGET = 220 * 1024;
 
@@ -170,9 +171,9 @@ struct Params {
     const float* cnorm;      // (M, 256)
     const float* cmax;       // (M) max_j |c_mj|
     uint8_t* codes;          // (n, M)
-    unsigned long long* fix_count;  // entries appended to fix_list (may exceed fix_cap)
-    unsigned long long* fix_list;   // row * M + m
-    unsigned long long fix_cap;
+    unsigned long long* fix_count;  // (M) rows appended per sub-quantizer (may exceed fix_cap)
+    uint32_t* fix_list;             // (M, fix_cap) row indices needing the exact 256-way scan
+    unsigned long long fix_cap;     // capacity per sub-quantizer
     unsigned long long* stats;      // optional: [0] += pairs re-ranked, [1] += candidates, [2] += fix-up entries
     int M, dsub;
     int KS;        // sub-quantizers resident per CTA
@@ -197,7 +198,7 @@ __device__ __forceinline__ uint32_t layout_type_of(int CH) { return CH == 32 ? 2
 __global__ void prepare_kernel(const float* __restrict__ centroids, const float* __restrict__ cnorm, int dsub,
                                float* __restrict__ bprep, float* __restrict__ bextra,
                                float* __restrict__ cmax, float* __restrict__ ones,
-                               unsigned long long* __restrict__ fix_count) {
+                               unsigned long long* __restrict__ fix_count) {  // (M) counters
     const int m = blockIdx.x, j = threadIdx.x;
     const size_t row = (size_t)m * KSUB + j;
     const float* c = centroids + row * dsub;
@@ -230,8 +231,8 @@ __global__ void prepare_kernel(const float* __restrict__ centroids, const float*
             o[0] = o[1] = o[2] = 1.f;
             o[3] = o[4] = o[5] = o[6] = o[7] = 0.f;
         }
-        if (j == 0) *fix_count = 0ull;
     }
+    if (j == 0) fix_count[m] = 0ull;
 }
 
 // Exact distance of the SIMT kernel (pq.cu: pq_assign_simt_kernel): sequential fp32 FMA chain
@@ -260,54 +261,55 @@ __device__ __noinline__ int exact_scan_thread(const float* xr, const float* cm, 
 }
 
 // ---------------------------------------------------------- fix-up kernel ---
-// One warp per listed (row, m): exact scan of all 256 centroids, identical arithmetic
-// and tie-breaking (lowest index) to pq_assign_simt_kernel. The sub-vector is staged in
-// shared memory; lane l evaluates centroids l, l+32, ... (the 32 rows a warp touches per
-// step are contiguous in memory), each with its own sequential FMA chain.
+// grid (blocks_per_m, M). The CTA stages the 256 centroids of sub-quantizer m in shared
+// memory dimension-major ([i][j]: lane j reads consecutive words, no bank conflicts) and its
+// warps walk that sub-quantizer's list: exact scan of all 256 centroids with the arithmetic
+// and tie-breaking (lowest index) of pq_assign_simt_kernel; lane l owns centroids l, l+32, ...
 constexpr int FIX_WARPS = 8;
 __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
-    __shared__ __align__(16) float xs_all[FIX_WARPS][128];
+    extern __shared__ __align__(16) float fsm[];
+    const int dsub = p.dsub, m = blockIdx.y;
+    float* cs = fsm;                         // [dsub][256]
+    float* cn = cs + (size_t)dsub * KSUB;    // [256]
+    float* xs_all = cn + KSUB;               // [FIX_WARPS][dsub]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float* xs = xs_all[w];
-    const unsigned long long wid = (unsigned long long)blockIdx.x * FIX_WARPS + w;
-    const unsigned long long nw = (unsigned long long)gridDim.x * FIX_WARPS;
-    unsigned long long cnt = *p.fix_count;
+    unsigned long long cnt = p.fix_count[m];
     if (p.stats && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(p.stats + 2, cnt);
     if (cnt > p.fix_cap) cnt = p.fix_cap;
-    const int dsub = p.dsub, units = dsub >> 2;
-    for (unsigned long long e = wid; e < cnt; e += nw) {
-        const unsigned long long key = p.fix_list[e];
-        const int64_t row = (int64_t)(key / (unsigned)p.M);
-        const int m = (int)(key % (unsigned)p.M);
+    if ((unsigned long long)blockIdx.x * FIX_WARPS >= cnt) return;
+    const float* cm = p.centroids + (size_t)m * KSUB * dsub;
+    for (int idx = threadIdx.x; idx < KSUB * dsub; idx += blockDim.x) {
+        const int j = idx / dsub, i = idx - j * dsub;   // coalesced global read
+        cs[i * KSUB + j] = cm[idx];
+    }
+    for (int j = threadIdx.x; j < KSUB; j += blockDim.x) cn[j] = p.cnorm[(size_t)m * KSUB + j];
+    __syncthreads();
+    float* xs = xs_all + w * dsub;
+    const uint32_t* list = p.fix_list + (size_t)m * p.fix_cap;
+    for (unsigned long long e = (unsigned long long)blockIdx.x * FIX_WARPS + w; e < cnt;
+         e += (unsigned long long)gridDim.x * FIX_WARPS) {
+        const int64_t row = (int64_t)list[e];
         const float* xr = p.x + row * p.ldx + (int64_t)m * dsub;
-        const float* cm = p.centroids + (size_t)m * KSUB * dsub;
-        const float* cnm = p.cnorm + (size_t)m * KSUB;
         __syncwarp();
         for (int i = lane; i < dsub; i += 32) xs[i] = xr[i];
         __syncwarp();
         float xn = 0.f;
         for (int i = 0; i < dsub; ++i) xn = __fmaf_rn(xs[i], xs[i], xn);
+        float acc[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc[t] = 0.f;
+        for (int i = 0; i < dsub; ++i) {
+            const float xv = xs[i];
+            const float* ci = cs + i * KSUB + lane;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) acc[t] = __fmaf_rn(xv, ci[32 * t], acc[t]);
+        }
         float best = __int_as_float(0x7f800000);
         int bk = 0x7fffffff;
-        for (int j = lane; j < KSUB; j += 32) {
-            const float4* c4 = reinterpret_cast<const float4*>(cm + (size_t)j * dsub);
-            float acc = 0.f;
-            for (int u0 = 0; u0 < units; u0 += 8) {
-                float4 cw[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (u0 + u < units) cw[u] = __ldg(c4 + u0 + u);
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (u0 + u < units) {
-                        const float4 xw = *reinterpret_cast<const float4*>(xs + 4 * (u0 + u));
-                        acc = __fmaf_rn(xw.x, cw[u].x, acc);
-                        acc = __fmaf_rn(xw.y, cw[u].y, acc);
-                        acc = __fmaf_rn(xw.z, cw[u].z, acc);
-                        acc = __fmaf_rn(xw.w, cw[u].w, acc);
-                    }
-            }
-            float d = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(xn, cnm[j])), 0.f);
+        for (int t = 0; t < 8; ++t) {
+            const int j = lane + 32 * t;
+            const float d = fmaxf(__fmaf_rn(-2.f, acc[t], __fadd_rn(xn, cn[j])), 0.f);
             if (d < best) {
                 best = d;
                 bk = j;
@@ -341,7 +343,7 @@ __host__ __device__ inline SmemPlan make_plan(int KS, int CH, int nchunk, int ns
     s.ax_off = s.bx_off + (uint32_t)KS * 8192;
     s.a_off = s.ax_off + 4096;
     s.bar_off = s.a_off + (uint32_t)nstages * s.a_stage_bytes;
-    s.total = s.bar_off + 256;
+    s.total = s.bar_off + 256 + 4096;   // barriers + epilogue exchange buffers
     return s;
 }
 
@@ -372,15 +374,15 @@ __global__ void __launch_bounds__(THREADS, 1)
         tma_prefetch_desc(&map_bx);
         tma_prefetch_desc(&map_ax);
         mbar_init(bar(BAR_B_FULL), 1);
-        mbar_init(bar(BAR_B_EMPTY), 1 + 4);  // MMA commit + 4 epilogue warps (they read B for the exact path)
+        mbar_init(bar(BAR_B_EMPTY), 1 + EPI_WARPS);  // MMA commit + 4 epilogue warps (they read B for the exact path)
         mbar_init(bar(BAR_AX_FULL), 1);
         for (int i = 0; i < MAX_STAGES; ++i) {
             mbar_init(bar(BAR_A_FULL + i), 1);
-            mbar_init(bar(BAR_A_EMPTY + i), 1 + 4);  // MMA commit + 4 epilogue warps
+            mbar_init(bar(BAR_A_EMPTY + i), 1 + EPI_WARPS);  // MMA commit + every epilogue warp
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar(BAR_T_FULL + i), 1);
-            mbar_init(bar(BAR_T_EMPTY + i), 4);
+            mbar_init(bar(BAR_T_EMPTY + i), 8);
         }
         fence_barrier_init();
     }
@@ -485,7 +487,13 @@ __global__ void __launch_bounds__(THREADS, 1)
         const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t pitch = (uint32_t)CH * 4u, swz = swizzle_mask(CH);
         const int units = CH / 4;
-        uint32_t st = 0, a_phase = 0, acc = 0, t_phase = 0;
+        // 16 epilogue warps: accumulator stage acc (units alternate), TMEM lane quarter q, column half hf.
+        // The two warps of a (acc, q) pair exchange partial results through shared memory.
+        const uint32_t eidx = (uint32_t)(warp - 2) >> 2;
+        const uint32_t acc = eidx & 1u, hf = eidx >> 1;
+        float* xch = reinterpret_cast<float*>(gbase + sp.bar_off + 256) + (acc * 4 + q) * 128;  // [4][32]
+        const uint32_t pair_bar = 1u + acc * 4u + (uint32_t)q;
+        uint32_t st = 0, a_phase = 0, t_phase = 0, unit = 0;
         for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
             const int g = (int)(item % p.groups);
             const int64_t rc = item / p.groups;
@@ -496,7 +504,8 @@ __global__ void __launch_bounds__(THREADS, 1)
                 const int64_t row = t * TILE_ROWS + r;
                 const bool live = row < p.n;
                 mbar_wait(bar(BAR_A_FULL + st), a_phase);
-                for (int s = 0; s < KS; ++s) {
+                for (int s = 0; s < KS; ++s, ++unit) {
+                    if ((unit & 1u) != acc) continue;
                     const int m = g * KS + s;
                     // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
                     float xn = 0.f;
@@ -520,8 +529,8 @@ __global__ void __launch_bounds__(THREADS, 1)
                     // pass 1: row minimum
                     float mn = __int_as_float(0x7f800000);
 #pragma unroll 1
-                    for (int cb = 0; cb < 8; ++cb) {
-                        tmem_ld32(taddr + cb * 32, v);
+                    for (int cb = 0; cb < 4; ++cb) {
+                        tmem_ld32(taddr + (hf * 4 + cb) * 32, v);
                         float a0 = fmin3(v[0], v[1], v[2]), a1 = fmin3(v[3], v[4], v[5]);
                         float a2 = fmin3(v[6], v[7], v[8]), a3 = fmin3(v[9], v[10], v[11]);
                         float a4 = fmin3(v[12], v[13], v[14]), a5 = fmin3(v[15], v[16], v[17]);
@@ -531,6 +540,9 @@ __global__ void __launch_bounds__(THREADS, 1)
                         float b3 = fmin3(a9, v[30], v[31]);
                         mn = fmin3(mn, fmin3(b0, b1, b2), b3);
                     }
+                    xch[hf * 32 + lane] = mn;
+                    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+                    mn = fminf(xch[lane], xch[32 + lane]);
                     // screen error bound: TF32 truncation of both operands (2^-9 |x||c| on x.c, doubled by
                     // the -2 factor), widened by 2 %, plus slack for fp32 accumulation and the norm split
                     const float xl = sqrtf(xn) * 1.0000005f;
@@ -541,11 +553,11 @@ __global__ void __launch_bounds__(THREADS, 1)
                     // pass 2: candidate count and index moments
                     float m1a = 0.f, m1b = 0.f, m2a = 0.f, m2b = 0.f;
 #pragma unroll
-                    for (int cb = 0; cb < 8; ++cb) {
-                        tmem_ld32(taddr + cb * 32, v);
+                    for (int cb = 0; cb < 4; ++cb) {
+                        tmem_ld32(taddr + (hf * 4 + cb) * 32, v);
 #pragma unroll
                         for (int i = 0; i < 32; i += 2) {
-                            const int j0 = cb * 32 + i, j1 = j0 + 1;
+                            const int j0 = cb * 32 + i, j1 = j0 + 1;   // index relative to this half
                             const float f0 = fset_le(v[i], thr), f1 = fset_le(v[i + 1], thr);
                             m1a = __fmaf_rn(f0, (float)(4096 + j0), m1a);
                             m1b = __fmaf_rn(f1, (float)(4096 + j1), m1b);
@@ -556,14 +568,21 @@ __global__ void __launch_bounds__(THREADS, 1)
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar(BAR_T_EMPTY + acc));
-                    if (++acc == 2) {
-                        acc = 0;
-                        t_phase ^= 1;
+                    t_phase ^= 1;
+                    // combine the halves: the upper-half warp hands its moments over and moves on
+                    if (hf == 1) {
+                        xch[64 + lane] = m1a + m1b;
+                        xch[96 + lane] = m2a + m2b;
                     }
-                    // resolve
-                    const float m1 = m1a + m1b, m2 = m2a + m2b;      // exact: all sums < 2^24
-                    const int cnt = (int)(m1 * (1.f / 4096.f));
-                    const int s1 = (int)m1 - cnt * 4096;
+                    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+                    if (hf == 1) continue;
+                    const float m1lo = m1a + m1b, m2lo = m2a + m2b;      // exact: all sums < 2^24
+                    const float m1hi = xch[64 + lane], m2hi = xch[96 + lane];
+                    const int cnt_lo = (int)(m1lo * (1.f / 4096.f)), cnt_hi = (int)(m1hi * (1.f / 4096.f));
+                    const int s1_lo = (int)m1lo - cnt_lo * 4096, s1_hi = (int)m1hi - cnt_hi * 4096;
+                    const int cnt = cnt_lo + cnt_hi;
+                    const int s1 = s1_lo + s1_hi + 128 * cnt_hi;
+                    const float m2 = m2lo + m2hi + (float)(256 * s1_hi + 16384 * cnt_hi);
                     int code = 0;
                     bool multi = false;
                     if (live) {
@@ -610,8 +629,8 @@ __global__ void __launch_bounds__(THREADS, 1)
                                 code = (db < da) ? jb : ja;
                             } else {
                                 // 0 (NaN input) or >= 3 candidates: exact scan later, or here if the list is full
-                                const unsigned long long slot = atomicAdd(p.fix_count, 1ull);
-                                if (slot < p.fix_cap) p.fix_list[slot] = (unsigned long long)row * (unsigned)p.M + m;
+                                const unsigned long long slot = atomicAdd(p.fix_count + m, 1ull);
+                                if (slot < p.fix_cap) p.fix_list[(size_t)m * p.fix_cap + slot] = (uint32_t)row;
                                 else code = exact_scan_thread(xr, cmx, cnm, p.dsub, xn);
                             }
                         }
@@ -733,11 +752,11 @@ static ScratchPlan plan_scratch(int64_t n, int M, int dsub) {
     s.ones = al(s.bextra + (size_t)M * KSUB * 8 * 4);
     s.cmax = al(s.ones + TILE_ROWS * 8 * 4);
     s.counter = al(s.cmax + (size_t)M * 4);
-    s.list = al(s.counter + 16);
-    unsigned long long cap = (unsigned long long)((n * (int64_t)M) / 8);
-    if (cap < 4096) cap = 4096;
+    s.list = al(s.counter + (size_t)M * 8);
+    unsigned long long cap = (unsigned long long)(n / 8);   // per sub-quantizer; overflow falls back inline
+    if (cap < 1024) cap = 1024;
     s.cap = cap;
-    s.total = al(s.list + cap * 8);
+    s.total = al(s.list + (size_t)M * cap * 4);
     return s;
 }
 
@@ -766,7 +785,7 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     VQ_CHECK_ARG(x && centroids && cnorm && codes, "pq_assign_tc: null pointer");
     VQ_CHECK_ARG(ldx >= (int64_t)M * dsub && ldx % 4 == 0 && ((uintptr_t)x & 15) == 0,
                  "pq_assign_tc: x must be 16-byte aligned with ldx %% 4 == 0 and ldx >= D");
-    VQ_CHECK_ARG(n < (1ll << 31) * TILE_ROWS, "pq_assign_tc: n too large for one call");
+    VQ_CHECK_ARG(n < (1ll << 32), "pq_assign_tc: n must be below 2^32 rows per call");
     ScratchPlan sc = plan_scratch(n, M, dsub);
     VQ_CHECK_ARG(scratch && scratch_bytes >= sc.total && ((uintptr_t)scratch & 255) == 0,
                  "pq_assign_tc: scratch too small or not 256-byte aligned (%zu < %zu)", scratch_bytes, sc.total);
@@ -777,7 +796,7 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     float* ones = reinterpret_cast<float*>(sb + sc.ones);
     float* cmax = reinterpret_cast<float*>(sb + sc.cmax);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(sb + sc.counter);
-    unsigned long long* list = reinterpret_cast<unsigned long long*>(sb + sc.list);
+    uint32_t* list = reinterpret_cast<uint32_t*>(sb + sc.list);
 
     prepare_kernel<<<M, KSUB, 0, st>>>(centroids, cnorm, dsub, bprep, bextra, cmax, ones, counter);
     VQ_LAUNCH_CHECK();
@@ -823,7 +842,14 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     VQ_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     assign_tc_kernel<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
     VQ_LAUNCH_CHECK();
-    fixup_kernel<<<sms * 8, FIX_WARPS * 32, 0, st>>>(p);
+    {
+        const size_t fsmem = ((size_t)dsub * KSUB + KSUB + (size_t)FIX_WARPS * dsub) * sizeof(float);
+        VQ_CUDA(cudaFuncSetAttribute(fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+        int bpm = (sms * 4 + M - 1) / M;
+        if (bpm < 1) bpm = 1;
+        dim3 fgrid((unsigned)bpm, (unsigned)M);
+        fixup_kernel<<<fgrid, FIX_WARPS * 32, fsmem, st>>>(p);
+    }
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
