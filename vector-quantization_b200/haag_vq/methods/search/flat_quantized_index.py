@@ -38,6 +38,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._D: int = 0
         self._codes_dev: Optional[torch.Tensor] = None
         self._recon_dev: Optional[torch.Tensor] = None
+        self._codes_rot: Optional[torch.Tensor] = None
 
     def fit(self, X: np.ndarray, metric: Literal['l2', 'ip'] = 'l2') -> None:
         X = np.ascontiguousarray(X, dtype=np.float32)
@@ -47,6 +48,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes = self._quantizer.compress(X)
         self._codes_dev = None
         self._recon_dev = None
+        self._codes_rot = None
 
     def attach_device_codes(self, codes_dev: torch.Tensor, D: int,
                             metric: Literal['l2', 'ip'] = 'l2') -> None:
@@ -60,6 +62,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes = None
         self._codes_dev = codes_dev
         self._recon_dev = None
+        self._codes_rot = None
 
     def search(self, Q: np.ndarray, k: int) -> np.ndarray:
         ids, _ = self.search_with_scores(Q, k)
@@ -95,7 +98,13 @@ class FlatQuantizedIndex(BaseSearchIndex):
         if codec is not None:
             if self._codes_dev is None:
                 self._codes_dev = host.to_device(np.ascontiguousarray(self._codes, dtype=np.uint8))
-            vals, ids = codec.search(self._codes_dev, q_dev, k, self._metric)
+            if codec.M % 32 == 0 and codec.M <= 96 and codec.ksub == 256:
+                # conflict-free scan layout (b200vq_pq_codes_to_scan_layout), built once per fit/load
+                if self._codes_rot is None:
+                    self._codes_rot = ops.pq_codes_to_scan_layout(self._codes_dev)
+                vals, ids = codec.search(self._codes_rot, q_dev, k, self._metric, n=self._N, rot=True)
+            else:
+                vals, ids = codec.search(self._codes_dev, q_dev, k, self._metric)
         else:
             vals, ids = ops.flat_topk(self._reconstructions(), q_dev, k, self._metric)
         return host.to_host(ids).view(np.uint32), host.to_host(vals)
@@ -142,3 +151,4 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._D = state['D']
         self._codes_dev = None
         self._recon_dev = None
+        self._codes_rot = None
