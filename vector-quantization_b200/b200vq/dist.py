@@ -50,11 +50,13 @@ def gather_topk(vals: torch.Tensor, ids_local: torch.Tensor, row_offset: int, gr
     if world == 1:
         return vals.unsqueeze(1).contiguous(), ids64.unsqueeze(1).contiguous()
     nq, k = vals.shape
-    gv = torch.empty((world, nq, k), dtype=vals.dtype, device=vals.device)
-    gi = torch.empty((world, nq, k), dtype=torch.int64, device=vals.device)
+    # (world * nq, k) concatenation along dim 0: the form both NCCL and gloo accept
+    gv = torch.empty((world * nq, k), dtype=vals.dtype, device=vals.device)
+    gi = torch.empty((world * nq, k), dtype=torch.int64, device=vals.device)
     dist.all_gather_into_tensor(gv, vals.contiguous(), group=group)
     dist.all_gather_into_tensor(gi, ids64.contiguous(), group=group)
-    return gv.permute(1, 0, 2).contiguous(), gi.permute(1, 0, 2).contiguous()
+    return (gv.view(world, nq, k).permute(1, 0, 2).contiguous(),
+            gi.view(world, nq, k).permute(1, 0, 2).contiguous())
 
 
 def sharded_topk(vals: torch.Tensor, ids_local: torch.Tensor, row_offset: int, k: int, metric,
