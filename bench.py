@@ -46,6 +46,7 @@ BATCH_ROWS = 1 << 20
 NQ = 1000
 E2E_ROWS = 1 << 18              # host batch of the e2e encode leg (1 GiB pinned)
 TRAIN_ROWS = 65_536             # 256 * ksub, faiss' training subset size
+print_line = None
 METRIC = "vectors/s encoded + ADC codes/s scanned at 1/2/4/8 B200, % of HBM roofline"
 
 
@@ -228,7 +229,7 @@ def run_reference(args):
                              "adc": {"value": adc, "unit": "codes/s"}, "sample": sample},
             "e2e": {"value": enc, "unit": "vectors/s", "adc": {"value": adc, "unit": "codes/s"},
                     "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print_line(line)
 
 
 def workload_config(args):
@@ -464,6 +465,15 @@ def run_e2e(args, ctx):
 
 def main():
     args = parse_args()
+    # libraries (NCCL's version banner) write to fd 1: keep stdout clean for the ONE JSON line
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+    global print_line
+    print_line = emit
     if args.impl == "reference":
         run_reference(args)
         return
@@ -473,7 +483,7 @@ def main():
     if ctx["rank"] == 0:
         if ctx["world"] == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg()
-        print(json.dumps(line), flush=True)
+        print_line(line)
     if ctx["world"] > 1:
         ctx["tdist"].barrier()
         ctx["tdist"].destroy_process_group()
