@@ -101,9 +101,10 @@ __global__ void __launch_bounds__(SCAN_THREADS)
 
 // ------------------------------------------------- conflict-free layout ---
 // Scan layout: rows are grouped in blocks of 32; sub-quantizers in groups of
-// 32. For block b, group g, lane i: 32 bytes at ((b*G + g)*32 + i)*32, byte s
-// = codes[b*32+i][g*32 + (i+s)%32]. In the scan, lane i then reads LUT column
-// (i+s) at step s, so the 32 lanes of a warp always hit 32 distinct banks.
+// 32. For block b, group g, lane i, step s: byte codes[b*32+i][g*32 + (i+s)%32]
+// lives at (b*G + g)*1024 + (s/16)*512 + i*16 + s%16. In the scan, lane i reads
+// LUT column (i+s) at step s, so the 32 lanes of a warp always hit 32 distinct
+// banks, and each of its two 128-bit code loads is a contiguous 512-byte request.
 __global__ void codes_to_scan_layout_kernel(const uint8_t* __restrict__ codes, int64_t n, int M,
                                             uint8_t* __restrict__ out) {
     const int G = M >> 5;
@@ -119,37 +120,41 @@ __global__ void codes_to_scan_layout_kernel(const uint8_t* __restrict__ codes, i
         int64_t row = b * 32 + i;
         uint8_t v = 0;
         if (row < n) v = codes[row * M + g * 32 + ((i + s) & 31)];
-        out[e] = v;
+        // the 32 bytes of a lane are stored as two 16-byte halves, each half contiguous across the
+        // 32 lanes (512 B), so that one 128-bit load per lane is one fully used 512-byte request
+        out[(bg << 10) + ((s >> 4) << 9) + (i << 4) + (s & 15)] = v;
     }
 }
 
 // LUT in shared memory as [g][k][64] floats: entry (k, j) = lut[g*32 + (j&31)][k],
 // i.e. every 32-column row is stored twice so that lane i can address column
 // i+s with the step s as a static immediate offset.
-template <int CAP>
+template <int CAP, int G>
 __global__ void __launch_bounds__(SCAN_THREADS)
-    adc_scan_rot_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, int M,
+    adc_scan_rot_kernel(const uint8_t* __restrict__ codes_rot, int64_t n,
                         const float* __restrict__ lut, int k, int64_t chunk_rows, int negate,
                         uint64_t* __restrict__ part) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int KSUB = 256;
-    const int G = M >> 5;
+    constexpr int M = G * 32;
     const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     float* lut_s = reinterpret_cast<float*>(smem_raw);
-    const size_t lut_bytes = (size_t)G * KSUB * 64 * 4;
+    constexpr size_t lut_bytes = (size_t)G * KSUB * 64 * 4;
     uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_raw + lut_bytes);
     const int n2 = next_pow2(SCAN_WARPS * k);
     uint64_t* mbuf = wbuf + SCAN_WARPS * CAP;
 
+    // LUT fill: a thread gathers entry kk of four consecutive sub-quantizers and stores them as one
+    // float4 (twice: columns j and j+32); the 8 lanes of a quarter warp write 128 contiguous bytes.
     const float* lut_q = lut + (size_t)q * M * KSUB;
-    for (int idx = threadIdx.x; idx < M * KSUB; idx += blockDim.x) {
-        int m = idx / KSUB, kk = idx - m * KSUB;  // coalesced read of lut[m][k]
-        int g = m >> 5, j = m & 31;
-        float v = lut_q[idx];
-        float* dst = lut_s + ((size_t)g * KSUB + kk) * 64;
-        dst[j] = v;
-        dst[j + 32] = v;
+    for (int idx = threadIdx.x; idx < G * KSUB * 8; idx += SCAN_THREADS) {
+        const int jq = idx & 7, kk = (idx >> 3) & (KSUB - 1), g = idx >> 11;
+        const float* src = lut_q + (size_t)(g * 32 + 4 * jq) * KSUB + kk;
+        float4 v = make_float4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
+        float4* dst = reinterpret_cast<float4*>(lut_s + ((size_t)g * KSUB + kk) * 64 + 4 * jq);
+        dst[0] = v;
+        dst[8] = v;
     }
     __syncthreads();
 
@@ -161,26 +166,44 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     const int64_t r0 = (int64_t)chunk * chunk_rows;  // multiple of 32
     int64_t r1 = r0 + chunk_rows;
     if (r1 > n) r1 = n;
-    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += SCAN_THREADS) {
-        const int64_t row = base + lane;
-        const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (base >> 5) * (int64_t)G * 1024);
-        float acc = 0.f;
-        for (int g = 0; g < G; ++g) {
-            uint4 v0 = ld_stream_u4(cb + (g * 32 + lane) * 2);
-            uint4 v1 = ld_stream_u4(cb + (g * 32 + lane) * 2 + 1);
-            uint32_t wds[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-            const unsigned char* lg = lbase + (size_t)g * (KSUB * 64 * 4);
+    // two 32-row blocks per iteration: both blocks' code loads are issued before the first lookup
+    constexpr int UNR = 2;
+    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += UNR * SCAN_THREADS) {
+        uint4 cv[UNR][2 * G];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+        for (int u = 0; u < UNR; ++u) {
+            // blocks past the chunk end are clamped to a valid block and masked out below
+            int64_t bb = base + (int64_t)u * SCAN_THREADS;
+            if (bb >= r1) bb = base;
+            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * 1024);
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    // address = (code << 8) | (lane << 2), built with one PRMT
-                    uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
-                    acc += *reinterpret_cast<const float*>(lg + off + (4 * j + b) * 4);
-                }
+            for (int g = 0; g < G; ++g) {
+                cv[u][2 * g] = ld_stream_u4(cb + g * 64 + lane);
+                cv[u][2 * g + 1] = ld_stream_u4(cb + g * 64 + 32 + lane);
             }
         }
-        tk.offer(row < r1, negate ? -acc : acc, (uint32_t)row);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const int64_t row = base + (int64_t)u * SCAN_THREADS + lane;
+            float acc = 0.f;
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                const uint32_t wds[8] = {cv[u][2 * g].x, cv[u][2 * g].y, cv[u][2 * g].z, cv[u][2 * g].w,
+                                         cv[u][2 * g + 1].x, cv[u][2 * g + 1].y, cv[u][2 * g + 1].z,
+                                         cv[u][2 * g + 1].w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        // address = (code << 8) | (lane << 2), built with one PRMT; the group and step
+                        // offsets are immediates of the LDS
+                        const uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
+                        acc += *reinterpret_cast<const float*>(lbase + off + g * (KSUB * 64 * 4) + (4 * j + b) * 4);
+                    }
+                }
+            }
+            tk.offer(row < r1, negate ? -acc : acc, (uint32_t)row);
+        }
     }
     block_emit_topk<CAP>(tk, mbuf, n2, k, part + ((size_t)q * nchunks + chunk) * k);
 }
@@ -526,20 +549,30 @@ extern "C" int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, i
     return B200VQ_OK;
 }
 
+template <int CAP, int G>
+static int adc_scan_rot_launch_g(const uint8_t* codes_rot, int64_t n, const float* lut, int nq, int k,
+                                 int negate, uint64_t* part, const ScanPlan& p, cudaStream_t st) {
+    const int n2 = next_pow2(SCAN_WARPS * k);
+    size_t smem = (size_t)G * 256 * 64 * 4 + (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
+    VQ_CHECK_ARG(smem <= 227 * 1024, "adc_scan_topk_rot: M=%d needs %zu B of shared memory", G * 32, smem);
+    VQ_CUDA(cudaFuncSetAttribute(adc_scan_rot_kernel<CAP, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
+    dim3 grid((unsigned)nq, (unsigned)p.nchunks);
+    adc_scan_rot_kernel<CAP, G><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, lut, k, p.chunk_rows, negate,
+                                                                  part);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
 template <int CAP>
 static int adc_scan_rot_launch(const uint8_t* codes_rot, int64_t n, int M, const float* lut, int nq,
                                int k, int negate, uint64_t* part, const ScanPlan& p,
                                cudaStream_t st) {
-    const int n2 = next_pow2(SCAN_WARPS * k);
-    size_t smem = (size_t)(M / 32) * 256 * 64 * 4 + (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
-    VQ_CHECK_ARG(smem <= 227 * 1024, "adc_scan_topk_rot: M=%d needs %zu B of shared memory", M, smem);
-    VQ_CUDA(cudaFuncSetAttribute(adc_scan_rot_kernel<CAP>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)nq, (unsigned)p.nchunks);
-    adc_scan_rot_kernel<CAP><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, M, lut, k,
-                                                               p.chunk_rows, negate, part);
-    VQ_LAUNCH_CHECK();
-    return B200VQ_OK;
+    switch (M / 32) {
+        case 1: return adc_scan_rot_launch_g<CAP, 1>(codes_rot, n, lut, nq, k, negate, part, p, st);
+        case 2: return adc_scan_rot_launch_g<CAP, 2>(codes_rot, n, lut, nq, k, negate, part, p, st);
+        default: return adc_scan_rot_launch_g<CAP, 3>(codes_rot, n, lut, nq, k, negate, part, p, st);
+    }
 }
 
 extern "C" int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksub,
