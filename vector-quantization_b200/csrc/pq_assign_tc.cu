@@ -12,7 +12,8 @@
 // no per-value add). v differs from the true distance by the row constant ||x_m||^2.
 //
 // TF32 truncates both operands to 10 mantissa bits, so the argmin of v is only a
-// SCREEN: |v - v_true| <= E with E = 2^-8 * 1.02 * |x_m| * max_j|c_mj| + slack.
+// SCREEN: |v - (1-2^-10) v_true| <= E with E = 2^-9 * 1.02 * |x_m| * max_j|c_mj| + slack
+// (the norm term is pre-scaled by 1-2^-10 to centre the one-sided truncation error).
 // The epilogue (one TMEM lane = one row) makes two passes over the accumulator:
 //   pass 1   row minimum m1 with 3-input FMNMX              (0.5 ALU op / value)
 //   pass 2   f = (v <= m1 + 2E); acc1 += f*(4096+j); acc2 += f*j*j
@@ -205,8 +206,12 @@ __global__ void prepare_kernel(const float* __restrict__ centroids, const float*
     float* b = bprep + row * dsub;
     for (int i = 0; i < dsub; ++i) b[i] = -2.0f * c[i];
     const float cn = cnorm[row];
-    const float hi = __uint_as_float(__float_as_uint(cn) & 0xFFFFE000u);
-    const float r1 = cn - hi;
+    // tcgen05 kind::tf32 TRUNCATES both operands (measured: tools/tf32_probe.cu), so every product
+    // x_i c_i shrinks by a factor in (1 - 2^-9, 1]: centre that at (1 - 2^-10) by scaling the norm
+    // term the same way. The screen then ranks (1 - 2^-10) * d with half the worst-case error.
+    const float cns = cn * 0.9990234375f;
+    const float hi = __uint_as_float(__float_as_uint(cns) & 0xFFFFE000u);
+    const float r1 = cns - hi;
     const float mid = __uint_as_float(__float_as_uint(r1) & 0xFFFFE000u);
     const float r2 = r1 - mid;
     const float lo = __uint_as_float(__float_as_uint(r2) & 0xFFFFE000u);
@@ -543,11 +548,11 @@ __global__ void __launch_bounds__(THREADS, 1)
                     xch[hf * 32 + lane] = mn;
                     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
                     mn = fminf(xch[lane], xch[32 + lane]);
-                    // screen error bound: TF32 truncation of both operands (2^-9 |x||c| on x.c, doubled by
-                    // the -2 factor), widened by 2 %, plus slack for fp32 accumulation and the norm split
+                    // screen error bound: after centring, TF32 truncation leaves |err| <= 2^-10 |x||c| on x.c,
+                    // doubled by the -2 factor; widened by 2 %, plus slack for accumulation and the norm split
                     const float xl = sqrtf(xn) * 1.0000005f;
                     const float cm = p.cmax[m];
-                    const float E = __fmaf_rn(0.00390625f * 1.02f, xl * cm,
+                    const float E = __fmaf_rn(0.001953125f * 1.02f, xl * cm,
                                               3.8147e-6f * __fmaf_rn(2.f * xl, cm, cm * cm));
                     const float thr = mn + 2.f * E;
                     // pass 2: candidate count and index moments
