@@ -74,6 +74,46 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+// Same wait for the single-thread producer / MMA roles: sleep between polls so the spinning
+// thread does not take issue slots from the epilogue warps that share its scheduler.
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        __nanosleep(64);
+    }
+}
+// Candidate bookkeeping of the epilogue's second pass, two instructions per value and no branch:
+// FSETP (ALU pipe) + predicated IMAD-immediate (FMA pipe):  if (v <= thr) acc += K(J), with
+//   K(J) = 1 | J << 8 | J*J << 17   ->  bits [0,8) count, [8,17) sum of J, [17,32) sum of J^2
+// (J < 128 is the column index inside the warp's half; the upper fields are exact whenever the
+// count is <= 2, the only case that reads them). `one` is a runtime 1 so the add stays an IMAD.
+template <int J>
+__device__ __forceinline__ void flag_accumulate(float v, float thr, uint32_t one, uint32_t& acc) {
+    constexpr uint32_t K = 1u | ((uint32_t)J << 8) | ((uint32_t)(J * J) << 17);
+    asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p mad.lo.u32 %0, %3, %4, %0;\n\t}"
+        : "+r"(acc)
+        : "f"(v), "f"(thr), "r"(one), "n"(K));
+}
+template <int CB>
+__device__ __forceinline__ void flag_chunk(const float (&v)[32], float thr, uint32_t one, uint32_t& ia,
+                                           uint32_t& ib) {
+#define B200VQ_FA(i) flag_accumulate<CB * 32 + (i)>(v[i], thr, one, ((i) & 1) ? ib : ia);
+    B200VQ_FA(0) B200VQ_FA(1) B200VQ_FA(2) B200VQ_FA(3) B200VQ_FA(4) B200VQ_FA(5) B200VQ_FA(6) B200VQ_FA(7)
+    B200VQ_FA(8) B200VQ_FA(9) B200VQ_FA(10) B200VQ_FA(11) B200VQ_FA(12) B200VQ_FA(13) B200VQ_FA(14) B200VQ_FA(15)
+    B200VQ_FA(16) B200VQ_FA(17) B200VQ_FA(18) B200VQ_FA(19) B200VQ_FA(20) B200VQ_FA(21) B200VQ_FA(22) B200VQ_FA(23)
+    B200VQ_FA(24) B200VQ_FA(25) B200VQ_FA(26) B200VQ_FA(27) B200VQ_FA(28) B200VQ_FA(29) B200VQ_FA(30) B200VQ_FA(31)
+#undef B200VQ_FA
+}
 __device__ __forceinline__ void fence_barrier_init() {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
@@ -409,7 +449,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                 const int64_t t0 = rc * p.tiles_per_item;
                 int64_t t1 = t0 + p.tiles_per_item;
                 if (t1 > p.ntiles) t1 = p.ntiles;
-                mbar_wait(bar(BAR_B_EMPTY), b_phase ^ 1);
+                mbar_wait_backoff(bar(BAR_B_EMPTY), b_phase ^ 1);
                 mbar_expect_tx(bar(BAR_B_FULL), (uint32_t)KS * (nchunk * sp.b_chunk_bytes + 8192));
                 for (int s = 0; s < KS; ++s) {
                     const int m = g * KS + s;
@@ -420,7 +460,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                 }
                 b_phase ^= 1;
                 for (int64_t t = t0; t < t1; ++t) {
-                    mbar_wait(bar(BAR_A_EMPTY + st), a_phase ^ 1);
+                    mbar_wait_backoff(bar(BAR_A_EMPTY + st), a_phase ^ 1);
                     mbar_expect_tx(bar(BAR_A_FULL + st), sp.a_stage_bytes);
                     for (int s = 0; s < KS; ++s)
                         for (int c = 0; c < nchunk; ++c)
@@ -442,19 +482,19 @@ __global__ void __launch_bounds__(THREADS, 1)
             const uint32_t sbo = 32u * (uint32_t)CH;
             const int kper = CH / 8;
             uint32_t st = 0, a_phase = 0, b_phase = 0, acc = 0, t_phase = 0;
-            mbar_wait(bar(BAR_AX_FULL), 0);
+            mbar_wait_backoff(bar(BAR_AX_FULL), 0);
             const uint64_t ax_desc = make_kmajor_desc(base + sp.ax_off, 256, 6);
             for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
                 const int64_t rc = item / p.groups;
                 const int64_t t0 = rc * p.tiles_per_item;
                 int64_t t1 = t0 + p.tiles_per_item;
                 if (t1 > p.ntiles) t1 = p.ntiles;
-                mbar_wait(bar(BAR_B_FULL), b_phase);
+                mbar_wait_backoff(bar(BAR_B_FULL), b_phase);
                 b_phase ^= 1;
                 for (int64_t t = t0; t < t1; ++t) {
-                    mbar_wait(bar(BAR_A_FULL + st), a_phase);
+                    mbar_wait_backoff(bar(BAR_A_FULL + st), a_phase);
                     for (int s = 0; s < KS; ++s) {
-                        mbar_wait(bar(BAR_T_EMPTY + acc), t_phase ^ 1);
+                        mbar_wait_backoff(bar(BAR_T_EMPTY + acc), t_phase ^ 1);
                         tc_fence_after();
                         const uint32_t d = tmem_base + acc * 256u;
                         uint32_t accum = 0;
@@ -498,6 +538,13 @@ __global__ void __launch_bounds__(THREADS, 1)
         const uint32_t acc = eidx & 1u, hf = eidx >> 1;
         float* xch = reinterpret_cast<float*>(gbase + sp.bar_off + 256) + (acc * 4 + q) * 128;  // [4][32]
         const uint32_t pair_bar = 1u + acc * 4u + (uint32_t)q;
+        const uint32_t one = p.nstages > 0 ? 1u : 0u;   // runtime 1 (see flag_accumulate)
+        uint32_t xoff[8];   // swizzled byte offsets of this lane's row inside one A chunk tile
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            uint32_t off = (uint32_t)r * pitch + (uint32_t)u * 16u;
+            xoff[u] = off ^ (((off >> 7) & swz) << 4);
+        }
         uint32_t st = 0, a_phase = 0, t_phase = 0, unit = 0;
         for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
             const int g = (int)(item % p.groups);
@@ -512,30 +559,35 @@ __global__ void __launch_bounds__(THREADS, 1)
                 for (int s = 0; s < KS; ++s, ++unit) {
                     if ((unit & 1u) != acc) continue;
                     const int m = g * KS + s;
+                    const uint8_t* atile = gbase + sp.a_off + st * sp.a_stage_bytes +
+                                           (uint32_t)(s * nchunk) * sp.a_chunk_bytes;
                     // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
+                    // (lower-half warp only: it owns the threshold and the exact path)
                     float xn = 0.f;
-                    for (int c = 0; c < nchunk; ++c) {
-                        const uint8_t* tile = gbase + sp.a_off + st * sp.a_stage_bytes +
-                                              (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes;
-                        for (int u = 0; u < units; ++u) {
-                            uint32_t off = (uint32_t)r * pitch + (uint32_t)u * 16u;
-                            off ^= ((off >> 7) & swz) << 4;
-                            const float4 w = *reinterpret_cast<const float4*>(tile + off);
-                            xn = __fmaf_rn(w.x, w.x, xn);
-                            xn = __fmaf_rn(w.y, w.y, xn);
-                            xn = __fmaf_rn(w.z, w.z, xn);
-                            xn = __fmaf_rn(w.w, w.w, xn);
+                    if (hf == 0) {
+                        for (int c = 0; c < nchunk; ++c) {
+#pragma unroll
+                            for (int u = 0; u < 8; ++u) {
+                                if (u < units) {
+                                    const float4 w = *reinterpret_cast<const float4*>(
+                                        atile + (uint32_t)c * sp.a_chunk_bytes + xoff[u]);
+                                    xn = __fmaf_rn(w.x, w.x, xn);
+                                    xn = __fmaf_rn(w.y, w.y, xn);
+                                    xn = __fmaf_rn(w.z, w.z, xn);
+                                    xn = __fmaf_rn(w.w, w.w, xn);
+                                }
+                            }
                         }
                     }
                     mbar_wait(bar(BAR_T_FULL + acc), t_phase);
                     tc_fence_after();
-                    const uint32_t taddr = lane_addr + acc * 256u;
+                    const uint32_t taddr = lane_addr + acc * 256u + hf * 128u;
                     float v[32];
-                    // pass 1: row minimum
+                    // pass 1: minimum of this warp's 128 columns
                     float mn = __int_as_float(0x7f800000);
 #pragma unroll 1
                     for (int cb = 0; cb < 4; ++cb) {
-                        tmem_ld32(taddr + (hf * 4 + cb) * 32, v);
+                        tmem_ld32(taddr + cb * 32, v);
                         float a0 = fmin3(v[0], v[1], v[2]), a1 = fmin3(v[3], v[4], v[5]);
                         float a2 = fmin3(v[6], v[7], v[8]), a3 = fmin3(v[9], v[10], v[11]);
                         float a4 = fmin3(v[12], v[13], v[14]), a5 = fmin3(v[15], v[16], v[17]);
@@ -546,91 +598,95 @@ __global__ void __launch_bounds__(THREADS, 1)
                         mn = fmin3(mn, fmin3(b0, b1, b2), b3);
                     }
                     xch[hf * 32 + lane] = mn;
-                    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-                    mn = fminf(xch[lane], xch[32 + lane]);
-                    // screen error bound: after centring, TF32 truncation leaves |err| <= 2^-10 |x||c| on x.c,
-                    // doubled by the -2 factor; widened by 2 %, plus slack for accumulation and the norm split
-                    const float xl = sqrtf(xn) * 1.0000005f;
-                    const float cm = p.cmax[m];
-                    const float E = __fmaf_rn(0.001953125f * 1.02f, xl * cm,
-                                              3.8147e-6f * __fmaf_rn(2.f * xl, cm, cm * cm));
-                    const float thr = mn + 2.f * E;
-                    // pass 2: candidate count and index moments
-                    float m1a = 0.f, m1b = 0.f, m2a = 0.f, m2b = 0.f;
-#pragma unroll
-                    for (int cb = 0; cb < 4; ++cb) {
-                        tmem_ld32(taddr + (hf * 4 + cb) * 32, v);
-#pragma unroll
-                        for (int i = 0; i < 32; i += 2) {
-                            const int j0 = cb * 32 + i, j1 = j0 + 1;   // index relative to this half
-                            const float f0 = fset_le(v[i], thr), f1 = fset_le(v[i + 1], thr);
-                            m1a = __fmaf_rn(f0, (float)(4096 + j0), m1a);
-                            m1b = __fmaf_rn(f1, (float)(4096 + j1), m1b);
-                            m2a = __fmaf_rn(f0, (float)(j0 * j0), m2a);
-                            m2b = __fmaf_rn(f1, (float)(j1 * j1), m2b);
-                        }
+                    if (hf == 0) {
+                        // screen error bound: after centring, TF32 truncation leaves |err| <= 2^-10 |x||c| on
+                        // x.c, doubled by the -2 factor; widened by 2 %, plus slack for accumulation and the
+                        // norm split
+                        const float xl = sqrtf(xn) * 1.0000005f;
+                        const float cm = p.cmax[m];
+                        const float E = __fmaf_rn(0.001953125f * 1.02f, xl * cm,
+                                                  3.8147e-6f * __fmaf_rn(2.f * xl, cm, cm * cm));
+                        xch[64 + lane] = 2.f * E;
                     }
+                    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+                    const float thr = fminf(xch[lane], xch[32 + lane]) + xch[64 + lane];
+                    // pass 2: one packed integer accumulator per candidate flag:
+                    //   bits [0,8) count, [8,17) sum of j, [17,32) sum of j^2  (j relative to this half;
+                    //   the upper fields are exact whenever the count is <= 2, which is all that reads them)
+                    uint32_t ia = 0, ib = 0;
+                    tmem_ld32(taddr, v);
+                    flag_chunk<0>(v, thr, one, ia, ib);
+                    tmem_ld32(taddr + 32, v);
+                    flag_chunk<1>(v, thr, one, ia, ib);
+                    tmem_ld32(taddr + 64, v);
+                    flag_chunk<2>(v, thr, one, ia, ib);
+                    tmem_ld32(taddr + 96, v);
+                    flag_chunk<3>(v, thr, one, ia, ib);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar(BAR_T_EMPTY + acc));
                     t_phase ^= 1;
-                    // combine the halves: the upper-half warp hands its moments over and moves on
-                    if (hf == 1) {
-                        xch[64 + lane] = m1a + m1b;
-                        xch[96 + lane] = m2a + m2b;
-                    }
+                    // combine the halves: the upper-half warp hands its accumulator over and moves on
+                    if (hf == 1) xch[96 + lane] = __uint_as_float(ia + ib);
                     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
                     if (hf == 1) continue;
-                    const float m1lo = m1a + m1b, m2lo = m2a + m2b;      // exact: all sums < 2^24
-                    const float m1hi = xch[64 + lane], m2hi = xch[96 + lane];
-                    const int cnt_lo = (int)(m1lo * (1.f / 4096.f)), cnt_hi = (int)(m1hi * (1.f / 4096.f));
-                    const int s1_lo = (int)m1lo - cnt_lo * 4096, s1_hi = (int)m1hi - cnt_hi * 4096;
+                    const uint32_t plo = ia + ib, phi = __float_as_uint(xch[96 + lane]);
+                    const int cnt_lo = plo & 0xFF, cnt_hi = phi & 0xFF;
                     const int cnt = cnt_lo + cnt_hi;
-                    const int s1 = s1_lo + s1_hi + 128 * cnt_hi;
-                    const float m2 = m2lo + m2hi + (float)(256 * s1_hi + 16384 * cnt_hi);
                     int code = 0;
                     bool multi = false;
                     if (live) {
                         if (cnt == 1) {
-                            code = s1;
+                            code = cnt_lo ? (int)((plo >> 8) & 0x1FF) : 128 + (int)((phi >> 8) & 0x1FF);
                         } else {
                             multi = true;
                             const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
                             const float* cmx = p.centroids + (size_t)m * KSUB * p.dsub;
                             const float* cnm = p.cnorm + (size_t)m * KSUB;
                             if (cnt == 2) {
-                                const int s2 = (int)m2;
-                                const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
-                                const int ja = (s1 - df) >> 1, jb = (s1 + df) >> 1;
-                                // both candidates with the SIMT kernel's arithmetic, operands from the
-                                // swizzled tiles already in shared memory (c = -0.5 * (-2c), exact)
+                                int ja, jb;
+                                if (cnt_lo == 1) {
+                                    ja = (int)((plo >> 8) & 0x1FF);
+                                    jb = 128 + (int)((phi >> 8) & 0x1FF);
+                                } else {
+                                    const uint32_t pk = cnt_lo ? plo : phi;
+                                    const int s1 = (int)((pk >> 8) & 0x1FF), s2 = (int)(pk >> 17);
+                                    const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
+                                    const int base_j = cnt_lo ? 0 : 128;
+                                    ja = base_j + ((s1 - df) >> 1);
+                                    jb = base_j + ((s1 + df) >> 1);
+                                }
+                                // both candidates with the SIMT kernel's arithmetic from the tiles in shared
+                                // memory: the chain runs on b = -2c, and fma(x, -2c, -2a) = -2 fma(x, c, a)
+                                // exactly, so (xn + cn) + chain equals fma(-2, x.c, xn + cn) bit for bit
                                 float acca = 0.f, accb = 0.f;
+                                const uint8_t* btile = gbase + sp.b_off + (uint32_t)(s * nchunk) * sp.b_chunk_bytes;
+                                const uint32_t rowa = (uint32_t)ja * pitch, rowb = (uint32_t)jb * pitch;
                                 for (int c = 0; c < nchunk; ++c) {
-                                    const uint8_t* at = gbase + sp.a_off + st * sp.a_stage_bytes +
-                                                        (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes;
-                                    const uint8_t* bt = gbase + sp.b_off + (uint32_t)(s * nchunk + c) * sp.b_chunk_bytes;
-                                    for (int u = 0; u < units; ++u) {
-                                        uint32_t ox = (uint32_t)r * pitch + (uint32_t)u * 16u;
-                                        uint32_t oa = (uint32_t)ja * pitch + (uint32_t)u * 16u;
-                                        uint32_t ob = (uint32_t)jb * pitch + (uint32_t)u * 16u;
-                                        ox ^= ((ox >> 7) & swz) << 4;
-                                        oa ^= ((oa >> 7) & swz) << 4;
-                                        ob ^= ((ob >> 7) & swz) << 4;
-                                        const float4 xw = *reinterpret_cast<const float4*>(at + ox);
-                                        const float4 ca = *reinterpret_cast<const float4*>(bt + oa);
-                                        const float4 cb4 = *reinterpret_cast<const float4*>(bt + ob);
-                                        acca = __fmaf_rn(xw.x, -0.5f * ca.x, acca);
-                                        acca = __fmaf_rn(xw.y, -0.5f * ca.y, acca);
-                                        acca = __fmaf_rn(xw.z, -0.5f * ca.z, acca);
-                                        acca = __fmaf_rn(xw.w, -0.5f * ca.w, acca);
-                                        accb = __fmaf_rn(xw.x, -0.5f * cb4.x, accb);
-                                        accb = __fmaf_rn(xw.y, -0.5f * cb4.y, accb);
-                                        accb = __fmaf_rn(xw.z, -0.5f * cb4.z, accb);
-                                        accb = __fmaf_rn(xw.w, -0.5f * cb4.w, accb);
+                                    const uint8_t* at = atile + (uint32_t)c * sp.a_chunk_bytes;
+                                    const uint8_t* bt = btile + (uint32_t)c * sp.b_chunk_bytes;
+#pragma unroll
+                                    for (int u = 0; u < 8; ++u) {
+                                        if (u < units) {
+                                            uint32_t oa = rowa + (uint32_t)u * 16u, ob = rowb + (uint32_t)u * 16u;
+                                            oa ^= ((oa >> 7) & swz) << 4;
+                                            ob ^= ((ob >> 7) & swz) << 4;
+                                            const float4 xw = *reinterpret_cast<const float4*>(at + xoff[u]);
+                                            const float4 ca = *reinterpret_cast<const float4*>(bt + oa);
+                                            const float4 cb4 = *reinterpret_cast<const float4*>(bt + ob);
+                                            acca = __fmaf_rn(xw.x, ca.x, acca);
+                                            acca = __fmaf_rn(xw.y, ca.y, acca);
+                                            acca = __fmaf_rn(xw.z, ca.z, acca);
+                                            acca = __fmaf_rn(xw.w, ca.w, acca);
+                                            accb = __fmaf_rn(xw.x, cb4.x, accb);
+                                            accb = __fmaf_rn(xw.y, cb4.y, accb);
+                                            accb = __fmaf_rn(xw.z, cb4.z, accb);
+                                            accb = __fmaf_rn(xw.w, cb4.w, accb);
+                                        }
                                     }
                                 }
-                                const float da = fmaxf(__fmaf_rn(-2.f, acca, __fadd_rn(xn, cnm[ja])), 0.f);
-                                const float db = fmaxf(__fmaf_rn(-2.f, accb, __fadd_rn(xn, cnm[jb])), 0.f);
+                                const float da = fmaxf(__fadd_rn(acca, __fadd_rn(xn, cnm[ja])), 0.f);
+                                const float db = fmaxf(__fadd_rn(accb, __fadd_rn(xn, cnm[jb])), 0.f);
                                 code = (db < da) ? jb : ja;
                             } else {
                                 // 0 (NaN input) or >= 3 candidates: exact scan later, or here if the list is full
