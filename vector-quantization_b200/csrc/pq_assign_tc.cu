@@ -34,6 +34,7 @@
 // 2..5 = epilogue (TMEM lanes 32*(warp%4)..). The two 256-column accumulators
 // double-buffer MMA against the epilogue.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -212,6 +213,7 @@ struct Params {
     const float* cnorm;      // (M, 256)
     const float* cmax;       // (M) max_j |c_mj|
     uint8_t* codes;          // (n, M)
+    uint8_t* cand2;          // (n, M) second candidate of a pair awaiting exact evaluation (0 = settled)
     unsigned long long* fix_count;  // (M) rows appended per sub-quantizer (may exceed fix_cap)
     uint32_t* fix_list;             // (M, fix_cap) row indices needing the exact 256-way scan
     unsigned long long fix_cap;     // capacity per sub-quantizer
@@ -225,6 +227,7 @@ struct Params {
     int64_t ntiles;          // ceil(n / 128)
     int64_t tiles_per_item;  // row tiles per work item
     int64_t nitems;          // groups * ceil(ntiles / tiles_per_item)
+    int debug;               // B200VQ_TC_DEBUG (profiling experiments only; 0 in production)
 };
 
 __device__ __forceinline__ uint32_t swizzle_mask(int CH) { return (uint32_t)(CH >> 2) - 1u; }  // 7, 3, 1
@@ -305,23 +308,113 @@ __device__ __noinline__ int exact_scan_thread(const float* xr, const float* cm, 
     return bk;
 }
 
+// ------------------------------------------------------ pair fix-up kernel ---
+// Scans cand2 (16 pairs per thread and step) and compacts the marked (row, m) into a shared
+// queue; then one thread per queued pair:
+//   second > code : two candidates -> both evaluated with the SIMT kernel's exact arithmetic
+//                   (operands from global memory / L2, 8 independent 128-bit loads per operand
+//                   in flight before the sequential FMA chains), lower index wins ties
+//   otherwise     : (255, 255) marker -> appended to the per-sub-quantizer list of fixup_kernel
+constexpr int PF_THREADS = 256;
+constexpr int PF_QUEUE = PF_THREADS * 16;
+__global__ void __launch_bounds__(PF_THREADS) pair_fixup_kernel(Params p) {
+    __shared__ uint32_t queue[PF_QUEUE];   // index of the pair inside the block's 4096-pair window
+    __shared__ int qn;
+    const int64_t total = p.n * (int64_t)p.M;
+    const int64_t total16 = (total + 15) >> 4;
+    const uint4* c16 = reinterpret_cast<const uint4*>(p.cand2);
+    for (int64_t g0 = (int64_t)blockIdx.x * PF_THREADS; g0 < total16; g0 += (int64_t)gridDim.x * PF_THREADS) {
+        if (threadIdx.x == 0) qn = 0;
+        __syncthreads();
+        const int64_t g = g0 + threadIdx.x;
+        if (g < total16) {
+            const uint4 w = __ldg(c16 + g);   // the scratch region is padded to a multiple of 16 bytes
+            if ((w.x | w.y | w.z | w.w) != 0u) {
+                const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    if ((wd[k >> 2] >> (8 * (k & 3))) & 0xFF) queue[atomicAdd(&qn, 1)] = threadIdx.x * 16 + k;
+            }
+        }
+        __syncthreads();
+        const int nq = qn;
+        for (int e = threadIdx.x; e < nq; e += PF_THREADS) {
+            const int64_t idx = g0 * 16 + queue[e];
+            if (idx >= total) continue;
+            const int64_t row = idx / p.M;
+            const int m = (int)(idx - row * p.M);
+            const int code = p.codes[idx], second = p.cand2[idx];
+            const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
+            const float* cm = p.centroids + (size_t)m * KSUB * p.dsub;
+            const float* cnm = p.cnorm + (size_t)m * KSUB;
+            if (second > code) {
+                float xn = 0.f, acca = 0.f, accb = 0.f;
+                const float4* x4 = reinterpret_cast<const float4*>(xr);     // dsub % 8 == 0, 16-byte rows
+                const float4* a4 = reinterpret_cast<const float4*>(cm + (size_t)code * p.dsub);
+                const float4* b4 = reinterpret_cast<const float4*>(cm + (size_t)second * p.dsub);
+                const int units = p.dsub >> 2;
+                for (int u0 = 0; u0 < units; u0 += 8) {
+                    float4 xv[8], av[8], bv[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (u0 + u < units) {
+                            xv[u] = x4[u0 + u];
+                            av[u] = __ldg(a4 + u0 + u);
+                            bv[u] = __ldg(b4 + u0 + u);
+                        }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (u0 + u < units) {
+                            xn = __fmaf_rn(xv[u].x, xv[u].x, xn);
+                            xn = __fmaf_rn(xv[u].y, xv[u].y, xn);
+                            xn = __fmaf_rn(xv[u].z, xv[u].z, xn);
+                            xn = __fmaf_rn(xv[u].w, xv[u].w, xn);
+                            acca = __fmaf_rn(xv[u].x, av[u].x, acca);
+                            acca = __fmaf_rn(xv[u].y, av[u].y, acca);
+                            acca = __fmaf_rn(xv[u].z, av[u].z, acca);
+                            acca = __fmaf_rn(xv[u].w, av[u].w, acca);
+                            accb = __fmaf_rn(xv[u].x, bv[u].x, accb);
+                            accb = __fmaf_rn(xv[u].y, bv[u].y, accb);
+                            accb = __fmaf_rn(xv[u].z, bv[u].z, accb);
+                            accb = __fmaf_rn(xv[u].w, bv[u].w, accb);
+                        }
+                }
+                const float da = fmaxf(__fmaf_rn(-2.f, acca, __fadd_rn(xn, cnm[code])), 0.f);
+                const float db = fmaxf(__fmaf_rn(-2.f, accb, __fadd_rn(xn, cnm[second])), 0.f);
+                if (db < da) p.codes[idx] = (uint8_t)second;
+            } else {
+                const unsigned long long slot = atomicAdd(p.fix_count + m, 1ull);
+                if (slot < p.fix_cap) {
+                    p.fix_list[(size_t)m * p.fix_cap + slot] = (uint32_t)row;
+                } else {
+                    float xn = 0.f;
+                    for (int i = 0; i < p.dsub; ++i) xn = __fmaf_rn(xr[i], xr[i], xn);
+                    p.codes[idx] = (uint8_t)exact_scan_thread(xr, cm, cnm, p.dsub, xn);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // ---------------------------------------------------------- fix-up kernel ---
 // grid (blocks_per_m, M). The CTA stages the 256 centroids of sub-quantizer m in shared
 // memory dimension-major ([i][j]: lane j reads consecutive words, no bank conflicts) and its
 // warps walk that sub-quantizer's list: exact scan of all 256 centroids with the arithmetic
 // and tie-breaking (lowest index) of pq_assign_simt_kernel; lane l owns centroids l, l+32, ...
 constexpr int FIX_WARPS = 8;
+constexpr int FIX_ROWS = 4;   // list entries scored together by one warp (centroid loads are shared)
 __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
     extern __shared__ __align__(16) float fsm[];
     const int dsub = p.dsub, m = blockIdx.y;
     float* cs = fsm;                         // [dsub][256]
     float* cn = cs + (size_t)dsub * KSUB;    // [256]
-    float* xs_all = cn + KSUB;               // [FIX_WARPS][dsub]
+    float* xs_all = cn + KSUB;               // [FIX_WARPS][FIX_ROWS][dsub]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     unsigned long long cnt = p.fix_count[m];
     if (p.stats && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(p.stats + 2, cnt);
     if (cnt > p.fix_cap) cnt = p.fix_cap;
-    if ((unsigned long long)blockIdx.x * FIX_WARPS >= cnt) return;
+    if ((unsigned long long)blockIdx.x * FIX_WARPS * FIX_ROWS >= cnt) return;
     const float* cm = p.centroids + (size_t)m * KSUB * dsub;
     for (int idx = threadIdx.x; idx < KSUB * dsub; idx += blockDim.x) {
         const int j = idx / dsub, i = idx - j * dsub;   // coalesced global read
@@ -329,47 +422,64 @@ __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
     }
     for (int j = threadIdx.x; j < KSUB; j += blockDim.x) cn[j] = p.cnorm[(size_t)m * KSUB + j];
     __syncthreads();
-    float* xs = xs_all + w * dsub;
+    float* xs = xs_all + (size_t)w * FIX_ROWS * dsub;
     const uint32_t* list = p.fix_list + (size_t)m * p.fix_cap;
-    for (unsigned long long e = (unsigned long long)blockIdx.x * FIX_WARPS + w; e < cnt;
-         e += (unsigned long long)gridDim.x * FIX_WARPS) {
-        const int64_t row = (int64_t)list[e];
-        const float* xr = p.x + row * p.ldx + (int64_t)m * dsub;
+    for (unsigned long long e0 = ((unsigned long long)blockIdx.x * FIX_WARPS + w) * FIX_ROWS; e0 < cnt;
+         e0 += (unsigned long long)gridDim.x * FIX_WARPS * FIX_ROWS) {
+        int64_t rows[FIX_ROWS];
         __syncwarp();
-        for (int i = lane; i < dsub; i += 32) xs[i] = xr[i];
-        __syncwarp();
-        float xn = 0.f;
-        for (int i = 0; i < dsub; ++i) xn = __fmaf_rn(xs[i], xs[i], xn);
-        float acc[8];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) acc[t] = 0.f;
+        for (int t = 0; t < FIX_ROWS; ++t) {
+            const unsigned long long e = e0 + t < cnt ? e0 + t : e0;   // pad with the first entry
+            rows[t] = (int64_t)list[e];
+            const float* xr = p.x + rows[t] * p.ldx + (int64_t)m * dsub;
+            for (int i = lane; i < dsub; i += 32) xs[t * dsub + i] = xr[i];
+        }
+        __syncwarp();
+        float xn[FIX_ROWS], acc[FIX_ROWS][8];
+#pragma unroll
+        for (int t = 0; t < FIX_ROWS; ++t) {
+            xn[t] = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[t][k] = 0.f;
+        }
         for (int i = 0; i < dsub; ++i) {
-            const float xv = xs[i];
             const float* ci = cs + i * KSUB + lane;
+            float cv[8];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) acc[t] = __fmaf_rn(xv, ci[32 * t], acc[t]);
-        }
-        float best = __int_as_float(0x7f800000);
-        int bk = 0x7fffffff;
+            for (int k = 0; k < 8; ++k) cv[k] = ci[32 * k];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) {
-            const int j = lane + 32 * t;
-            const float d = fmaxf(__fmaf_rn(-2.f, acc[t], __fadd_rn(xn, cn[j])), 0.f);
-            if (d < best) {
-                best = d;
-                bk = j;
+            for (int t = 0; t < FIX_ROWS; ++t) {
+                const float xv = xs[t * dsub + i];
+                xn[t] = __fmaf_rn(xv, xv, xn[t]);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[t][k] = __fmaf_rn(xv, cv[k], acc[t][k]);
             }
         }
-        for (int o = 16; o > 0; o >>= 1) {
-            float ob = __shfl_xor_sync(FULL_MASK, best, o);
-            int ok = __shfl_xor_sync(FULL_MASK, bk, o);
-            if (ob < best || (ob == best && ok < bk)) {
-                best = ob;
-                bk = ok;
+#pragma unroll
+        for (int t = 0; t < FIX_ROWS; ++t) {
+            float best = __int_as_float(0x7f800000);
+            int bk = 0x7fffffff;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int j = lane + 32 * k;
+                const float d = fmaxf(__fmaf_rn(-2.f, acc[t][k], __fadd_rn(xn[t], cn[j])), 0.f);
+                if (d < best) {
+                    best = d;
+                    bk = j;
+                }
             }
+            for (int o = 16; o > 0; o >>= 1) {
+                float ob = __shfl_xor_sync(FULL_MASK, best, o);
+                int ok = __shfl_xor_sync(FULL_MASK, bk, o);
+                if (ob < best || (ob == best && ok < bk)) {
+                    best = ob;
+                    bk = ok;
+                }
+            }
+            if (bk == 0x7fffffff) bk = 0;  // all distances NaN: the SIMT kernel keeps index 0
+            if (lane == 0 && e0 + t < cnt) p.codes[rows[t] * p.M + m] = (uint8_t)bk;
         }
-        if (bk == 0x7fffffff) bk = 0;  // all distances NaN: the SIMT kernel keeps index 0
-        if (lane == 0) p.codes[row * p.M + m] = (uint8_t)bk;
     }
 }
 
@@ -419,7 +529,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         tma_prefetch_desc(&map_bx);
         tma_prefetch_desc(&map_ax);
         mbar_init(bar(BAR_B_FULL), 1);
-        mbar_init(bar(BAR_B_EMPTY), 1 + EPI_WARPS);  // MMA commit + 4 epilogue warps (they read B for the exact path)
+        mbar_init(bar(BAR_B_EMPTY), 1);  // MMA commit + 4 epilogue warps (they read B for the exact path)
         mbar_init(bar(BAR_AX_FULL), 1);
         for (int i = 0; i < MAX_STAGES; ++i) {
             mbar_init(bar(BAR_A_FULL + i), 1);
@@ -562,9 +672,9 @@ __global__ void __launch_bounds__(THREADS, 1)
                     const uint8_t* atile = gbase + sp.a_off + st * sp.a_stage_bytes +
                                            (uint32_t)(s * nchunk) * sp.a_chunk_bytes;
                     // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
-                    // (lower-half warp only: it owns the threshold and the exact path)
+                    // (upper-half warp only: the lower-half warp of the pair does the bookkeeping)
                     float xn = 0.f;
-                    if (hf == 0) {
+                    if (hf == 1) {
                         for (int c = 0; c < nchunk; ++c) {
 #pragma unroll
                             for (int u = 0; u < 8; ++u) {
@@ -598,7 +708,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                         mn = fmin3(mn, fmin3(b0, b1, b2), b3);
                     }
                     xch[hf * 32 + lane] = mn;
-                    if (hf == 0) {
+                    if (hf == 1) {
                         // screen error bound: after centring, TF32 truncation leaves |err| <= 2^-10 |x||c| on
                         // x.c, doubled by the -2 factor; widened by 2 %, plus slack for accumulation and the
                         // norm split
@@ -614,6 +724,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                     //   bits [0,8) count, [8,17) sum of j, [17,32) sum of j^2  (j relative to this half;
                     //   the upper fields are exact whenever the count is <= 2, which is all that reads them)
                     uint32_t ia = 0, ib = 0;
+                    if (p.debug & 1) { ia = 1; } else {
                     tmem_ld32(taddr, v);
                     flag_chunk<0>(v, thr, one, ia, ib);
                     tmem_ld32(taddr + 32, v);
@@ -622,6 +733,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                     flag_chunk<2>(v, thr, one, ia, ib);
                     tmem_ld32(taddr + 96, v);
                     flag_chunk<3>(v, thr, one, ia, ib);
+                    }
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar(BAR_T_EMPTY + acc));
@@ -633,69 +745,35 @@ __global__ void __launch_bounds__(THREADS, 1)
                     const uint32_t plo = ia + ib, phi = __float_as_uint(xch[96 + lane]);
                     const int cnt_lo = plo & 0xFF, cnt_hi = phi & 0xFF;
                     const int cnt = cnt_lo + cnt_hi;
-                    int code = 0;
+                    // 1 candidate: it is the exact argmin. 2: provisional code = lower index, the other goes
+                    // to cand2 and pair_fixup_kernel evaluates both exactly. Otherwise (>= 3, or 0 for NaN
+                    // rows) the (255, 255) marker sends the pair to the exact 256-way scan. Plain stores
+                    // only: nothing here waits on memory.
+                    int code = 0, second = 0;
                     bool multi = false;
                     if (live) {
-                        if (cnt == 1) {
+                        if (cnt == 1 || (p.debug & 2)) {
                             code = cnt_lo ? (int)((plo >> 8) & 0x1FF) : 128 + (int)((phi >> 8) & 0x1FF);
+                        } else if (cnt == 2) {
+                            multi = true;
+                            if (cnt_lo == 1) {
+                                code = (int)((plo >> 8) & 0x1FF);
+                                second = 128 + (int)((phi >> 8) & 0x1FF);
+                            } else {
+                                const uint32_t pk = cnt_lo ? plo : phi;
+                                const int s1 = (int)((pk >> 8) & 0x1FF), s2 = (int)(pk >> 17);
+                                const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
+                                const int base_j = cnt_lo ? 0 : 128;
+                                code = base_j + ((s1 - df) >> 1);
+                                second = base_j + ((s1 + df) >> 1);
+                            }
                         } else {
                             multi = true;
-                            const float* xr = p.x + row * p.ldx + (int64_t)m * p.dsub;
-                            const float* cmx = p.centroids + (size_t)m * KSUB * p.dsub;
-                            const float* cnm = p.cnorm + (size_t)m * KSUB;
-                            if (cnt == 2) {
-                                int ja, jb;
-                                if (cnt_lo == 1) {
-                                    ja = (int)((plo >> 8) & 0x1FF);
-                                    jb = 128 + (int)((phi >> 8) & 0x1FF);
-                                } else {
-                                    const uint32_t pk = cnt_lo ? plo : phi;
-                                    const int s1 = (int)((pk >> 8) & 0x1FF), s2 = (int)(pk >> 17);
-                                    const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
-                                    const int base_j = cnt_lo ? 0 : 128;
-                                    ja = base_j + ((s1 - df) >> 1);
-                                    jb = base_j + ((s1 + df) >> 1);
-                                }
-                                // both candidates with the SIMT kernel's arithmetic from the tiles in shared
-                                // memory: the chain runs on b = -2c, and fma(x, -2c, -2a) = -2 fma(x, c, a)
-                                // exactly, so (xn + cn) + chain equals fma(-2, x.c, xn + cn) bit for bit
-                                float acca = 0.f, accb = 0.f;
-                                const uint8_t* btile = gbase + sp.b_off + (uint32_t)(s * nchunk) * sp.b_chunk_bytes;
-                                const uint32_t rowa = (uint32_t)ja * pitch, rowb = (uint32_t)jb * pitch;
-                                for (int c = 0; c < nchunk; ++c) {
-                                    const uint8_t* at = atile + (uint32_t)c * sp.a_chunk_bytes;
-                                    const uint8_t* bt = btile + (uint32_t)c * sp.b_chunk_bytes;
-#pragma unroll
-                                    for (int u = 0; u < 8; ++u) {
-                                        if (u < units) {
-                                            uint32_t oa = rowa + (uint32_t)u * 16u, ob = rowb + (uint32_t)u * 16u;
-                                            oa ^= ((oa >> 7) & swz) << 4;
-                                            ob ^= ((ob >> 7) & swz) << 4;
-                                            const float4 xw = *reinterpret_cast<const float4*>(at + xoff[u]);
-                                            const float4 ca = *reinterpret_cast<const float4*>(bt + oa);
-                                            const float4 cb4 = *reinterpret_cast<const float4*>(bt + ob);
-                                            acca = __fmaf_rn(xw.x, ca.x, acca);
-                                            acca = __fmaf_rn(xw.y, ca.y, acca);
-                                            acca = __fmaf_rn(xw.z, ca.z, acca);
-                                            acca = __fmaf_rn(xw.w, ca.w, acca);
-                                            accb = __fmaf_rn(xw.x, cb4.x, accb);
-                                            accb = __fmaf_rn(xw.y, cb4.y, accb);
-                                            accb = __fmaf_rn(xw.z, cb4.z, accb);
-                                            accb = __fmaf_rn(xw.w, cb4.w, accb);
-                                        }
-                                    }
-                                }
-                                const float da = fmaxf(__fadd_rn(acca, __fadd_rn(xn, cnm[ja])), 0.f);
-                                const float db = fmaxf(__fadd_rn(accb, __fadd_rn(xn, cnm[jb])), 0.f);
-                                code = (db < da) ? jb : ja;
-                            } else {
-                                // 0 (NaN input) or >= 3 candidates: exact scan later, or here if the list is full
-                                const unsigned long long slot = atomicAdd(p.fix_count + m, 1ull);
-                                if (slot < p.fix_cap) p.fix_list[(size_t)m * p.fix_cap + slot] = (uint32_t)row;
-                                else code = exact_scan_thread(xr, cmx, cnm, p.dsub, xn);
-                            }
+                            code = 255;
+                            second = 255;
                         }
                         p.codes[row * p.M + m] = (uint8_t)code;
+                        if (second) p.cand2[row * p.M + m] = (uint8_t)second;
                     }
                     if (p.stats) {
                         const unsigned mm = __ballot_sync(FULL_MASK, multi);
@@ -712,8 +790,6 @@ __global__ void __launch_bounds__(THREADS, 1)
                     a_phase ^= 1;
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(BAR_B_EMPTY));
         }
     }
     tc_fence_before();
@@ -802,7 +878,7 @@ static TcShape plan_shape(int M, int dsub) {
 
 // scratch layout (all offsets 256-byte aligned)
 struct ScratchPlan {
-    size_t bprep, bextra, ones, cmax, counter, list, total;
+    size_t bprep, bextra, ones, cmax, counter, list, cand2, total;
     unsigned long long cap;
 };
 static ScratchPlan plan_scratch(int64_t n, int M, int dsub) {
@@ -817,7 +893,8 @@ static ScratchPlan plan_scratch(int64_t n, int M, int dsub) {
     unsigned long long cap = (unsigned long long)(n / 8);   // per sub-quantizer; overflow falls back inline
     if (cap < 1024) cap = 1024;
     s.cap = cap;
-    s.total = al(s.list + (size_t)M * cap * 4);
+    s.cand2 = al(s.list + (size_t)M * cap * 4);
+    s.total = al(s.cand2 + (((size_t)n * M + 15) & ~(size_t)15));
     return s;
 }
 
@@ -858,6 +935,8 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     float* cmax = reinterpret_cast<float*>(sb + sc.cmax);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(sb + sc.counter);
     uint32_t* list = reinterpret_cast<uint32_t*>(sb + sc.list);
+    uint8_t* cand2 = sb + sc.cand2;
+    VQ_CUDA(cudaMemsetAsync(cand2, 0, (((size_t)n * M + 15) & ~(size_t)15), st));
 
     prepare_kernel<<<M, KSUB, 0, st>>>(centroids, cnorm, dsub, bprep, bextra, cmax, ones, counter);
     VQ_LAUNCH_CHECK();
@@ -879,6 +958,7 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     p.cnorm = cnorm;
     p.cmax = cmax;
     p.codes = codes;
+    p.cand2 = cand2;
     p.fix_count = counter;
     p.fix_list = list;
     p.fix_cap = sc.cap;
@@ -898,13 +978,23 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     if (tpi > 64) tpi = 64;
     p.tiles_per_item = tpi;
     p.nitems = (int64_t)p.groups * ((p.ntiles + tpi - 1) / tpi);
+    {
+        const char* dbg = getenv("B200VQ_TC_DEBUG");
+        p.debug = dbg ? atoi(dbg) : 0;
+    }
     int grid = (int)(p.nitems < sms ? p.nitems : sms);
     const size_t smem = ts.sp.total + 1024;
     VQ_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     assign_tc_kernel<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
     VQ_LAUNCH_CHECK();
     {
-        const size_t fsmem = ((size_t)dsub * KSUB + KSUB + (size_t)FIX_WARPS * dsub) * sizeof(float);
+        int64_t pg = ((p.n * (int64_t)M + 15) / 16 + PF_THREADS - 1) / PF_THREADS;
+        if (pg > (int64_t)sms * 8) pg = (int64_t)sms * 8;
+        pair_fixup_kernel<<<(int)pg, PF_THREADS, 0, st>>>(p);
+        VQ_LAUNCH_CHECK();
+    }
+    {
+        const size_t fsmem = ((size_t)dsub * KSUB + KSUB + (size_t)FIX_WARPS * FIX_ROWS * dsub) * sizeof(float);
         VQ_CUDA(cudaFuncSetAttribute(fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
         int bpm = (sms * 4 + M - 1) / M;
         if (bpm < 1) bpm = 1;
