@@ -12,10 +12,11 @@ cs = torch.linspace(4.0, 0.2, D, device=dev)
 xt = ops_sq.synth_rows(65536, D, 1 << 40, 1234, cs, True, device=dev)
 C = dpq.pq_train(xt, M, 8, niter=8, seed=1234)
 x = ops_sq.synth_rows(n, D, 0, 1234, cs, True, device=dev)
-stats = torch.zeros(3, dtype=torch.int64, device=dev)
+stats = torch.zeros(8, dtype=torch.int64, device=dev)
 codes = ops.pq_assign(x, C, impl="tc", stats=stats)
 torch.cuda.synchronize()
 st = stats.tolist()
+print("mma-thread cycles (sum over CTAs): a_full wait, t_empty wait, b_full wait, total:", st[3:7])
 print(f"pairs={n*M} re-evaluated={st[0]} ({st[0]/(n*M):.4f}) candidates={st[1]} fixup={st[2]} ({st[2]/(n*M):.5f})")
 for impl in ("tc", "simt"):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

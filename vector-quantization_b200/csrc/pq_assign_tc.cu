@@ -106,13 +106,14 @@ __device__ __forceinline__ void flag_accumulate(float v, float thr, uint32_t one
         : "f"(v), "f"(thr), "r"(one), "n"(K));
 }
 template <int CB>
-__device__ __forceinline__ void flag_chunk(const float (&v)[32], float thr, uint32_t one, uint32_t& ia,
+__device__ __forceinline__ void flag_chunk(const float (&v)[64], float thr, uint32_t one, uint32_t& ia,
                                            uint32_t& ib) {
-#define B200VQ_FA(i) flag_accumulate<CB * 32 + (i)>(v[i], thr, one, ((i) & 1) ? ib : ia);
-    B200VQ_FA(0) B200VQ_FA(1) B200VQ_FA(2) B200VQ_FA(3) B200VQ_FA(4) B200VQ_FA(5) B200VQ_FA(6) B200VQ_FA(7)
-    B200VQ_FA(8) B200VQ_FA(9) B200VQ_FA(10) B200VQ_FA(11) B200VQ_FA(12) B200VQ_FA(13) B200VQ_FA(14) B200VQ_FA(15)
-    B200VQ_FA(16) B200VQ_FA(17) B200VQ_FA(18) B200VQ_FA(19) B200VQ_FA(20) B200VQ_FA(21) B200VQ_FA(22) B200VQ_FA(23)
-    B200VQ_FA(24) B200VQ_FA(25) B200VQ_FA(26) B200VQ_FA(27) B200VQ_FA(28) B200VQ_FA(29) B200VQ_FA(30) B200VQ_FA(31)
+#define B200VQ_FA(i) flag_accumulate<CB * 64 + (i)>(v[i], thr, one, ((i) & 1) ? ib : ia);
+#define B200VQ_FA8(b) B200VQ_FA(b) B200VQ_FA(b + 1) B200VQ_FA(b + 2) B200VQ_FA(b + 3) \
+                      B200VQ_FA(b + 4) B200VQ_FA(b + 5) B200VQ_FA(b + 6) B200VQ_FA(b + 7)
+    B200VQ_FA8(0) B200VQ_FA8(8) B200VQ_FA8(16) B200VQ_FA8(24) B200VQ_FA8(32) B200VQ_FA8(40) B200VQ_FA8(48)
+    B200VQ_FA8(56)
+#undef B200VQ_FA8
 #undef B200VQ_FA
 }
 __device__ __forceinline__ void fence_barrier_init() {
@@ -176,6 +177,28 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
           "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
           "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
           "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// 32 lanes x 64 consecutive fp32 columns -> 64 registers per thread.
+__device__ __forceinline__ void tmem_ld64(uint32_t taddr, float (&v)[64]) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+        "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+        "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+          "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+          "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+          "=r"(r[29]), "=r"(r[30]), "=r"(r[31]), "=r"(r[32]), "=r"(r[33]), "=r"(r[34]), "=r"(r[35]),
+          "=r"(r[36]), "=r"(r[37]), "=r"(r[38]), "=r"(r[39]), "=r"(r[40]), "=r"(r[41]), "=r"(r[42]),
+          "=r"(r[43]), "=r"(r[44]), "=r"(r[45]), "=r"(r[46]), "=r"(r[47]), "=r"(r[48]), "=r"(r[49]),
+          "=r"(r[50]), "=r"(r[51]), "=r"(r[52]), "=r"(r[53]), "=r"(r[54]), "=r"(r[55]), "=r"(r[56]),
+          "=r"(r[57]), "=r"(r[58]), "=r"(r[59]), "=r"(r[60]), "=r"(r[61]), "=r"(r[62]), "=r"(r[63])
         : "r"(taddr)
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -577,7 +600,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                             tma_load_2d(base + sp.a_off + st * sp.a_stage_bytes +
                                             (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes,
                                         &map_x, bar(BAR_A_FULL + st), (g * KS + s) * p.dsub + c * CH,
-                                        (int)(t * TILE_ROWS));
+                                        (p.debug & 16) ? 0 : (int)(t * TILE_ROWS));
                     if (++st == (uint32_t)NST) {
                         st = 0;
                         a_phase ^= 1;
@@ -592,6 +615,8 @@ __global__ void __launch_bounds__(THREADS, 1)
             const uint32_t sbo = 32u * (uint32_t)CH;
             const int kper = CH / 8;
             uint32_t st = 0, a_phase = 0, b_phase = 0, acc = 0, t_phase = 0;
+            long long w_a = 0, w_t = 0, w_b = 0;
+            const long long t_begin = clock64();
             mbar_wait_backoff(bar(BAR_AX_FULL), 0);
             const uint64_t ax_desc = make_kmajor_desc(base + sp.ax_off, 256, 6);
             for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
@@ -599,12 +624,12 @@ __global__ void __launch_bounds__(THREADS, 1)
                 const int64_t t0 = rc * p.tiles_per_item;
                 int64_t t1 = t0 + p.tiles_per_item;
                 if (t1 > p.ntiles) t1 = p.ntiles;
-                mbar_wait_backoff(bar(BAR_B_FULL), b_phase);
+                { const long long c0 = clock64(); mbar_wait_backoff(bar(BAR_B_FULL), b_phase); w_b += clock64() - c0; }
                 b_phase ^= 1;
                 for (int64_t t = t0; t < t1; ++t) {
-                    mbar_wait_backoff(bar(BAR_A_FULL + st), a_phase);
+                    { const long long c0 = clock64(); mbar_wait_backoff(bar(BAR_A_FULL + st), a_phase); w_a += clock64() - c0; }
                     for (int s = 0; s < KS; ++s) {
-                        mbar_wait_backoff(bar(BAR_T_EMPTY + acc), t_phase ^ 1);
+                        { const long long c0 = clock64(); mbar_wait_backoff(bar(BAR_T_EMPTY + acc), t_phase ^ 1); w_t += clock64() - c0; }
                         tc_fence_after();
                         const uint32_t d = tmem_base + acc * 256u;
                         uint32_t accum = 0;
@@ -633,6 +658,12 @@ __global__ void __launch_bounds__(THREADS, 1)
                     }
                 }
                 umma_commit(bar(BAR_B_EMPTY));
+            }
+            if (p.stats && (p.debug & 32)) {
+                atomicAdd(p.stats + 3, (unsigned long long)w_a);
+                atomicAdd(p.stats + 4, (unsigned long long)w_t);
+                atomicAdd(p.stats + 5, (unsigned long long)w_b);
+                atomicAdd(p.stats + 6, (unsigned long long)(clock64() - t_begin));
             }
         }
     } else {
@@ -674,7 +705,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                     // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
                     // (upper-half warp only: the lower-half warp of the pair does the bookkeeping)
                     float xn = 0.f;
-                    if (hf == 1) {
+                    if (hf == 1 && !(p.debug & 4)) {
                         for (int c = 0; c < nchunk; ++c) {
 #pragma unroll
                             for (int u = 0; u < 8; ++u) {
@@ -692,20 +723,21 @@ __global__ void __launch_bounds__(THREADS, 1)
                     mbar_wait(bar(BAR_T_FULL + acc), t_phase);
                     tc_fence_after();
                     const uint32_t taddr = lane_addr + acc * 256u + hf * 128u;
-                    float v[32];
-                    // pass 1: minimum of this warp's 128 columns
+                    float v[64];
+                    // pass 1: minimum of this warp's 128 columns (two 64-column TMEM loads)
                     float mn = __int_as_float(0x7f800000);
 #pragma unroll 1
-                    for (int cb = 0; cb < 4; ++cb) {
-                        tmem_ld32(taddr + cb * 32, v);
-                        float a0 = fmin3(v[0], v[1], v[2]), a1 = fmin3(v[3], v[4], v[5]);
-                        float a2 = fmin3(v[6], v[7], v[8]), a3 = fmin3(v[9], v[10], v[11]);
-                        float a4 = fmin3(v[12], v[13], v[14]), a5 = fmin3(v[15], v[16], v[17]);
-                        float a6 = fmin3(v[18], v[19], v[20]), a7 = fmin3(v[21], v[22], v[23]);
-                        float a8 = fmin3(v[24], v[25], v[26]), a9 = fmin3(v[27], v[28], v[29]);
-                        float b0 = fmin3(a0, a1, a2), b1 = fmin3(a3, a4, a5), b2 = fmin3(a6, a7, a8);
-                        float b3 = fmin3(a9, v[30], v[31]);
-                        mn = fmin3(mn, fmin3(b0, b1, b2), b3);
+                    for (int cb = 0; cb < ((p.debug & 8) ? 0 : 2); ++cb) {
+                        tmem_ld64(taddr + cb * 64, v);
+                        float t[22];
+#pragma unroll
+                        for (int k = 0; k < 21; ++k) t[k] = fmin3(v[3 * k], v[3 * k + 1], v[3 * k + 2]);
+                        t[21] = v[63];
+                        float u0 = fmin3(t[0], t[1], t[2]), u1 = fmin3(t[3], t[4], t[5]), u2 = fmin3(t[6], t[7], t[8]);
+                        float u3 = fmin3(t[9], t[10], t[11]), u4 = fmin3(t[12], t[13], t[14]);
+                        float u5 = fmin3(t[15], t[16], t[17]), u6 = fmin3(t[18], t[19], t[20]);
+                        float w0 = fmin3(u0, u1, u2), w1 = fmin3(u3, u4, u5), w2 = fmin3(u6, t[21], mn);
+                        mn = fmin3(w0, w1, w2);
                     }
                     xch[hf * 32 + lane] = mn;
                     if (hf == 1) {
@@ -725,14 +757,10 @@ __global__ void __launch_bounds__(THREADS, 1)
                     //   the upper fields are exact whenever the count is <= 2, which is all that reads them)
                     uint32_t ia = 0, ib = 0;
                     if (p.debug & 1) { ia = 1; } else {
-                    tmem_ld32(taddr, v);
+                    tmem_ld64(taddr, v);
                     flag_chunk<0>(v, thr, one, ia, ib);
-                    tmem_ld32(taddr + 32, v);
+                    tmem_ld64(taddr + 64, v);
                     flag_chunk<1>(v, thr, one, ia, ib);
-                    tmem_ld32(taddr + 64, v);
-                    flag_chunk<2>(v, thr, one, ia, ib);
-                    tmem_ld32(taddr + 96, v);
-                    flag_chunk<3>(v, thr, one, ia, ib);
                     }
                     tc_fence_before();
                     __syncwarp();
