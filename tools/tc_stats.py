@@ -10,7 +10,7 @@ n = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 20
 dev = torch.device("cuda")
 cs = torch.linspace(4.0, 0.2, D, device=dev)
 xt = ops_sq.synth_rows(65536, D, 1 << 40, 1234, cs, True, device=dev)
-C = dpq.pq_train(xt, M, 8, niter=8, seed=1234)
+C = dpq.pq_train(xt, M, 8, niter=8, seed=1234, impl=os.environ.get("TRAIN_IMPL", "auto"))
 x = ops_sq.synth_rows(n, D, 0, 1234, cs, True, device=dev)
 stats = torch.zeros(8, dtype=torch.int64, device=dev)
 codes = ops.pq_assign(x, C, impl="tc", stats=stats)

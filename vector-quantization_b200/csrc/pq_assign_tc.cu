@@ -67,12 +67,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "{\n\t"
         ".reg .pred p;\n\t"
         "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra WAIT_DONE;\n\t"
         "bra WAIT_LOOP;\n\t"
         "WAIT_DONE:\n\t"
         "}" ::"r"(bar),
-        "r"(parity)
+        "r"(parity), "r"(0x989680u)   // suspend-time hint: sleep in hardware instead of re-polling
         : "memory");
 }
 // Same wait for the single-thread producer / MMA roles: sleep between polls so the spinning
@@ -83,11 +83,11 @@ __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity)
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t"
             "}"
             : "=r"(done)
-            : "r"(bar), "r"(parity)
+            : "r"(bar), "r"(parity), "r"(0x989680u)
             : "memory");
         if (done) break;
         __nanosleep(64);
@@ -106,9 +106,9 @@ __device__ __forceinline__ void flag_accumulate(float v, float thr, uint32_t one
         : "f"(v), "f"(thr), "r"(one), "n"(K));
 }
 template <int CB>
-__device__ __forceinline__ void flag_chunk(const float (&v)[64], float thr, uint32_t one, uint32_t& ia,
-                                           uint32_t& ib) {
-#define B200VQ_FA(i) flag_accumulate<CB * 64 + (i)>(v[i], thr, one, ((i) & 1) ? ib : ia);
+__device__ __forceinline__ void flag_chunk(const float (&v)[64], float thr, uint32_t one, uint32_t (&ia)[4]) {
+    // four independent accumulator chains: the IMADs of one chain are 4 cycles apart
+#define B200VQ_FA(i) flag_accumulate<CB * 64 + (i)>(v[i], thr, one, ia[(i) & 3]);
 #define B200VQ_FA8(b) B200VQ_FA(b) B200VQ_FA(b + 1) B200VQ_FA(b + 2) B200VQ_FA(b + 3) \
                       B200VQ_FA(b + 4) B200VQ_FA(b + 5) B200VQ_FA(b + 6) B200VQ_FA(b + 7)
     B200VQ_FA8(0) B200VQ_FA8(8) B200VQ_FA8(16) B200VQ_FA8(24) B200VQ_FA8(32) B200VQ_FA8(40) B200VQ_FA8(48)
@@ -529,6 +529,9 @@ __host__ __device__ inline SmemPlan make_plan(int KS, int CH, int nchunk, int ns
 enum { BAR_B_FULL = 0, BAR_B_EMPTY = 1, BAR_AX_FULL = 2, BAR_A_FULL = 3, BAR_A_EMPTY = 7, BAR_T_FULL = 11,
        BAR_T_EMPTY = 13, BAR_TMEM_PTR = 15 };
 
+// DBG = true compiles the ablation switches (Params::debug, set from B200VQ_TC_DEBUG) in; the
+// production instantiation has none of them.
+template <bool DBG>
 __global__ void __launch_bounds__(THREADS, 1)
     assign_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_b,
                      const __grid_constant__ CUtensorMap map_bx, const __grid_constant__ CUtensorMap map_ax,
@@ -545,6 +548,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KS = p.KS, CH = p.CH, nchunk = p.nchunk, NST = p.nstages;
+    const int dbg = DBG ? p.debug : 0;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
@@ -600,7 +604,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                             tma_load_2d(base + sp.a_off + st * sp.a_stage_bytes +
                                             (uint32_t)(s * nchunk + c) * sp.a_chunk_bytes,
                                         &map_x, bar(BAR_A_FULL + st), (g * KS + s) * p.dsub + c * CH,
-                                        (p.debug & 16) ? 0 : (int)(t * TILE_ROWS));
+                                        (dbg & 16) ? 0 : (int)(t * TILE_ROWS));
                     if (++st == (uint32_t)NST) {
                         st = 0;
                         a_phase ^= 1;
@@ -659,7 +663,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                 }
                 umma_commit(bar(BAR_B_EMPTY));
             }
-            if (p.stats && (p.debug & 32)) {
+            if (p.stats && (dbg & 32)) {
                 atomicAdd(p.stats + 3, (unsigned long long)w_a);
                 atomicAdd(p.stats + 4, (unsigned long long)w_t);
                 atomicAdd(p.stats + 5, (unsigned long long)w_b);
@@ -697,15 +701,17 @@ __global__ void __launch_bounds__(THREADS, 1)
                 const int64_t row = t * TILE_ROWS + r;
                 const bool live = row < p.n;
                 mbar_wait(bar(BAR_A_FULL + st), a_phase);
-                for (int s = 0; s < KS; ++s, ++unit) {
-                    if ((unit & 1u) != acc) continue;
+                // units alternate between the two accumulator stages: this warp takes every second one
+                const int s_first = (int)((unit & 1u) ^ acc);
+                unit += (uint32_t)KS;
+                for (int s = s_first; s < KS; s += 2) {
                     const int m = g * KS + s;
                     const uint8_t* atile = gbase + sp.a_off + st * sp.a_stage_bytes +
                                            (uint32_t)(s * nchunk) * sp.a_chunk_bytes;
                     // ||x_m||^2 with the SIMT kernel's sequential FMA chain, from the swizzled A tile
                     // (upper-half warp only: the lower-half warp of the pair does the bookkeeping)
                     float xn = 0.f;
-                    if (hf == 1 && !(p.debug & 4)) {
+                    if (hf == 1 && !(dbg & 4)) {
                         for (int c = 0; c < nchunk; ++c) {
 #pragma unroll
                             for (int u = 0; u < 8; ++u) {
@@ -726,8 +732,9 @@ __global__ void __launch_bounds__(THREADS, 1)
                     float v[64];
                     // pass 1: minimum of this warp's 128 columns (two 64-column TMEM loads)
                     float mn = __int_as_float(0x7f800000);
-#pragma unroll 1
-                    for (int cb = 0; cb < ((p.debug & 8) ? 0 : 2); ++cb) {
+#pragma unroll
+                    for (int cb = 0; cb < 2; ++cb) {
+                        if (dbg & 8) break;
                         tmem_ld64(taddr + cb * 64, v);
                         float t[22];
 #pragma unroll
@@ -755,22 +762,23 @@ __global__ void __launch_bounds__(THREADS, 1)
                     // pass 2: one packed integer accumulator per candidate flag:
                     //   bits [0,8) count, [8,17) sum of j, [17,32) sum of j^2  (j relative to this half;
                     //   the upper fields are exact whenever the count is <= 2, which is all that reads them)
-                    uint32_t ia = 0, ib = 0;
-                    if (p.debug & 1) { ia = 1; } else {
+                    uint32_t ia[4] = {0, 0, 0, 0};
+                    if (dbg & 1) { ia[0] = 1; } else {
                     tmem_ld64(taddr, v);
-                    flag_chunk<0>(v, thr, one, ia, ib);
+                    flag_chunk<0>(v, thr, one, ia);
                     tmem_ld64(taddr + 64, v);
-                    flag_chunk<1>(v, thr, one, ia, ib);
+                    flag_chunk<1>(v, thr, one, ia);
                     }
+                    const uint32_t isum = (ia[0] + ia[1]) + (ia[2] + ia[3]);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar(BAR_T_EMPTY + acc));
                     t_phase ^= 1;
                     // combine the halves: the upper-half warp hands its accumulator over and moves on
-                    if (hf == 1) xch[96 + lane] = __uint_as_float(ia + ib);
+                    if (hf == 1) xch[96 + lane] = __uint_as_float(isum);
                     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
                     if (hf == 1) continue;
-                    const uint32_t plo = ia + ib, phi = __float_as_uint(xch[96 + lane]);
+                    const uint32_t plo = isum, phi = __float_as_uint(xch[96 + lane]);
                     const int cnt_lo = plo & 0xFF, cnt_hi = phi & 0xFF;
                     const int cnt = cnt_lo + cnt_hi;
                     // 1 candidate: it is the exact argmin. 2: provisional code = lower index, the other goes
@@ -780,7 +788,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                     int code = 0, second = 0;
                     bool multi = false;
                     if (live) {
-                        if (cnt == 1 || (p.debug & 2)) {
+                        if (cnt == 1 || (dbg & 2)) {
                             code = cnt_lo ? (int)((plo >> 8) & 0x1FF) : 128 + (int)((phi >> 8) & 0x1FF);
                         } else if (cnt == 2) {
                             multi = true;
@@ -1012,8 +1020,9 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     }
     int grid = (int)(p.nitems < sms ? p.nitems : sms);
     const size_t smem = ts.sp.total + 1024;
-    VQ_CUDA(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    assign_tc_kernel<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
+    auto kern = p.debug ? assign_tc_kernel<true> : assign_tc_kernel<false>;
+    VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
     VQ_LAUNCH_CHECK();
     {
         int64_t pg = ((p.n * (int64_t)M + 15) / 16 + PF_THREADS - 1) / PF_THREADS;
