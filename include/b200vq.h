@@ -232,6 +232,42 @@ int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D, const uint3
                              float* out_vals, uint32_t* out_ids, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* ------------------------------------------------ SAQ engine (CAQ) path ---
+ * The reference's C++ engine external/saq, reached through SaqEngineAdapter
+ * (src/haag_vq/benchmarks/quantizer_adapters.py:113-135): IVF(n, D, K=1).fit / decompress.
+ *
+ * b200vq_saq_plan_dp: HOST function (no device work). Joint segmentation + bit allocation,
+ * SaqDataMaker::dynamic_programming (external/saq/src/quantization_plan.cpp:144-255):
+ * variance (d_pad) fp32 on the host, d_pad % 64 == 0; writes up to d_pad/64 (length, bits)
+ * pairs and their count.
+ *
+ * b200vq_caq_encode_t: CAQEncoder::encode_and_fac for every row of one segment
+ * (external/saq/include/saq/caq_encoder.h:170-261, code_adjustment :67-140; driven by
+ * quantizer.h:84-102). oT is the TRANSPOSED rotated segment, element (j, row) at
+ * oT[j*ld + row]; c_rot (len, may be NULL) is subtracted first (quantizer.h:66-72).
+ * codesT (len, ldc) uint16 receives the integer codes, also transposed; l2norm / rescale /
+ * error are the stored factors (o_l2norm, fac_rescale after rescale_vmx_to1, fac_error),
+ * mse = recon_mse, cosv = norm_ip_o_oa. Codes are bit-identical to the CPU order of
+ * operations (fp64 state, no contraction); rd_lmt = 6 and adj_eps = 1e-8 are the engine's
+ * defaults (config.h:17-18).
+ *
+ * b200vq_caq_pack_t: codesT -> packed (n, len*bits/8) MSB-first bit string (the HBM-resident
+ * form; the engine's short/long AVX-512 layouts, cluster_packer.h:62-142, are not kept).
+ *
+ * b200vq_caq_decode: per-segment dequantisation of IVF::decompress
+ * (external/saq/src/ivf_index.cpp:296-338) for rows ids[0..m) (NULL = 0..m-1):
+ * mode 0: out = ((code+0.5)*2/2^bits - 1) * l2norm/|.|  (before the P^T un-rotation);
+ * mode 1: out = code as fp32 (operand of the estimator, caq_estimator.h:254-283). */
+int b200vq_saq_plan_dp(const float* variance, int d_pad, float avg_bits, int* seg_len, int* seg_bits,
+                       int* n_segments);
+int b200vq_caq_encode_t(const float* oT, int64_t n, int64_t ld, int len, const float* c_rot, int bits,
+                        int rd_lmt, float adj_eps, uint16_t* codesT, int64_t ldc, float* l2norm,
+                        float* rescale, float* error, float* mse, float* cosv, void* stream);
+int b200vq_caq_pack_t(const uint16_t* codesT, int64_t n, int64_t ldc, int len, int bits, uint8_t* packed,
+                      void* stream);
+int b200vq_caq_decode(const uint8_t* packed, int64_t n_total, const int64_t* ids, int64_t m, int len,
+                      int bits, const float* l2norm, int mode, float* out, int64_t ldo, void* stream);
+
 /* ------------------------------------------------------------ utilities ---
  * Deterministic synthetic rows for throughput runs (Philox-4x32-10 keyed by
  * (seed, global row, column/4); anisotropic N(0,1)*scale[col], optional row

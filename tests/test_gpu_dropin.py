@@ -43,7 +43,9 @@ def test_registry_errors_and_constants():
     with pytest.raises(ValueError):
         mr.build_quantizer("nope", 4.0, 48)
     with pytest.raises(NotImplementedError):
-        mr.build_quantizer("saq_paper", 4.0, 48)
+        mr.build_quantizer("ours", 4.0, 48)          # greedy allocation + derived codebooks: SURVEY §8f
+    from haag_vq.benchmarks.quantizer_adapters import SaqEngineAdapter
+    assert isinstance(mr.build_quantizer("saq_paper", 4.0, 48), SaqEngineAdapter)
 
 
 def test_adapter_code_bytes_and_sq_mse():

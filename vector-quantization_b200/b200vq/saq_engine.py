@@ -1,0 +1,267 @@
+"""Host side of the SAQ engine path: `saq.IVF(n, D, K=1, cfg).fit(X, apply_pca, 1, seed, threads)`
+and `.decompress(ids)` as driven by SaqEngineAdapter (reference
+src/haag_vq/benchmarks/quantizer_adapters.py:113-135), plus the engine's accurate estimator.
+
+Pipeline (external/saq/src/ivf_index.cpp:186-243, saq_quantizer.h:49-83, quantizer.h:56-104):
+  PCA (covariance GEMM on the device, fp64 eigh) -> K = 1 "k-means" centroid (a seed row, see
+  kmeans1_row) -> DP plan on the PCA variances (b200vq_saq_plan_dp, host) -> per segment:
+  rotate by P_s, subtract the rotated centroid, CAQ-encode every row (b200vq_caq_encode_t),
+  bit-pack (b200vq_caq_pack_t). Codes stay in HBM segment by segment as MSB-first bit strings
+  with three fp32 factors per (row, segment).
+
+The GEMMs (PCA projection, per-segment rotation, un-rotation) are plain library SGEMMs in
+strict fp32; everything per-row runs in libb200vq.so. There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check
+from .ops import _stream, require_cuda
+
+BLK = 64
+
+
+def pad64(d: int) -> int:
+    return (d + BLK - 1) // BLK * BLK
+
+
+def _mm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        return torch.matmul(a, b)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+
+
+def mt19937_first(seed: int) -> int:
+    """First 32-bit output of std::mt19937(seed) (kmeans_eigen.cpp:20)."""
+    state = [seed & 0xFFFFFFFF]
+    for i in range(1, 624):
+        prev = state[-1]
+        state.append((1812433253 * (prev ^ (prev >> 30)) + i) & 0xFFFFFFFF)
+    y = (state[0] & 0x80000000) | (state[1] & 0x7FFFFFFF)
+    x = state[397] ^ (y >> 1) ^ (0x9908B0DF if (y & 1) else 0)
+    x ^= x >> 11
+    x ^= (x << 7) & 0x9D2C5680
+    x ^= (x << 15) & 0xEFC60000
+    x ^= x >> 18
+    return x & 0xFFFFFFFF
+
+
+def kmeans1_row(n: int, seed: int) -> int:
+    """With K = 1 the engine's Lloyd loop (kmeans_eigen.cpp:40-56) exits before its first update
+    (every assignment already is 0), so the centroid is the row drawn by
+    uniform_int_distribution<int>(0, n-1) from mt19937(seed): libstdc++'s multiply-shift."""
+    prod = mt19937_first(seed) * n
+    if (prod & 0xFFFFFFFF) < (((1 << 32) - n) % n):
+        raise NotImplementedError("first draw rejected; use another seed")
+    return prod >> 32
+
+
+def plan_dp(variance: np.ndarray, avg_bits: float) -> List[Tuple[int, int]]:
+    var = np.ascontiguousarray(variance, dtype=np.float32)
+    d_pad = int(var.shape[0])
+    cap = d_pad // BLK + 1
+    seg_len = np.zeros(cap, dtype=np.int32)
+    seg_bits = np.zeros(cap, dtype=np.int32)
+    ns = C.c_int(0)
+    check(_lib.load().b200vq_saq_plan_dp(var.ctypes.data, d_pad, C.c_float(avg_bits), seg_len.ctypes.data,
+                                         seg_bits.ctypes.data, C.addressof(ns)), "saq_plan_dp")
+    return [(int(seg_len[i]), int(seg_bits[i])) for i in range(ns.value)]
+
+
+def equal_segmentation(d_pad: int, avg_bits: float, num_segs: int) -> List[Tuple[int, int]]:
+    """quantization_plan.cpp:125-138."""
+    plan, d = [], 0
+    for i in range(num_segs):
+        if d >= d_pad:
+            break
+        t = pad64((d_pad - d) // (num_segs - i))
+        plan.append((t, int(avg_bits)))
+        d += t
+    return plan
+
+
+def caq_encode_t(oT: torch.Tensor, bits: int, c_rot: Optional[torch.Tensor] = None, rd_lmt: int = 6,
+                 adj_eps: float = 1e-8):
+    """oT (len, n) fp32 on the device (row stride >= n). Returns codesT (len, n) uint16 and the five
+    (n,) fp32 outputs (l2norm, rescale, error, mse, cos)."""
+    require_cuda()
+    ln, n = oT.shape
+    if oT.stride(1) != 1:
+        raise ValueError("caq_encode_t: oT must be row-major (len, n)")
+    codesT = torch.empty((ln, n), dtype=torch.int16, device=oT.device)
+    outs = [torch.empty((n,), dtype=torch.float32, device=oT.device) for _ in range(5)]
+    check(_lib.load().b200vq_caq_encode_t(oT.data_ptr(), n, oT.stride(0), ln,
+                                          c_rot.data_ptr() if c_rot is not None else None, bits, rd_lmt,
+                                          C.c_float(adj_eps), codesT.data_ptr(), n,
+                                          *[o.data_ptr() for o in outs], _stream()), "caq_encode_t")
+    return codesT, outs
+
+
+def caq_pack_t(codesT: torch.Tensor, bits: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    ln, n = codesT.shape
+    if out is None:
+        out = torch.empty((n, ln * bits // 8), dtype=torch.uint8, device=codesT.device)
+    check(_lib.load().b200vq_caq_pack_t(codesT.data_ptr(), n, codesT.stride(0), ln, bits, out.data_ptr(),
+                                        _stream()), "caq_pack_t")
+    return out
+
+
+def caq_decode(packed: torch.Tensor, ln: int, bits: int, l2norm: Optional[torch.Tensor],
+               ids: Optional[torch.Tensor] = None, mode: int = 0) -> torch.Tensor:
+    n_total = packed.shape[0]
+    m = n_total if ids is None else int(ids.shape[0])
+    out = torch.empty((m, ln), dtype=torch.float32, device=packed.device)
+    check(_lib.load().b200vq_caq_decode(packed.data_ptr(), n_total, ids.data_ptr() if ids is not None else None, m,
+                                        ln, bits, l2norm.data_ptr() if l2norm is not None else None, mode,
+                                        out.data_ptr(), ln, _stream()), "caq_decode")
+    return out
+
+
+class SaqEngine:
+    """Device-resident single-cluster SAQ index (the K = 1 configuration SaqEngineAdapter uses)."""
+
+    def __init__(self, avg_bits: float, apply_pca: bool = True, seed: int = 0, rot_seed: int = 20240607,
+                 rd_lmt: int = 6, adj_eps: float = 1e-8, seg_eqseg: int = 0, batch_rows: int = 1 << 17):
+        self.avg_bits, self.apply_pca, self.seed, self.rot_seed = float(avg_bits), bool(apply_pca), seed, rot_seed
+        self.rd_lmt, self.adj_eps, self.seg_eqseg, self.batch_rows = rd_lmt, adj_eps, seg_eqseg, batch_rows
+        self.n = self.D = self.d_pad = 0
+        self.plan: List[Tuple[int, int]] = []
+        self.segs: list = []
+
+    # ---- training state
+    def _pca(self, X: torch.Tensor):
+        n, D = X.shape
+        mean = X.mean(dim=0)
+        cov = torch.zeros((D, D), dtype=torch.float32, device=X.device)
+        for s in range(0, n, self.batch_rows):
+            xc = X[s:s + self.batch_rows] - mean
+            cov += _mm(xc.t(), xc)
+        evals, evecs = torch.linalg.eigh(cov.double() / float(n - 1))
+        return mean, evecs.flip(1).float().contiguous(), evals.flip(0).clamp_min(0).float()
+
+    def _train(self, X: torch.Tensor, state: Optional[dict]):
+        dev = X.device
+        n, D = X.shape
+        if state is not None:
+            self.mean = torch.as_tensor(state["mean"], device=dev)
+            self.rot = torch.as_tensor(state["rot"], device=dev)
+            self.var = torch.as_tensor(state["var"], device=dev)
+            self.cent_row = int(state["cent_row"])
+            self.plan = [(int(a), int(b)) for a, b in state["plan"]]
+            self.P = [torch.as_tensor(p, device=dev) for p in state["P"]]
+            return
+        if self.apply_pca:
+            self.mean, self.rot, self.var = self._pca(X)
+        else:
+            self.mean = torch.zeros(D, device=dev)
+            self.rot = torch.eye(D, device=dev)
+            self.var = torch.ones(D, device=dev)
+        self.cent_row = kmeans1_row(n, self.seed)
+        var_pad = np.zeros(self.d_pad, np.float32)
+        var_pad[:D] = self.var.cpu().numpy()
+        self.plan = (equal_segmentation(self.d_pad, self.avg_bits, self.seg_eqseg) if self.seg_eqseg > 0
+                     else plan_dp(var_pad, self.avg_bits))
+        g = torch.Generator(device="cpu").manual_seed(self.rot_seed)
+        self.P = []
+        for ln, _ in self.plan:   # P = Q^T of a QR of a Gaussian matrix (rotator.h:43-48)
+            Q, _r = torch.linalg.qr(torch.randn((ln, ln), generator=g, dtype=torch.float64))
+            self.P.append(Q.t().float().contiguous().to(dev))
+
+    def _project(self, Xb: torch.Tensor) -> torch.Tensor:
+        Xp = _mm(Xb - self.mean, self.rot) if self.apply_pca else Xb
+        if self.d_pad != self.D:
+            Xp = torch.nn.functional.pad(Xp, (0, self.d_pad - self.D))
+        return Xp
+
+    # ---- fit
+    def fit(self, X: torch.Tensor, state: Optional[dict] = None) -> "SaqEngine":
+        require_cuda()
+        if X.dtype != torch.float32 or X.dim() != 2 or not X.is_cuda:
+            raise ValueError("SaqEngine.fit expects a float32 (n, D) CUDA tensor")
+        n, D = X.shape
+        self.n, self.D, self.d_pad = n, D, pad64(D)
+        self._train(X, state)
+        dev = X.device
+        cen = self._project(X[self.cent_row:self.cent_row + 1])[0]
+        self.centroid = cen
+        self.segs, off = [], 0
+        for (ln, bits), P in zip(self.plan, self.P):
+            c_rot = _mm(cen[off:off + ln].unsqueeze(0), P)[0].contiguous()
+            self.segs.append(dict(len=ln, bits=bits, off=off, c_rot=c_rot,
+                                  packed=(torch.empty((n, ln * bits // 8), dtype=torch.uint8, device=dev)
+                                          if bits else None),
+                                  l2norm=torch.empty(n, device=dev), rescale=torch.empty(n, device=dev),
+                                  error=torch.empty(n, device=dev), mse=torch.empty(n, device=dev),
+                                  cos=torch.empty(n, device=dev)))
+            off += ln
+        for s in range(0, n, self.batch_rows):
+            e = min(n, s + self.batch_rows)
+            Xp = self._project(X[s:e])
+            for seg, P in zip(self.segs, self.P):
+                ln, bits, o0 = seg["len"], seg["bits"], seg["off"]
+                oT = _mm(P.t(), Xp[:, o0:o0 + ln].t())          # (len, rows): rotated segment, transposed
+                codesT, outs = caq_encode_t(oT, bits, seg["c_rot"], self.rd_lmt, self.adj_eps)
+                for key, o in zip(("l2norm", "rescale", "error", "mse", "cos"), outs):
+                    seg[key][s:e] = o
+                if bits:
+                    caq_pack_t(codesT, bits, out=seg["packed"][s:e])
+        return self
+
+    # ---- queries on the fitted index
+    def recon_mse(self) -> float:
+        """Mean over rows of sum over segments of recon_mse * len / d_pad (engine metric)."""
+        tot = sum((seg["mse"].double().sum().item() * seg["len"]) for seg in self.segs)
+        return tot / (self.n * self.d_pad)
+
+    def stored_bytes(self) -> int:
+        return sum((seg["packed"].numel() if seg["packed"] is not None else 0) + 12 * self.n for seg in self.segs)
+
+    def reconstruct(self, ids: torch.Tensor) -> torch.Tensor:
+        """IVF::decompress (ivf_index.cpp:245-374): ids int64 on the device -> (m, D) fp32."""
+        m = int(ids.shape[0])
+        o_rot = torch.empty((m, self.d_pad), dtype=torch.float32, device=ids.device)
+        for seg, P in zip(self.segs, self.P):
+            ln, bits, off = seg["len"], seg["bits"], seg["off"]
+            cen_unrot = _mm(seg["c_rot"].unsqueeze(0), P.t())[0]
+            if bits == 0:
+                o_rot[:, off:off + ln] = cen_unrot
+            else:
+                oa = caq_decode(seg["packed"], ln, bits, seg["l2norm"], ids, mode=0)
+                o_rot[:, off:off + ln] = _mm(oa, P.t()) + cen_unrot
+        o_rot = o_rot[:, :self.D]
+        return (_mm(o_rot, self.rot.t()) + self.mean) if self.apply_pca else o_rot.contiguous()
+
+    def accurate_dist(self, Q: torch.Tensor, ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Engine estimator (caq_estimator.h:254-283, saq_estimator.h:183-190), squared L2:
+        sum_s |o_s|^2 + |q_s|^2 - 2 rescale_s <q_s, oa_s>, q_s = Q_pca[:, seg] P_s - c_rot_s."""
+        Qp = self._project(Q)
+        m = self.n if ids is None else int(ids.shape[0])
+        out = torch.zeros((Q.shape[0], m), dtype=torch.float32, device=Q.device)
+        for seg, P in zip(self.segs, self.P):
+            ln, bits, off = seg["len"], seg["bits"], seg["off"]
+            q = _mm(Qp[:, off:off + ln], P) - seg["c_rot"]
+            q2 = (q * q).sum(1)
+            l2 = seg["l2norm"] if ids is None else seg["l2norm"][ids]
+            o2 = l2 * l2
+            if bits == 0:
+                out += o2[None, :] + q2[:, None]
+                continue
+            delta = 2.0 / (1 << bits)
+            codes = caq_decode(seg["packed"], ln, bits, None, ids, mode=1)
+            ip = _mm(q, codes.t()) * delta + (-1.0 + delta / 2) * q.sum(1)[:, None]
+            rs = seg["rescale"] if ids is None else seg["rescale"][ids]
+            out += o2[None, :] + q2[:, None] - 2.0 * rs[None, :] * ip
+        return out
+
+    def export_state(self) -> dict:
+        return dict(mean=self.mean.cpu().numpy(), rot=self.rot.cpu().numpy(), var=self.var.cpu().numpy(),
+                    cent_row=self.cent_row, plan=list(self.plan), P=[p.cpu().numpy() for p in self.P])

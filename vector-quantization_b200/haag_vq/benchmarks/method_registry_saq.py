@@ -1,11 +1,11 @@
 """Registry for the SAQ-study methods outside the faiss family.
 
 Mirrors src/haag_vq/benchmarks/method_registry_saq.py:17-74 for the methods on
-the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)). The
-other names of SAQ_METHODS are the reference's C++-engine / per-dimension
-codebook studies (saq_paper, ours*, lvq, rankaware*, perdim_mse*), which
-SURVEY.md §8(f) ranks as "next"; they raise NotImplementedError here instead of
-silently falling back to anything.
+the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)) and
+``saq_paper`` -> SaqEngineAdapter(CAQ, DP allocation) (SURVEY.md §8 rows a9-a11,
+a16). The other names of SAQ_METHODS (ours*, lvq, rankaware*, perdim_mse*) are
+the greedy-allocation / per-dimension codebook studies SURVEY.md §8(f) ranks as
+"next"; they raise NotImplementedError here instead of silently falling back.
 """
 from __future__ import annotations
 
@@ -15,6 +15,12 @@ SAQ_METHODS = ("saq_paper", "ours", "ours_exact", "rabitq", "lvq",
 
 def build_saq_quantizer(method: str, bpd: float, D: int):
     b = int(round(bpd))
+    if method == "saq_paper":
+        import os
+        from haag_vq.benchmarks.quantizer_adapters import SaqEngineAdapter
+        # VQ_SAQ_APPLY_PCA=0 skips the internal PCA for already-rotated inputs (reference :24-27)
+        return SaqEngineAdapter(quant_type="CAQ", avg_bits=bpd, greedy=False, derive_codebooks=False,
+                                apply_pca=os.environ.get("VQ_SAQ_APPLY_PCA", "1") != "0")
     if method == "rabitq":
         from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
         from haag_vq.methods.extended_rabitq import ExtendedRaBitQuantizer

@@ -49,3 +49,56 @@ class FaissQuantizerAdapter:
         if self._codes is None:
             raise RuntimeError("FaissQuantizerAdapter.code_bytes() before fit()")
         return int(self._codes.nbytes) + self._n * NORM_SIDECHANNEL_BYTES
+
+
+class SaqEngineAdapter:
+    """The SAQ engine behind the Quantizer protocol: a single-cluster (K = 1) index whose
+    reconstruct() is the engine's decompress(ids).
+
+    Mirrors src/haag_vq/benchmarks/quantizer_adapters.py:62-135 (same constructor keywords, same
+    errors, same code_bytes formula). The engine itself (`saq.IVF(n, D, K, cfg).fit / .decompress`)
+    is b200vq.saq_engine.SaqEngine on the device. Built here: quant_type "CAQ" with the DP
+    allocator and the engine's default uniform codebook (method ``saq_paper``). The greedy
+    allocator and derived per-dimension codebooks (methods ``ours`` / ``ours_exact``) are
+    SURVEY.md §8(f) items and raise NotImplementedError - there is no fallback.
+    """
+
+    def __init__(self, *, quant_type: str = "CAQ", avg_bits: float = 4.0, greedy: bool = False,
+                 derive_codebooks: bool = False, exact_codebooks: bool = False, apply_pca: bool = True,
+                 K: int = 1, num_threads: int = 8, seed: int = 0, max_bits: int = 13) -> None:
+        if quant_type != "CAQ":
+            raise ValueError(f"SaqEngineAdapter: unsupported quant_type {quant_type!r} (CAQ only)")
+        if greedy or derive_codebooks or exact_codebooks:
+            raise NotImplementedError("greedy allocation / derived codebooks are not built on the B200 path yet "
+                                      "(SURVEY.md §8f); no fallback is provided")
+        if K != 1:
+            raise NotImplementedError("SaqEngineAdapter on the B200 path is the K = 1 (flat) configuration")
+        self._avg_bits = float(avg_bits)
+        self._apply_pca = apply_pca
+        self._K, self._num_threads, self._seed, self._max_bits = K, num_threads, seed, max_bits
+        self._index = None
+        self._n = 0
+        self._D = 0
+
+    def fit(self, X: np.ndarray) -> None:
+        import torch
+        from b200vq.saq_engine import SaqEngine
+        X = np.ascontiguousarray(X, dtype=np.float32)
+        self._n, self._D = X.shape
+        eng = SaqEngine(self._avg_bits, apply_pca=self._apply_pca, seed=self._seed)
+        eng.fit(torch.from_numpy(X).cuda())
+        self._index = eng
+
+    def reconstruct(self, ids: np.ndarray) -> np.ndarray:
+        if self._index is None:
+            raise RuntimeError("SaqEngineAdapter.reconstruct() before fit()")
+        import torch
+        ids = np.ascontiguousarray(ids, dtype=np.uint32)
+        out = self._index.reconstruct(torch.from_numpy(ids.astype(np.int64)).cuda())
+        return np.asarray(out.cpu().numpy(), dtype=np.float32)
+
+    def code_bytes(self) -> int:
+        if self._index is None:
+            raise RuntimeError("SaqEngineAdapter.code_bytes() before fit()")
+        code = int(self._n * self._D * self._avg_bits / 8.0)
+        return code + self._n * NORM_SIDECHANNEL_BYTES
