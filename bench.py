@@ -382,6 +382,15 @@ def run_b200(args):
     scan_gbs = scan_bytes / (knl / steps * 1e-3) / 1e9
     assign_tflops = 2.0 * D * KSUB * B / (enc / steps * 1e-3) / 1e12
     tf32_peak = peaks["bf16_tflops_sustained"] / 2.0
+    # DRAM bytes of one scan launch from the committed ncu --set full capture, valid for that launch shape only
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            rec = json.load(f).get("adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel")
+        if rec and (rec["rows"], rec["queries"], rec["M"]) == (n, nq, M):
+            traffic = rec["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        traffic = None
     line = {
         "metric": METRIC, "value": enc_vps, "unit": "vectors/s",
         "adc": {"value": adc_cps, "unit": "codes/s"},
@@ -391,7 +400,7 @@ def run_b200(args):
         "data": "synthetic", "config": dict(workload_config(args), assign_impl=impl, scan_layout=layout),
         "roofline": {"kernel": "adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel", "bound": "hbm",
                      "achieved": scan_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": scan_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks["source"],
+                     "frac": scan_gbs / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peaks["source"],
                      "algorithmic_bytes_per_launch": scan_bytes},
         "roofline_assign": {"kernel": "pq_assign_tc_kernel" if impl == "tc" else "pq_assign_simt_kernel",
                             "bound": "tensor", "achieved": assign_tflops, "peak": tf32_peak, "unit": "TFLOP/s",

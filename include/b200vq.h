@@ -129,8 +129,13 @@ int b200vq_adc_scan_topk(const uint8_t* codes, int64_t n, int M, int ksub, const
                          void* scratch, size_t scratch_bytes, void* stream);
 
 /* Same scan over the conflict-free "scan layout" produced by
- * b200vq_pq_codes_to_scan_layout (blocks of 32 rows, byte s of lane i holds
- * sub-quantizer (i+s) mod 32 of the 32-wide group). Requires M % 32 == 0. */
+ * b200vq_pq_codes_to_scan_layout: blocks of 32 rows x groups of 32 sub-quantizers
+ * (1 KiB each, row block major). Inside a block, lane i = row i of the block owns 32
+ * bytes, byte s = its code for sub-quantizer (i+s) mod 32 of the group (so at step s
+ * the 32 lanes address 32 distinct table columns = 32 distinct banks); the bytes are
+ * stored as two 16-byte halves, each half contiguous across the 32 lanes:
+ * out[block*1024 + (s/16)*512 + i*16 + s%16]. Requires M % 32 == 0, M <= 96; out has
+ * ceil(n/32)*32*M bytes (rows past n are padding). */
 int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, int M, uint8_t* out,
                                    void* stream);
 int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksub,

@@ -14,25 +14,29 @@
 // TF32 truncates both operands to 10 mantissa bits, so the argmin of v is only a
 // SCREEN: |v - (1-2^-10) v_true| <= E with E = 2^-9 * 1.02 * |x_m| * max_j|c_mj| + slack
 // (the norm term is pre-scaled by 1-2^-10 to centre the one-sided truncation error).
-// The epilogue (one TMEM lane = one row) makes two passes over the accumulator:
-//   pass 1   row minimum m1 with 3-input FMNMX              (0.5 ALU op / value)
-//   pass 2   f = (v <= m1 + 2E); acc1 += f*(4096+j); acc2 += f*j*j
-//            (FSET.BF on the ALU pipe, two FFMA-immediates on the FMA pipe)
-// which yields the candidate count and, for 1 or 2 candidates, their indices with
-// no branch per value. One candidate: it IS the exact argmin. Two: both are
-// re-evaluated with the SIMT kernel's exact fp32 arithmetic (sequential FMA chain,
-// (||x||^2 + ||c||^2) - 2 x.c, clamp at 0, lower index wins ties). Three or more
-// (< 1 % of pairs on the benchmark data): the pair is appended to a fix-up list and a
-// second small kernel runs the exact 256-way scan for it. The result is therefore
-// bit-identical to b200vq_pq_assign_f32 whenever E bounds the screen error.
+// The epilogue (one TMEM lane = one row, 128 columns per warp) makes two passes over the accumulator:
+//   pass 1   row minimum with 3-input FMNMX                  (0.5 ALU op / value); the two warps of a
+//            pair exchange their minima and 2E through shared memory (64-thread named barrier)
+//   pass 2   per value FSETP + predicated IMAD-immediate on four independent chains:
+//            acc += 1 | j << 8 | j*j << 17   (count, sum j, sum j^2 of the candidates v <= min + 2E)
+// which yields the candidate count and, for 1 or 2 candidates, their indices with no branch per
+// value. One candidate: it IS the exact argmin. Two: the lower index is stored as the provisional
+// code, the other in the byte side array cand2, and pair_fixup_kernel evaluates both with the SIMT
+// kernel's exact fp32 arithmetic (sequential FMA chain, (||x||^2 + ||c||^2) - 2 x.c, clamp at 0,
+// lower index wins ties). Three or more, or none (NaN rows) (0.3 % of pairs on the benchmark data):
+// marker (255, 255); pair_fixup_kernel appends the pair to a per-sub-quantizer list and
+// fixup_kernel runs the exact 256-way scan for it. The result is bit-identical to
+// b200vq_pq_assign_f32 whenever E bounds the screen error. Nothing in the main kernel waits on
+// global memory.
 //
-// Data movement: persistent CTAs, one per SM. A CTA keeps the (-2 c) tiles of KS
-// consecutive sub-quantizers resident in shared memory (TMA, hardware swizzle) and
-// streams 128-row slices of x (only the KS*dsub columns it needs) through an
-// NST-deep TMA ring, so x is read from HBM exactly once and the centroids are not
-// re-read per tile. Warp roles: 0 = TMA producer, 1 = MMA issuer (owns TMEM),
-// 2..5 = epilogue (TMEM lanes 32*(warp%4)..). The two 256-column accumulators
-// double-buffer MMA against the epilogue.
+// Data movement: persistent CTAs, one per SM. A CTA keeps the (-2 c) tiles of KS consecutive
+// sub-quantizers resident in shared memory (TMA, hardware swizzle) and streams 128-row slices of
+// x (only the KS*dsub columns it needs) through an NST-deep TMA ring, so x is read from HBM
+// exactly once and the centroids are not re-read per tile. Warp roles: 0 = TMA producer,
+// 1 = MMA issuer (owns TMEM), 2..17 = epilogue (accumulator stage x TMEM lane quarter x column
+// half). The two 256-column accumulators double-buffer MMA against the epilogue.
+// Launch sequence: memset(cand2) -> prepare_kernel -> assign_tc_kernel -> pair_fixup_kernel ->
+// fixup_kernel, all on the caller's stream.
 #include <cuda.h>
 #include <stdlib.h>
 
