@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--nq", type=int, default=NQ)
     ap.add_argument("--assign-impl", default="auto", choices=["auto", "simt", "tc"])
     ap.add_argument("--scan-layout", default="auto", choices=["auto", "rows", "rot"])
+    ap.add_argument("--scan-impl", default="auto", choices=["auto", "exact", "screen"],
+                    help="screen = four-queries-per-lookup screened scan (scan layout only), same results")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -318,9 +320,14 @@ def run_b200(args):
         layout = "rows"
     del lut0
 
+    screen = layout == "rot" and args.scan_impl in ("auto", "screen")
+    if args.scan_impl == "screen" and not screen:
+        raise SystemExit("--scan-impl screen needs the scan layout (M % 32 == 0)")
+    q_tile = 4 if screen else 1
+
     def scan(lut):
         if layout == "rot":
-            return ops.adc_scan_topk(codes_rot, lut, K, "l2", n=n, rot=True)
+            return ops.adc_scan_topk(codes_rot, lut, K, "l2", n=n, rot=True, screen=screen)
         return ops.adc_scan_topk(codes, lut, K, "l2")
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -378,7 +385,10 @@ def run_b200(args):
     adc_cps = float(n) * world * nq * steps / (scn * 1e-3)
 
     # roofline: algorithmic bytes per launch / average launch duration (per GPU)
-    scan_bytes = float(n) * M * nq                     # rows x M bytes per query pass, Q_tile = 1
+    # rows x M code bytes per query-tile pass (N * M * ceil(Q / Q_tile)); the launch duration is
+    # the whole scan call (for the screened scan: sample + prepare + screen + finish + gated fallback)
+    scan_bytes = float(n) * M * ((nq + q_tile - 1) // q_tile)
+    scan_kernel = "adc_screen_kernel" if screen else ("adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel")
     scan_gbs = scan_bytes / (knl / steps * 1e-3) / 1e9
     assign_tflops = 2.0 * D * KSUB * B / (enc / steps * 1e-3) / 1e12
     tf32_peak = peaks["bf16_tflops_sustained"] / 2.0
@@ -386,7 +396,7 @@ def run_b200(args):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            rec = json.load(f).get("adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel")
+            rec = json.load(f).get(scan_kernel)
         if rec and (rec["rows"], rec["queries"], rec["M"]) == (n, nq, M):
             traffic = rec["dram_bytes_per_launch"]
     except (OSError, ValueError, KeyError):
@@ -397,11 +407,13 @@ def run_b200(args):
         "n_gpus": world, "steps": steps, "warmup": max(3, args.warmup), "ms_per_step": tot / steps,
         "ms_encode_per_step": enc / steps, "ms_scan_per_step": scn / steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": dict(workload_config(args), assign_impl=impl, scan_layout=layout),
-        "roofline": {"kernel": "adc_scan_rot_kernel" if layout == "rot" else "adc_scan_kernel", "bound": "hbm",
+        "data": "synthetic", "config": dict(workload_config(args), assign_impl=impl, scan_layout=layout,
+                                             scan_impl="screen" if screen else "exact", scan_query_tile=q_tile),
+        "roofline": {"kernel": scan_kernel, "bound": "hbm",
                      "achieved": scan_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": scan_gbs / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peaks["source"],
-                     "algorithmic_bytes_per_launch": scan_bytes},
+                     "algorithmic_bytes_per_launch": scan_bytes, "query_tile": q_tile,
+                     "table_lookups_per_s": float(n) * M * nq / (knl / steps * 1e-3)},
         "roofline_assign": {"kernel": "pq_assign_tc_kernel" if impl == "tc" else "pq_assign_simt_kernel",
                             "bound": "tensor", "achieved": assign_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
                             "frac": assign_tflops / tf32_peak,

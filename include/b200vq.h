@@ -143,6 +143,19 @@ int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksu
                              uint32_t* out_ids, void* scratch, size_t scratch_bytes,
                              void* stream);
 
+/* Screened scan over the scan layout: the SAME result as b200vq_adc_scan_topk_rot (exact fp32
+ * scores, (value, id) order), obtained faster for large n. The table entries of four queries are
+ * quantised to 6 bits and packed into one 32-bit word, so one shared-memory lookup serves four
+ * queries; the integer sum is a rigorous lower bound of the score and only rows that can still
+ * reach the top-k (threshold = exact k-th best of a 65 536-row sample) are re-evaluated exactly.
+ * Queries whose survivor list overflows are re-done by the exact kernel. Falls back to the exact
+ * scan for n < 524 288, nq < 4 or k > 64. Scratch: b200vq_adc_scan_screen_scratch_bytes. */
+size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq, int k);
+int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, int M, int ksub,
+                                const float* lut, int nq, int metric, int k, float* out_vals,
+                                uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                                void* stream);
+
 /* ---------------------------------------------------- exact flat search ---
  * Exact top-k of queries against raw fp32 rows (faiss IndexFlatL2/IndexFlatIP.search:
  * src/haag_vq/benchmarks/exact_search.py:44-51,72-77, search_bench.py:42-56).

@@ -1,0 +1,87 @@
+"""Screened ADC scan (b200vq_adc_scan_topk_screen) == exact scan, through the C ABI.
+
+The screen is a rigorous filter, so the ids must be IDENTICAL to the exact kernels' and the values
+equal up to the fp32 summation order (the scan-layout kernel adds the table entries in a
+lane-rotated order, the screen's exact finish in increasing sub-quantizer order)."""
+import numpy as np
+import pytest
+
+from oracle import pq as opq
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def T():
+    import torch
+    import b200vq
+    from b200vq import ops
+    b200vq.load()
+
+    class NS:
+        pass
+    ns = NS()
+    ns.torch, ns.ops = torch, ops
+    return ns
+
+
+def _case(T, n, M, nq, seed, lut_kind="uniform"):
+    g = T.torch.Generator(device="cuda").manual_seed(seed)
+    codes = T.torch.randint(0, 256, (n, M), dtype=T.torch.uint8, device="cuda", generator=g)
+    if lut_kind == "uniform":
+        lut = T.torch.rand((nq, M, 256), device="cuda", generator=g)
+    else:   # signed, wide dynamic range per sub-quantizer (inner-product-like tables)
+        lut = T.torch.randn((nq, M, 256), device="cuda", generator=g) * T.torch.logspace(-2, 1, M, device="cuda")[None, :, None]
+    return codes, lut.contiguous()
+
+
+@pytest.mark.parametrize("n,M,nq,k,metric,kind", [
+    (600_001, 32, 10, 10, "l2", "uniform"),
+    (600_001, 32, 10, 10, "ip", "signed"),
+    (540_000, 64, 5, 32, "l2", "signed"),
+    (524_288, 96, 4, 1, "ip", "uniform"),
+    (700_000, 32, 7, 64, "l2", "uniform"),
+])
+def test_screen_equals_exact_scan(T, n, M, nq, k, metric, kind):
+    codes, lut = _case(T, n, M, nq, seed=n % 1000 + M + k, lut_kind=kind)
+    rot = T.ops.pq_codes_to_scan_layout(codes)
+    v0, i0 = T.ops.adc_scan_topk(rot, lut, k, metric, n=n, rot=True)
+    v1, i1 = T.ops.adc_scan_topk(rot, lut, k, metric, n=n, rot=True, screen=True)
+    assert T.torch.equal(i0, i1)
+    assert T.torch.allclose(v0, v1, rtol=2e-6, atol=1e-6)
+    # and against the oracle on a few queries
+    sc = opq.adc_scores(codes.cpu().numpy(), lut[:2].cpu().numpy())
+    ov, oi = opq.topk_sorted(sc, k, opq.L2 if metric == "l2" else opq.IP)
+    assert np.array_equal(i1[:2].cpu().numpy().view(np.uint32), oi)
+
+
+def test_screen_planted_neighbours_and_small_inputs_fall_back(T):
+    n, M, nq, k = 650_000, 32, 8, 10
+    codes, lut = _case(T, n, M, nq, seed=3)
+    # plant rows that hit every table minimum (score far below everything else), inside and outside the sample
+    amin = lut.argmin(dim=2).to(T.torch.uint8)          # (nq, M)
+    for q in range(nq):
+        codes[100 + q] = amin[q]
+        codes[n - 1 - q] = amin[q]
+    rot = T.ops.pq_codes_to_scan_layout(codes)
+    v0, i0 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True)
+    v1, i1 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True, screen=True)
+    assert T.torch.equal(i0, i1)
+    assert all(int(i1[q, 0]) == 100 + q and int(i1[q, 1]) == n - 1 - q for q in range(nq))
+    small = rot[:32 * 1024 * M]
+    a = T.ops.adc_scan_topk(small, lut, k, "l2", n=32 * 1024, rot=True)
+    b = T.ops.adc_scan_topk(small, lut, k, "l2", n=32 * 1024, rot=True, screen=True)
+    assert T.torch.equal(a[1], b[1]) and T.torch.equal(a[0], b[0])
+
+
+def test_screen_overflow_goes_through_the_exact_fallback(T):
+    """Every row identical: every row survives the screen, the per-query lists overflow and the gated
+    exact kernels produce the result (ties broken by the lower id)."""
+    n, M, nq, k = 600_000, 32, 6, 10
+    codes = T.torch.full((n, M), 7, dtype=T.torch.uint8, device="cuda")
+    codes[::3, 5] = 9                      # two distinct scores only
+    _, lut = _case(T, 1, M, nq, seed=5)
+    rot = T.ops.pq_codes_to_scan_layout(codes)
+    v0, i0 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True)
+    v1, i1 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True, screen=True)
+    assert T.torch.equal(i0, i1) and T.torch.allclose(v0, v1, rtol=2e-6)

@@ -136,14 +136,17 @@ class PQCodec:
         return ops.adc_lut(queries, self.centroids, metric)
 
     def search(self, codes: torch.Tensor, queries: torch.Tensor, k: int, metric, n: int | None = None,
-               rot: bool = False, q_batch: int = 4096):
-        """ADC top-k over (n, M) codes. Returns (vals (nq,k) fp32, ids (nq,k) int32-as-uint32)."""
+               rot: bool = False, q_batch: int = 4096, screen: bool | None = None):
+        """ADC top-k over (n, M) codes. Returns (vals (nq,k) fp32, ids (nq,k) int32-as-uint32).
+        screen (scan layout only; default on): four-queries-per-lookup screened scan, same results."""
+        if screen is None:
+            screen = rot
         nq = queries.shape[0]
         vals = torch.empty((nq, k), dtype=torch.float32, device=queries.device)
         ids = torch.empty((nq, k), dtype=torch.int32, device=queries.device)
         for s in range(0, nq, q_batch):
             e = min(nq, s + q_batch)
             lut = self.luts(queries[s:e], metric)
-            v, i = ops.adc_scan_topk(codes, lut, k, metric, n=n, rot=rot)
+            v, i = ops.adc_scan_topk(codes, lut, k, metric, n=n, rot=rot, screen=bool(screen and rot))
             vals[s:e], ids[s:e] = v, i
         return vals, ids

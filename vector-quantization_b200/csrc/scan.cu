@@ -133,11 +133,14 @@ template <int CAP, int G>
 __global__ void __launch_bounds__(SCAN_THREADS)
     adc_scan_rot_kernel(const uint8_t* __restrict__ codes_rot, int64_t n,
                         const float* __restrict__ lut, int k, int64_t chunk_rows, int negate,
-                        uint64_t* __restrict__ part) {
+                        uint64_t* __restrict__ part, const uint32_t* __restrict__ gate = nullptr,
+                        uint32_t gate_cap = 0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int KSUB = 256;
     constexpr int M = G * 32;
     const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+    // gated launch (fallback of the screened scan): only queries whose candidate list overflowed
+    if (gate && gate[q] <= gate_cap) return;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     float* lut_s = reinterpret_cast<float*>(smem_raw);
     constexpr size_t lut_bytes = (size_t)G * KSUB * 64 * 4;
@@ -207,6 +210,10 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     }
     block_emit_topk<CAP>(tk, mbuf, n2, k, part + ((size_t)q * nchunks + chunk) * k);
 }
+
+}  // namespace b200vq
+#include "scan_screen.cuh"
+namespace b200vq {
 
 // ------------------------------------------------------------ row norms ---
 // One warp per row, lanes stride the row; fp32 partial chains + shuffle tree.
@@ -463,8 +470,9 @@ static size_t partial_bytes(int64_t n, int nq, int k, int nq_ctas) {
 
 template <int TILE>
 static int launch_merge(const uint64_t* part, int nq, int nparts, int k, int negate,
-                        float* out_vals, uint32_t* out_ids, cudaStream_t st) {
-    merge_partials_kernel<TILE><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids);
+                        float* out_vals, uint32_t* out_ids, cudaStream_t st, const uint32_t* gate = nullptr,
+                        uint32_t gate_cap = 0) {
+    merge_partials_kernel<TILE><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids, gate, gate_cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -551,7 +559,8 @@ extern "C" int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, i
 
 template <int CAP, int G>
 static int adc_scan_rot_launch_g(const uint8_t* codes_rot, int64_t n, const float* lut, int nq, int k,
-                                 int negate, uint64_t* part, const ScanPlan& p, cudaStream_t st) {
+                                 int negate, uint64_t* part, const ScanPlan& p, cudaStream_t st,
+                                 const uint32_t* gate = nullptr, uint32_t gate_cap = 0) {
     const int n2 = next_pow2(SCAN_WARPS * k);
     size_t smem = (size_t)G * 256 * 64 * 4 + (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
     VQ_CHECK_ARG(smem <= 227 * 1024, "adc_scan_topk_rot: M=%d needs %zu B of shared memory", G * 32, smem);
@@ -559,7 +568,7 @@ static int adc_scan_rot_launch_g(const uint8_t* codes_rot, int64_t n, const floa
                                  (int)smem));
     dim3 grid((unsigned)nq, (unsigned)p.nchunks);
     adc_scan_rot_kernel<CAP, G><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, lut, k, p.chunk_rows, negate,
-                                                                  part);
+                                                                  part, gate, gate_cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -567,11 +576,11 @@ static int adc_scan_rot_launch_g(const uint8_t* codes_rot, int64_t n, const floa
 template <int CAP>
 static int adc_scan_rot_launch(const uint8_t* codes_rot, int64_t n, int M, const float* lut, int nq,
                                int k, int negate, uint64_t* part, const ScanPlan& p,
-                               cudaStream_t st) {
+                               cudaStream_t st, const uint32_t* gate = nullptr, uint32_t gate_cap = 0) {
     switch (M / 32) {
-        case 1: return adc_scan_rot_launch_g<CAP, 1>(codes_rot, n, lut, nq, k, negate, part, p, st);
-        case 2: return adc_scan_rot_launch_g<CAP, 2>(codes_rot, n, lut, nq, k, negate, part, p, st);
-        default: return adc_scan_rot_launch_g<CAP, 3>(codes_rot, n, lut, nq, k, negate, part, p, st);
+        case 1: return adc_scan_rot_launch_g<CAP, 1>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
+        case 2: return adc_scan_rot_launch_g<CAP, 2>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
+        default: return adc_scan_rot_launch_g<CAP, 3>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
     }
 }
 
@@ -596,6 +605,136 @@ extern "C" int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int
                        : adc_scan_rot_launch<256>(codes_rot, n, M, lut, nq, k, negate, part, p, st);
     if (rc != B200VQ_OK) return rc;
     return launch_merge<2048>(part, nq, p.nchunks, k, negate, out_vals, out_ids, st);
+}
+
+// ---- screened scan: sample threshold -> packed 6-bit tables -> screen -> exact finish (+ gated fallback)
+struct ScreenPlan {
+    int64_t n_sample;
+    int ngroups;
+    uint32_t cap;
+    size_t off_vals, off_ids, off_part, off_qlut, off_thr, off_count, off_cand, total;
+};
+static ScreenPlan plan_screen(int64_t n, int M, int nq, int k) {
+    ScreenPlan s;
+    s.n_sample = SCREEN_SAMPLE;
+    s.ngroups = (nq + 3) / 4;
+    int64_t cap = n / 256;
+    if (cap < 4096) cap = 4096;
+    if (cap > (1 << 20)) cap = 1 << 20;
+    s.cap = (uint32_t)cap;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t o = 0;
+    s.off_vals = o; o = up(o + (size_t)nq * k * 4);
+    s.off_ids = o;  o = up(o + (size_t)nq * k * 4);
+    size_t part = partial_bytes(n, nq, k, nq);   // fallback partials; the sample's (smaller) alias them
+    size_t part_s = partial_bytes(s.n_sample, nq, k, nq);
+    s.off_part = o; o = up(o + (part > part_s ? part : part_s));
+    s.off_qlut = o; o = up(o + (size_t)s.ngroups * M * 256 * 4);
+    s.off_thr = o;  o = up(o + (size_t)s.ngroups * 4 * 4);
+    s.off_count = o; o = up(o + (size_t)s.ngroups * 4 * 4);
+    s.off_cand = o; o = up(o + (size_t)s.ngroups * 4 * s.cap * 4);
+    s.total = o;
+    return s;
+}
+static bool screen_applies(int64_t n, int nq, int k) { return n >= 8 * (int64_t)SCREEN_SAMPLE && nq >= 4 && k <= 64; }
+
+extern "C" size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq, int k) {
+    if (n < 0 || nq <= 0 || k <= 0 || M <= 0) return 0;
+    if (!screen_applies(n, nq, k)) return partial_bytes(n, nq, k, nq);
+    return plan_screen(n, M, nq, k).total;
+}
+
+template <int G>
+static int screen_launch_g(const uint8_t* codes_rot, int64_t n, const uint32_t* qlut4, const int* thr,
+                           const ScanPlan& p, int ngroups, uint32_t* cand, uint32_t* count, uint32_t cap,
+                           cudaStream_t st) {
+    const size_t smem = (size_t)G * 256 * 64 * 4;
+    VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)ngroups, (unsigned)p.nchunks);
+    adc_screen_kernel<G><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows, cand, count, cap);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+template <int CAP>
+static int screen_finish_launch(const uint8_t* codes_rot, int M, const float* lut, const uint32_t* cand,
+                                const uint32_t* count, uint32_t cap, int nq, int k, int negate, float* out_vals,
+                                uint32_t* out_ids, cudaStream_t st) {
+    const int n2 = next_pow2(SCAN_WARPS * k);
+    const size_t smem = (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
+    VQ_CUDA(cudaFuncSetAttribute(screen_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    screen_finish_kernel<CAP><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, M, lut, cand, count, cap, k, negate,
+                                                             out_vals, out_ids);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, int M, int ksub, const float* lut,
+                                           int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                                           void* scratch, size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(codes_rot && lut && out_vals && out_ids, "adc_scan_topk_screen: null pointer");
+    VQ_CHECK_ARG(ksub == 256 && M > 0 && M % 32 == 0 && M <= 96,
+                 "adc_scan_topk_screen: needs ksub == 256 and M in {32,64,96} (M=%d ksub=%d)", M, ksub);
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && nq >= 0, "adc_scan_topk_screen: bad n/nq");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "adc_scan_topk_screen: k must be in [1,128], got %d", k);
+    if (nq == 0) return B200VQ_OK;
+    if (!screen_applies(n, nq, k))   // small problems: the exact kernel is already launch-bound
+        return b200vq_adc_scan_topk_rot(codes_rot, n, M, ksub, lut, nq, metric, k, out_vals, out_ids, scratch,
+                                        scratch_bytes, stream);
+    const ScreenPlan sp = plan_screen(n, M, nq, k);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= sp.total, "adc_scan_topk_screen: scratch too small");
+    cudaStream_t st = as_stream(stream);
+    uint8_t* base = reinterpret_cast<uint8_t*>(scratch);
+    float* s_vals = reinterpret_cast<float*>(base + sp.off_vals);
+    uint32_t* s_ids = reinterpret_cast<uint32_t*>(base + sp.off_ids);
+    uint64_t* part = reinterpret_cast<uint64_t*>(base + sp.off_part);
+    uint32_t* qlut4 = reinterpret_cast<uint32_t*>(base + sp.off_qlut);
+    int* thr = reinterpret_cast<int*>(base + sp.off_thr);
+    uint32_t* count = reinterpret_cast<uint32_t*>(base + sp.off_count);
+    uint32_t* cand = reinterpret_cast<uint32_t*>(base + sp.off_cand);
+    const int negate = metric == B200VQ_METRIC_IP;
+    // 1. threshold sample: exact top-k of the first n_sample rows
+    {
+        ScanPlan p = plan_scan(sp.n_sample, nq);
+        int rc = (k <= 32) ? adc_scan_rot_launch<128>(codes_rot, sp.n_sample, M, lut, nq, k, negate, part, p, st)
+                           : adc_scan_rot_launch<256>(codes_rot, sp.n_sample, M, lut, nq, k, negate, part, p, st);
+        if (rc != B200VQ_OK) return rc;
+        rc = launch_merge<2048>(part, nq, p.nchunks, k, negate, s_vals, s_ids, st);
+        if (rc != B200VQ_OK) return rc;
+    }
+    // 2. packed 6-bit tables + integer thresholds
+    VQ_CUDA(cudaMemsetAsync(qlut4, 0, (size_t)sp.ngroups * M * 256 * 4, st));
+    VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)sp.ngroups * 4 * 4, st));      // -1: unused query slots never pass
+    VQ_CUDA(cudaMemsetAsync(count, 0, (size_t)sp.ngroups * 4 * 4, st));
+    screen_prepare_kernel<<<nq, 256, 0, st>>>(lut, nq, M, s_vals, k, negate, reinterpret_cast<uint8_t*>(qlut4), thr);
+    VQ_LAUNCH_CHECK();
+    // 3. screen every row, four queries per lookup
+    {
+        ScanPlan p = plan_scan(n, sp.ngroups);
+        int rc;
+        switch (M / 32) {
+            case 1: rc = screen_launch_g<1>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+            case 2: rc = screen_launch_g<2>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+            default: rc = screen_launch_g<3>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+        }
+        if (rc != B200VQ_OK) return rc;
+    }
+    // 4. exact scores of the survivors + top-k
+    {
+        int rc = (k <= 32) ? screen_finish_launch<128>(codes_rot, M, lut, cand, count, sp.cap, nq, k, negate,
+                                                       out_vals, out_ids, st)
+                           : screen_finish_launch<256>(codes_rot, M, lut, cand, count, sp.cap, nq, k, negate,
+                                                       out_vals, out_ids, st);
+        if (rc != B200VQ_OK) return rc;
+    }
+    // 5. queries whose list overflowed: exact scan, gated per query (CTAs of the others exit at once)
+    {
+        ScanPlan p = plan_scan(n, nq);
+        int rc = (k <= 32) ? adc_scan_rot_launch<128>(codes_rot, n, M, lut, nq, k, negate, part, p, st, count, sp.cap)
+                           : adc_scan_rot_launch<256>(codes_rot, n, M, lut, nq, k, negate, part, p, st, count, sp.cap);
+        if (rc != B200VQ_OK) return rc;
+        return launch_merge<2048>(part, nq, p.nchunks, k, negate, out_vals, out_ids, st, count, sp.cap);
+    }
 }
 
 extern "C" int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out,

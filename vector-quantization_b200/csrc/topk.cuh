@@ -44,9 +44,11 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, int n2) {
 template <int TILE>
 __global__ void merge_partials_kernel(const uint64_t* __restrict__ part, int nparts, int k,
                                       int negate, float* __restrict__ out_vals,
-                                      uint32_t* __restrict__ out_ids) {
+                                      uint32_t* __restrict__ out_ids, const uint32_t* __restrict__ gate = nullptr,
+                                      uint32_t gate_cap = 0) {
     __shared__ uint64_t keys[TILE];
     const int q = blockIdx.x;
+    if (gate && gate[q] <= gate_cap) return;   // gated launch: see adc_scan_rot_kernel
     const int total = nparts * k;
     const uint64_t* src = part + (size_t)q * total;
     const int kpad = k;  // the best k live in keys[0..k)
