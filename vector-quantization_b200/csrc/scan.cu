@@ -644,14 +644,16 @@ extern "C" size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq,
     return plan_screen(n, M, nq, k).total;
 }
 
-template <int G>
+template <int G, bool ABS>
 static int screen_launch_g(const uint8_t* codes_rot, int64_t n, const uint32_t* qlut4, const int* thr,
                            const ScanPlan& p, int ngroups, uint32_t* cand, uint32_t* count, uint32_t cap,
                            cudaStream_t st) {
-    const size_t smem = (size_t)G * 256 * 64 * 4;
-    VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // ABS: up to 64 KiB of padding in front of the table (it starts at a multiple of 64 KiB of the shared window)
+    const size_t smem = (size_t)G * 256 * 64 * 4 + (ABS ? 65536 : 0);
+    VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G, ABS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ngroups, (unsigned)p.nchunks);
-    adc_screen_kernel<G><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows, cand, count, cap);
+    adc_screen_kernel<G, ABS><<<grid, ABS ? 1024 : SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows,
+                                                                            cand, count, cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -713,9 +715,9 @@ extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, 
         ScanPlan p = plan_scan(n, sp.ngroups);
         int rc;
         switch (M / 32) {
-            case 1: rc = screen_launch_g<1>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
-            case 2: rc = screen_launch_g<2>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
-            default: rc = screen_launch_g<3>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+            case 1: rc = screen_launch_g<1, true>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+            case 2: rc = screen_launch_g<2, true>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
+            default: rc = screen_launch_g<3, false>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
         }
         if (rc != B200VQ_OK) return rc;
     }

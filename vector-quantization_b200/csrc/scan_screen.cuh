@@ -85,21 +85,57 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
     }
 }
 
+// ld.shared with a compile-time immediate offset from a 32-bit shared-window address
+template <int IMM>
+__device__ __forceinline__ uint32_t lds_abs(uint32_t addr) {
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(IMM));
+    return v;
+}
+// Lookups of code word W (4 code bytes = 4 consecutive steps) of the 8*G words of a lane, unrolled at
+// compile time so that the group / step offsets are LDS immediates.
+template <int G, int W>
+struct ScreenWords {
+    static __device__ __forceinline__ void run(const uint32_t (&wds)[8 * G], uint32_t lane4, uint32_t& lo16,
+                                               uint32_t& hi16) {
+        constexpr int g = W / 8, j = W % 8;
+        constexpr int imm = g * (256 * 64 * 4) + (4 * j) * 4;
+        uint32_t t4 = lds_abs<imm>(__byte_perm(wds[W], lane4, 0x7604u));
+        t4 += lds_abs<imm + 4>(__byte_perm(wds[W], lane4, 0x7614u));
+        t4 += lds_abs<imm + 8>(__byte_perm(wds[W], lane4, 0x7624u));
+        t4 += lds_abs<imm + 12>(__byte_perm(wds[W], lane4, 0x7634u));
+        lo16 += t4 & 0x00FF00FFu;
+        hi16 += (t4 >> 8) & 0x00FF00FFu;
+        ScreenWords<G, W + 1>::run(wds, lane4, lo16, hi16);
+    }
+};
+template <int G>
+struct ScreenWords<G, 8 * G> {
+    static __device__ __forceinline__ void run(const uint32_t (&)[8 * G], uint32_t, uint32_t&, uint32_t&) {}
+};
+
 // grid (query groups of 4, row chunks). Table in shared memory as [g][code][64] uint32 (columns
 // stored twice, as in adc_scan_rot_kernel). Survivors are appended to cand[q * cap + pos].
-template <int G>
-__global__ void __launch_bounds__(SCAN_THREADS)
+// ABS = true: the table starts at an ABSOLUTE shared-window address that is a multiple of 64 KiB,
+// so the PRMT that merges (code << 8) with (lane << 2) also supplies the upper address bytes and
+// its result IS the LDS address (no per-lookup base add). That costs up to 64 KiB of padding, so
+// the CTA is 1024 threads (one per SM) instead of three CTAs of 256.
+template <int G, bool ABS>
+__global__ void __launch_bounds__(ABS ? 1024 : SCAN_THREADS)
 adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32_t* __restrict__ qlut4,
                   const int* __restrict__ thr, int64_t chunk_rows, uint32_t* __restrict__ cand,
                   uint32_t* __restrict__ count, uint32_t cap) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int KSUB = 256;
     constexpr int M = G * 32;
+    constexpr int THREADS = ABS ? 1024 : SCAN_THREADS;
     const int grp = blockIdx.x, chunk = blockIdx.y;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw);
+    const uint32_t base32 = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    const uint32_t tab32 = ABS ? ((base32 + 0xFFFFu) & ~0xFFFFu) : base32;
+    uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw + (tab32 - base32));
     const uint32_t* src_q = qlut4 + (size_t)grp * M * KSUB;
-    for (int idx = threadIdx.x; idx < G * KSUB * 8; idx += SCAN_THREADS) {
+    for (int idx = threadIdx.x; idx < G * KSUB * 8; idx += THREADS) {
         const int jq = idx & 7, kk = (idx >> 3) & (KSUB - 1), g = idx >> 11;
         const uint32_t* src = src_q + (size_t)(g * 32 + 4 * jq) * KSUB + kk;
         uint4 v = make_uint4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
@@ -110,17 +146,17 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
     const int t0 = thr[grp * 4 + 0], t1 = thr[grp * 4 + 1], t2 = thr[grp * 4 + 2], t3 = thr[grp * 4 + 3];
     __syncthreads();
 
-    const unsigned char* lbase = smem_raw;
-    const uint32_t lane4 = (uint32_t)lane << 2;
+    // second PRMT operand: byte 0 = lane * 4, bytes 2..3 = upper bytes of the table address (ABS)
+    const uint32_t lane4 = ((uint32_t)lane << 2) | (ABS ? (tab32 & 0xFFFF0000u) : 0u);
     const int64_t r0 = (int64_t)chunk * chunk_rows;  // multiple of 32
     int64_t r1 = r0 + chunk_rows;
     if (r1 > n) r1 = n;
     constexpr int UNR = 2;
-    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += UNR * SCAN_THREADS) {
+    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += UNR * THREADS) {
         uint4 cv[UNR][2 * G];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
-            int64_t bb = base + (int64_t)u * SCAN_THREADS;
+            int64_t bb = base + (int64_t)u * THREADS;
             if (bb >= r1) bb = base;
             const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * 1024);
 #pragma unroll
@@ -131,23 +167,35 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
-            const int64_t row = base + (int64_t)u * SCAN_THREADS + lane;
+            const int64_t row = base + (int64_t)u * THREADS + lane;
             uint32_t lo16 = 0, hi16 = 0;   // 16-bit fields: (query 0, query 2) and (query 1, query 3)
+            if (ABS) {
+                uint32_t wds[8 * G];
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                const uint32_t wds[8] = {cv[u][2 * g].x, cv[u][2 * g].y, cv[u][2 * g].z, cv[u][2 * g].w,
-                                         cv[u][2 * g + 1].x, cv[u][2 * g + 1].y, cv[u][2 * g + 1].z,
-                                         cv[u][2 * g + 1].w};
+                for (int g = 0; g < G; ++g) {
+                    wds[8 * g + 0] = cv[u][2 * g].x; wds[8 * g + 1] = cv[u][2 * g].y;
+                    wds[8 * g + 2] = cv[u][2 * g].z; wds[8 * g + 3] = cv[u][2 * g].w;
+                    wds[8 * g + 4] = cv[u][2 * g + 1].x; wds[8 * g + 5] = cv[u][2 * g + 1].y;
+                    wds[8 * g + 6] = cv[u][2 * g + 1].z; wds[8 * g + 7] = cv[u][2 * g + 1].w;
+                }
+                ScreenWords<G, 0>::run(wds, lane4, lo16, hi16);
+            } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    uint32_t t4 = 0;
+                for (int g = 0; g < G; ++g) {
+                    const uint32_t wds[8] = {cv[u][2 * g].x, cv[u][2 * g].y, cv[u][2 * g].z, cv[u][2 * g].w,
+                                             cv[u][2 * g + 1].x, cv[u][2 * g + 1].y, cv[u][2 * g + 1].z,
+                                             cv[u][2 * g + 1].w};
 #pragma unroll
-                    for (int b = 0; b < 4; ++b) {
-                        const uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
-                        t4 += *reinterpret_cast<const uint32_t*>(lbase + off + g * (KSUB * 64 * 4) + (4 * j + b) * 4);
+                    for (int j = 0; j < 8; ++j) {
+                        uint32_t t4 = 0;
+#pragma unroll
+                        for (int b = 0; b < 4; ++b) {
+                            const uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
+                            t4 += *reinterpret_cast<const uint32_t*>(smem_raw + off + g * (KSUB * 64 * 4) + (4 * j + b) * 4);
+                        }
+                        lo16 += t4 & 0x00FF00FFu;
+                        hi16 += (t4 >> 8) & 0x00FF00FFu;
                     }
-                    lo16 += t4 & 0x00FF00FFu;
-                    hi16 += (t4 >> 8) & 0x00FF00FFu;
                 }
             }
             const bool live = row < r1;
