@@ -168,6 +168,18 @@ int b200vq_flat_topk(const float* x, int64_t n, int64_t ldx, int D, const float*
                      int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
                      size_t scratch_bytes, void* stream);
 
+/* Same search, same results (ids and values are those of b200vq_flat_topk's fp32 arithmetic), with the
+ * tensor cores as a screen: TF32 tcgen05 products of 128 rows x 256 queries give a rigorous lower
+ * bound of every exact key; rows are processed in geometric stages against the thresholds of the
+ * exact top-k so far and only the survivors are scored exactly. xnorm (n) = squared norms of the
+ * RAW rows is required (it also bounds the screen error). Falls back to b200vq_flat_topk for
+ * n < 65 536, D % 32 != 0, unaligned rows, or L2 with row_scale. */
+size_t b200vq_flat_topk_tc_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                        const float* row_scale, const float* queries, int nq, int64_t ldq,
+                        int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
+                        size_t scratch_bytes, void* stream);
+
 /* Row squared norms (compute_exact_norms, exact_search.py:20-24, before the sqrt). */
 int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out, void* stream);
 

@@ -47,6 +47,8 @@ SIGNATURES = {
     "b200vq_adc_scan_topk_screen": (_i, [_p, _i64, _i, _i, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_flat_topk_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_flat_topk": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_flat_topk_tc_scratch_bytes": (_sz, [_i64, _i, _i]),
+    "b200vq_flat_topk_tc": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_row_sqnorms": (_i, [_p, _i64, _i64, _i, _p, _p]),
     "b200vq_topk_merge": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "b200vq_sq_minmax": (_i, [_p, _i64, _i64, _i, _p, _p, _p]),

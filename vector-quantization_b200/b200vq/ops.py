@@ -235,7 +235,10 @@ def row_sqnorms(x: torch.Tensor) -> torch.Tensor:
 
 
 def flat_topk(x: torch.Tensor, queries: torch.Tensor, k: int, metric, xnorm: torch.Tensor | None = None,
-              row_scale: torch.Tensor | None = None):
+              row_scale: torch.Tensor | None = None, impl: str = "auto"):
+    """Exact top-k of queries against raw rows. impl: "simt" = exact fp32 kernel; "tc" / "auto" = tensor-core
+    screen + exact re-scoring (same results; the library falls back to the SIMT kernel for shapes the screen
+    does not cover). xnorm = squared norms of the raw rows (computed here when absent)."""
     _chk(x, torch.float32, "x")
     _chk(queries, torch.float32, "queries")
     ptr, n, ld, D = _rows(x, "x")
@@ -247,6 +250,17 @@ def flat_topk(x: torch.Tensor, queries: torch.Tensor, k: int, metric, xnorm: tor
         xnorm = row_sqnorms(x)
     lib = _lib.load()
     vals, ids = _topk_out(nq, k, x.device)
+    if impl not in ("auto", "tc", "simt"):
+        raise B200VQError(f"flat_topk: unknown impl {impl!r}")
+    if impl != "simt" and tc_available() and k <= 128:
+        if xnorm is None:
+            xnorm = row_sqnorms(x)
+        nbytes = lib.b200vq_flat_topk_tc_scratch_bytes(n, nq, k)
+        sc = scratch(nbytes, x.device, "flat_tc")
+        check(lib.b200vq_flat_topk_tc(ptr, n, ld, D, _p(xnorm), _p(row_scale), qptr, nq, ldq, mid, k,
+                                      vals.data_ptr(), ids.data_ptr(), sc.data_ptr(), sc.numel(), _stream()),
+              "flat_topk_tc")
+        return vals, ids
     nbytes = lib.b200vq_flat_topk_scratch_bytes(n, nq, k)
     sc = scratch(nbytes, x.device, "scan")
     check(lib.b200vq_flat_topk(ptr, n, ld, D, _p(xnorm), _p(row_scale), qptr, nq, ldq, mid, k,

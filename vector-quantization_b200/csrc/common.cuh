@@ -49,6 +49,12 @@ static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStre
 
 int device_sm_count();
 
+// scan.cu: exact SIMT flat search restricted to the queries with gate[q] != 0 (scratch sized by
+// b200vq_flat_topk_scratch_bytes); the gated fallback of the tensor-core search in flat_tc.cu
+int flat_topk_gated(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm, const float* row_scale,
+                    const float* queries, int nq, int64_t ldq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                    void* scratch, const uint32_t* gate, cudaStream_t st);
+
 // --------------------------------------------------------- device helpers ---
 #ifdef __CUDACC__
 

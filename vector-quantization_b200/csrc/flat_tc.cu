@@ -1,0 +1,469 @@
+// Exact flat search (ground truth) on the sm_100a tensor cores.
+//
+// Replaces faiss IndexFlatL2 / IndexFlatIP.search as driven by the reference at
+// src/haag_vq/benchmarks/exact_search.py:44-51,72-77, search_bench.py:42-56 and
+// data/datasets.py:21-34; same contract and the SAME results as the exact fp32 SIMT kernel
+// b200vq_flat_topk (scan.cu): that kernel's arithmetic (sequential fp32 FMA chain over d,
+// (|q|^2 + |x|^2) - 2 q.x clamped at 0, (value, id) order) is what the final scores are
+// computed with. The tensor cores only SCREEN:
+//
+//   P[i][q] = x_i . q   with tcgen05.mma kind::tf32 (operands truncated to 10 mantissa bits),
+//   128 rows x 256 queries per accumulator, K = D streamed through a 4-stage TMA ring.
+//   |P (1 + 2^-10) - x_i.q| <= E_i = (2^-10 * 1.02 + 3 D 2^-24) |x_i| max_q|q|  (truncation is
+//   one-sided, hence the centring factor; the D 2^-24 terms cover both fp32 accumulations),
+//   so LB = a_i P + b_i is a rigorous lower bound of the exact key of (row i, query q) and the
+//   row can only enter the top-k if LB <= T_q (T_q from the current exact k-th best).
+//
+// Rows are processed in geometric stages (8192 rows by the SIMT kernel, then x4 per stage):
+// each stage screens its rows against the thresholds of the exact top-k so far, appends the
+// survivors to per-query lists, and flat_finish_kernel scores them exactly and merges them
+// into the running top-k, which tightens the thresholds for the next, four times larger,
+// stage. A query whose list overflows is flagged and redone by the SIMT kernel (gated launch)
+// at the end, so the result never depends on the screen. x is read from HBM once (the query
+// tiles of a row tile are consumed back to back, out of L2).
+#include "tc_common.cuh"
+#include "topk.cuh"
+
+namespace b200vq {
+namespace ftc {
+using namespace tc;
+
+constexpr int TILE_ROWS = 128;
+constexpr int TILE_Q = 256;
+constexpr int CH = 32;                       // K chunk: 32 floats = one 128-byte swizzle row
+constexpr int NST = 4;
+constexpr int EPI_WARPS = 8;                 // 2 accumulator stages x 4 TMEM lane quarters
+constexpr int THREADS = 64 + 32 * EPI_WARPS;
+constexpr uint32_t A_BYTES = TILE_ROWS * CH * 4;
+constexpr uint32_t B_BYTES = TILE_Q * CH * 4;
+constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr uint32_t BAR_OFF = NST * STAGE_BYTES;
+constexpr uint32_t THR_OFF = BAR_OFF + 256;
+constexpr uint32_t SMEM_BYTES = THR_OFF + 2 * TILE_Q * 4 + 1024;   // + alignment slack
+enum { B_FULL = 0, B_EMPTY = NST, B_TFULL = 2 * NST, B_TEMPTY = 2 * NST + 2, B_TMEM = 2 * NST + 4 };
+
+struct Params {
+    const float* xnorm;       // (n) squared norms of the raw rows
+    const float* row_scale;   // (n) or null
+    const float* thr;         // (ntq * 256) T_q, NaN for padding queries
+    const float* qstats;      // [0] = max_q |q|^2
+    uint32_t* cand;           // (nq, cap)
+    uint32_t* count;          // (nq)
+    uint32_t cap;
+    int64_t r0, r1;           // rows of this stage
+    int nq, nchunk, ntq;      // queries, D / 32, query tiles
+    int64_t ntr;              // row tiles of this stage
+    int metric;
+    float ebound;             // 2^-10 * 1.02 + 3 D 2^-24
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q, const Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - raw);
+    const uint32_t bar0 = base + BAR_OFF;
+    auto bar = [&](int slot) { return bar0 + 8u * (uint32_t)slot; };
+    volatile uint32_t* tmem_ptr_smem = reinterpret_cast<volatile uint32_t*>(gbase + BAR_OFF + 8 * B_TMEM);
+    float* thr_s = reinterpret_cast<float*>(gbase + THR_OFF);    // [2][TILE_Q]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t nunits = p.ntr * p.ntq;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_q);
+        for (int i = 0; i < NST; ++i) {
+            mbar_init(bar(B_FULL + i), 1);
+            mbar_init(bar(B_EMPTY + i), 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar(B_TFULL + i), 1);
+            mbar_init(bar(B_TEMPTY + i), 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(bar(B_TMEM), 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t st = 0, phase = 0;
+            for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+                const int64_t t = unit / p.ntq;
+                const int u = (int)(unit - t * p.ntq);
+                const int row0 = (int)(p.r0 + t * TILE_ROWS);
+                for (int c = 0; c < p.nchunk; ++c) {
+                    mbar_wait_backoff(bar(B_EMPTY + st), phase ^ 1);
+                    mbar_expect_tx(bar(B_FULL + st), STAGE_BYTES);
+                    tma_load_2d(base + st * STAGE_BYTES, &map_x, bar(B_FULL + st), c * CH, row0);
+                    tma_load_2d(base + st * STAGE_BYTES + A_BYTES, &map_q, bar(B_FULL + st), c * CH, u * TILE_Q);
+                    if (++st == NST) { st = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            uint32_t st = 0, phase = 0, acc = 0, t_phase = 0;
+            for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+                mbar_wait_backoff(bar(B_TEMPTY + acc), t_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d = tmem_base + acc * 256u;
+                uint32_t accum = 0;
+                for (int c = 0; c < p.nchunk; ++c) {
+                    mbar_wait_backoff(bar(B_FULL + st), phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = base + st * STAGE_BYTES, b_addr = a_addr + A_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < CH / 8; ++kk) {
+                        umma_tf32(d, make_kmajor_desc(a_addr + kk * 32, 1024, 2), make_kmajor_desc(b_addr + kk * 32, 1024, 2),
+                                  IDESC_TF32_128x256, accum);
+                        accum = 1;
+                    }
+                    umma_commit(bar(B_EMPTY + st));
+                    if (++st == NST) { st = 0; phase ^= 1; }
+                }
+                umma_commit(bar(B_TFULL + acc));
+                if (++acc == 2) { acc = 0; t_phase ^= 1; }
+            }
+        }
+    } else {
+        const uint32_t acc = (uint32_t)(warp - 2) >> 2;      // accumulator stage served by this warp
+        const int q4 = warp & 3;                              // TMEM lane quarter this warp may read
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q4 * 32) << 16) + acc * 256u;
+        float* ts = thr_s + acc * TILE_Q;
+        const int gt = (warp - 2 - (int)acc * 4) * 32 + lane;  // 0..127 inside the group
+        const uint32_t grp_bar = 1u + acc;
+        const float qn_max = p.qstats[0], q_max = sqrtf(qn_max) * 1.0000005f;
+        uint32_t t_phase = 0;
+        int64_t unit = blockIdx.x;
+        for (uint32_t it = 0; unit < nunits; unit += gridDim.x, ++it) {
+            if ((it & 1u) != acc) continue;
+            const int64_t t = unit / p.ntq;
+            const int u = (int)(unit - t * p.ntq);
+            const int64_t row = p.r0 + t * TILE_ROWS + q4 * 32 + lane;
+            const bool live = row < p.r1;
+            float a = 0.f, b = 0.f;
+            if (live) {
+                const float xn = p.xnorm[row];
+                const float rs = p.row_scale ? p.row_scale[row] : 1.f;
+                const float nrm = sqrtf(xn) * fabsf(rs) * 1.0000005f;
+                const float E = p.ebound * nrm * q_max + 2.4e-7f * (xn * rs * rs + qn_max);
+                if (p.metric == B200VQ_METRIC_L2) {
+                    a = -2.f * 1.0009765625f * rs;
+                    b = xn - 2.f * E;
+                } else {
+                    a = -1.0009765625f * rs;
+                    b = -E;
+                }
+            }
+            asm volatile("bar.sync %0, 128;" ::"r"(grp_bar) : "memory");   // previous unit's thresholds consumed
+            ts[gt] = p.thr[(size_t)u * TILE_Q + gt];
+            ts[gt + 128] = p.thr[(size_t)u * TILE_Q + gt + 128];
+            asm volatile("bar.sync %0, 128;" ::"r"(grp_bar) : "memory");
+            mbar_wait(bar(B_TFULL + acc), t_phase);
+            tc_fence_after();
+            float v[64];
+#pragma unroll 1
+            for (int cb = 0; cb < 4; ++cb) {
+                tmem_ld64(lane_addr + cb * 64, v);
+                const float4* t4 = reinterpret_cast<const float4*>(ts + cb * 64);
+#pragma unroll
+                for (int j4 = 0; j4 < 16; ++j4) {
+                    const float4 tt = t4[j4];
+                    const float th[4] = {tt.x, tt.y, tt.z, tt.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float lb = __fmaf_rn(a, v[4 * j4 + e], b);
+                        if (live && lb <= th[e]) {
+                            const int q = u * TILE_Q + cb * 64 + 4 * j4 + e;
+                            const uint32_t pos = atomicAdd(p.count + q, 1u);
+                            if (pos < p.cap) p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(B_TEMPTY + acc));
+            t_phase ^= 1;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// |q|^2 of every query with the SIMT kernel's arithmetic (lane-strided FMA chain + xor tree), and their maximum.
+__global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, int64_t ldq, int D, float* __restrict__ qn,
+                                   float* __restrict__ qstats) {
+    const int lane = threadIdx.x & 31;
+    const int q = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (q >= nq) return;
+    const float* pq = queries + (int64_t)q * ldq;
+    float acc = 0.f;
+    for (int i = lane; i < D; i += 32) acc = __fmaf_rn(pq[i], pq[i], acc);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
+    if (lane == 0) {
+        qn[q] = acc;
+        atomicMax(reinterpret_cast<int*>(qstats), __float_as_int(acc));   // non-negative floats order as ints
+    }
+}
+
+// Running list from the SIMT kernel's result on the first rows: keys, thresholds, cleared counters.
+__global__ void flat_seed_kernel(const float* __restrict__ vals, const uint32_t* __restrict__ ids, int nq, int k,
+                                 int metric, const float* __restrict__ qn, uint64_t* __restrict__ running,
+                                 float* __restrict__ thr, uint32_t* __restrict__ count, uint32_t* __restrict__ flags) {
+    const int q = blockIdx.x;
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        const uint32_t id = ids[(size_t)q * k + j];
+        const float v = vals[(size_t)q * k + j];
+        running[(size_t)q * k + j] = (id == 0xffffffffu) ? KEY_INF : make_key(metric == B200VQ_METRIC_IP ? -v : v, id);
+    }
+    if (threadIdx.x == 0) {
+        const uint32_t id = ids[(size_t)q * k + k - 1];
+        const float v = vals[(size_t)q * k + k - 1];
+        float t = __int_as_float(0x7f800000);
+        if (id != 0xffffffffu) t = (metric == B200VQ_METRIC_IP) ? -v : v - qn[q];
+        thr[q] = t;
+        count[q] = 0;
+        flags[q] = 0;
+    }
+}
+
+constexpr int FIN_THREADS = 256;
+// One CTA per query: exact keys of the listed rows (the SIMT kernel's arithmetic), merged with the running list.
+template <int CAP>
+__global__ void __launch_bounds__(FIN_THREADS)
+flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float* __restrict__ xnorm,
+                   const float* __restrict__ row_scale, const float* __restrict__ queries, int64_t ldq, int metric, int k,
+                   const uint32_t* __restrict__ cand, uint32_t* __restrict__ count, uint32_t cap,
+                   uint64_t* __restrict__ running, float* __restrict__ thr, uint32_t* __restrict__ flags, int last,
+                   float* __restrict__ out_vals, uint32_t* __restrict__ out_ids) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint64_t best[128];
+    __shared__ float qn_s;
+    const int q = blockIdx.x;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* qs = reinterpret_cast<float*>(smem_raw);                       // [D]
+    uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_raw + (((size_t)D * 4 + 15) & ~(size_t)15));
+    const int n2 = next_pow2((FIN_THREADS / 32) * k);
+    uint64_t* mbuf = wbuf + (FIN_THREADS / 32) * CAP;
+    const float* pq = queries + (int64_t)q * ldq;
+    for (int i = threadIdx.x; i < D; i += FIN_THREADS) qs[i] = pq[i];
+    if (w == 0) {
+        float acc = 0.f;
+        for (int i = lane; i < D; i += 32) acc = __fmaf_rn(pq[i], pq[i], acc);
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
+        if (lane == 0) qn_s = acc;
+    }
+    __syncthreads();
+    const float qn = qn_s;
+    uint32_t cnt = count[q];
+    if (cnt > cap) {
+        if (threadIdx.x == 0) flags[q] = 1;     // redone by the gated SIMT launch
+        cnt = cap;
+    }
+    WarpTopK<CAP> tk;
+    tk.init(wbuf + w * CAP, k);
+    // the running list first
+    for (int e0 = 0; e0 < k; e0 += FIN_THREADS) {
+        const int e = e0 + threadIdx.x;
+        uint64_t key = KEY_INF;
+        if (e < k) key = running[(size_t)q * k + e];
+        tk.offer(key != KEY_INF, key_value(key), key_id(key));
+    }
+    const uint32_t* list = cand + (size_t)q * cap;
+    const uint32_t rounds = (cnt + FIN_THREADS - 1) / FIN_THREADS;
+    for (uint32_t itr = 0; itr < rounds; ++itr) {
+        const uint32_t e = itr * FIN_THREADS + threadIdx.x;
+        const bool valid = e < cnt;
+        float key = 0.f;
+        uint32_t row = 0;
+        if (valid) {
+            row = list[e];
+            const float4* xr = reinterpret_cast<const float4*>(x + (int64_t)row * ldx);
+            const float rs = row_scale ? row_scale[row] : 1.f;
+            float acc = 0.f;
+            for (int d4 = 0; d4 < D / 4; ++d4) {
+                float4 xv = __ldg(xr + d4);
+                if (row_scale) {
+                    xv.x = __fmul_rn(xv.x, rs); xv.y = __fmul_rn(xv.y, rs);
+                    xv.z = __fmul_rn(xv.z, rs); xv.w = __fmul_rn(xv.w, rs);
+                }
+                acc = __fmaf_rn(qs[4 * d4], xv.x, acc);
+                acc = __fmaf_rn(qs[4 * d4 + 1], xv.y, acc);
+                acc = __fmaf_rn(qs[4 * d4 + 2], xv.z, acc);
+                acc = __fmaf_rn(qs[4 * d4 + 3], xv.w, acc);
+            }
+            if (metric == B200VQ_METRIC_L2) key = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(qn, xnorm[row])), 0.f);
+            else key = -acc;
+        }
+        tk.offer(valid, key, row);
+    }
+    block_emit_topk<CAP>(tk, mbuf, n2, k, best);
+    __syncthreads();
+    for (int j = threadIdx.x; j < k; j += FIN_THREADS) {
+        const uint64_t kk = best[j];
+        running[(size_t)q * k + j] = kk;
+        if (last) {
+            float v;
+            uint32_t id;
+            if (kk == KEY_INF) {
+                v = __int_as_float(0x7f800000);
+                id = 0xffffffffu;
+            } else {
+                v = key_value(kk);
+                id = key_id(kk);
+            }
+            if (metric == B200VQ_METRIC_IP) v = -v;
+            out_vals[(size_t)q * k + j] = v;
+            out_ids[(size_t)q * k + j] = id;
+        }
+    }
+    if (threadIdx.x == 0) {
+        const uint64_t kk = best[k - 1];
+        float t = __int_as_float(0x7f800000);
+        if (kk != KEY_INF) t = (metric == B200VQ_METRIC_IP) ? key_value(kk) : key_value(kk) - qn;
+        thr[q] = t;
+        count[q] = 0;
+    }
+}
+
+}  // namespace ftc
+}  // namespace b200vq
+
+using namespace b200vq;
+using namespace b200vq::ftc;
+
+namespace {
+constexpr int64_t SEED_ROWS = 8192;
+struct FlatPlan {
+    uint32_t cap;
+    int ntq;
+    size_t off_simt, off_running, off_thr, off_count, off_flags, off_qn, off_qstats, off_svals, off_sids, off_cand, total;
+};
+FlatPlan plan_flat(int64_t n, int nq, int k) {
+    FlatPlan f;
+    f.ntq = (nq + TILE_Q - 1) / TILE_Q;
+    int64_t cap = 64 * (int64_t)k;
+    if (cap < 4096) cap = 4096;
+    f.cap = (uint32_t)cap;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t o = 0;
+    f.off_simt = o;    o = up(o + b200vq_flat_topk_scratch_bytes(n, nq, k));
+    f.off_running = o; o = up(o + (size_t)nq * k * 8);
+    f.off_thr = o;     o = up(o + (size_t)f.ntq * TILE_Q * 4);
+    f.off_count = o;   o = up(o + (size_t)nq * 4);
+    f.off_flags = o;   o = up(o + (size_t)nq * 4);
+    f.off_qn = o;      o = up(o + (size_t)nq * 4);
+    f.off_qstats = o;  o = up(o + 16);
+    f.off_svals = o;   o = up(o + (size_t)nq * k * 4);
+    f.off_sids = o;    o = up(o + (size_t)nq * k * 4);
+    f.off_cand = o;    o = up(o + (size_t)nq * f.cap * 4);
+    f.total = o;
+    return f;
+}
+bool tc_applies(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm, const float* row_scale,
+                const float* queries, int nq, int64_t ldq, int metric, int k) {
+    return n >= 8 * SEED_ROWS && n < (1ll << 31) && D % 32 == 0 && D <= 8192 && ldx % 4 == 0 && ldq % 4 == 0 &&
+           ((uintptr_t)x & 15) == 0 && ((uintptr_t)queries & 15) == 0 && xnorm != nullptr && nq >= 1 && k <= 128 &&
+           !(metric == B200VQ_METRIC_L2 && row_scale != nullptr);
+}
+}  // namespace
+
+extern "C" size_t b200vq_flat_topk_tc_scratch_bytes(int64_t n, int nq, int k) {
+    if (n < 0 || nq <= 0 || k <= 0) return 0;
+    return plan_flat(n, nq, k).total;
+}
+
+template <int CAP>
+static int finish_launch(const float* x, int64_t ldx, int D, const float* xnorm, const float* row_scale,
+                         const float* queries, int nq, int64_t ldq, int metric, int k, const uint32_t* cand,
+                         uint32_t* count, uint32_t cap, uint64_t* running, float* thr, uint32_t* flags, int last,
+                         float* out_vals, uint32_t* out_ids, cudaStream_t st) {
+    const int n2 = next_pow2((FIN_THREADS / 32) * k);
+    const size_t smem = (((size_t)D * 4 + 15) & ~(size_t)15) + (size_t)((FIN_THREADS / 32) * CAP + n2) * 8;
+    VQ_CUDA(cudaFuncSetAttribute(flat_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    flat_finish_kernel<CAP><<<nq, FIN_THREADS, smem, st>>>(x, ldx, D, xnorm, row_scale, queries, ldq, metric, k, cand,
+                                                         count, cap, running, thr, flags, last, out_vals, out_ids);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                                   const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
+                                   int k, float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                                   void* stream) {
+    VQ_CHECK_ARG(x && queries && out_vals && out_ids, "flat_topk_tc: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && ldx >= D && ldq >= D && nq >= 0, "flat_topk_tc: bad shape");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "flat_topk_tc: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "flat_topk_tc: bad metric");
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_IP || xnorm, "flat_topk_tc: L2 needs xnorm");
+    if (nq == 0) return B200VQ_OK;
+    const FlatPlan fp = plan_flat(n, nq, k);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= fp.total, "flat_topk_tc: scratch too small (%zu < %zu)", scratch_bytes,
+                 fp.total);
+    uint8_t* sb = reinterpret_cast<uint8_t*>(scratch);
+    if (!tc_applies(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k))   // shapes the screen does not cover
+        return b200vq_flat_topk(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids,
+                                sb + fp.off_simt, fp.off_running - fp.off_simt, stream);
+    cudaStream_t st = as_stream(stream);
+    uint64_t* running = reinterpret_cast<uint64_t*>(sb + fp.off_running);
+    float* thr = reinterpret_cast<float*>(sb + fp.off_thr);
+    uint32_t* count = reinterpret_cast<uint32_t*>(sb + fp.off_count);
+    uint32_t* flags = reinterpret_cast<uint32_t*>(sb + fp.off_flags);
+    float* qn = reinterpret_cast<float*>(sb + fp.off_qn);
+    float* qstats = reinterpret_cast<float*>(sb + fp.off_qstats);
+    float* svals = reinterpret_cast<float*>(sb + fp.off_svals);
+    uint32_t* sids = reinterpret_cast<uint32_t*>(sb + fp.off_sids);
+    uint32_t* cand = reinterpret_cast<uint32_t*>(sb + fp.off_cand);
+
+    // query norms, their maximum, the exact top-k of the first rows, and the first thresholds
+    VQ_CUDA(cudaMemsetAsync(qstats, 0, 16, st));
+    flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats);
+    VQ_LAUNCH_CHECK();
+    int rc = b200vq_flat_topk(x, SEED_ROWS, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, svals, sids,
+                              sb + fp.off_simt, fp.off_running - fp.off_simt, stream);
+    if (rc != B200VQ_OK) return rc;
+    VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)fp.ntq * TILE_Q * 4, st));   // NaN: padding queries never pass
+    flat_seed_kernel<<<nq, 128, 0, st>>>(svals, sids, nq, k, metric, qn, running, thr, count, flags);
+    VQ_LAUNCH_CHECK();
+
+    CUtensorMap map_x, map_q;
+    if ((rc = encode_2d(&map_x, x, (uint64_t)n, (uint64_t)D, (uint64_t)ldx, TILE_ROWS, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
+        return rc;
+    if ((rc = encode_2d(&map_q, queries, (uint64_t)nq, (uint64_t)D, (uint64_t)ldq, TILE_Q, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
+        return rc;
+    VQ_CUDA(cudaFuncSetAttribute(flat_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    Params p;
+    p.xnorm = xnorm; p.row_scale = row_scale; p.thr = thr; p.qstats = qstats; p.cand = cand; p.count = count;
+    p.cap = fp.cap; p.nq = nq; p.nchunk = D / CH; p.ntq = fp.ntq; p.metric = metric;
+    p.ebound = 0.0009765625f * 1.02f + 3.0f * (float)D * 5.9604645e-8f;
+    const int sms = device_sm_count();
+    for (int64_t r = SEED_ROWS; r < n;) {
+        int64_t r1 = r * 4;
+        if (r1 > n || n - r1 < r) r1 = n;      // fold a short tail into the last stage
+        p.r0 = r; p.r1 = r1;
+        p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
+        const int64_t units = p.ntr * p.ntq;
+        flat_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, SMEM_BYTES, st>>>(map_x, map_q, p);
+        VQ_LAUNCH_CHECK();
+        const int last = r1 == n;
+        rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
+                                           running, thr, flags, last, out_vals, out_ids, st)
+                       : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
+                                            running, thr, flags, last, out_vals, out_ids, st);
+        if (rc != B200VQ_OK) return rc;
+        r = r1;
+    }
+    // queries whose survivor list overflowed in some stage: exact SIMT search, gated per query
+    return flat_topk_gated(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids,
+                           sb + fp.off_simt, flags, st);
+}

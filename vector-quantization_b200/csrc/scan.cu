@@ -17,20 +17,6 @@ namespace b200vq {
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_WARPS = SCAN_THREADS / 32;
 
-// Emit the CTA's best k: gather every warp's sorted list into `mbuf`
-// (n2 = pow2 >= SCAN_WARPS*k), sort, write k keys to dst.
-template <int CAP>
-__device__ __forceinline__ void block_emit_topk(WarpTopK<CAP>& tk, uint64_t* mbuf, int n2, int k,
-                                                uint64_t* dst) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    tk.finish();
-    for (int i = threadIdx.x; i < n2; i += blockDim.x) mbuf[i] = KEY_INF;
-    __syncthreads();
-    for (int i = lane; i < tk.count; i += 32) mbuf[w * k + i] = tk.buf[i];
-    block_bitonic_sort(mbuf, n2);
-    for (int j = threadIdx.x; j < k; j += blockDim.x) dst[j] = mbuf[j];
-}
-
 // ------------------------------------------------------------ ADC scan ---
 // grid (nq, nchunks). Each CTA loads one query's LUT (M*ksub fp32) into shared
 // memory and streams `chunk_rows` rows of codes. Thread = row.
@@ -242,8 +228,14 @@ __global__ void __launch_bounds__(FT_THREADS)
     flat_topk_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
                      const float* __restrict__ xnorm, const float* __restrict__ row_scale,
                      const float* __restrict__ queries, int nq, int64_t ldq, int metric, int k,
-                     int64_t chunk_rows, uint64_t* __restrict__ part) {
+                     int64_t chunk_rows, uint64_t* __restrict__ part, const uint32_t* __restrict__ gate = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (gate) {   // gated launch (fallback of the tensor-core search): skip tiles without a flagged query
+        int any = 0;
+        const int qq = blockIdx.x * FT_Q + (threadIdx.x & (FT_Q - 1));
+        if (qq < nq && gate[qq] != 0) any = 1;
+        if (!__syncthreads_or(any)) return;
+    }
     float* Qs = reinterpret_cast<float*>(smem_raw);            // [FT_K][FT_Q+4]
     float* Xs = Qs + FT_K * (FT_Q + 4);                        // [FT_K][FT_N+4]
     float* ds = Xs + FT_K * (FT_N + 4);                        // [FT_Q][FT_N+1]
@@ -759,17 +751,33 @@ extern "C" size_t b200vq_flat_topk_scratch_bytes(int64_t n, int nq, int k) {
 template <int CAP>
 static int flat_launch(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
                        const float* row_scale, const float* queries, int nq, int64_t ldq,
-                       int metric, int k, uint64_t* part, const ScanPlan& p, cudaStream_t st) {
+                       int metric, int k, uint64_t* part, const ScanPlan& p, cudaStream_t st,
+                       const uint32_t* gate = nullptr) {
     size_t smem = (size_t)(FT_K * (FT_Q + 4) + FT_K * (FT_N + 4) + FT_Q * (FT_N + 1) + 3 * FT_Q) * 4 +
                   16 + (size_t)FT_Q * CAP * sizeof(uint64_t);
     VQ_CUDA(cudaFuncSetAttribute(flat_topk_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
     dim3 grid((unsigned)((nq + FT_Q - 1) / FT_Q), (unsigned)p.nchunks);
     flat_topk_kernel<CAP><<<grid, FT_THREADS, smem, st>>>(x, n, ldx, D, xnorm, row_scale, queries,
-                                                          nq, ldq, metric, k, p.chunk_rows, part);
+                                                          nq, ldq, metric, k, p.chunk_rows, part, gate);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
+
+// SIMT exact search restricted to the queries with gate[q] != 0 (internal: used by flat_tc.cu)
+namespace b200vq {
+int flat_topk_gated(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm, const float* row_scale,
+                    const float* queries, int nq, int64_t ldq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                    void* scratch, const uint32_t* gate, cudaStream_t st) {
+    int nqc = (nq + FT_Q - 1) / FT_Q;
+    ScanPlan p = plan_scan(n, nqc);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32) ? flat_launch<64>(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, part, p, st, gate)
+                       : flat_launch<256>(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, part, p, st, gate);
+    if (rc != B200VQ_OK) return rc;
+    return launch_merge<2048>(part, nq, p.nchunks, k, metric == B200VQ_METRIC_IP, out_vals, out_ids, st, gate, 0);
+}
+}  // namespace b200vq
 
 extern "C" int b200vq_flat_topk(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
                                 const float* row_scale, const float* queries, int nq, int64_t ldq,

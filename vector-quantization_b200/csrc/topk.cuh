@@ -35,6 +35,20 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, int n2) {
     __syncthreads();
 }
 
+// Emit the CTA's best k: gather every warp's sorted list into `mbuf`
+// (n2 = pow2 >= SCAN_WARPS*k), sort, write k keys to dst.
+template <int CAP>
+__device__ __forceinline__ void block_emit_topk(WarpTopK<CAP>& tk, uint64_t* mbuf, int n2, int k,
+                                                uint64_t* dst) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    tk.finish();
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) mbuf[i] = KEY_INF;
+    __syncthreads();
+    for (int i = lane; i < tk.count; i += 32) mbuf[w * k + i] = tk.buf[i];
+    block_bitonic_sort(mbuf, n2);
+    for (int j = threadIdx.x; j < k; j += blockDim.x) dst[j] = mbuf[j];
+}
+
 // Partial results layout: part[(q * nparts + p) * k + j], u64 keys ascending,
 // KEY_INF padded.
 //
