@@ -14,10 +14,10 @@
 //   so LB = a_i P + b_i is a rigorous lower bound of the exact key of (row i, query q) and the
 //   row can only enter the top-k if LB <= T_q (T_q from the current exact k-th best).
 //
-// Rows are processed in geometric stages (8192 rows by the SIMT kernel, then x4 per stage):
+// Rows are processed in geometric stages (the first 1024 rows scored exactly, then x2 per stage):
 // each stage screens its rows against the thresholds of the exact top-k so far, appends the
 // survivors to per-query lists, and flat_finish_kernel scores them exactly and merges them
-// into the running top-k, which tightens the thresholds for the next, four times larger,
+// into the running top-k, which tightens the thresholds for the next, twice as large,
 // stage. A query whose list overflows is flagged and redone by the SIMT kernel (gated launch)
 // at the end, so the result never depends on the screen. x is read from HBM once (the query
 // tiles of a row tile are consumed back to back, out of L2).
@@ -216,27 +216,6 @@ __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, in
     }
 }
 
-// Running list from the SIMT kernel's result on the first rows: keys, thresholds, cleared counters.
-__global__ void flat_seed_kernel(const float* __restrict__ vals, const uint32_t* __restrict__ ids, int nq, int k,
-                                 int metric, const float* __restrict__ qn, uint64_t* __restrict__ running,
-                                 float* __restrict__ thr, uint32_t* __restrict__ count, uint32_t* __restrict__ flags) {
-    const int q = blockIdx.x;
-    for (int j = threadIdx.x; j < k; j += blockDim.x) {
-        const uint32_t id = ids[(size_t)q * k + j];
-        const float v = vals[(size_t)q * k + j];
-        running[(size_t)q * k + j] = (id == 0xffffffffu) ? KEY_INF : make_key(metric == B200VQ_METRIC_IP ? -v : v, id);
-    }
-    if (threadIdx.x == 0) {
-        const uint32_t id = ids[(size_t)q * k + k - 1];
-        const float v = vals[(size_t)q * k + k - 1];
-        float t = __int_as_float(0x7f800000);
-        if (id != 0xffffffffu) t = (metric == B200VQ_METRIC_IP) ? -v : v - qn[q];
-        thr[q] = t;
-        count[q] = 0;
-        flags[q] = 0;
-    }
-}
-
 constexpr int FIN_THREADS = 256;
 // One CTA per query: exact keys of the listed rows (the SIMT kernel's arithmetic), merged with the running list.
 template <int CAP>
@@ -245,7 +224,7 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
                    const float* __restrict__ row_scale, const float* __restrict__ queries, int64_t ldq, int metric, int k,
                    const uint32_t* __restrict__ cand, uint32_t* __restrict__ count, uint32_t cap,
                    uint64_t* __restrict__ running, float* __restrict__ thr, uint32_t* __restrict__ flags, int last,
-                   float* __restrict__ out_vals, uint32_t* __restrict__ out_ids) {
+                   float* __restrict__ out_vals, uint32_t* __restrict__ out_ids, uint32_t seed_rows) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint64_t best[128];
     __shared__ float qn_s;
@@ -265,8 +244,9 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
     }
     __syncthreads();
     const float qn = qn_s;
-    uint32_t cnt = count[q];
-    if (cnt > cap) {
+    // seed_rows > 0: the "list" is rows [0, seed_rows) (first stage: exact top-k of the first rows)
+    uint32_t cnt = seed_rows ? seed_rows : count[q];
+    if (!seed_rows && cnt > cap) {
         if (threadIdx.x == 0) flags[q] = 1;     // redone by the gated SIMT launch
         cnt = cap;
     }
@@ -287,7 +267,7 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
         float key = 0.f;
         uint32_t row = 0;
         if (valid) {
-            row = list[e];
+            row = seed_rows ? e : list[e];
             const float4* xr = reinterpret_cast<const float4*>(x + (int64_t)row * ldx);
             const float rs = row_scale ? row_scale[row] : 1.f;
             float acc = 0.f;
@@ -343,11 +323,12 @@ using namespace b200vq;
 using namespace b200vq::ftc;
 
 namespace {
-constexpr int64_t SEED_ROWS = 8192;
+constexpr int64_t SEED_ROWS = 1024;   // scored exactly by flat_finish_kernel (identity list); stages double from here
+constexpr int64_t MIN_ROWS = 65536;   // below this the SIMT kernel alone is as fast
 struct FlatPlan {
     uint32_t cap;
     int ntq;
-    size_t off_simt, off_running, off_thr, off_count, off_flags, off_qn, off_qstats, off_svals, off_sids, off_cand, total;
+    size_t off_simt, off_running, off_thr, off_count, off_flags, off_qn, off_qstats, off_cand, total;
 };
 FlatPlan plan_flat(int64_t n, int nq, int k) {
     FlatPlan f;
@@ -364,15 +345,13 @@ FlatPlan plan_flat(int64_t n, int nq, int k) {
     f.off_flags = o;   o = up(o + (size_t)nq * 4);
     f.off_qn = o;      o = up(o + (size_t)nq * 4);
     f.off_qstats = o;  o = up(o + 16);
-    f.off_svals = o;   o = up(o + (size_t)nq * k * 4);
-    f.off_sids = o;    o = up(o + (size_t)nq * k * 4);
     f.off_cand = o;    o = up(o + (size_t)nq * f.cap * 4);
     f.total = o;
     return f;
 }
 bool tc_applies(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm, const float* row_scale,
                 const float* queries, int nq, int64_t ldq, int metric, int k) {
-    return n >= 8 * SEED_ROWS && n < (1ll << 31) && D % 32 == 0 && D <= 8192 && ldx % 4 == 0 && ldq % 4 == 0 &&
+    return n >= MIN_ROWS && n < (1ll << 31) && D % 32 == 0 && D <= 8192 && ldx % 4 == 0 && ldq % 4 == 0 &&
            ((uintptr_t)x & 15) == 0 && ((uintptr_t)queries & 15) == 0 && xnorm != nullptr && nq >= 1 && k <= 128 &&
            !(metric == B200VQ_METRIC_L2 && row_scale != nullptr);
 }
@@ -387,12 +366,13 @@ template <int CAP>
 static int finish_launch(const float* x, int64_t ldx, int D, const float* xnorm, const float* row_scale,
                          const float* queries, int nq, int64_t ldq, int metric, int k, const uint32_t* cand,
                          uint32_t* count, uint32_t cap, uint64_t* running, float* thr, uint32_t* flags, int last,
-                         float* out_vals, uint32_t* out_ids, cudaStream_t st) {
+                         float* out_vals, uint32_t* out_ids, cudaStream_t st, uint32_t seed_rows = 0) {
     const int n2 = next_pow2((FIN_THREADS / 32) * k);
     const size_t smem = (((size_t)D * 4 + 15) & ~(size_t)15) + (size_t)((FIN_THREADS / 32) * CAP + n2) * 8;
     VQ_CUDA(cudaFuncSetAttribute(flat_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     flat_finish_kernel<CAP><<<nq, FIN_THREADS, smem, st>>>(x, ldx, D, xnorm, row_scale, queries, ldq, metric, k, cand,
-                                                         count, cap, running, thr, flags, last, out_vals, out_ids);
+                                                         count, cap, running, thr, flags, last, out_vals, out_ids,
+                                                         seed_rows);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -421,20 +401,20 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     uint32_t* flags = reinterpret_cast<uint32_t*>(sb + fp.off_flags);
     float* qn = reinterpret_cast<float*>(sb + fp.off_qn);
     float* qstats = reinterpret_cast<float*>(sb + fp.off_qstats);
-    float* svals = reinterpret_cast<float*>(sb + fp.off_svals);
-    uint32_t* sids = reinterpret_cast<uint32_t*>(sb + fp.off_sids);
     uint32_t* cand = reinterpret_cast<uint32_t*>(sb + fp.off_cand);
 
-    // query norms, their maximum, the exact top-k of the first rows, and the first thresholds
+    // query norms and their maximum; exact top-k of the first rows (finish kernel on the identity list)
     VQ_CUDA(cudaMemsetAsync(qstats, 0, 16, st));
     flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats);
     VQ_LAUNCH_CHECK();
-    int rc = b200vq_flat_topk(x, SEED_ROWS, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, svals, sids,
-                              sb + fp.off_simt, fp.off_running - fp.off_simt, stream);
-    if (rc != B200VQ_OK) return rc;
     VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)fp.ntq * TILE_Q * 4, st));   // NaN: padding queries never pass
-    flat_seed_kernel<<<nq, 128, 0, st>>>(svals, sids, nq, k, metric, qn, running, thr, count, flags);
-    VQ_LAUNCH_CHECK();
+    VQ_CUDA(cudaMemsetAsync(running, 0xFF, (size_t)nq * k * 8, st));        // KEY_INF
+    VQ_CUDA(cudaMemsetAsync(flags, 0, (size_t)nq * 4, st));
+    int rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
+                                           running, thr, flags, 0, out_vals, out_ids, st, (uint32_t)SEED_ROWS)
+                       : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
+                                            running, thr, flags, 0, out_vals, out_ids, st, (uint32_t)SEED_ROWS);
+    if (rc != B200VQ_OK) return rc;
 
     CUtensorMap map_x, map_q;
     if ((rc = encode_2d(&map_x, x, (uint64_t)n, (uint64_t)D, (uint64_t)ldx, TILE_ROWS, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
@@ -448,8 +428,8 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     p.ebound = 0.0009765625f * 1.02f + 3.0f * (float)D * 5.9604645e-8f;
     const int sms = device_sm_count();
     for (int64_t r = SEED_ROWS; r < n;) {
-        int64_t r1 = r * 4;
-        if (r1 > n || n - r1 < r) r1 = n;      // fold a short tail into the last stage
+        int64_t r1 = r * 2;
+        if (r1 > n || n - r1 < r / 2) r1 = n;  // fold a short tail into the last stage
         p.r0 = r; p.r1 = r1;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
