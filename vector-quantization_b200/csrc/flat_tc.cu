@@ -217,6 +217,7 @@ __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, in
 }
 
 constexpr int FIN_THREADS = 256;
+constexpr int FIN_TILE_LD = 36;             // padded tile row (floats): conflict-free 128-bit stores and loads
 // One CTA per query: exact keys of the listed rows (the SIMT kernel's arithmetic), merged with the running list.
 template <int CAP>
 __global__ void __launch_bounds__(FIN_THREADS)
@@ -260,31 +261,61 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
         tk.offer(key != KEY_INF, key_value(key), key_id(key));
     }
     const uint32_t* list = cand + (size_t)q * cap;
-    const uint32_t rounds = (cnt + FIN_THREADS - 1) / FIN_THREADS;
-    for (uint32_t itr = 0; itr < rounds; ++itr) {
-        const uint32_t e = itr * FIN_THREADS + threadIdx.x;
+    // One warp per group of 32 candidates. The rows are fetched with coalesced 128-byte
+    // requests (8 lanes x float4 per row chunk, four rows per instruction) into a padded
+    // warp-private tile and each lane then runs the FMA chain of ITS candidate over the tile
+    // row: the chain is the SIMT kernel's (d = 0 .. D-1, one accumulator), only the loads
+    // are shared. (A lane-per-row gather moved 32-byte sectors for 16-byte loads and sat on
+    // the L2 sector rate.)
+    float* tile = reinterpret_cast<float*>(mbuf + n2) + w * (32 * FIN_TILE_LD);
+    const uint32_t ngroups = (cnt + 31) / 32;
+    const int sub = lane >> 3, l8 = lane & 7;
+    const int nchunk = D / 32;
+    for (uint32_t g = w; g < ngroups; g += FIN_THREADS / 32) {
+        const uint32_t e = g * 32 + lane;
         const bool valid = e < cnt;
-        float key = 0.f;
-        uint32_t row = 0;
-        if (valid) {
-            row = seed_rows ? e : list[e];
-            const float4* xr = reinterpret_cast<const float4*>(x + (int64_t)row * ldx);
-            const float rs = row_scale ? row_scale[row] : 1.f;
-            float acc = 0.f;
-            for (int d4 = 0; d4 < D / 4; ++d4) {
-                float4 xv = __ldg(xr + d4);
+        const uint32_t row = valid ? (seed_rows ? e : list[e]) : 0u;
+        const float rs = (row_scale && valid) ? row_scale[row] : 1.f;
+        const float4* src[8];
+        bool ok[8];
+        float4 cur[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t rj = __shfl_sync(FULL_MASK, row, 4 * j + sub);
+            ok[j] = g * 32 + 4 * j + sub < cnt;
+            src[j] = reinterpret_cast<const float4*>(x + (int64_t)rj * ldx) + l8;
+            cur[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok[j]) cur[j] = __ldg(src[j]);
+        }
+        float acc = 0.f;
+        for (int c = 0; c < nchunk; ++c) {
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(tile + (4 * j + sub) * FIN_TILE_LD + 4 * l8) = cur[j];
+            if (c + 1 < nchunk) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (ok[j]) cur[j] = __ldg(src[j] + (c + 1) * 8);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float4 xv = *reinterpret_cast<const float4*>(tile + lane * FIN_TILE_LD + 4 * i);
                 if (row_scale) {
                     xv.x = __fmul_rn(xv.x, rs); xv.y = __fmul_rn(xv.y, rs);
                     xv.z = __fmul_rn(xv.z, rs); xv.w = __fmul_rn(xv.w, rs);
                 }
-                acc = __fmaf_rn(qs[4 * d4], xv.x, acc);
-                acc = __fmaf_rn(qs[4 * d4 + 1], xv.y, acc);
-                acc = __fmaf_rn(qs[4 * d4 + 2], xv.z, acc);
-                acc = __fmaf_rn(qs[4 * d4 + 3], xv.w, acc);
+                const float4 qv = *reinterpret_cast<const float4*>(qs + c * 32 + 4 * i);
+                acc = __fmaf_rn(qv.x, xv.x, acc);
+                acc = __fmaf_rn(qv.y, xv.y, acc);
+                acc = __fmaf_rn(qv.z, xv.z, acc);
+                acc = __fmaf_rn(qv.w, xv.w, acc);
             }
-            if (metric == B200VQ_METRIC_L2) key = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(qn, xnorm[row])), 0.f);
-            else key = -acc;
         }
+        float key;
+        if (metric == B200VQ_METRIC_L2) key = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(qn, valid ? xnorm[row] : 0.f)), 0.f);
+        else key = -acc;
         tk.offer(valid, key, row);
     }
     block_emit_topk<CAP>(tk, mbuf, n2, k, best);
@@ -368,7 +399,8 @@ static int finish_launch(const float* x, int64_t ldx, int D, const float* xnorm,
                          uint32_t* count, uint32_t cap, uint64_t* running, float* thr, uint32_t* flags, int last,
                          float* out_vals, uint32_t* out_ids, cudaStream_t st, uint32_t seed_rows = 0) {
     const int n2 = next_pow2((FIN_THREADS / 32) * k);
-    const size_t smem = (((size_t)D * 4 + 15) & ~(size_t)15) + (size_t)((FIN_THREADS / 32) * CAP + n2) * 8;
+    const size_t smem = (((size_t)D * 4 + 15) & ~(size_t)15) + (size_t)((FIN_THREADS / 32) * CAP + n2) * 8 +
+                        (size_t)(FIN_THREADS / 32) * 32 * FIN_TILE_LD * 4;
     VQ_CUDA(cudaFuncSetAttribute(flat_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     flat_finish_kernel<CAP><<<nq, FIN_THREADS, smem, st>>>(x, ldx, D, xnorm, row_scale, queries, ldq, metric, k, cand,
                                                          count, cap, running, thr, flags, last, out_vals, out_ids,
