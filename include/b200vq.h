@@ -180,6 +180,20 @@ int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const flo
                         int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
                         size_t scratch_bytes, void* stream);
 
+/* fp32-accurate rotation GEMM on the tensor cores: Y (n x N) = X (n x K) . W^T, W (N x K) row-major.
+ * Replaces the sgemm of faiss OPQMatrix.apply / reverse_transform (optimized_product_quantization.py:30-34)
+ * and the SAQ engine's segment rotations (external/saq/include/saq/quantizer.h:66-72). Three TF32
+ * product passes over round-to-nearest hi/lo operand splits, fp32 accumulation: error of a few 2^-22
+ * per product. _prepare splits W once into `wsplit` (rotate_tc_scratch_bytes(N, K) bytes, 16-byte
+ * aligned, reusable for every batch); _applies tells whether a shape is covered (K % 32 == 0,
+ * ldx % 4 == 0, ldy % 4 == 0); x, y 16-byte aligned. */
+int b200vq_rotate_tc_applies(int64_t n, int64_t ldx, int64_t N, int64_t K, int64_t ldy);
+size_t b200vq_rotate_tc_scratch_bytes(int64_t N, int64_t K);
+int b200vq_rotate_tc_prepare(const float* w, int64_t ldw, int64_t N, int64_t K, void* wsplit,
+                             size_t wsplit_bytes, void* stream);
+int b200vq_rotate_tc(const float* x, int64_t n, int64_t ldx, const void* wsplit, int64_t N, int64_t K,
+                     float* y, int64_t ldy, void* stream);
+
 /* Row squared norms (compute_exact_norms, exact_search.py:20-24, before the sqrt). */
 int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out, void* stream);
 

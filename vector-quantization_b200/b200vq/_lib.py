@@ -49,6 +49,10 @@ SIGNATURES = {
     "b200vq_flat_topk": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_flat_topk_tc_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_flat_topk_tc": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_rotate_tc_applies": (_i, [_i64, _i64, _i64, _i64, _i64]),
+    "b200vq_rotate_tc_scratch_bytes": (_sz, [_i64, _i64]),
+    "b200vq_rotate_tc_prepare": (_i, [_p, _i64, _i64, _i64, _p, _sz, _p]),
+    "b200vq_rotate_tc": (_i, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _p]),
     "b200vq_row_sqnorms": (_i, [_p, _i64, _i64, _i, _p, _p]),
     "b200vq_topk_merge": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "b200vq_sq_minmax": (_i, [_p, _i64, _i64, _i, _p, _p, _p]),

@@ -226,6 +226,42 @@ def pq_codes_to_scan_layout(codes: torch.Tensor) -> torch.Tensor:
     return out
 
 
+class RotationTC:
+    """W (N, K) prepared for y = x W^T on the tensor cores (three TF32 passes over hi/lo operand
+    splits, fp32-accurate; csrc/rotate_tc.cu). The split of W is made once and reused."""
+
+    def __init__(self, w: torch.Tensor):
+        require_cuda()
+        w = _chk(w, torch.float32, "w")
+        wptr, self.N, ldw, self.K = _rows(w, "w")
+        lib = _lib.load()
+        self.wsplit = torch.empty(lib.b200vq_rotate_tc_scratch_bytes(self.N, self.K), dtype=torch.uint8,
+                                  device=w.device)
+        check(lib.b200vq_rotate_tc_prepare(wptr, ldw, self.N, self.K, self.wsplit.data_ptr(), self.wsplit.numel(),
+                                           _stream()), "rotate_tc_prepare")
+
+    def applies(self, x: torch.Tensor) -> bool:
+        if x.dim() != 2 or x.shape[1] != self.K or x.dtype != torch.float32 or x.shape[0] == 0:
+            return False
+        _, n, ldx, _ = _rows(x, "x")
+        return bool(_lib.load().b200vq_rotate_tc_applies(n, ldx, self.N, self.K, (self.N + 3) // 4 * 4)) and \
+            x.data_ptr() % 16 == 0
+
+    def __call__(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        x = _chk(x, torch.float32, "x")
+        xptr, n, ldx, K = _rows(x, "x")
+        if K != self.K:
+            raise B200VQError(f"rotate_tc: x has {K} columns, W has {self.K}")
+        if out is None:
+            ldy = (self.N + 3) // 4 * 4
+            buf = torch.empty((n, ldy), dtype=torch.float32, device=x.device)
+            out = buf[:, :self.N]
+        yptr, _, ldy, _ = _rows(out, "out")
+        check(_lib.load().b200vq_rotate_tc(xptr, n, ldx, self.wsplit.data_ptr(), self.N, self.K, yptr, ldy, _stream()),
+              "rotate_tc")
+        return out
+
+
 def row_sqnorms(x: torch.Tensor) -> torch.Tensor:
     _chk(x, torch.float32, "x")
     ptr, n, ld, D = _rows(x, "x")

@@ -76,9 +76,33 @@ def random_rotation(D: int, seed: int) -> np.ndarray:
     return np.ascontiguousarray(Qm.astype(np.float32))
 
 
-def rotate(x: torch.Tensor, A: torch.Tensor, transpose: bool = True) -> torch.Tensor:
-    """y = x A^T (OPQMatrix.apply) or y = x A (reverse_transform). Plain library GEMM in
-    strict fp32 (TF32 off) so the rotated values match an fp32 sgemm."""
+_rot_cache: dict = {}
+TC_ROTATE_MIN_ROWS = 1024
+
+
+def _rotation_tc(A: torch.Tensor, transpose: bool) -> ops.RotationTC:
+    """RotationTC for y = x A^T (transpose) or y = x A, cached on the matrix's storage and version."""
+    key = (A.data_ptr(), A._version, tuple(A.shape), transpose)
+    r = _rot_cache.get(key)
+    if r is None:
+        if len(_rot_cache) > 8:
+            _rot_cache.clear()
+        r = _rot_cache[key] = ops.RotationTC(A if transpose else A.t().contiguous())
+    return r
+
+
+def rotate(x: torch.Tensor, A: torch.Tensor, transpose: bool = True, impl: str = "auto") -> torch.Tensor:
+    """y = x A^T (OPQMatrix.apply) or y = x A (reverse_transform), fp32-accurate.
+    impl "tc": the three-pass TF32 tensor-core GEMM (csrc/rotate_tc.cu); "lib": the library sgemm
+    in strict fp32 (TF32 off); "auto": tc for batches of >= 1024 rows it covers, else lib."""
+    if impl not in ("auto", "tc", "lib"):
+        raise ValueError(f"rotate: unknown impl {impl!r}")
+    if impl != "lib" and x.is_cuda and (impl == "tc" or x.shape[0] >= TC_ROTATE_MIN_ROWS):
+        r = _rotation_tc(A, transpose)
+        if r.applies(x):
+            return r(x)
+        if impl == "tc":
+            raise ops.B200VQError("rotate: shape not covered by the tensor-core rotation")
     prev = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = False
     try:
