@@ -57,6 +57,53 @@ def test_sq_bit_exact_vs_oracle_at_size(T, n, D):
         assert np.array_equal(rec, osq.sq_decompress(ref, vmin, vmax, bits))
 
 
+@pytest.mark.parametrize("bits", [4, 8, 16])
+def test_sq_constant_division_is_ieee_division(T, bits):
+    """The vector kernels divide by a per-column constant with reciprocal + one correction step
+    (csrc/sq.cu div_const); the codes must be those of IEEE division on every input: 2^26 random
+    (x - min, range) pairs with ranges from 1e-7 to 1e7, level boundaries, out-of-range and special values."""
+    torch = T.torch
+    g = torch.Generator(device="cuda").manual_seed(100 + bits)
+    n, D = 1 << 14, 4096
+    lm1 = float((1 << bits) - 1)
+    vmin = (torch.rand(D, generator=g, device="cuda") - 0.5) * torch.pow(10.0, torch.rand(D, generator=g, device="cuda") * 8 - 4)
+    span = torch.pow(10.0, torch.rand(D, generator=g, device="cuda") * 14 - 7)
+    vmax = vmin + span
+    u = torch.rand((n, D), generator=g, device="cuda") * 1.2 - 0.1
+    # a third of the rows sit on level boundaries (k + 0.5) / (L - 1), where rounding decides the code
+    kk = torch.randint(0, int(lm1), (n // 3, D), generator=g, device="cuda").float()
+    u[: n // 3] = (kk + 0.5) / lm1
+    x = vmin + u * (vmax - vmin)
+    x[-1, :8] = torch.tensor([float("inf"), float("-inf"), float("nan"), 3e38, -3e38, 0.0, 1e-42, -1e-42], device="cuda")
+    vmin[8], vmax[8] = 0.0, float("inf")            # divisor not finite: per-column IEEE fallback
+    vmin[9], vmax[9] = -3e38, 3e38                  # range overflows
+    rng = (vmax - vmin) + 1e-8
+    ref = torch.nan_to_num(torch.round(((x - vmin) / rng) * lm1), nan=0.0, posinf=lm1, neginf=0.0).clamp(0, lm1)
+    got = T.ops_sq.sq_encode(x, vmin, vmax, bits)
+    if bits == 4:
+        want = (ref[:, 0::2].to(torch.uint8) << 4) | ref[:, 1::2].to(torch.uint8)
+        assert torch.equal(got, want)
+    elif bits == 8:
+        assert torch.equal(got, ref.to(torch.uint8))
+    else:
+        assert torch.equal(got.to(torch.int32) & 0xFFFF, ref.to(torch.int32))
+    # decode: every level of every width against separate IEEE ops
+    L = 1 << bits
+    q = (torch.arange(L * 64, device="cuda") % L).reshape(-1, 64)
+    vmn, vmx = vmin[:64].contiguous(), vmax[:64].contiguous()
+    rr = (vmx - vmn) + 1e-8
+    if bits == 4:
+        codes = ((q[:, 0::2] << 4) | q[:, 1::2]).to(torch.uint8)
+    elif bits == 8:
+        codes = q.to(torch.uint8)
+    else:
+        codes = q.to(torch.int16)
+    rec = T.ops_sq.sq_decode(codes, vmn, vmx, bits, 64)
+    # tensor / tensor: torch turns tensor / python-scalar into a multiplication by the reciprocal
+    want = (q.float() / torch.full_like(rr, lm1)) * rr + vmn
+    assert torch.equal(torch.nan_to_num(rec, nan=-1.0), torch.nan_to_num(want, nan=-1.0))
+
+
 def test_sq_minmax_accumulates_over_batches_and_saturates(T):
     X = make_data(3000, 64, 3, normalize=False)
     a = T.ops_sq.sq_minmax(T.dev(X[:1000]))

@@ -99,25 +99,6 @@ __global__ void sq_encode_kernel(const float* __restrict__ x, int64_t n, int64_t
     }
 }
 
-// Vector 8-bit encode: 4 dims per thread, 128-bit load, 32-bit store.
-// grid.y strides rows so that the per-column parameters stay in registers.
-__global__ void sq_encode8_v4_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
-                                     const float* __restrict__ vmin, const float* __restrict__ vmax,
-                                     uint8_t* __restrict__ codes) {
-    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;  // group of 4 columns
-    if (c4 * 4 >= D) return;
-    const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
-    const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
-    const float r0 = sq_range(mn.x, mx.x), r1 = sq_range(mn.y, mx.y), r2 = sq_range(mn.z, mx.z),
-                r3 = sq_range(mn.w, mx.w);
-    for (int64_t row = blockIdx.y; row < n; row += gridDim.y) {
-        float4 v = ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4);
-        uint32_t q = sq_quant(v.x, mn.x, r0, 255.f) | (sq_quant(v.y, mn.y, r1, 255.f) << 8) |
-                     (sq_quant(v.z, mn.z, r2, 255.f) << 16) | (sq_quant(v.w, mn.w, r3, 255.f) << 24);
-        reinterpret_cast<uint32_t*>(codes + row * (int64_t)D)[c4] = q;
-    }
-}
-
 template <int BITS>
 __global__ void sq_decode_kernel(const void* __restrict__ codes, int64_t n, int D,
                                  const float* __restrict__ vmin, const float* __restrict__ vmax,
@@ -142,23 +123,123 @@ __global__ void sq_decode_kernel(const void* __restrict__ codes, int64_t n, int 
     }
 }
 
-__global__ void sq_decode8_v4_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
-                                     const float* __restrict__ vmin, const float* __restrict__ vmax,
-                                     float* __restrict__ out, int64_t ldo) {
+// ------------------------------------------------------- vector kernels ---
+// Division by a per-column constant, correctly rounded like __fdiv_rn but without the per-element
+// reciprocal: with r = RN(1/b) precomputed, q0 = RN(a r), rem = a - q0 b (exact, one FMA),
+// q1 = RN(q0 + rem r) is the IEEE quotient (Markstein's correction step) whenever every quantity
+// is a normal number. Where it is not, the quantiser's result does not depend on the low bits:
+// |q0| >= 2^100 saturates after the clamp either way (q0 is returned so that inf stays inf instead
+// of turning into NaN), a quotient below 2^-100 rounds to level 0 either way, NaN stays NaN.
+// Columns whose divisor is not a normal number in [2^-100, 2^100] take __fdiv_rn.
+// tests/test_gpu_sq.py checks the codes against IEEE division on 2^26 random (a, b) pairs per width.
+struct DivConst {
+    float b, r;
+    bool fast;
+};
+__device__ __forceinline__ DivConst make_div(float b) {
+    DivConst c;
+    c.b = b;
+    c.r = __frcp_rn(b);
+    c.fast = b >= 7.8886091e-31f && b <= 1.2676506e30f;   // [2^-100, 2^100]; false for NaN
+    return c;
+}
+__device__ __forceinline__ float div_const(float a, const DivConst& c) {
+    if (!c.fast) return __fdiv_rn(a, c.b);
+    const float q0 = __fmul_rn(a, c.r);
+    const float rem = __fmaf_rn(-q0, c.b, a);
+    const float q1 = __fmaf_rn(rem, c.r, q0);
+    return fabsf(q0) < 1.2676506e30f ? q1 : q0;
+}
+__device__ __forceinline__ uint32_t sq_quant_c(float x, float mn, const DivConst& c, float lm1) {
+    float q = rintf(__fmul_rn(div_const(__fsub_rn(x, mn), c), lm1));
+    q = fminf(fmaxf(q, 0.f), lm1);  // NaN -> 0 via fmaxf
+    return (uint32_t)q;
+}
+
+// Four consecutive columns per thread (their constants live in registers), rows strided over
+// grid.y and unrolled by four so that four 128-bit loads are in flight per thread.
+// BITS = 4: 2 output bytes per row and thread, 8: 4 bytes, 16: 8 bytes.
+template <int BITS>
+__global__ void __launch_bounds__(128)
+sq_encode_vec_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D, const float* __restrict__ vmin,
+                     const float* __restrict__ vmax, uint8_t* __restrict__ codes) {
     const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
     if (c4 * 4 >= D) return;
+    constexpr float lm1 = (float)((1 << BITS) - 1);
+    const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
+    const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
+    const DivConst d0 = make_div(sq_range(mn.x, mx.x)), d1 = make_div(sq_range(mn.y, mx.y)),
+                   d2 = make_div(sq_range(mn.z, mx.z)), d3 = make_div(sq_range(mn.w, mx.w));
+    const int64_t row_bytes = BITS == 4 ? D / 2 : (BITS == 8 ? D : 2 * (int64_t)D);
+    auto put = [&](int64_t row, const float4& v) {
+        const uint32_t q0 = sq_quant_c(v.x, mn.x, d0, lm1), q1 = sq_quant_c(v.y, mn.y, d1, lm1),
+                       q2 = sq_quant_c(v.z, mn.z, d2, lm1), q3 = sq_quant_c(v.w, mn.w, d3, lm1);
+        uint8_t* o = codes + row * row_bytes;
+        if (BITS == 4) {
+            reinterpret_cast<uint16_t*>(o)[c4] = (uint16_t)(((q0 << 4) | q1) | (((q2 << 4) | q3) << 8));
+        } else if (BITS == 8) {
+            reinterpret_cast<uint32_t*>(o)[c4] = q0 | (q1 << 8) | (q2 << 16) | (q3 << 24);
+        } else {
+            reinterpret_cast<uint2*>(o)[c4] = make_uint2(q0 | (q1 << 16), q2 | (q3 << 16));
+        }
+    };
+    const int64_t step = gridDim.y;
+    int64_t row = blockIdx.y;
+    for (; row + 3 * step < n; row += 4 * step) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = ld_stream_f4(reinterpret_cast<const float4*>(x + (row + u * step) * ldx) + c4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) put(row + u * step, v[u]);
+    }
+    for (; row < n; row += step) put(row, ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4));
+}
+
+template <int BITS>
+__global__ void __launch_bounds__(128)
+sq_decode_vec_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, const float* __restrict__ vmin,
+                     const float* __restrict__ vmax, float* __restrict__ out, int64_t ldo) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c4 * 4 >= D) return;
+    constexpr float lm1 = (float)((1 << BITS) - 1);
     const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
     const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
     const float r0 = sq_range(mn.x, mx.x), r1 = sq_range(mn.y, mx.y), r2 = sq_range(mn.z, mx.z),
                 r3 = sq_range(mn.w, mx.w);
-    for (int64_t row = blockIdx.y; row < n; row += gridDim.y) {
-        uint32_t q = __ldg(reinterpret_cast<const uint32_t*>(codes + row * (int64_t)D) + c4);
-        float4 o;
-        o.x = sq_dequant(q & 0xff, mn.x, r0, 255.f);
-        o.y = sq_dequant((q >> 8) & 0xff, mn.y, r1, 255.f);
-        o.z = sq_dequant((q >> 16) & 0xff, mn.z, r2, 255.f);
-        o.w = sq_dequant(q >> 24, mn.w, r3, 255.f);
-        reinterpret_cast<float4*>(out + row * ldo)[c4] = o;
+    const DivConst dl = make_div(lm1);   // q / (L - 1): exact-division constant, every q checked by the tests
+    const int64_t row_bytes = BITS == 4 ? D / 2 : (BITS == 8 ? D : 2 * (int64_t)D);
+    auto get = [&](int64_t row, uint32_t (&q)[4]) {
+        const uint8_t* o = codes + row * row_bytes;
+        if (BITS == 4) {
+            const uint32_t w = __ldg(reinterpret_cast<const uint16_t*>(o) + c4);
+            q[0] = (w >> 4) & 0xf; q[1] = w & 0xf; q[2] = (w >> 12) & 0xf; q[3] = (w >> 8) & 0xf;
+        } else if (BITS == 8) {
+            const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(o) + c4);
+            q[0] = w & 0xff; q[1] = (w >> 8) & 0xff; q[2] = (w >> 16) & 0xff; q[3] = w >> 24;
+        } else {
+            const uint2 w = __ldg(reinterpret_cast<const uint2*>(o) + c4);
+            q[0] = w.x & 0xffff; q[1] = w.x >> 16; q[2] = w.y & 0xffff; q[3] = w.y >> 16;
+        }
+    };
+    auto deq = [&](uint32_t q, float m, float range) {
+        return __fadd_rn(__fmul_rn(div_const((float)q, dl), range), m);
+    };
+    const int64_t step = gridDim.y;
+    int64_t row = blockIdx.y;
+    for (; row + 3 * step < n; row += 4 * step) {
+        uint32_t q[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) get(row + u * step, q[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            reinterpret_cast<float4*>(out + (row + u * step) * ldo)[c4] =
+                make_float4(deq(q[u][0], mn.x, r0), deq(q[u][1], mn.y, r1), deq(q[u][2], mn.z, r2), deq(q[u][3], mn.w, r3));
+    }
+    for (; row < n; row += step) {
+        uint32_t q[4];
+        get(row, q);
+        reinterpret_cast<float4*>(out + row * ldo)[c4] =
+            make_float4(deq(q[0], mn.x, r0), deq(q[1], mn.y, r1), deq(q[2], mn.z, r2), deq(q[3], mn.w, r3));
     }
 }
 
@@ -272,21 +353,20 @@ extern "C" int b200vq_sq_encode(const float* x, int64_t n, int64_t ldx, int D, c
                  bits);
     if (n == 0) return B200VQ_OK;
     cudaStream_t st = as_stream(stream);
-    if (bits == 8) {
-        bool v4 = (D % 4 == 0) && (ldx % 4 == 0) && (((uintptr_t)x & 15) == 0) &&
-                  (((uintptr_t)vmin & 15) == 0) && (((uintptr_t)vmax & 15) == 0) &&
-                  (((uintptr_t)codes & 3) == 0);
-        if (v4) {
-            int gx = (D / 4 + 127) / 128;
-            int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
-            if (gy > n) gy = n;
-            if (gy > 65535) gy = 65535;
-            sq_encode8_v4_kernel<<<dim3(gx, (unsigned)gy), 128, 0, st>>>(
-                x, n, ldx, D, vmin, vmax, reinterpret_cast<uint8_t*>(codes));
-        } else {
-            sq_encode_kernel<8><<<sq_grid(n * (int64_t)D, 256), 256, 0, st>>>(x, n, ldx, D, vmin,
-                                                                              vmax, codes);
-        }
+    const bool vec = (D % 4 == 0) && (ldx % 4 == 0) && (((uintptr_t)x & 15) == 0) && (((uintptr_t)vmin & 15) == 0) &&
+                     (((uintptr_t)vmax & 15) == 0) && (((uintptr_t)codes & 15) == 0);
+    if (vec) {
+        int gx = (D / 4 + 127) / 128;
+        int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+        if (gy > n) gy = n;
+        if (gy > 65535) gy = 65535;
+        const dim3 grid(gx, (unsigned)gy);
+        uint8_t* c8 = reinterpret_cast<uint8_t*>(codes);
+        if (bits == 4) sq_encode_vec_kernel<4><<<grid, 128, 0, st>>>(x, n, ldx, D, vmin, vmax, c8);
+        else if (bits == 8) sq_encode_vec_kernel<8><<<grid, 128, 0, st>>>(x, n, ldx, D, vmin, vmax, c8);
+        else sq_encode_vec_kernel<16><<<grid, 128, 0, st>>>(x, n, ldx, D, vmin, vmax, c8);
+    } else if (bits == 8) {
+        sq_encode_kernel<8><<<sq_grid(n * (int64_t)D, 256), 256, 0, st>>>(x, n, ldx, D, vmin, vmax, codes);
     } else if (bits == 4) {
         sq_encode_kernel<4><<<sq_grid(n * (int64_t)((D + 1) / 2), 256), 256, 0, st>>>(
             x, n, ldx, D, vmin, vmax, codes);
@@ -307,20 +387,20 @@ extern "C" int b200vq_sq_decode(const void* codes, int64_t n, int D, const float
     if (n == 0) return B200VQ_OK;
     cudaStream_t st = as_stream(stream);
     int g = sq_grid(n * (int64_t)D, 256);
-    if (bits == 8) {
-        bool v4 = (D % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
-                  (((uintptr_t)vmin & 15) == 0) && (((uintptr_t)vmax & 15) == 0) &&
-                  (((uintptr_t)codes & 3) == 0);
-        if (v4) {
-            int gx = (D / 4 + 127) / 128;
-            int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
-            if (gy > n) gy = n;
-            if (gy > 65535) gy = 65535;
-            sq_decode8_v4_kernel<<<dim3(gx, (unsigned)gy), 128, 0, st>>>(
-                reinterpret_cast<const uint8_t*>(codes), n, D, vmin, vmax, out, ldo);
-        } else {
-            sq_decode_kernel<8><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
-        }
+    const bool vec = (D % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) && (((uintptr_t)vmin & 15) == 0) &&
+                     (((uintptr_t)vmax & 15) == 0) && (((uintptr_t)codes & 15) == 0);
+    if (vec) {
+        int gx = (D / 4 + 127) / 128;
+        int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+        if (gy > n) gy = n;
+        if (gy > 65535) gy = 65535;
+        const dim3 grid(gx, (unsigned)gy);
+        const uint8_t* c8 = reinterpret_cast<const uint8_t*>(codes);
+        if (bits == 4) sq_decode_vec_kernel<4><<<grid, 128, 0, st>>>(c8, n, D, vmin, vmax, out, ldo);
+        else if (bits == 8) sq_decode_vec_kernel<8><<<grid, 128, 0, st>>>(c8, n, D, vmin, vmax, out, ldo);
+        else sq_decode_vec_kernel<16><<<grid, 128, 0, st>>>(c8, n, D, vmin, vmax, out, ldo);
+    } else if (bits == 8) {
+        sq_decode_kernel<8><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
     } else if (bits == 4) {
         sq_decode_kernel<4><<<g, 256, 0, st>>>(codes, n, D, vmin, vmax, out, ldo);
     } else {
