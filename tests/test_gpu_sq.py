@@ -144,3 +144,21 @@ def test_saq_odd_widths_and_uniform_mode(T):
         fill = np.where(plan["dim_bits"] == 0, plan["mean"], plan["vmin"]).astype(np.float32)
         rec = T.ops_sq.saq_decode(codes, T.dev(fill), T.dev(plan["vmax"]), bits, off, D).cpu().numpy()
         assert np.array_equal(rec, osq.saq_decompress(ref, plan)), allowed
+
+
+def test_saq_decode_trailing_zero_width_dimensions(T):
+    """Dimensions of width 0 at the end of the row have bit_offset == total bits (one past the last code word)."""
+    torch = T.torch
+    D, n = 256, 3000
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = torch.randn((n, D), generator=g, device="cuda")
+    vmin, vmax = T.ops_sq.sq_minmax(x)
+    bits = np.repeat(np.array([8, 4, 0, 0], dtype=np.int32), D // 4)
+    off = np.concatenate([[0], np.cumsum(bits)]).astype(np.int32)
+    code_bytes = int(off[-1] + 7) // 8
+    db, bo = T.dev(bits), T.dev(off)
+    codes = T.ops_sq.saq_encode(x, vmin, vmax, db, bo, code_bytes)
+    rec = T.ops_sq.saq_decode(codes, vmin, vmax, db, bo, D)
+    assert torch.equal(rec[:, D // 2:], vmin[D // 2:].expand(n, -1))          # 0-bit dims decode to the fill value
+    err = (rec[:, : D // 4] - x[:, : D // 4]).abs().max().item()
+    assert err <= (vmax - vmin)[: D // 4].max().item() / 255 * 0.51

@@ -88,6 +88,11 @@ __device__ __forceinline__ uint4 ld_stream_u4(const uint4* p) {
                  : "l"(p));
     return r;
 }
+__device__ __forceinline__ float ld_stream_f32(const float* p) {
+    float r;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
     float4 r;
     asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"

@@ -31,25 +31,45 @@ __global__ void rabitq1_encode_kernel(const float* __restrict__ x, int64_t n, in
     const int nbytes = (D + 7) >> 3;
     const int code_size = nbytes + 8;
     const float inv_d_sqrt = 1.0f / sqrtf((float)D);
+    const bool word_rows = (code_size & 3) == 0 && ((reinterpret_cast<uintptr_t>(codes) & 3) == 0);
     for (int64_t row = wid; row < n; row += nw) {
         const float* xr = x + row * ldx;
         uint8_t* code = codes + row * (int64_t)code_size;
         float norm = 0.f, orl2 = 0.f, dp = 0.f;
-        for (int j0 = 0; j0 < D; j0 += 32) {
-            int j = j0 + lane;
-            float v = 0.f, omc = 0.f;
-            if (j < D) {
-                v = xr[j];
-                omc = v - (centroid ? centroid[j] : 0.f);
+        // eight 128-byte loads in flight per warp; the per-lane accumulation order (j = lane, lane + 32, ...)
+        // is the one the oracle restates, only the loads are batched
+        for (int j0 = 0; j0 < D; j0 += 256) {
+            float vv[8], cc[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = j0 + 32 * u + lane;
+                vv[u] = (j < D) ? ld_stream_f32(xr + j) : 0.f;
+                cc[u] = (j < D && centroid) ? __ldg(centroid + j) : 0.f;
             }
-            norm = __fmaf_rn(omc, omc, norm);
-            orl2 = __fmaf_rn(v, v, orl2);
-            bool xb = omc > 0.f;
-            dp += fabsf(omc);
-            unsigned word = __ballot_sync(FULL_MASK, xb);
-            if (lane < 4) {
-                int byte = (j0 >> 3) + lane;
-                if (byte < nbytes) code[byte] = (uint8_t)(word >> (8 * lane));
+            unsigned mine = 0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = j0 + 32 * u + lane;
+                if (j0 + 32 * u < D) {       // warp-uniform
+                    const float v = vv[u];
+                    const float omc = (j < D) ? v - cc[u] : 0.f;
+                    norm = __fmaf_rn(omc, omc, norm);
+                    orl2 = __fmaf_rn(v, v, orl2);
+                    dp += fabsf(omc);
+                    const unsigned word = __ballot_sync(FULL_MASK, omc > 0.f);
+                    if (lane == u) mine = word;
+                }
+            }
+            // lane u holds the sign word of dimensions [j0 + 32 u, j0 + 32 u + 32)
+            const int byte0 = (j0 >> 3) + 4 * lane;
+            if (lane < 8 && byte0 < nbytes) {
+                if (word_rows && byte0 + 4 <= nbytes) {
+                    *reinterpret_cast<uint32_t*>(code + byte0) = mine;
+                } else {
+#pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                        if (byte0 + b < nbytes) code[byte0 + b] = (uint8_t)(mine >> (8 * b));
+                }
             }
         }
         for (int o = 16; o > 0; o >>= 1) {
@@ -84,23 +104,45 @@ __device__ __forceinline__ float load_f32_unaligned(const uint8_t* p) {
     return __uint_as_float(u);
 }
 
+// One warp per row: the two possible magnitudes (bit - 0.5) * dp_multiplier * 2 * inv_d_sqrt are formed
+// once per row with faiss' left-to-right products, then every lane selects by sign bit and adds the
+// centroid for four consecutive dimensions (128-bit stores when the output rows are aligned).
 __global__ void rabitq1_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
                                       const float* __restrict__ centroid, float* __restrict__ out,
                                       int64_t ldo) {
     const int nbytes = (D + 7) >> 3;
     const int code_size = nbytes + 8;
     const float inv_d_sqrt = 1.0f / sqrtf((float)D);
-    const int64_t total = n * (int64_t)D;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t row = e / D;
-        int j = (int)(e - row * D);
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const bool vec = (D % 4 == 0) && (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0) &&
+                     (!centroid || (reinterpret_cast<uintptr_t>(centroid) & 15) == 0);
+    for (int64_t row = wid; row < n; row += nw) {
         const uint8_t* code = codes + row * (int64_t)code_size;
-        float dpm = load_f32_unaligned(code + nbytes + 4);
-        float bit = ((code[j >> 3] >> (j & 7)) & 1) ? 1.f : 0.f;
+        const float dpm = load_f32_unaligned(code + nbytes + 4);
         // (bit - 0.5f) * dp_multiplier * 2 * inv_d_sqrt + c[j], left to right like faiss
-        float v = __fmul_rn(__fmul_rn(__fmul_rn(bit - 0.5f, dpm), 2.f), inv_d_sqrt);
-        out[row * ldo + j] = __fadd_rn(v, centroid ? centroid[j] : 0.f);
+        const float vpos = __fmul_rn(__fmul_rn(__fmul_rn(0.5f, dpm), 2.f), inv_d_sqrt);
+        const float vneg = __fmul_rn(__fmul_rn(__fmul_rn(-0.5f, dpm), 2.f), inv_d_sqrt);
+        float* o = out + row * ldo;
+        if (vec) {
+            for (int j = 4 * lane; j < D; j += 128) {
+                const uint32_t nib = ((uint32_t)__ldg(code + (j >> 3)) >> (j & 4)) & 0xFu;
+                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (centroid) c = __ldg(reinterpret_cast<const float4*>(centroid + j));
+                float4 r;
+                r.x = __fadd_rn((nib & 1u) ? vpos : vneg, c.x);
+                r.y = __fadd_rn((nib & 2u) ? vpos : vneg, c.y);
+                r.z = __fadd_rn((nib & 4u) ? vpos : vneg, c.z);
+                r.w = __fadd_rn((nib & 8u) ? vpos : vneg, c.w);
+                *reinterpret_cast<float4*>(o + j) = r;
+            }
+        } else {
+            for (int j = lane; j < D; j += 32) {
+                const bool bit = (code[j >> 3] >> (j & 7)) & 1;
+                o[j] = __fadd_rn(bit ? vpos : vneg, centroid ? centroid[j] : 0.f);
+            }
+        }
     }
 }
 
@@ -490,7 +532,7 @@ extern "C" int b200vq_rabitq1_decode(const uint8_t* codes, int64_t n, int D, con
                                      float* out, int64_t ldo, void* stream) {
     VQ_CHECK_ARG((codes || n == 0) && (out || n == 0) && n >= 0 && D > 0 && ldo >= D, "rabitq1_decode: bad args");
     if (n == 0) return B200VQ_OK;
-    int64_t g = (n * (int64_t)D + 255) / 256;
+    int64_t g = (n * 32 + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;
     if (g > cap) g = cap;
     rabitq1_decode_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, centroid, out, ldo);

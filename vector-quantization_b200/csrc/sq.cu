@@ -51,6 +51,36 @@ __global__ void sq_minmax_kernel(const float* __restrict__ x, int64_t n, int64_t
     }
 }
 
+// Aligned rows: four columns per thread, rows strided over grid.y, four 128-bit loads in flight.
+__global__ void __launch_bounds__(128)
+sq_minmax_vec_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D, float* __restrict__ vmin,
+                     float* __restrict__ vmax) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c4 * 4 >= D) return;
+    const float inf = __int_as_float(0x7f800000);
+    float4 mn = make_float4(inf, inf, inf, inf), mx = make_float4(-inf, -inf, -inf, -inf);
+    auto acc = [&](const float4& v) {
+        mn.x = fminf(mn.x, v.x); mn.y = fminf(mn.y, v.y); mn.z = fminf(mn.z, v.z); mn.w = fminf(mn.w, v.w);
+        mx.x = fmaxf(mx.x, v.x); mx.y = fmaxf(mx.y, v.y); mx.z = fmaxf(mx.z, v.z); mx.w = fmaxf(mx.w, v.w);
+    };
+    const int64_t step = gridDim.y;
+    int64_t row = blockIdx.y;
+    for (; row + 3 * step < n; row += 4 * step) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = ld_stream_f4(reinterpret_cast<const float4*>(x + (row + u * step) * ldx) + c4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc(v[u]);
+    }
+    for (; row < n; row += step) acc(ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4));
+    float* pm = vmin + c4 * 4;
+    float* px = vmax + c4 * 4;
+    if (mn.x <= mx.x) { atomic_min_f32(pm + 0, mn.x); atomic_max_f32(px + 0, mx.x); }
+    if (mn.y <= mx.y) { atomic_min_f32(pm + 1, mn.y); atomic_max_f32(px + 1, mx.y); }
+    if (mn.z <= mx.z) { atomic_min_f32(pm + 2, mn.z); atomic_max_f32(px + 2, mx.z); }
+    if (mn.w <= mx.w) { atomic_min_f32(pm + 3, mn.w); atomic_max_f32(px + 3, mx.w); }
+}
+
 __device__ __forceinline__ float sq_range(float mn, float mx) {
     return __fadd_rn(__fsub_rn(mx, mn), 1e-8f);
 }
@@ -318,6 +348,96 @@ __global__ void saq_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, 
     }
 }
 
+// Aligned output rows: four consecutive dimensions per thread (their widths, bit offsets and affine
+// constants live in registers), rows strided over grid.y, two rows in flight. The code bytes of a
+// warp's 128 dimensions are adjacent, so the byte loads coalesce in L1.
+__global__ void __launch_bounds__(128)
+saq_decode_vec_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, const float* __restrict__ vmin,
+                      const float* __restrict__ vmax, const int* __restrict__ dim_bits,
+                      const int* __restrict__ bit_offset, int code_bytes, float* __restrict__ out, int64_t ldo) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c4 * 4 >= D) return;
+    int nb[4], byte[4], shift[4];
+    float mn[4], range[4];
+    DivConst dl[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int d = c4 * 4 + j;
+        nb[j] = dim_bits[d];
+        const int off = bit_offset[d];
+        byte[j] = off >> 3;
+        shift[j] = 16 - ((off & 7) + nb[j]);
+        mn[j] = vmin[d];
+        range[j] = sq_range(mn[j], vmax[d]);
+        dl[j] = make_div((float)((1 << nb[j]) - 1));
+    }
+    // Word path (code rows 4-byte aligned, every width <= 8): the four fields span at most 32 bits, so
+    // two aligned 32-bit loads, byte-swapped into one big-endian 64-bit window, hold all of them.
+    bool words = (code_bytes & 3) == 0 && (reinterpret_cast<uintptr_t>(codes) & 3) == 0;
+    const int w0 = bit_offset[c4 * 4] >> 5;
+    int wsh[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        words = words && nb[j] <= 8;
+        wsh[j] = 64 - ((bit_offset[c4 * 4 + j] - 32 * w0) + nb[j]);
+    }
+    const bool first = w0 < (code_bytes >> 2), second = w0 + 1 < (code_bytes >> 2);   // trailing 0-bit dims sit at the end
+    auto dequant = [&](int j, uint32_t q) {
+        // 0-bit dimensions decode to the fill value the host put in vmin
+        return nb[j] ? __fadd_rn(__fmul_rn(div_const((float)q, dl[j]), range[j]), mn[j]) : mn[j];
+    };
+    const int64_t step = gridDim.y;
+    int64_t row = blockIdx.y;
+    if (words) {
+        auto fetch = [&](int64_t r) {
+            const uint32_t* cw = reinterpret_cast<const uint32_t*>(codes + r * (int64_t)code_bytes) + w0;
+            const uint32_t a = first ? __ldg(cw) : 0u, b2 = second ? __ldg(cw + 1) : 0u;
+            return ((uint64_t)__byte_perm(a, 0, 0x0123) << 32) | __byte_perm(b2, 0, 0x0123);
+        };
+        auto emit = [&](int64_t r, uint64_t win) {
+            float v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = dequant(j, (uint32_t)(win >> (wsh[j] & 63)) & ((1u << nb[j]) - 1u));
+            reinterpret_cast<float4*>(out + r * ldo)[c4] = make_float4(v[0], v[1], v[2], v[3]);
+        };
+        for (; row + 3 * step < n; row += 4 * step) {
+            uint64_t win[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) win[u] = fetch(row + u * step);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) emit(row + u * step, win[u]);
+        }
+        for (; row < n; row += step) emit(row, fetch(row));
+        return;
+    }
+    auto fetch = [&](int64_t r, uint32_t (&w)[4]) {
+        const uint8_t* c = codes + r * (int64_t)code_bytes;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            w[j] = 0;
+            if (nb[j]) w[j] = ((uint32_t)__ldg(c + byte[j]) << 8) | (byte[j] + 1 < code_bytes ? (uint32_t)__ldg(c + byte[j] + 1) : 0u);
+        }
+    };
+    auto emit = [&](int64_t r, const uint32_t (&w)[4]) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = dequant(j, (w[j] >> shift[j]) & ((1u << nb[j]) - 1u));
+        reinterpret_cast<float4*>(out + r * ldo)[c4] = make_float4(v[0], v[1], v[2], v[3]);
+    };
+    for (; row + step < n; row += 2 * step) {
+        uint32_t wa[4], wb[4];
+        fetch(row, wa);
+        fetch(row + step, wb);
+        emit(row, wa);
+        emit(row + step, wb);
+    }
+    for (; row < n; row += step) {
+        uint32_t wa[4];
+        fetch(row, wa);
+        emit(row, wa);
+    }
+}
+
 static inline int sq_grid(int64_t work, int block) {
     int64_t g = (work + block - 1) / block;
     int64_t cap = (int64_t)device_sm_count() * 16;
@@ -334,6 +454,15 @@ extern "C" int b200vq_sq_minmax(const float* x, int64_t n, int64_t ldx, int D, f
                                 float* vmax, void* stream) {
     VQ_CHECK_ARG((x || n == 0) && vmin && vmax && n >= 0 && D > 0 && ldx >= D, "sq_minmax: bad args");
     if (n == 0) return B200VQ_OK;
+    if ((D % 4 == 0) && (ldx % 4 == 0) && (((uintptr_t)x & 15) == 0) && n >= 64) {
+        int gx = (D / 4 + 127) / 128;
+        int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+        if (gy > n) gy = n;
+        if (gy > 65535) gy = 65535;
+        sq_minmax_vec_kernel<<<dim3(gx, (unsigned)gy), 128, 0, as_stream(stream)>>>(x, n, ldx, D, vmin, vmax);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     int gx = (D + 31) / 32;
     int64_t gy = (n + 7) / 8;
     int64_t cap = ((int64_t)device_sm_count() * 8 + gx - 1) / gx;
@@ -430,6 +559,16 @@ extern "C" int b200vq_saq_decode(const uint8_t* codes, int64_t n, int D, const f
                      ldo >= D && code_bytes > 0,
                  "saq_decode: bad args");
     if (n == 0) return B200VQ_OK;
+    if ((D % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0)) {
+        int gx = (D / 4 + 127) / 128;
+        int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+        if (gy > n) gy = n;
+        if (gy > 65535) gy = 65535;
+        saq_decode_vec_kernel<<<dim3(gx, (unsigned)gy), 128, 0, as_stream(stream)>>>(
+            codes, n, D, vmin, vmax, dim_bits, bit_offset, code_bytes, out, ldo);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     saq_decode_kernel<<<sq_grid(n * (int64_t)D, 256), 256, 0, as_stream(stream)>>>(
         codes, n, D, vmin, vmax, dim_bits, bit_offset, code_bytes, out, ldo);
     VQ_LAUNCH_CHECK();
