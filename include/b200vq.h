@@ -276,6 +276,16 @@ int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D, const uint3
                              float* out_vals, uint32_t* out_ids, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* Same scan, same results, with the integer part of the estimator on the tensor cores: the
+ * (row, query) term sum_d bit_d * qv_d is an exact FP8 (E4M3) GEMM of the sign bits with the quantised
+ * query values (tcgen05 kind::f8f6f4, fp32 accumulate), screened against the running top-k thresholds;
+ * survivors get the canonical estimate. Falls back to b200vq_rabitq1_scan_topk for n < 32 768,
+ * D % 64 != 0, qb > 4 or unaligned codes. */
+size_t b200vq_rabitq1_scan_tc_scratch_bytes(int64_t n, int D, int nq, int k);
+int b200vq_rabitq1_scan_topk_tc(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
+                                const float* qfac, int nq, int qb, int metric, int k, float* out_vals,
+                                uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream);
+
 /* ------------------------------------------------ SAQ engine (CAQ) path ---
  * The reference's C++ engine external/saq, reached through SaqEngineAdapter
  * (src/haag_vq/benchmarks/quantizer_adapters.py:113-135): IVF(n, D, K=1).fit / decompress.

@@ -136,7 +136,11 @@ def c4():
     add("C4", "rabitq1_decode", timed(lambda: ops_sq.rabitq1_decode(codes, D, cen)), n, "vectors",
         bytes_=n * (4 * D + D // 8 + 8))
     planes, qfac = ops_sq.rabitq1_prepare_queries(q, cen, 4)
-    add("C4", "rabitq1_scan_topk qb=4 k=10", timed(lambda: ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2")),
+    add("C4", "rabitq1_scan_topk_tc qb=4 k=10", timed(lambda: ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2")),
+        n * nq, "codes", bytes_=float(n) * (D // 8 + 8) * ((nq + 255) // 256), flops=2.0 * n * nq * D,
+        note="query tile 256; FLOP = FP8 tensor work, fraction quoted against TF32 peak/1 (FP8 peak is 4x)")
+    add("C4", "rabitq1_scan_topk simt qb=4 k=10",
+        timed(lambda: ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2", impl="simt"), reps=2, warm=1),
         n * nq, "codes", bytes_=float(n) * (D // 8 + 8) * nq, note="query tile 1")
     del x
     # extended RaBitQ, B = 4: pack / unpack on fp64 rotated rows (the rotation itself is an fp64 library GEMM)

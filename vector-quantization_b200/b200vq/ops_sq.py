@@ -150,13 +150,23 @@ def rabitq1_prepare_queries(queries: torch.Tensor, centroid: torch.Tensor | None
 
 
 def rabitq1_scan_topk(codes: torch.Tensor, D: int, planes: torch.Tensor, qfac: torch.Tensor, qb: int,
-                      k: int, metric):
+                      k: int, metric, impl: str = "auto"):
+    """impl "auto"/"tc": tensor-core scan (csrc/rabitq_tc.cu; it falls back by itself for shapes it does
+    not cover); "simt": the AND+popcount kernel. Same ids and values either way."""
     _chk(codes, torch.uint8, "codes")
     codes = codes.contiguous()
     n = codes.shape[0]
     nq = planes.shape[0]
     lib = _lib.load()
     vals, ids = _topk_out(nq, k, codes.device)
+    if impl not in ("auto", "tc", "simt"):
+        raise ValueError(f"rabitq1_scan_topk: unknown impl {impl!r}")
+    if impl != "simt":
+        sc = scratch(lib.b200vq_rabitq1_scan_tc_scratch_bytes(n, D, nq, k), codes.device, "scan")
+        check(lib.b200vq_rabitq1_scan_topk_tc(codes.data_ptr(), n, D, planes.data_ptr(), qfac.data_ptr(), nq, qb,
+                                              metric_id(metric), k, vals.data_ptr(), ids.data_ptr(), sc.data_ptr(),
+                                              sc.numel(), _stream()), "rabitq1_scan_topk_tc")
+        return vals, ids
     sc = scratch(lib.b200vq_rabitq1_scan_scratch_bytes(n, nq, k), codes.device, "scan")
     check(lib.b200vq_rabitq1_scan_topk(codes.data_ptr(), n, D, planes.data_ptr(), qfac.data_ptr(), nq, qb,
                                        metric_id(metric), k, vals.data_ptr(), ids.data_ptr(), sc.data_ptr(),

@@ -55,6 +55,12 @@ int flat_topk_gated(const float* x, int64_t n, int64_t ldx, int D, const float* 
                     const float* queries, int nq, int64_t ldq, int metric, int k, float* out_vals, uint32_t* out_ids,
                     void* scratch, const uint32_t* gate, cudaStream_t st);
 
+// rabitq.cu: SIMT 1-bit RaBitQ scan restricted to the queries with gate[q] != 0; the gated fallback of
+// the tensor-core scan in rabitq_tc.cu
+int rabitq1_scan_gated(const uint8_t* codes, int64_t n, int D, const uint32_t* planes, const float* qfac, int nq,
+                       int qb, int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
+                       const uint32_t* gate, cudaStream_t st);
+
 // --------------------------------------------------------- device helpers ---
 #ifdef __CUDACC__
 

@@ -16,6 +16,7 @@
 //     rescale factor t, MSB-first B-bit packing with float32 (nrm, t) trailer.
 #include "common.cuh"
 #include "topk.cuh"
+#include "rabitq_est.cuh"
 
 namespace b200vq {
 
@@ -237,9 +238,11 @@ template <int CAP>
 __global__ void __launch_bounds__(256)
     rabitq1_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
                         const uint32_t* __restrict__ planes, const float* __restrict__ qfac, int qb,
-                        int metric, int k, int64_t chunk_rows, uint64_t* __restrict__ part) {
+                        int metric, int k, int64_t chunk_rows, uint64_t* __restrict__ part,
+                        const uint32_t* __restrict__ gate = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+    if (gate && gate[q] == 0) return;   // gated launch: only flagged queries (rabitq_tc.cu fallback)
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int W = (D + 31) >> 5;
     const int nbytes = (D + 7) >> 3;
@@ -300,11 +303,7 @@ __global__ void __launch_bounds__(256)
             }
             float f0 = load_f32_unaligned(cb + nbytes);
             float f1 = load_f32_unaligned(cb + nbytes + 4);
-            float final_dot = c1 * (float)dot;
-            final_dot += c2 * (float)sumq;
-            final_dot -= c34;
-            float pre = f0 + qc2 - 2.f * f1 * final_dot;
-            est = (metric == B200VQ_METRIC_L2) ? pre : 0.5f * (pre - qn2);  // IP: key = -ip
+            est = rabitq1_estimate((float)dot, (float)sumq, f0, -2.f * f1, c1, c2, c34, qc2, qn2, metric);
         }
         tk.offer(valid, est, (uint32_t)(base + lane));
     }
@@ -566,7 +565,7 @@ extern "C" size_t b200vq_rabitq1_scan_scratch_bytes(int64_t n, int nq, int k) {
 template <int CAP>
 static int rabitq1_scan_launch(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
                                const float* qfac, int nq, int qb, int metric, int k, uint64_t* part,
-                               const RPlan& p, cudaStream_t st) {
+                               const RPlan& p, cudaStream_t st, const uint32_t* gate = nullptr) {
     const int W = (D + 31) >> 5;
     const int code_size = ((D + 7) >> 3) + 8;
     const int pitch_w = ((code_size + 3) >> 2) | 1;
@@ -578,7 +577,23 @@ static int rabitq1_scan_launch(const uint8_t* codes, int64_t n, int D, const uin
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)nq, (unsigned)p.nchunks);
     rabitq1_scan_kernel<CAP><<<grid, 256, smem, st>>>(codes, n, D, planes, qfac, qb, metric, k,
-                                                      p.chunk_rows, part);
+                                                      p.chunk_rows, part, gate);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+// SIMT scan restricted to the queries with gate[q] != 0 (scratch sized by b200vq_rabitq1_scan_scratch_bytes).
+int b200vq::rabitq1_scan_gated(const uint8_t* codes, int64_t n, int D, const uint32_t* planes, const float* qfac,
+                               int nq, int qb, int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
+                               const uint32_t* gate, cudaStream_t st) {
+    RPlan p = rplan(n, nq);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32)
+                 ? rabitq1_scan_launch<128>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st, gate)
+                 : rabitq1_scan_launch<256>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st, gate);
+    if (rc != B200VQ_OK) return rc;
+    merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, p.nchunks, k, metric == B200VQ_METRIC_IP, out_vals, out_ids,
+                                                    gate, 0u);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
