@@ -11,7 +11,7 @@
 // tcgen05.mma kind::f8f6f4 with fp32 accumulation returns `dot` EXACTLY: the tensor pipe replaces
 // D/32 * qb AND+POPC pairs per (row, query) of the SIMT kernel.
 //
-// Per (128-row, 256-query) unit: four converter warps expand the sign bits of a 128-dimension chunk
+// Per (128-row, 256-query) unit: eight converter warps expand the sign bits of a 128-dimension chunk
 // (16 bytes per row, read straight from the code rows in global memory, prefetched one chunk ahead)
 // into a K-major SWIZZLE_128B tile of E4M3 0x00 / 0x38 bytes; TMA brings the matching 256 x 128-byte
 // tile of query values; one thread issues four tcgen05.mma (128 x 256 x 32) per chunk into one of two
@@ -34,7 +34,7 @@ constexpr int TILE_ROWS = 128;
 constexpr int TILE_Q = 256;
 constexpr int CHB = 128;                     // K chunk: 128 dimensions = 128 bytes = one swizzle row
 constexpr int NST = 4;
-constexpr int CONV_WARPS = 4, EPI_WARPS = 8;
+constexpr int CONV_WARPS = 8, EPI_WARPS = 8;
 constexpr int THREADS = 64 + 32 * (CONV_WARPS + EPI_WARPS);
 constexpr uint32_t A_BYTES = TILE_ROWS * CHB;      // 16 KB
 constexpr uint32_t B_BYTES = TILE_Q * CHB;         // 32 KB
@@ -70,7 +70,7 @@ struct Params {
     uint32_t cap;
     int64_t r0, r1;           // rows of this stage
     int code_size, nchunk, ntq;
-    int D;
+    int D, seed;              // seed: first stage, thresholds are +inf
     int64_t ntr;
 };
 
@@ -209,46 +209,40 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
         }
     } else if (warp < 2 + CONV_WARPS) {
         // ======================================================= converters ===
-        // thread = tile row: 16 code bytes per chunk -> 128 E4M3 bytes (0x38 where the bit is set) at the
-        // SWIZZLE_128B position of the row; the next chunk's bytes are in flight meanwhile
-        const int r = threadIdx.x - 64;
+        // thread = (tile row, 8-byte half of the chunk): 64 sign bits -> 64 E4M3 bytes (0x38 where the bit is
+        // set) at the SWIZZLE_128B position of the row; the next chunk's bytes are in flight meanwhile
+        const int cth = threadIdx.x - 64;
+        const int r = cth & 127, half = cth >> 7;
         const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u;
+        const int half_chunks = p.D >> 6;                     // 8-byte groups of sign bits in a row
         uint32_t st = 0, phase = 0;
         for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
             const int64_t t = unit / p.ntq;
             const int64_t row = p.r0 + t * TILE_ROWS + r;
             const bool live = row < p.r1;
-            const uint2* src = reinterpret_cast<const uint2*>(p.codes + row * (int64_t)p.code_size);
-            const int half_chunks = p.D >> 6;                 // 8-byte groups of sign bits in a row
-            uint2 cur0 = make_uint2(0, 0), cur1 = make_uint2(0, 0);
-            if (live) {
-                cur0 = __ldg(src);
-                if (1 < half_chunks) cur1 = __ldg(src + 1);
-            }
+            const uint2* src = reinterpret_cast<const uint2*>(p.codes + row * (int64_t)p.code_size) + half;
+            uint2 cur = make_uint2(0, 0);
+            if (live && half < half_chunks) cur = __ldg(src);
             for (int c = 0; c < p.nchunk; ++c) {
-                uint2 nx0 = make_uint2(0, 0), nx1 = make_uint2(0, 0);
-                if (live && c + 1 < p.nchunk) {
-                    nx0 = __ldg(src + 2 * c + 2);
-                    if (2 * c + 3 < half_chunks) nx1 = __ldg(src + 2 * c + 3);
-                }
+                uint2 nxt = make_uint2(0, 0);
+                if (live && 2 * c + 2 + half < half_chunks) nxt = __ldg(src + 2 * c + 2);
                 mbar_wait(bar(B_EMPTY + st), phase ^ 1);
                 uint8_t* a_tile = gbase + st * STAGE_BYTES + row_off;
-                const uint32_t w[4] = {cur0.x, cur0.y, cur1.x, cur1.y};
+                const uint32_t w[2] = {cur.x, cur.y};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {                 // 16 dimensions = 16 bits -> one 16-byte unit
+                for (int j = 0; j < 4; ++j) {                 // 16 dimensions = 16 bits -> one 16-byte unit
                     const uint32_t bits = (w[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
                     uint4 o;
                     o.x = (((bits & 0xFu) * 0x00204081u) & 0x01010101u) * 0x38u;
                     o.y = ((((bits >> 4) & 0xFu) * 0x00204081u) & 0x01010101u) * 0x38u;
                     o.z = ((((bits >> 8) & 0xFu) * 0x00204081u) & 0x01010101u) * 0x38u;
                     o.w = (((bits >> 12) * 0x00204081u) & 0x01010101u) * 0x38u;
-                    *reinterpret_cast<uint4*>(a_tile + ((j ^ (r & 7)) << 4)) = o;
+                    *reinterpret_cast<uint4*>(a_tile + (((half * 4 + j) ^ (r & 7)) << 4)) = o;
                 }
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_CONV + st));
-                cur0 = nx0;
-                cur1 = nx1;
+                cur = nxt;
                 if (++st == NST) { st = 0; phase ^= 1; }
             }
         }
@@ -277,6 +271,31 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
             asm volatile("bar.sync %0, 128;" ::"r"(grp_bar) : "memory");
             mbar_wait(bar(B_TFULL + acc), t_phase);
             tc_fence_after();
+            if (p.seed) {
+                // first stage (thresholds +inf): every row passes, so the appends are aggregated per warp
+#pragma unroll 1
+                for (int cb = 0; cb < TILE_Q / 32; ++cb) {
+                    float v[32];
+                    tmem_ld32(lane_addr + cb * 32, v);
+#pragma unroll 1
+                    for (int j = 0; j < 32; ++j) {
+                        const int q = u * TILE_Q + cb * 32 + j;
+                        const float4 c = qs[cb * 32 + j];
+                        const bool hit = live && !(c.w != c.w);           // padding queries carry NaN
+                        const unsigned m = __ballot_sync(FULL_MASK, hit);
+                        if (m == 0) continue;
+                        uint32_t pos0 = 0;
+                        if (lane == 0) pos0 = atomicAdd(p.count + q, (uint32_t)__popc(m));
+                        pos0 = __shfl_sync(FULL_MASK, pos0, 0);
+                        const uint32_t pos = pos0 + __popc(m & ((1u << lane) - 1u));
+                        float vj = 0.f;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) vj = (e == j) ? v[e] : vj;
+                        if (hit && pos < p.cap)
+                            p.cand[(size_t)q * p.cap + pos] = ((uint64_t)__float_as_uint(vj) << 32) | (uint32_t)row;
+                    }
+                }
+            } else {
 #pragma unroll 1
             for (int cb = 0; cb < TILE_Q / 32; ++cb) {
                 float v[32];
@@ -294,6 +313,7 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
                             p.cand[(size_t)q * p.cap + pos] = ((uint64_t)__float_as_uint(v[j]) << 32) | (uint32_t)row;
                     }
                 }
+            }
             }
             tc_fence_before();
             __syncwarp();
@@ -514,9 +534,9 @@ extern "C" int b200vq_rabitq1_scan_topk_tc(const uint8_t* codes, int64_t n, int 
     p.codes = codes; p.rowinfo = rowinfo; p.qscreen = qscreen; p.cand = cand; p.count = count; p.cap = fp.cap;
     p.code_size = D / 8 + 8; p.nchunk = fp.Dp / CHB; p.ntq = fp.ntq; p.D = D;
     for (int64_t r = 0; r < n;) {
-        int64_t r1 = r == 0 ? SEED_ROWS : r * 2;
-        if (r1 > n || n - r1 < r1 / 4) r1 = n;   // fold a short tail into the last stage
-        p.r0 = r; p.r1 = r1;
+        int64_t r1 = r == 0 ? SEED_ROWS : r * 4;   // x4: about 3k expected survivors per query and stage
+        if (r1 > n || n - r1 < r1 / 2) r1 = n;     // fold a short tail into the last stage
+        p.r0 = r; p.r1 = r1; p.seed = r == 0;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
         rq_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, SMEM_BYTES, st>>>(map_b, p);
