@@ -34,7 +34,7 @@ constexpr int TILE_ROWS = 128;
 constexpr int TILE_Q = 256;
 constexpr int CHB = 128;                     // K chunk: 128 dimensions = 128 bytes = one swizzle row
 constexpr int NST = 4;
-constexpr int CONV_WARPS = 8, EPI_WARPS = 8;
+constexpr int CONV_WARPS = 8, EPI_WARPS = 16;
 constexpr int THREADS = 64 + 32 * (CONV_WARPS + EPI_WARPS);
 constexpr uint32_t A_BYTES = TILE_ROWS * CHB;      // 16 KB
 constexpr uint32_t B_BYTES = TILE_Q * CHB;         // 32 KB
@@ -71,6 +71,7 @@ struct Params {
     int64_t r0, r1;           // rows of this stage
     int code_size, nchunk, ntq;
     int D, seed;              // seed: first stage, thresholds are +inf
+    unsigned long long* dbg;  // optional (B200VQ_RQ_DEBUG): MMA-thread wait cycles [t_empty, b_full, conv, total]
     int64_t ntr;
 };
 
@@ -156,7 +157,7 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar(B_TFULL + i), 1);
-            mbar_init(bar(B_TEMPTY + i), 4);
+            mbar_init(bar(B_TEMPTY + i), 8);
         }
         fence_barrier_init();
     }
@@ -184,14 +185,16 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
         // ======================================================= MMA issuer ===
         if (lane == 0) {
             uint32_t st = 0, phase = 0, acc = 0, t_phase = 0;
+            long long w_t = 0, w_b = 0, w_c = 0;
+            const long long t_begin = clock64();
             for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
-                mbar_wait_backoff(bar(B_TEMPTY + acc), t_phase ^ 1, 32);
+                { const long long c0 = clock64(); mbar_wait_backoff(bar(B_TEMPTY + acc), t_phase ^ 1, 32); w_t += clock64() - c0; }
                 tc_fence_after();
                 const uint32_t d = tmem_base + acc * 256u;
                 uint32_t accum = 0;
                 for (int c = 0; c < p.nchunk; ++c) {
-                    mbar_wait_backoff(bar(B_FULL + st), phase, 32);
-                    mbar_wait_backoff(bar(B_CONV + st), phase, 32);
+                    { const long long c0 = clock64(); mbar_wait_backoff(bar(B_FULL + st), phase, 32); w_b += clock64() - c0; }
+                    { const long long c0 = clock64(); mbar_wait_backoff(bar(B_CONV + st), phase, 32); w_c += clock64() - c0; }
                     tc_fence_after();
                     const uint32_t a_addr = base + st * STAGE_BYTES, b_addr = a_addr + A_BYTES;
 #pragma unroll
@@ -206,6 +209,12 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
                 umma_commit(bar(B_TFULL + acc));
                 if (++acc == 2) { acc = 0; t_phase ^= 1; }
             }
+            if (p.dbg) {
+                atomicAdd(p.dbg + 0, (unsigned long long)w_t);
+                atomicAdd(p.dbg + 1, (unsigned long long)w_b);
+                atomicAdd(p.dbg + 2, (unsigned long long)w_c);
+                atomicAdd(p.dbg + 3, (unsigned long long)(clock64() - t_begin));
+            }
         }
     } else if (warp < 2 + CONV_WARPS) {
         // ======================================================= converters ===
@@ -215,17 +224,44 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
         const int r = cth & 127, half = cth >> 7;
         const uint32_t row_off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u;
         const int half_chunks = p.D >> 6;                     // 8-byte groups of sign bits in a row
+        // The code bytes come straight from global memory (L2), PD chunks ahead of their use: a prefetch
+        // cursor walks the same (unit, chunk) sequence as the main loop, across unit boundaries.
+        constexpr int PD = 4;
+        int64_t k_unit = blockIdx.x;
+        int k_c = 0;
+        const uint2* k_src = nullptr;
+        bool k_live = false;
+        auto k_open = [&]() {
+            k_live = false;
+            if (k_unit < nunits) {
+                const int64_t row = p.r0 + (k_unit / p.ntq) * TILE_ROWS + r;
+                k_live = row < p.r1;
+                k_src = reinterpret_cast<const uint2*>(p.codes + row * (int64_t)p.code_size) + half;
+            }
+        };
+        auto k_fetch = [&]() {
+            uint2 v = make_uint2(0, 0);
+            if (k_unit < nunits) {
+                if (k_live && 2 * k_c + half < half_chunks) v = __ldg(k_src + 2 * k_c);
+                if (++k_c == p.nchunk) {
+                    k_c = 0;
+                    k_unit += gridDim.x;
+                    k_open();
+                }
+            }
+            return v;
+        };
+        k_open();
+        uint2 ring[PD];
+#pragma unroll
+        for (int i = 0; i < PD; ++i) ring[i] = k_fetch();
         uint32_t st = 0, phase = 0;
         for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
-            const int64_t t = unit / p.ntq;
-            const int64_t row = p.r0 + t * TILE_ROWS + r;
-            const bool live = row < p.r1;
-            const uint2* src = reinterpret_cast<const uint2*>(p.codes + row * (int64_t)p.code_size) + half;
-            uint2 cur = make_uint2(0, 0);
-            if (live && half < half_chunks) cur = __ldg(src);
             for (int c = 0; c < p.nchunk; ++c) {
-                uint2 nxt = make_uint2(0, 0);
-                if (live && 2 * c + 2 + half < half_chunks) nxt = __ldg(src + 2 * c + 2);
+                const uint2 cur = ring[0];
+#pragma unroll
+                for (int i = 0; i + 1 < PD; ++i) ring[i] = ring[i + 1];
+                ring[PD - 1] = k_fetch();
                 mbar_wait(bar(B_EMPTY + st), phase ^ 1);
                 uint8_t* a_tile = gbase + st * STAGE_BYTES + row_off;
                 const uint32_t w[2] = {cur.x, cur.y};
@@ -242,45 +278,48 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(B_CONV + st));
-                cur = nxt;
                 if (++st == NST) { st = 0; phase ^= 1; }
             }
         }
     } else {
         // ========================================================= epilogue ===
-        const int ew = warp - 2 - CONV_WARPS;                 // 0..7
-        const uint32_t acc = (uint32_t)ew >> 2;               // accumulator stage served by this warp
+        const int ew = warp - 2 - CONV_WARPS;                 // 0..15
+        const uint32_t acc = (uint32_t)ew >> 3;               // accumulator stage served by this warp
         const int q4 = warp & 3;                              // TMEM lane quarter this warp may read
-        const uint32_t lane_addr = tmem_base + ((uint32_t)(q4 * 32) << 16) + acc * 256u;
+        const int ch = (ew >> 2) & 1;                         // column half of the 256-query tile
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q4 * 32) << 16) + acc * 256u + (uint32_t)ch * 128u;
         float4* qs = qc_s + acc * TILE_Q;
-        const int gt = (ew & 3) * 32 + lane;                  // 0..127 inside the stage group
+        const int gt = (ew & 7) * 32 + lane;                  // 0..255 inside the stage group
         const uint32_t grp_bar = 1u + acc;
         uint32_t t_phase = 0;
-        int64_t unit = blockIdx.x;
-        for (uint32_t it = 0; unit < nunits; unit += gridDim.x, ++it) {
-            if ((it & 1u) != acc) continue;
+        int64_t unit = blockIdx.x + (int64_t)acc * gridDim.x;  // this group takes every second unit of the CTA
+        float4 myq = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (unit < nunits) myq = p.qscreen[(size_t)(unit % p.ntq) * TILE_Q + gt];
+        for (; unit < nunits; unit += 2 * (int64_t)gridDim.x) {
             const int64_t t = unit / p.ntq;
             const int u = (int)(unit - t * p.ntq);
             const int64_t row = p.r0 + t * TILE_ROWS + q4 * 32 + lane;
             const bool live = row < p.r1;
             float4 ri = make_float4(0.f, 0.f, 0.f, 0.f);
             if (live) ri = __ldg(p.rowinfo + row);
-            asm volatile("bar.sync %0, 128;" ::"r"(grp_bar) : "memory");   // previous unit's constants consumed
-            qs[gt] = p.qscreen[(size_t)u * TILE_Q + gt];
-            qs[gt + 128] = p.qscreen[(size_t)u * TILE_Q + gt + 128];
-            asm volatile("bar.sync %0, 128;" ::"r"(grp_bar) : "memory");
+            asm volatile("bar.sync %0, 256;" ::"r"(grp_bar) : "memory");   // previous unit's constants consumed
+            qs[gt] = myq;
+            asm volatile("bar.sync %0, 256;" ::"r"(grp_bar) : "memory");
+            // the group's next unit: its constants travel while this one is processed
+            const int64_t nu = unit + 2 * (int64_t)gridDim.x;
+            if (nu < nunits) myq = p.qscreen[(size_t)(nu % p.ntq) * TILE_Q + gt];
             mbar_wait(bar(B_TFULL + acc), t_phase);
             tc_fence_after();
             if (p.seed) {
                 // first stage (thresholds +inf): every row passes, so the appends are aggregated per warp
 #pragma unroll 1
-                for (int cb = 0; cb < TILE_Q / 32; ++cb) {
+                for (int cb = 0; cb < 4; ++cb) {
                     float v[32];
                     tmem_ld32(lane_addr + cb * 32, v);
 #pragma unroll 1
                     for (int j = 0; j < 32; ++j) {
-                        const int q = u * TILE_Q + cb * 32 + j;
-                        const float4 c = qs[cb * 32 + j];
+                        const int q = u * TILE_Q + ch * 128 + cb * 32 + j;
+                        const float4 c = qs[ch * 128 + cb * 32 + j];
                         const bool hit = live && !(c.w != c.w);           // padding queries carry NaN
                         const unsigned m = __ballot_sync(FULL_MASK, hit);
                         if (m == 0) continue;
@@ -297,17 +336,17 @@ rq_screen_kernel(const __grid_constant__ CUtensorMap map_b, const Params p) {
                 }
             } else {
 #pragma unroll 1
-            for (int cb = 0; cb < TILE_Q / 32; ++cb) {
+            for (int cb = 0; cb < 4; ++cb) {
                 float v[32];
                 tmem_ld32(lane_addr + cb * 32, v);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const float4 c = qs[cb * 32 + j];          // {c1, c2, -c34, T'}
+                    const float4 c = qs[ch * 128 + cb * 32 + j];          // {c1, c2, -c34, T'}
                     const float wq = __fmaf_rn(c.y, ri.z, c.z);
                     const float inner = __fmaf_rn(c.x, v[j], wq);
                     const float e = __fmaf_rn(ri.y, inner, ri.x);
                     if (live && e <= c.w) {
-                        const int q = u * TILE_Q + cb * 32 + j;
+                        const int q = u * TILE_Q + ch * 128 + cb * 32 + j;
                         const uint32_t pos = atomicAdd(p.count + q, 1u);
                         if (pos < p.cap)
                             p.cand[(size_t)q * p.cap + pos] = ((uint64_t)__float_as_uint(v[j]) << 32) | (uint32_t)row;
@@ -533,14 +572,26 @@ extern "C" int b200vq_rabitq1_scan_topk_tc(const uint8_t* codes, int64_t n, int 
     Params p;
     p.codes = codes; p.rowinfo = rowinfo; p.qscreen = qscreen; p.cand = cand; p.count = count; p.cap = fp.cap;
     p.code_size = D / 8 + 8; p.nchunk = fp.Dp / CHB; p.ntq = fp.ntq; p.D = D;
+    p.dbg = nullptr;
+    const bool debug = getenv("B200VQ_RQ_DEBUG") != nullptr;
+    unsigned long long* dbg_dev = reinterpret_cast<unsigned long long*>(amax + 8);   // inside the 256-byte amax slot
     for (int64_t r = 0; r < n;) {
         int64_t r1 = r == 0 ? SEED_ROWS : r * 4;   // x4: about 3k expected survivors per query and stage
         if (r1 > n || n - r1 < r1 / 2) r1 = n;     // fold a short tail into the last stage
         p.r0 = r; p.r1 = r1; p.seed = r == 0;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
+        p.dbg = (debug && r1 == n) ? dbg_dev : nullptr;
         rq_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, SMEM_BYTES, st>>>(map_b, p);
         VQ_LAUNCH_CHECK();
+        if (p.dbg) {
+            unsigned long long h[4];
+            VQ_CUDA(cudaMemcpyAsync(h, dbg_dev, sizeof(h), cudaMemcpyDeviceToHost, st));
+            VQ_CUDA(cudaStreamSynchronize(st));
+            fprintf(stderr, "rq_screen last stage: MMA-thread cycles summed over CTAs: t_empty %llu, b_full %llu, conv %llu, total %llu\n",
+                    h[0], h[1], h[2], h[3]);
+            VQ_CUDA(cudaMemsetAsync(dbg_dev, 0, 32, st));
+        }
         const int last = r1 == n;
         rc = (k <= 32) ? rq_finish_launch<64>(rowinfo, qfac, amax, D, qb, metric, k, cand, count, fp.cap, running, qscreen,
                                               flags, last, out_vals, out_ids, nq, st)
