@@ -270,6 +270,57 @@ __global__ void adc_lut_kernel(const float* __restrict__ queries, int64_t ldq,
     }
 }
 
+// Batched LUT build: grid (M, ceil(nq / 32)), 256 threads. The CTA stages the 256 centroids of its
+// sub-quantizer dimension-major ([i][k]: thread k reads consecutive words) and 32 query sub-vectors
+// dimension-major ([i][32]) once, then thread k runs the same sequential fp32 chain as adc_lut_kernel
+// for four queries at a time (one centroid load per dimension serves four chains).
+constexpr int LUT_QB = 32;
+__global__ void __launch_bounds__(256)
+adc_lut_batched_kernel(const float* __restrict__ queries, int nq, int64_t ldq, const float* __restrict__ centroids,
+                       int M, int dsub, int metric, float* __restrict__ lut) {
+    extern __shared__ __align__(16) float lsm[];
+    float* cs = lsm + (size_t)dsub * LUT_QB;      // [dsub][257] (padded: conflict-free transposed staging)
+    float* qs = lsm;                              // [dsub][LUT_QB]
+    const int m = blockIdx.x, q0 = blockIdx.y * LUT_QB, k = threadIdx.x;
+    const float* cm = centroids + (size_t)m * 256 * dsub;
+    for (int idx = threadIdx.x; idx < 256 * dsub; idx += 256) {
+        const int j = idx / dsub, i = idx - j * dsub;     // coalesced global read
+        cs[i * 257 + j] = cm[idx];
+    }
+    for (int idx = threadIdx.x; idx < LUT_QB * dsub; idx += 256) {
+        const int qq = idx / dsub, i = idx - qq * dsub;
+        qs[i * LUT_QB + qq] = (q0 + qq < nq) ? queries[(int64_t)(q0 + qq) * ldq + (int64_t)m * dsub + i] : 0.f;
+    }
+    __syncthreads();
+    for (int g = 0; g < LUT_QB && q0 + g < nq; g += 4) {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        if (metric == B200VQ_METRIC_L2) {
+            for (int i = 0; i < dsub; ++i) {
+                const float c = cs[i * 257 + k];
+                const float4 qv = *reinterpret_cast<const float4*>(qs + i * LUT_QB + g);
+                const float d0 = __fsub_rn(qv.x, c), d1 = __fsub_rn(qv.y, c), d2 = __fsub_rn(qv.z, c), d3 = __fsub_rn(qv.w, c);
+                a0 = __fmaf_rn(d0, d0, a0);
+                a1 = __fmaf_rn(d1, d1, a1);
+                a2 = __fmaf_rn(d2, d2, a2);
+                a3 = __fmaf_rn(d3, d3, a3);
+            }
+        } else {
+            for (int i = 0; i < dsub; ++i) {
+                const float c = cs[i * 257 + k];
+                const float4 qv = *reinterpret_cast<const float4*>(qs + i * LUT_QB + g);
+                a0 = __fmaf_rn(qv.x, c, a0);
+                a1 = __fmaf_rn(qv.y, c, a1);
+                a2 = __fmaf_rn(qv.z, c, a2);
+                a3 = __fmaf_rn(qv.w, c, a3);
+            }
+        }
+        const float av[4] = {a0, a1, a2, a3};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (q0 + g + e < nq) lut[((size_t)(q0 + g + e) * M + m) * 256 + k] = av[e];
+    }
+}
+
 }  // namespace b200vq
 
 using namespace b200vq;
@@ -406,6 +457,14 @@ extern "C" int b200vq_adc_lut(const float* queries, int nq, int64_t ldq, const f
     VQ_CHECK_ARG(M <= 65535, "adc_lut: M > 65535");
     VQ_CHECK_ARG((size_t)dsub * sizeof(float) <= 48 * 1024, "adc_lut: dsub too large");
     if (nq == 0) return B200VQ_OK;
+    const size_t bsm = ((size_t)dsub * 257 + (size_t)dsub * LUT_QB) * sizeof(float);
+    if (ksub == 256 && nq >= 8 && bsm <= 200 * 1024) {
+        VQ_CUDA(cudaFuncSetAttribute(adc_lut_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsm));
+        adc_lut_batched_kernel<<<dim3((unsigned)M, (unsigned)((nq + LUT_QB - 1) / LUT_QB)), 256, bsm, as_stream(stream)>>>(
+            queries, nq, ldq, centroids, M, dsub, metric, lut);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     dim3 grid((unsigned)nq, (unsigned)M);
     int block = ksub >= 256 ? 256 : ((ksub + 31) / 32) * 32;
     adc_lut_kernel<<<grid, block, dsub * sizeof(float), as_stream(stream)>>>(
