@@ -11,7 +11,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200vq.so")
+# B200VQ_LIB: A/B a second build of the same C ABI (tools/ only); the in-tree library is the product
+LIB_PATH = os.environ.get("B200VQ_LIB") or os.path.join(_HERE, "libb200vq.so")
 
 OK = 0
 METRIC_L2, METRIC_IP = 0, 1

@@ -32,8 +32,8 @@
 // Data movement: persistent CTAs, one per SM. A CTA keeps the (-2 c) tiles of KS consecutive
 // sub-quantizers resident in shared memory (TMA, hardware swizzle) and streams 128-row slices of
 // x (only the KS*dsub columns it needs) through an NST-deep TMA ring, so x is read from HBM
-// exactly once and the centroids are not re-read per tile. Warp roles: 0 = TMA producer,
-// 1 = MMA issuer (owns TMEM), 2..17 = epilogue (accumulator stage x TMEM lane quarter x column
+// exactly once and the centroids are not re-read per tile. Warp roles: 16 = TMA producer,
+// 17 = MMA issuer (owns TMEM), 0..15 = epilogue (accumulator stage x TMEM lane quarter x column
 // half). The two 256-column accumulators double-buffer MMA against the epilogue.
 // Launch sequence: memset(cand2) -> prepare_kernel -> assign_tc_kernel -> pair_fixup_kernel ->
 // fixup_kernel, all on the caller's stream.
@@ -46,6 +46,9 @@ constexpr int TILE_ROWS = 128;
 constexpr int KSUB = 256;
 constexpr int EPI_WARPS = 16;   // 2 accumulator stages x 4 TMEM lane quarters x 2 column halves
 constexpr int THREADS = 64 + 32 * EPI_WARPS;
+// Warps 0-15 = epilogue, 16 = TMA producer, 17 = MMA issuer: the warp scheduler favours high warp
+// ids, so the two single-thread roles are never queued behind the epilogue's arithmetic.
+constexpr int SVC_WARP = EPI_WARPS;
 constexpr int MAX_STAGES = 4;
 constexpr uint32_t SMEM_BUDGET = 220 * 1024;
 
@@ -406,7 +409,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     const int KS = p.KS, CH = p.CH, nchunk = p.nchunk, NST = p.nstages;
     const int dbg = DBG ? p.debug : 0;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == SVC_WARP && lane == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_b);
         tma_prefetch_desc(&map_bx);
@@ -424,13 +427,13 @@ __global__ void __launch_bounds__(THREADS, 1)
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(bar(BAR_TMEM_PTR), 512);
+    if (warp == SVC_WARP + 1) tmem_alloc(bar(BAR_TMEM_PTR), 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    if (warp == 0) {
+    if (warp == SVC_WARP) {
         // ===================================================== TMA producer ===
         if (lane == 0) {
             mbar_expect_tx(bar(BAR_AX_FULL), 4096);
@@ -468,7 +471,7 @@ __global__ void __launch_bounds__(THREADS, 1)
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == SVC_WARP + 1) {
         // ======================================================= MMA issuer ===
         if (lane == 0) {
             const uint32_t lt = layout_type_of(CH);
@@ -535,7 +538,7 @@ __global__ void __launch_bounds__(THREADS, 1)
         const int units = CH / 4;
         // 16 epilogue warps: accumulator stage acc (units alternate), TMEM lane quarter q, column half hf.
         // The two warps of a (acc, q) pair exchange partial results through shared memory.
-        const uint32_t eidx = (uint32_t)(warp - 2) >> 2;
+        const uint32_t eidx = (uint32_t)warp >> 2;
         const uint32_t acc = eidx & 1u, hf = eidx >> 1;
         float* xch = reinterpret_cast<float*>(gbase + sp.bar_off + 256) + (acc * 4 + q) * 128;  // [4][32]
         const uint32_t pair_bar = 1u + acc * 4u + (uint32_t)q;
@@ -686,7 +689,7 @@ __global__ void __launch_bounds__(THREADS, 1)
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) {
+    if (warp == SVC_WARP + 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
