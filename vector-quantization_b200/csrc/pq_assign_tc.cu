@@ -280,12 +280,16 @@ __global__ void __launch_bounds__(PF_THREADS) pair_fixup_kernel(Params p) {
 }
 
 // ---------------------------------------------------------- fix-up kernel ---
-// grid (blocks_per_m, M). The CTA stages the 256 centroids of sub-quantizer m in shared
+// grid (chunks, M): CTA (c, m) owns entries [c, c + 1) * FIX_CHUNK of sub-quantizer m's list and exits
+// at once when the list is shorter (the lists are very uneven: the error bound scales with |x_m||c|,
+// so high-variance sub-spaces collect most entries; a fixed number of CTAs per m left most of the
+// device idle behind the longest list). The CTA stages the 256 centroids of sub-quantizer m in shared
 // memory dimension-major ([i][j]: lane j reads consecutive words, no bank conflicts) and its
-// warps walk that sub-quantizer's list: exact scan of all 256 centroids with the arithmetic
+// warps walk their share: exact scan of all 256 centroids with the arithmetic
 // and tie-breaking (lowest index) of pq_assign_simt_kernel; lane l owns centroids l, l+32, ...
 constexpr int FIX_WARPS = 8;
 constexpr int FIX_ROWS = 4;   // list entries scored together by one warp (centroid loads are shared)
+constexpr int FIX_CHUNK = 256; // list entries per CTA
 __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
     extern __shared__ __align__(16) float fsm[];
     const int dsub = p.dsub, m = blockIdx.y;
@@ -296,23 +300,32 @@ __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
     unsigned long long cnt = p.fix_count[m];
     if (p.stats && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(p.stats + 2, cnt);
     if (cnt > p.fix_cap) cnt = p.fix_cap;
-    if ((unsigned long long)blockIdx.x * FIX_WARPS * FIX_ROWS >= cnt) return;
+    const unsigned long long c_begin = (unsigned long long)blockIdx.x * FIX_CHUNK;
+    if (c_begin >= cnt) return;
+    const unsigned long long c_end = c_begin + FIX_CHUNK < cnt ? c_begin + FIX_CHUNK : cnt;
     const float* cm = p.centroids + (size_t)m * KSUB * dsub;
-    for (int idx = threadIdx.x; idx < KSUB * dsub; idx += blockDim.x) {
-        const int j = idx / dsub, i = idx - j * dsub;   // coalesced global read
-        cs[i * KSUB + j] = cm[idx];
+    // thread j stages centroid j: 128-bit global loads, conflict-free transposed stores
+    for (int j = threadIdx.x; j < KSUB; j += blockDim.x) {
+        const float4* c4 = reinterpret_cast<const float4*>(cm + (size_t)j * dsub);
+        for (int i4 = 0; i4 < (dsub >> 2); ++i4) {
+            const float4 c = __ldg(c4 + i4);
+            cs[(4 * i4 + 0) * KSUB + j] = c.x;
+            cs[(4 * i4 + 1) * KSUB + j] = c.y;
+            cs[(4 * i4 + 2) * KSUB + j] = c.z;
+            cs[(4 * i4 + 3) * KSUB + j] = c.w;
+        }
+        cn[j] = p.cnorm[(size_t)m * KSUB + j];
     }
-    for (int j = threadIdx.x; j < KSUB; j += blockDim.x) cn[j] = p.cnorm[(size_t)m * KSUB + j];
     __syncthreads();
     float* xs = xs_all + (size_t)w * FIX_ROWS * dsub;
     const uint32_t* list = p.fix_list + (size_t)m * p.fix_cap;
-    for (unsigned long long e0 = ((unsigned long long)blockIdx.x * FIX_WARPS + w) * FIX_ROWS; e0 < cnt;
-         e0 += (unsigned long long)gridDim.x * FIX_WARPS * FIX_ROWS) {
+    for (unsigned long long e0 = c_begin + (unsigned long long)w * FIX_ROWS; e0 < c_end;
+         e0 += (unsigned long long)FIX_WARPS * FIX_ROWS) {
         int64_t rows[FIX_ROWS];
         __syncwarp();
 #pragma unroll
         for (int t = 0; t < FIX_ROWS; ++t) {
-            const unsigned long long e = e0 + t < cnt ? e0 + t : e0;   // pad with the first entry
+            const unsigned long long e = e0 + t < c_end ? e0 + t : e0;   // pad with the first entry
             rows[t] = (int64_t)list[e];
             const float* xr = p.x + rows[t] * p.ldx + (int64_t)m * dsub;
             for (int i = lane; i < dsub; i += 32) xs[t * dsub + i] = xr[i];
@@ -360,7 +373,7 @@ __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
                 }
             }
             if (bk == 0x7fffffff) bk = 0;  // all distances NaN: the SIMT kernel keeps index 0
-            if (lane == 0 && e0 + t < cnt) p.codes[rows[t] * p.M + m] = (uint8_t)bk;
+            if (lane == 0 && e0 + t < c_end) p.codes[rows[t] * p.M + m] = (uint8_t)bk;
         }
     }
 }
@@ -852,9 +865,8 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     {
         const size_t fsmem = ((size_t)dsub * KSUB + KSUB + (size_t)FIX_WARPS * FIX_ROWS * dsub) * sizeof(float);
         VQ_CUDA(cudaFuncSetAttribute(fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
-        int bpm = (sms * 4 + M - 1) / M;
-        if (bpm < 1) bpm = 1;
-        dim3 fgrid((unsigned)bpm, (unsigned)M);
+        const unsigned long long chunks = (sc.cap + FIX_CHUNK - 1) / FIX_CHUNK;
+        dim3 fgrid((unsigned)chunks, (unsigned)M);
         fixup_kernel<<<fgrid, FIX_WARPS * 32, fsmem, st>>>(p);
     }
     VQ_LAUNCH_CHECK();
