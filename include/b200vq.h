@@ -254,6 +254,20 @@ int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B, cons
                              float* out_vals, uint32_t* out_ids, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* ----------------------------------------------------------------- LVQ ---
+ * Locally-adaptive vector quantization, single level: replaces the numpy code of
+ * src/haag_vq/methods/lvq_quantization.py:44-141 (LVQQuantizer.compress / decompress; registry
+ * method "lvq", benchmarks/method_registry_saq.py:49-52) with identical bytes. Row layout:
+ * ceil(D * num_bits / 8) bytes of MSB-first packed indices, then lo and delta as fp32.
+ * codes (n, ceil(D*num_bits/8) + 8) uint8; mu (D) fp32 global mean; 1 <= num_bits <= 8. */
+int b200vq_lvq_encode(const float* x, int64_t n, int64_t ldx, int D, const float* mu, int num_bits,
+                      uint8_t* codes, void* stream);
+int b200vq_lvq_decode(const uint8_t* codes, int64_t n, int D, const float* mu, int num_bits,
+                      float* out, int64_t ldo, void* stream);
+/* Column means with numpy's summation order (X.mean(axis=0) of a C-contiguous fp32 matrix: rows
+ * added one after another in fp32, then / n): lvq_quantization.py:44-46. mean (D) fp32. */
+int b200vq_col_mean_seq(const float* x, int64_t n, int64_t ldx, int D, float* mean, void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):

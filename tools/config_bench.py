@@ -123,6 +123,15 @@ def c3():
         "vectors", bytes_=n * (4 * D + code_bytes))
     add("C3", "saq_decode avg 4 bits", timed(lambda: ops_sq.saq_decode(codes, vmin, vmax, dim_bits, off, D)), n,
         "vectors", bytes_=n * (4 * D + code_bytes))
+    # LVQ (registry method "lvq"): per-row lo / delta, B-bit MSB-first packing
+    mu = ops_sq.col_mean_seq(x[:65536])
+    for bits in (8, 4):
+        cs = ops_sq.lvq_code_size(D, bits)
+        lc = ops_sq.lvq_encode(x, mu, bits)
+        add("C3", f"lvq_encode {bits}-bit", timed(lambda: ops_sq.lvq_encode(x, mu, bits, out=lc)), n, "vectors",
+            bytes_=n * (4 * D + cs))
+        add("C3", f"lvq_decode {bits}-bit", timed(lambda: ops_sq.lvq_decode(lc, mu, bits)), n, "vectors",
+            bytes_=n * (4 * D + cs))
 
 
 def c4():

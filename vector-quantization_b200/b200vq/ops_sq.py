@@ -119,6 +119,43 @@ def erabitq_scan_topk(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Ten
 
 
 # ------------------------------------------------------------------ 1-bit RaBitQ
+def lvq_code_size(D: int, bits: int) -> int:
+    return (D * bits + 7) // 8 + 8
+
+
+def lvq_encode(x: torch.Tensor, mu: torch.Tensor, bits: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    _chk(mu, torch.float32, "mu")
+    ptr, n, ld, D = _rows(x, "x")
+    if mu.numel() != D:
+        raise B200VQError(f"lvq_encode: mu has {mu.numel()} entries, rows have {D}")
+    if out is None:
+        out = torch.empty((n, lvq_code_size(D, bits)), dtype=torch.uint8, device=x.device)
+    check(_lib.load().b200vq_lvq_encode(ptr, n, ld, D, mu.data_ptr(), bits, out.data_ptr(), _stream()), "lvq_encode")
+    return out
+
+
+def lvq_decode(codes: torch.Tensor, mu: torch.Tensor, bits: int) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    D, n = mu.numel(), codes.shape[0]
+    if codes.shape[1] != lvq_code_size(D, bits):
+        raise B200VQError(f"lvq_decode: code rows have {codes.shape[1]} bytes, expected {lvq_code_size(D, bits)}")
+    out = torch.empty((n, D), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_lvq_decode(codes.data_ptr(), n, D, mu.data_ptr(), bits, out.data_ptr(), out.stride(0),
+                                        _stream()), "lvq_decode")
+    return out
+
+
+def col_mean_seq(x: torch.Tensor) -> torch.Tensor:
+    """Column means in numpy's X.mean(axis=0) order (sequential fp32 row adds, then / n)."""
+    _chk(x, torch.float32, "x")
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.empty((D,), dtype=torch.float32, device=x.device)
+    check(_lib.load().b200vq_col_mean_seq(ptr, n, ld, D, out.data_ptr(), _stream()), "col_mean_seq")
+    return out
+
+
 def rabitq1_encode(x: torch.Tensor, centroid: torch.Tensor | None, metric) -> torch.Tensor:
     _chk(x, torch.float32, "x")
     ptr, n, ld, D = _rows(x, "x")

@@ -3,7 +3,8 @@
 Mirrors src/haag_vq/benchmarks/method_registry_saq.py:17-74 for the methods on
 the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)) and
 ``saq_paper`` -> SaqEngineAdapter(CAQ, DP allocation) (SURVEY.md §8 rows a9-a11,
-a16). The other names of SAQ_METHODS (ours*, lvq, rankaware*, perdim_mse*) are
+a16) and ``lvq`` -> LVQQuantizer(num_bits=round(bpd)) (reference :49-52). The other
+names of SAQ_METHODS (ours*, rankaware*, perdim_mse*) are
 the greedy-allocation / per-dimension codebook studies SURVEY.md §8(f) ranks as
 "next"; they raise NotImplementedError here instead of silently falling back.
 """
@@ -25,6 +26,10 @@ def build_saq_quantizer(method: str, bpd: float, D: int):
         from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
         from haag_vq.methods.extended_rabitq import ExtendedRaBitQuantizer
         return FaissQuantizerAdapter(ExtendedRaBitQuantizer(num_bits=b))
+    if method == "lvq":
+        from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
+        from haag_vq.methods.lvq_quantization import LVQQuantizer
+        return FaissQuantizerAdapter(LVQQuantizer(num_bits=b))
     if method in SAQ_METHODS:
         raise NotImplementedError(
             f"method {method!r} is not built on the B200 path yet (SURVEY.md §8f); no fallback is provided")
