@@ -93,7 +93,7 @@ struct Params {
     int64_t n, ldx;
     const float* centroids;  // (M, 256, dsub) original fp32 centroids (exact re-evaluation)
     const float* cnorm;      // (M, 256)
-    const float* cmax;       // (M) max_j |c_mj|
+    const float2* cmax;      // (M) error-bound constants of sub-quantizer m: 2E = |x_m| * .x + .y
     uint8_t* codes;          // (n, M)
     uint8_t* cand2;          // (n, M) second candidate of a pair awaiting exact evaluation (0 = settled)
     unsigned long long* fix_count;  // (M) rows appended per sub-quantizer (may exceed fix_cap)
@@ -119,11 +119,12 @@ __device__ __forceinline__ uint32_t layout_type_of(int CH) { return CH == 32 ? 2
 // grid M, block 256: thread j prepares centroid j of sub-quantizer m.
 //   bprep  (M*256, dsub)  = -2 c           (exact scaling)
 //   bextra (M*256, 8)     = {hi, mid, lo, 0...} TF32-truncation split of ||c||^2
-//   cmax   (M)            = max_j |c_mj|
+//   cmax   (M)            = {2a, 2b}: the screen's error bound is 2E = |x_m| 2a + 2b with c = max_j |c_mj|,
+//                            a = c (k1 + 2 k2), b = k2 c^2, k1 = 2^-9 * 1.02, k2 = 3.8147e-6
 //   ones   (128, 8)       = {1,1,1,0,0,0,0,0} per row; counter zeroed.
 __global__ void prepare_kernel(const float* __restrict__ centroids, const float* __restrict__ cnorm, int dsub,
                                float* __restrict__ bprep, float* __restrict__ bextra,
-                               float* __restrict__ cmax, float* __restrict__ ones,
+                               float2* __restrict__ cmax, float* __restrict__ ones,
                                unsigned long long* __restrict__ fix_count) {  // (M) counters
     const int m = blockIdx.x, j = threadIdx.x;
     const size_t row = (size_t)m * KSUB + j;
@@ -153,7 +154,10 @@ __global__ void prepare_kernel(const float* __restrict__ centroids, const float*
     if (j == 0) {
         float mx = red[0];
         for (int w = 1; w < KSUB / 32; ++w) mx = fmaxf(mx, red[w]);
-        cmax[m] = mx;
+        // |err| <= E = k1 |x||c| + k2 (2 |x||c| + c^2): TF32 truncation after centring (2^-10 |x||c| on
+        // x.c, doubled by the -2 factor, widened by 2 %) plus slack for accumulation and the norm split
+        const float k1 = 0.001953125f * 1.02f, k2 = 3.8147e-6f;
+        cmax[m] = make_float2(2.f * mx * (k1 + 2.f * k2) * 1.000001f, 2.f * k2 * mx * mx * 1.000001f);
     }
     if (m == 0) {
         if (j < TILE_ROWS) {
@@ -620,14 +624,12 @@ __global__ void __launch_bounds__(THREADS, 1)
                     }
                     xch[hf * 32 + lane] = mn;
                     if (hf == 1) {
-                        // screen error bound: after centring, TF32 truncation leaves |err| <= 2^-10 |x||c| on
-                        // x.c, doubled by the -2 factor; widened by 2 %, plus slack for accumulation and the
-                        // norm split
-                        const float xl = sqrtf(xn) * 1.0000005f;
-                        const float cm = p.cmax[m];
-                        const float E = __fmaf_rn(0.001953125f * 1.02f, xl * cm,
-                                                  3.8147e-6f * __fmaf_rn(2.f * xl, cm, cm * cm));
-                        xch[64 + lane] = 2.f * E;
+                        // 2E = |x_m| e2.x + e2.y (constants of prepare_kernel); only an upper bound of |x_m| is
+                        // needed: 1.00001 covers the approximate square root (2^-22)
+                        const float2 e2 = p.cmax[m];
+                        float xl;
+                        asm("sqrt.approx.f32 %0, %1;" : "=f"(xl) : "f"(xn));
+                        xch[64 + lane] = __fmaf_rn(xl * 1.00001f, e2.x, e2.y);
                     }
                     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
                     const float thr = fminf(xch[lane], xch[32 + lane]) + xch[64 + lane];
@@ -651,35 +653,27 @@ __global__ void __launch_bounds__(THREADS, 1)
                     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
                     if (hf == 1) continue;
                     const uint32_t plo = isum, phi = __float_as_uint(xch[96 + lane]);
-                    const int cnt_lo = plo & 0xFF, cnt_hi = phi & 0xFF;
-                    const int cnt = cnt_lo + cnt_hi;
+                    // Branch-free decode: with the upper half's moments moved to row-wide column indices
+                    // (J = 128 + j) count, sum J and sum J^2 add up, and with D = cnt S2 - S1^2 (0 for one
+                    // candidate, (J1 - J2)^2 for two) the candidates are (S1 -+ sqrt D) / cnt.
                     // 1 candidate: it is the exact argmin. 2: provisional code = lower index, the other goes
                     // to cand2 and pair_fixup_kernel evaluates both exactly. Otherwise (>= 3, or 0 for NaN
                     // rows) the (255, 255) marker sends the pair to the exact 256-way scan. Plain stores
                     // only: nothing here waits on memory.
-                    int code = 0, second = 0;
-                    bool multi = false;
+                    const uint32_t cnt_hi = phi & 0xFFu, s1_hi = (phi >> 8) & 0x1FFu;
+                    const uint32_t ucnt = (plo & 0xFFu) + cnt_hi;
+                    const uint32_t S1 = ((plo >> 8) & 0x1FFu) + s1_hi + 128u * cnt_hi;
+                    const uint32_t S2 = (plo >> 17) + (phi >> 17) + 256u * s1_hi + 16384u * cnt_hi;
+                    const bool ok = (ucnt - 1u) < 2u || (DBG && (dbg & 2));
+                    float df;
+                    asm("sqrt.approx.f32 %0, %1;" : "=f"(df) : "f"((float)(int)(ucnt * S2 - S1 * S1)));
+                    const uint32_t dd = (uint32_t)(int)(df + 0.5f), sh = (ucnt - 1u) & 1u;
+                    const uint32_t lo_j = (S1 - dd) >> sh, hi_j = (S1 + dd) >> sh;
+                    const int cnt = (int)ucnt;
+                    const int code = ok ? (int)(lo_j & 0xFFu) : 255;
+                    const int second = ok ? (hi_j != lo_j ? (int)(hi_j & 0xFFu) : 0) : 255;
+                    const bool multi = live && second != 0;
                     if (live) {
-                        if (cnt == 1 || (dbg & 2)) {
-                            code = cnt_lo ? (int)((plo >> 8) & 0x1FF) : 128 + (int)((phi >> 8) & 0x1FF);
-                        } else if (cnt == 2) {
-                            multi = true;
-                            if (cnt_lo == 1) {
-                                code = (int)((plo >> 8) & 0x1FF);
-                                second = 128 + (int)((phi >> 8) & 0x1FF);
-                            } else {
-                                const uint32_t pk = cnt_lo ? plo : phi;
-                                const int s1 = (int)((pk >> 8) & 0x1FF), s2 = (int)(pk >> 17);
-                                const int df = (int)(sqrtf((float)(2 * s2 - s1 * s1)) + 0.5f);
-                                const int base_j = cnt_lo ? 0 : 128;
-                                code = base_j + ((s1 - df) >> 1);
-                                second = base_j + ((s1 + df) >> 1);
-                            }
-                        } else {
-                            multi = true;
-                            code = 255;
-                            second = 255;
-                        }
                         p.codes[row * p.M + m] = (uint8_t)code;
                         if (second) p.cand2[row * p.M + m] = (uint8_t)second;
                     }
@@ -756,7 +750,7 @@ static ScratchPlan plan_scratch(int64_t n, int M, int dsub) {
     s.bextra = al(s.bprep + (size_t)M * KSUB * dsub * 4);
     s.ones = al(s.bextra + (size_t)M * KSUB * 8 * 4);
     s.cmax = al(s.ones + TILE_ROWS * 8 * 4);
-    s.counter = al(s.cmax + (size_t)M * 4);
+    s.counter = al(s.cmax + (size_t)M * 8);
     s.list = al(s.counter + (size_t)M * 8);
     unsigned long long cap = (unsigned long long)(n / 8);   // per sub-quantizer; overflow falls back inline
     if (cap < 1024) cap = 1024;
@@ -800,7 +794,7 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     float* bprep = reinterpret_cast<float*>(sb + sc.bprep);
     float* bextra = reinterpret_cast<float*>(sb + sc.bextra);
     float* ones = reinterpret_cast<float*>(sb + sc.ones);
-    float* cmax = reinterpret_cast<float*>(sb + sc.cmax);
+    float2* cmax = reinterpret_cast<float2*>(sb + sc.cmax);
     unsigned long long* counter = reinterpret_cast<unsigned long long*>(sb + sc.counter);
     uint32_t* list = reinterpret_cast<uint32_t*>(sb + sc.list);
     uint8_t* cand2 = sb + sc.cand2;
