@@ -85,3 +85,29 @@ def test_screen_overflow_goes_through_the_exact_fallback(T):
     v0, i0 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True)
     v1, i1 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True, screen=True)
     assert T.torch.equal(i0, i1) and T.torch.allclose(v0, v1, rtol=2e-6)
+
+
+@pytest.mark.parametrize("M,n", [(16, 100_000), (80, 70_000), (48, 66_000), (16, 5_000), (16, 1_000_000)])
+def test_padded_scan_layout_matches_row_layout(M, n):
+    """M not a multiple of 32 (BASELINE config 1: M = 16): codes padded to the scan layout's group width
+    with all-zero tables give the row-layout exact kernel's ids and value bits; n >= 65536 takes the
+    screened path (threshold sample = n / 8 rows), smaller n the exact scan-layout kernel."""
+    import torch
+    from b200vq import ops, ops_sq, pq as dpq
+    dev = torch.device("cuda")
+    D = M * 8
+    x = ops_sq.synth_rows(n, D, 0, 77, None, True, device=dev)
+    q = ops_sq.synth_rows(37, D, 1 << 30, 78, None, True, device=dev)
+    C = dpq.pq_train(x[:20000], M, 8, niter=3, seed=5)
+    codec = dpq.PQCodec(C)
+    codes = codec.encode(x)
+    crot = ops.pq_codes_to_scan_layout(codec.pad_codes_for_scan(codes))
+    mp = (M + 31) // 32 * 32
+    for metric in ("l2", "ip"):
+        v0, i0 = codec.search(codes, q, 10, metric)
+        v1, i1 = codec.search(crot, q, 10, metric, n=n, rot=True, m_pad=mp)
+        assert torch.equal(i0, i1)
+        if n >= 65536:   # screened path: exact finish in the row-layout kernel's summation order
+            assert torch.equal(v0.view(torch.int32), v1.view(torch.int32))
+        else:            # exact scan-layout kernel: rotated summation order, last-bit differences
+            assert torch.allclose(v0, v1, rtol=1e-6, atol=0)

@@ -159,10 +159,23 @@ class PQCodec:
             queries = rotate(queries, self.rotation)  # orthonormal: distances are preserved
         return ops.adc_lut(queries, self.centroids, metric)
 
+    def pad_codes_for_scan(self, codes: torch.Tensor) -> torch.Tensor:
+        """(n, M) codes -> (n, M_pad) with M_pad the next multiple of 32 (the scan layout's group width);
+        the extra sub-quantizers hold code 0 and their tables are all zero (search(m_pad=...)), so every score
+        keeps its bits: x + 0.0 is exact and the real sub-quantizers are still summed first, in order."""
+        n, M = codes.shape
+        mp = (M + 31) // 32 * 32
+        if mp == M:
+            return codes
+        out = torch.zeros((n, mp), dtype=torch.uint8, device=codes.device)
+        out[:, :M] = codes
+        return out
+
     def search(self, codes: torch.Tensor, queries: torch.Tensor, k: int, metric, n: int | None = None,
-               rot: bool = False, q_batch: int = 4096, screen: bool | None = None):
+               rot: bool = False, q_batch: int = 4096, screen: bool | None = None, m_pad: int | None = None):
         """ADC top-k over (n, M) codes. Returns (vals (nq,k) fp32, ids (nq,k) int32-as-uint32).
-        screen (scan layout only; default on): four-queries-per-lookup screened scan, same results."""
+        screen (scan layout only; default on): four-queries-per-lookup screened scan, same results.
+        m_pad: the codes were padded to m_pad sub-quantizers (pad_codes_for_scan); the tables are padded with zeros."""
         if screen is None:
             screen = rot
         nq = queries.shape[0]
@@ -171,6 +184,10 @@ class PQCodec:
         for s in range(0, nq, q_batch):
             e = min(nq, s + q_batch)
             lut = self.luts(queries[s:e], metric)
+            if m_pad is not None and m_pad != self.M:
+                lp = torch.zeros((e - s, m_pad, self.ksub), dtype=torch.float32, device=lut.device)
+                lp[:, :self.M] = lut
+                lut = lp
             v, i = ops.adc_scan_topk(codes, lut, k, metric, n=n, rot=rot, screen=bool(screen and rot))
             vals[s:e], ids[s:e] = v, i
         return vals, ids

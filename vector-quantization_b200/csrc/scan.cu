@@ -608,7 +608,12 @@ struct ScreenPlan {
 };
 static ScreenPlan plan_screen(int64_t n, int M, int nq, int k) {
     ScreenPlan s;
-    s.n_sample = SCREEN_SAMPLE;
+    // threshold sample: an eighth of the rows, between 8192 and SCREEN_SAMPLE (a smaller sample only loosens
+    // the thresholds; the result stays exact)
+    int64_t ns = (n / 8) & ~(int64_t)31;
+    if (ns < 8192) ns = 8192;
+    if (ns > SCREEN_SAMPLE) ns = SCREEN_SAMPLE;
+    s.n_sample = ns;
     s.ngroups = (nq + 3) / 4;
     int64_t cap = n / 256;
     if (cap < 4096) cap = 4096;
@@ -628,7 +633,7 @@ static ScreenPlan plan_screen(int64_t n, int M, int nq, int k) {
     s.total = o;
     return s;
 }
-static bool screen_applies(int64_t n, int nq, int k) { return n >= 8 * (int64_t)SCREEN_SAMPLE && nq >= 4 && k <= 64; }
+static bool screen_applies(int64_t n, int nq, int k) { return n >= 65536 && nq >= 4 && k <= 64; }
 
 extern "C" size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq, int k) {
     if (n < 0 || nq <= 0 || k <= 0 || M <= 0) return 0;
