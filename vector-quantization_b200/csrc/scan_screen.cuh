@@ -29,21 +29,35 @@ constexpr int SCREEN_SAMPLE = 65536;     // rows of the threshold sample
 __global__ void __launch_bounds__(256)
 screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float* __restrict__ sample_vals, int k,
                       int negate, uint8_t* __restrict__ qlut4, int* __restrict__ thr) {
-    __shared__ float red[8];
+    __shared__ float red[8], redx[8];
     __shared__ float lo_s[96];
+    __shared__ int active_s;
     __shared__ float step_s;
     const int q = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
     const float* T = lut + (size_t)q * M * 256;
     const float sgn = negate ? -1.f : 1.f;
+    if (t == 0) active_s = 0;
     for (int m = 0; m < M; ++m) {
-        float v = sgn * T[m * 256 + t];
-        for (int s = 16; s > 0; s >>= 1) v = fminf(v, __shfl_xor_sync(FULL_MASK, v, s));
-        if (lane == 0) red[w] = v;
+        float v = sgn * T[m * 256 + t], vx = v;
+        for (int s = 16; s > 0; s >>= 1) {
+            v = fminf(v, __shfl_xor_sync(FULL_MASK, v, s));
+            vx = fmaxf(vx, __shfl_xor_sync(FULL_MASK, vx, s));
+        }
+        if (lane == 0) {
+            red[w] = v;
+            redx[w] = vx;
+        }
         __syncthreads();
         if (t == 0) {
-            float mn = red[0];
-            for (int i = 1; i < 8; ++i) mn = fminf(mn, red[i]);
+            float mn = red[0], mx = redx[0];
+            for (int i = 1; i < 8; ++i) {
+                mn = fminf(mn, red[i]);
+                mx = fmaxf(mx, redx[i]);
+            }
             lo_s[m] = mn;
+            // constant tables (the all-zero tables of sub-quantizers added by padding M to the scan layout's
+            // group width) always contribute exactly lo: they take no share of the budget
+            if (mx > mn) ++active_s;
         }
         __syncthreads();
     }
@@ -62,8 +76,8 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
             const double margin = 7.63e-6 * (fabs(tau) + sum_abs) + 1e-30;
             double budget = tau - sum_lo;
             if (budget < 0) budget = 0;
-            // clip level of one table entry = 6x the mean per-sub-quantizer budget of a threshold row
-            double st = budget * 6.0 / ((double)M * SCREEN_QMAX);
+            // clip level of one table entry = 6x the mean budget per (non-constant) sub-quantizer of a threshold row
+            double st = budget * 6.0 / ((double)(active_s > 0 ? active_s : 1) * SCREEN_QMAX);
             const double floor_st = (fabs(tau) + sum_abs + 1e-30) * 1e-9;
             if (st < floor_st) st = floor_st;
             step = (float)st;
