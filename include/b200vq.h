@@ -268,6 +268,17 @@ int b200vq_lvq_decode(const uint8_t* codes, int64_t n, int D, const float* mu, i
  * added one after another in fp32, then / n): lvq_quantization.py:44-46. mean (D) fp32. */
 int b200vq_col_mean_seq(const float* x, int64_t n, int64_t ldx, int D, float* mean, void* stream);
 
+/* --------------------------------------------------------- FFD packing ---
+ * Byte-aligned packing of per-dimension codes: src/haag_vq/methods/ffd_packing.py:84-98 (ffd_encode)
+ * and :101-117 (ffd_decode). The layout of ffd_layout (:25-81) is passed as small device tables:
+ * byte_dims (n_bytes, 8) int32 = dimensions stored in each byte (-1 padded); dim_byte (D) int32 (-1 for
+ * zero-width dimensions); dim_shift (D) uint8 = byte_cap - bit_off - width; dim_mask (D) uint8.
+ * codes (n, D) uint8 (one code per dimension, < 2^width); packed (n, n_bytes) uint8. */
+int b200vq_ffd_pack(const uint8_t* codes, int64_t n, int D, const int* byte_dims, const uint8_t* dim_shift,
+                    int n_bytes, uint8_t* out, void* stream);
+int b200vq_ffd_unpack(const uint8_t* packed, int64_t n, int n_bytes, const int* dim_byte,
+                      const uint8_t* dim_shift, const uint8_t* dim_mask, int D, uint8_t* codes, void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):
