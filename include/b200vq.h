@@ -279,6 +279,20 @@ int b200vq_ffd_pack(const uint8_t* codes, int64_t n, int D, const int* byte_dims
 int b200vq_ffd_unpack(const uint8_t* packed, int64_t n, int n_bytes, const int* dim_byte,
                       const uint8_t* dim_shift, const uint8_t* dim_mask, int D, uint8_t* codes, void* stream);
 
+/* ------------------------------------------ per-dimension codebooks ---
+ * RankAwareQuantizer data path (src/haag_vq/methods/rank_aware_quantization.py:229-235 nearest level by
+ * searchsorted into codebook mid-points; :252-279 FFD / dense MSB-first packing; :283-320 decode).
+ * y / yhat (n, D) fp64 projected coordinates; bits (D) uint8 widths (0..8); bitpos (D) int32 MSB-first bit
+ * position of each field in the row (dense: cumulative widths; FFD: 8 * byte_idx + bit_off);
+ * bounds = concatenated mid-points (2^b - 1 per dimension) at bound_off (D); cb = concatenated levels
+ * (2^b per dimension) at cb_off (D); codes (n, code_size) uint8. */
+int b200vq_perdim_encode(const double* y, int64_t n, int64_t ldy, int D, const double* bounds,
+                         const int* bound_off, const uint8_t* bits, const int* bitpos, int code_size,
+                         uint8_t* codes, void* stream);
+int b200vq_perdim_decode(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits,
+                         const int* bitpos, const double* cb, const int* cb_off, double* yhat, int64_t ldy,
+                         void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):

@@ -4,8 +4,9 @@ Mirrors src/haag_vq/benchmarks/method_registry_saq.py:17-74 for the methods on
 the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)) and
 ``saq_paper`` -> SaqEngineAdapter(CAQ, DP allocation) (SURVEY.md §8 rows a9-a11,
 a16) and ``lvq`` -> LVQQuantizer(num_bits=round(bpd)) (reference :49-52). The other
-names of SAQ_METHODS (ours*, rankaware*, perdim_mse*) are
-the greedy-allocation / per-dimension codebook studies SURVEY.md §8(f) ranks as
+names of SAQ_METHODS (ours*, rankaware*, perdim_mse*) need the SAQ engine's greedy allocator / data-fit
+codebook builders (RankAwareQuantizer itself is built with codebook="gaussian", haag_vq/methods/
+rank_aware_quantization.py); they are the studies SURVEY.md §8(f) ranks as
 "next"; they raise NotImplementedError here instead of silently falling back.
 """
 from __future__ import annotations

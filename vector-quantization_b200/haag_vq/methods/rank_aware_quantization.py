@@ -1,0 +1,222 @@
+"""RankAwareQuantizer on the B200 kernels.
+
+Mirrors src/haag_vq/methods/rank_aware_quantization.py:57-329: centre -> PCA rotate -> per-dimension
+scalar codebook scaled by sqrt(var_d), with per-dimension bit widths from a greedy whose marginal gain is
+var_d^(1+alpha) * (Dg[b] - Dg[b+1]); codes are per-row bit strings (``packing="dense"``, MSB-first) or FFD
+byte layouts (``packing="ffd"``). Same constructor, public state (mu, V, var, bits, cb, D, code_size) and
+errors as the reference.
+
+Device work: mean / covariance (fp64 accumulation) and the eigendecomposition in ``fit``; the fp64
+projection GEMMs; nearest-level search + packing (``b200vq_perdim_encode``) and the inverse gather
+(``b200vq_perdim_decode``). The 1-D Lloyd-Max tables for N(0,1) and the greedy allocation are host
+training logic (a few thousand scalar steps). ``codebook="gaussian"`` only: the data-fit codebooks
+('lloyd', 'exact') come from the SAQ engine's C++ builders (external/saq), which are not built here.
+Given the same trained state, codes are identical to the reference's wherever a projected coordinate is
+not within rounding distance (1e-12 relative) of a codebook mid-point: the fp64 GEMM's summation order is
+the library's, not numpy's.
+"""
+from __future__ import annotations
+
+import functools
+
+import numpy as np
+import torch
+
+from b200vq import _lib, host
+from b200vq._lib import check
+from b200vq.ops import _stream
+
+from .base_quantizer import BaseQuantizer
+from .ffd_packing import ffd_layout
+
+
+@functools.lru_cache(maxsize=64)   # deterministic in its arguments; a fit needs nine tables
+def _lloyd_1d_normal(num_levels: int, seed: int, n_samples: int = 200_000, max_iter: int = 100, tol: float = 1e-7):
+    """(levels, normalised MSE) of the Lloyd-Max quantizer of N(0,1) on a seeded sample
+    (rank_aware_quantization.py:7-54): quantile start, nearest-level assignment by mid-points,
+    centroid update, stop when no level moves by more than ``tol``."""
+    x = np.random.default_rng(seed).standard_normal(n_samples)
+    power = float(np.mean(x ** 2))
+    if num_levels == 1:
+        return np.array([0.0]), float(np.mean(x ** 2) / power)
+    levels = np.quantile(x, (np.arange(num_levels) + 0.5) / num_levels)
+    for _ in range(max_iter):
+        cell = np.searchsorted(0.5 * (levels[:-1] + levels[1:]), x)
+        moved = levels.copy()
+        for k in range(num_levels):
+            members = cell == k
+            if np.any(members):
+                moved[k] = x[members].mean()
+        moved.sort()
+        step = float(np.max(np.abs(moved - levels)))
+        levels = moved
+        if step < tol:
+            break
+    cell = np.searchsorted(0.5 * (levels[:-1] + levels[1:]), x)
+    return levels.astype(np.float64), float(np.mean((x - levels[cell]) ** 2) / power)
+
+
+class RankAwareQuantizer(BaseQuantizer):
+    def __init__(self, avg_bits: float, alpha: float = 1.0, max_bits: int = 8, seed: int = 0,
+                 packing: str = "dense", codebook: str = "gaussian"):
+        if max_bits < 1 or max_bits > 8:
+            raise ValueError("max_bits must be in [1, 8]")
+        if packing not in ("dense", "ffd"):
+            raise ValueError("packing must be 'dense' or 'ffd'")
+        if codebook not in ("gaussian", "lloyd", "exact"):
+            raise ValueError("codebook must be 'gaussian', 'lloyd', or 'exact'")
+        if codebook != "gaussian":
+            raise NotImplementedError(
+                f"codebook={codebook!r} needs the SAQ engine's codebook builders, which are not built on the "
+                "B200 path yet (SURVEY.md 8f); no fallback is provided")
+        self.codebook = codebook
+        self.avg_bits = float(avg_bits)
+        self.alpha = float(alpha)
+        self.max_bits = int(max_bits)
+        self.seed = int(seed)
+        self.packing = packing
+        self.mu = self.V = self.var = self.bits = self.cb = None
+        self.D = None
+        self._offsets = None
+        self.code_size = None
+        self._ffd_byte_idx = self._ffd_bit_off = self._ffd_n_bytes = None
+        self._dev = None
+
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        st["_dev"] = None
+        return st
+
+    # ------------------------------------------------------------------ fit
+    def fit(self, X: np.ndarray) -> None:
+        X = np.asarray(X)
+        N, D = X.shape
+        self.D = int(D)
+        dev = host.device()
+        S = torch.zeros(D, dtype=torch.float64, device=dev)
+        G = torch.zeros((D, D), dtype=torch.float64, device=dev)
+        rows = max(1, min(N, (1 << 28) // max(1, 8 * D)))
+        for s in range(0, N, rows):
+            blk = host.to_device(np.ascontiguousarray(X[s:s + rows])).to(torch.float64)
+            S += blk.sum(dim=0)
+            G += blk.t() @ blk
+        mu = S / N
+        C = G / N - torch.outer(mu, mu)
+        w, Vt = torch.linalg.eigh(C)                       # ascending
+        order = torch.argsort(w, descending=True)
+        self.mu = host.to_host(mu).copy()
+        self.var = np.clip(host.to_host(w[order]), 1e-12, None)
+        self.V = host.to_host(Vt[:, order]).copy()
+
+        self._levels = [None] * (self.max_bits + 1)
+        Dg = np.empty(self.max_bits + 1, dtype=np.float64)
+        for b in range(self.max_bits + 1):
+            lv, Dg[b] = _lloyd_1d_normal(2 ** b, seed=self.seed + b)
+            self._levels[b] = lv.copy()
+        Dg[0] = 1.0
+        self._Dg = Dg
+        self.bits = self._allocate(self.var, Dg, int(round(self.avg_bits * D)))
+        scale = np.sqrt(self.var)
+        self.cb = [self._levels[int(b)] * scale[d] for d, b in enumerate(self.bits)]
+        self._finish_layout()
+
+    def _allocate(self, var: np.ndarray, Dg: np.ndarray, total: int) -> np.ndarray:
+        """Greedy of rank_aware_quantization.py:148-181: one bit at a time to the dimension with the largest
+        var^(1+alpha) * (Dg[b] - Dg[b+1]); first index wins ties (np.argmax); stops when every dimension is capped."""
+        D = var.shape[0]
+        weight = var ** (1.0 + self.alpha)
+        drop = Dg[:-1] - Dg[1:]
+        bits = np.zeros(D, dtype=np.int64)
+        gain = weight * drop[0]
+        for _ in range(total):
+            d = int(np.argmax(gain))
+            if not np.isfinite(gain[d]):
+                break
+            bits[d] += 1
+            gain[d] = weight[d] * drop[bits[d]] if bits[d] < self.max_bits else -np.inf
+        return bits
+
+    def _finish_layout(self) -> None:
+        self.bits = np.asarray(self.bits, dtype=np.int64)
+        self._offsets = np.concatenate(([0], np.cumsum(self.bits))).astype(np.int64)
+        if self.packing == "ffd":
+            self._ffd_byte_idx, self._ffd_bit_off, n_bytes = ffd_layout(self.bits)
+            self._ffd_n_bytes = int(n_bytes)
+            self.code_size = int(n_bytes)
+        else:
+            self.code_size = (int(self.bits.sum()) + 7) // 8
+        self._dev = None
+
+    def set_state(self, mu, V, var, bits, cb) -> None:
+        """Adopt trained state (e.g. exported by the reference class): parity tests and load paths."""
+        self.mu = np.asarray(mu, dtype=np.float64)
+        self.V = np.asarray(V, dtype=np.float64)
+        self.var = np.asarray(var, dtype=np.float64)
+        self.bits = np.asarray(bits, dtype=np.int64)
+        self.cb = [np.asarray(c, dtype=np.float64) for c in cb]
+        self.D = int(self.mu.shape[0])
+        self._finish_layout()
+
+    # -------------------------------------------------------------- device tables
+    def _tables(self):
+        if self._dev is None:
+            D = self.D
+            bits = self.bits
+            if self.packing == "ffd":
+                pos = np.where(bits > 0, self._ffd_byte_idx * 8 + self._ffd_bit_off, 0)
+            else:
+                pos = self._offsets[:-1]
+            bounds = [0.5 * (c[:-1] + c[1:]) if b > 0 else np.zeros(0) for c, b in zip(self.cb, bits)]
+            boff = np.concatenate(([0], np.cumsum([len(x) for x in bounds])))[:-1]
+            cboff = np.concatenate(([0], np.cumsum([len(c) for c in self.cb])))[:-1]
+            t = lambda a, dt: host.to_device(np.ascontiguousarray(a, dtype=dt))
+            self._dev = {
+                "mu": t(self.mu, np.float64), "V": t(self.V, np.float64),
+                "bits": t(bits, np.uint8), "pos": t(pos, np.int32),
+                "bounds": t(np.concatenate(bounds + [np.zeros(1)]), np.float64), "boff": t(boff, np.int32),
+                "cb": t(np.concatenate(list(self.cb)), np.float64), "cboff": t(cboff, np.int32),
+            }
+        return self._dev
+
+    # ------------------------------------------------------------- compress
+    def compress(self, X: np.ndarray) -> np.ndarray:
+        if self.V is None:
+            raise RuntimeError("Quantizer must be fit before compress().")
+        X = np.asarray(X)
+        N, D = X.shape
+        if D != self.D:
+            raise ValueError(f"compress() got D={D}, but fit() saw D={self.D}")
+        T = self._tables()
+        out = torch.empty((N, self.code_size), dtype=torch.uint8, device=host.device())
+        rows = max(1, min(max(N, 1), (1 << 28) // max(1, 8 * D)))
+        lib = _lib.load()
+        for s in range(0, N, rows):
+            e = min(N, s + rows)
+            Y = (host.to_device(np.ascontiguousarray(X[s:e])).to(torch.float64) - T["mu"]) @ T["V"]
+            check(lib.b200vq_perdim_encode(Y.data_ptr(), e - s, Y.stride(0), D, T["bounds"].data_ptr(),
+                                           T["boff"].data_ptr(), T["bits"].data_ptr(), T["pos"].data_ptr(),
+                                           self.code_size, out[s:e].data_ptr(), _stream()), "perdim_encode")
+        return host.to_host(out)
+
+    # ----------------------------------------------------------- decompress
+    def decompress(self, codes: np.ndarray) -> np.ndarray:
+        if self.V is None:
+            raise RuntimeError("Quantizer must be fit before decompress().")
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        N, D = codes.shape[0], self.D
+        T = self._tables()
+        out = np.empty((N, D), dtype=np.float32)
+        rows = max(1, min(max(N, 1), (1 << 28) // max(1, 8 * D)))
+        lib = _lib.load()
+        for s in range(0, N, rows):
+            e = min(N, s + rows)
+            c = host.to_device(codes[s:e])
+            Yh = torch.empty((e - s, D), dtype=torch.float64, device=c.device)
+            check(lib.b200vq_perdim_decode(c.data_ptr(), e - s, self.code_size, D, T["bits"].data_ptr(),
+                                           T["pos"].data_ptr(), T["cb"].data_ptr(), T["cboff"].data_ptr(),
+                                           Yh.data_ptr(), Yh.stride(0), _stream()), "perdim_decode")
+            out[s:e] = host.to_host((Yh @ T["V"].t() + T["mu"]).to(torch.float32))
+        return out
+
+    def get_compression_ratio(self, X: np.ndarray) -> float:
+        return float(int(X.shape[1]) * 4 / self.code_size)
