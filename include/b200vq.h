@@ -248,6 +248,11 @@ int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B, const d
  * level LUT, score = ||q-c||^2 + nrm^2 - 2 nrm t/sqrt(D) <levels[idx], qrot>  (L2)
  * with qrot = (q-c) P and qconst = ||q-c||^2; inner product: score = qconst +
  * nrm t/sqrt(D) <levels[idx], qrot> with qrot = q P and qconst = q.c. */
+/* Decode for the tensor-core form of the same estimator: x (n, D) fp32 = a_i * levels[idx], a_i = nrm t / sqrt(D),
+ * xnorm (n) = ||x_i||^2. The estimator then equals the exact flat search of the rotated queries over x
+ * (b200vq_flat_topk_tc with this xnorm): squared L2 for the L2 form, inner product for the IP form. */
+int b200vq_erabitq_decode_f32(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
+                              float* x, int64_t ldx, float* xnorm, void* stream);
 size_t b200vq_erabitq_scan_scratch_bytes(int64_t n, int nq, int k);
 int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
                              const float* qrot, const float* qconst, int nq, int metric, int k,

@@ -141,3 +141,33 @@ def test_rabitq_index_contract(T, tmp_path):
     gt = np.argsort(true, axis=1)[:, :10]
     rec = np.mean([len(set(gt[i]) & set(ids[i])) / 10 for i in range(11)])
     assert rec > 0.3
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+@pytest.mark.parametrize("B", [2, 4, 8])
+def test_erabitq_scan_tensor_core_path_matches_simt(T, B, metric):
+    """The estimator scan as an exact flat search over the decoded rows (b200vq_erabitq_decode_f32 +
+    b200vq_flat_topk_tc) against the code-domain SIMT kernel: same top-k up to fp32 rounding of the
+    differently associated sums (values within 1e-4 relative, ids equal outside near-ties)."""
+    import torch
+    n, D, nq, k = 70_000, 128, 33, 10
+    g = torch.Generator(device="cuda").manual_seed(B * 10 + metric)
+    levels = torch.sort(torch.randn(1 << B, generator=g, device="cuda"))[0].contiguous()
+    ib = (D * B + 7) // 8
+    codes = torch.randint(0, 256, (n, ib + 8), generator=g, device="cuda", dtype=torch.uint8)
+    nrm = torch.rand(n, generator=g, device="cuda") + 0.5
+    t = torch.rand(n, generator=g, device="cuda") * 0.2 + 0.9
+    codes[:, ib:ib + 4] = nrm.view(torch.uint8).reshape(n, 4)
+    codes[:, ib + 4:] = t.view(torch.uint8).reshape(n, 4)
+    qrot = torch.randn(nq, D, generator=g, device="cuda")
+    qconst = (qrot * qrot).sum(1) if metric == 0 else torch.randn(nq, generator=g, device="cuda")
+    v0, i0 = T.ops_sq.erabitq_scan_topk(codes, D, B, levels, qrot, qconst, k, metric, impl="simt")
+    v1, i1 = T.ops_sq.erabitq_scan_topk(codes, D, B, levels, qrot, qconst, k, metric, impl="tc")
+    scale = v0.abs().max().item()
+    assert torch.allclose(v0, v1, rtol=1e-4, atol=1e-5 * scale)
+    same = (i0 == i1)
+    assert same.float().mean().item() > 0.98
+    # where the ids differ, the two candidates' scores are within rounding distance
+    bad = torch.nonzero(~same)
+    for a, b in bad.tolist():
+        assert abs(v0[a, b].item() - v1[a, b].item()) <= 1e-4 * scale

@@ -169,6 +169,23 @@ def c4():
         "vectors", bytes_=nb * (8 * D + D * B // 8 + 8))
     add("C4", "erabitq_unpack B=4 (fp64 out)", timed(lambda: ops_sq.erabitq_unpack(ecodes, D, B, levels)), nb, "vectors",
         bytes_=nb * (8 * D + D * B // 8 + 8))
+    # extended RaBitQ estimator scan in the code domain (BASELINE config 4): <levels[idx], q P> per (code, query)
+    qrot = torch.randn((nq, D), generator=g, device=dev, dtype=torch.float32)
+    qconst = torch.rand((nq,), generator=g, device=dev, dtype=torch.float32)
+    lv32 = levels.to(torch.float32).contiguous()
+    add("C4", f"erabitq_scan_topk simt B=4 k=10 ({nb} codes)",
+        timed(lambda: ops_sq.erabitq_scan_topk(ecodes, D, B, lv32, qrot, qconst, 10, "l2", impl="simt"), reps=1, warm=1),
+        nb * nq, "codes", bytes_=float(nb) * (D * B // 8 + 8) * nq, note="query tile 1")
+    add("C4", f"erabitq_scan_topk tc B=4 k=10 ({nb} codes; decode + flat search)",
+        timed(lambda: ops_sq.erabitq_scan_topk(ecodes, D, B, lv32, qrot, qconst, 10, "l2", impl="tc"), reps=3, warm=2),
+        nb * nq, "codes", bytes_=float(nb) * (D * B // 8 + 8) * ((nq + 255) // 256), flops=2.0 * nb * nq * D,
+        note="query tile 256")
+    big = ecodes.repeat(8, 1)[:1_000_000].contiguous()
+    add("C4", "erabitq_scan_topk tc B=4 k=10 (1M codes; decode + flat search)",
+        timed(lambda: ops_sq.erabitq_scan_topk(big, D, B, lv32, qrot, qconst, 10, "l2", impl="tc"), reps=3, warm=2),
+        1_000_000 * nq, "codes", bytes_=1e6 * (D * B // 8 + 8) * ((nq + 255) // 256), flops=2.0 * 1e6 * nq * D,
+        note="query tile 256")
+    del big
     P = torch.randn((D, D), generator=g, device=dev, dtype=torch.float64)
     add("C4", "fp64 rotation GEMM (library)", timed(lambda: torch.matmul(srot, P), reps=2, warm=1), nb, "vectors",
         flops=2.0 * nb * D * D)

@@ -64,6 +64,7 @@ SIGNATURES = {
     "b200vq_erabitq_pack": (_i, [_p, _p, _i64, _i, _i, _p, _p, _p, _p]),
     "b200vq_erabitq_unpack": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p]),
     "b200vq_erabitq_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
+    "b200vq_erabitq_decode_f32": (_i, [_p, _i64, _i, _i, _p, _p, _i64, _p, _p]),
     "b200vq_erabitq_scan_topk": (_i, [_p, _i64, _i, _i, _p, _p, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_perdim_encode": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _i, _p, _p]),
     "b200vq_perdim_decode": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p, _p, _i64, _p]),

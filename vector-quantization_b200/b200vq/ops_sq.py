@@ -102,12 +102,41 @@ def erabitq_unpack(codes: torch.Tensor, D: int, B: int, levels: torch.Tensor):
     return shat, nrm
 
 
+def erabitq_decode_f32(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Tensor):
+    """x (n, D) fp32 = nrm t / sqrt(D) * levels[idx] and its squared row norms (b200vq_erabitq_decode_f32)."""
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n = codes.shape[0]
+    x = torch.empty((n, D), dtype=torch.float32, device=codes.device)
+    xn = torch.empty((n,), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_erabitq_decode_f32(codes.data_ptr(), n, D, B, levels_f32.data_ptr(), x.data_ptr(),
+                                                x.stride(0), xn.data_ptr(), _stream()), "erabitq_decode_f32")
+    return x, xn
+
+
 def erabitq_scan_topk(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Tensor, qrot: torch.Tensor,
-                      qconst: torch.Tensor, k: int, metric):
+                      qconst: torch.Tensor, k: int, metric, impl: str = "auto"):
+    """Extended-RaBitQ estimator top-k. impl "simt": the code-domain kernel (one level look-up per dimension and
+    query); "tc" / "auto": decode once to fp32 rows, then the exact flat search on the tensor cores — the
+    estimator qc + a^2 sum l^2 - 2 a <l, q> is the squared distance between the decoded row and the rotated
+    query (inner-product form: qc + a <l, q>), with qc put back in place of ||q||^2. Same ranking and values up
+    to fp32 rounding of the differently associated sums (1e-5 relative)."""
+    from .ops import flat_topk, row_sqnorms, tc_available
     _chk(codes, torch.uint8, "codes")
     codes = codes.contiguous()
     n = codes.shape[0]
     nq = qrot.shape[0]
+    if impl not in ("auto", "tc", "simt"):
+        raise B200VQError(f"erabitq_scan_topk: unknown impl {impl!r}")
+    if impl != "simt" and tc_available() and D % 32 == 0 and n >= 65536 and k <= 128:
+        x, xn = erabitq_decode_f32(codes, D, B, levels_f32)
+        q = qrot.contiguous()
+        vals, ids = flat_topk(x, q, k, metric, xnorm=xn)
+        if metric_id(metric) == 0:   # L2: the flat search used ||q||^2 where the estimator has qconst
+            vals = vals + (qconst - row_sqnorms(q))[:, None]
+        else:
+            vals = vals + qconst[:, None]
+        return vals, ids
     lib = _lib.load()
     vals, ids = _topk_out(nq, k, codes.device)
     sc = scratch(lib.b200vq_erabitq_scan_scratch_bytes(n, nq, k), codes.device, "scan")

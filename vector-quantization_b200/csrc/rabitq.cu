@@ -422,6 +422,38 @@ __global__ void erabitq_unpack_kernel(const uint8_t* __restrict__ codes, int64_t
 // Code-domain scan: thread = row, levels (fp32) and the rotated query in shared
 // memory. est = qconst + nrm^2 t^2 sum(l^2)/D - 2 nrm t/sqrt(D) <l[idx], qrot>  (L2)
 //        ip  = qc_dot + nrm t/sqrt(D) <l[idx], qrot>                         (IP; qconst = q.c)
+// Decode for the tensor-core estimator scan: x_i = a_i * levels[idx] (fp32), a_i = nrm_i t_i / sqrt(D), and
+// ||x_i||^2 = a_i^2 * sum levels[idx]^2. With these the estimator of erabitq_scan_kernel,
+// qc + a^2 l2 - 2 a <levels[idx], q>, IS the squared L2 distance between x_i and the rotated query (and
+// qc + a <levels[idx], q> the inner product), so the exact flat search on tcgen05 (flat_tc.cu) serves it.
+// One warp per row; HBM-bound: ceil(D B / 8) + 8 bytes in, 4 D + 4 out.
+__global__ void __launch_bounds__(256) erabitq_decode_f32_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
+                                                                 const float* __restrict__ levels,
+                                                                 float* __restrict__ x, int64_t ldx,
+                                                                 float* __restrict__ xnorm) {
+    __shared__ float lv[256];
+    for (int i = threadIdx.x; i < (1 << B); i += blockDim.x) lv[i] = levels[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int ibytes = (D * B + 7) >> 3, code_size = ibytes + 8;
+    const float inv_sqrt_d = 1.0f / sqrtf((float)D);
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = wid; row < n; row += nw) {
+        const uint8_t* code = codes + row * (int64_t)code_size;
+        const float a = load_f32_unaligned(code + ibytes) * load_f32_unaligned(code + ibytes + 4) * inv_sqrt_d;
+        float l2 = 0.f;
+        float* o = x + row * ldx;
+        for (int d = lane; d < D; d += 32) {
+            const float l = lv[erabitq_index(code, d, B, ibytes)];
+            l2 = __fmaf_rn(l, l, l2);
+            o[d] = a * l;
+        }
+        for (int s = 16; s > 0; s >>= 1) l2 += __shfl_xor_sync(FULL_MASK, l2, s);
+        if (lane == 0) xnorm[row] = a * a * l2;
+    }
+}
+
 template <int CAP>
 __global__ void __launch_bounds__(256)
     erabitq_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
@@ -654,6 +686,19 @@ extern "C" int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int
     if (g > cap) g = cap;
     erabitq_unpack_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, B, levels, shat,
                                                                  nrm_out);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_decode_f32(const uint8_t* codes, int64_t n, int D, int B, const float* levels,
+                                         float* x, int64_t ldx, float* xnorm, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && D > 0 && B >= 1 && B <= 8 && ldx >= D, "erabitq_decode_f32: bad shape");
+    if (n == 0) return B200VQ_OK;
+    VQ_CHECK_ARG(codes && levels && x && xnorm, "erabitq_decode_f32: null pointer");
+    int64_t g = (n * 32 + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    erabitq_decode_f32_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, B, levels, x, ldx, xnorm);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
