@@ -292,7 +292,8 @@ __global__ void __launch_bounds__(PF_THREADS) pair_fixup_kernel(Params p) {
 // warps walk their share: exact scan of all 256 centroids with the arithmetic
 // and tie-breaking (lowest index) of pq_assign_simt_kernel; lane l owns centroids l, l+32, ...
 constexpr int FIX_WARPS = 8;
-constexpr int FIX_ROWS = 4;   // list entries scored together by one warp (centroid loads are shared)
+constexpr int FIX_ROWS = 4;   // list entries scored together by one warp (centroid loads are shared; 8 rows need 194
+                              // registers and halve the occupancy: measured slower)
 constexpr int FIX_CHUNK = 256; // list entries per CTA
 __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
     extern __shared__ __align__(16) float fsm[];
@@ -342,17 +343,24 @@ __global__ void __launch_bounds__(FIX_WARPS * 32) fixup_kernel(Params p) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[t][k] = 0.f;
         }
-        for (int i = 0; i < dsub; ++i) {
-            const float* ci = cs + i * KSUB + lane;
-            float cv[8];
+        for (int i0 = 0; i0 < dsub; i0 += 4) {
+            // four dimensions of every row with one broadcast 128-bit load each
+            float4 xq[FIX_ROWS];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) cv[k] = ci[32 * k];
+            for (int t = 0; t < FIX_ROWS; ++t) xq[t] = *reinterpret_cast<const float4*>(xs + t * dsub + i0);
 #pragma unroll
-            for (int t = 0; t < FIX_ROWS; ++t) {
-                const float xv = xs[t * dsub + i];
-                xn[t] = __fmaf_rn(xv, xv, xn[t]);
+            for (int ii = 0; ii < 4; ++ii) {
+                const float* ci = cs + (i0 + ii) * KSUB + lane;
+                float cv[8];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) acc[t][k] = __fmaf_rn(xv, cv[k], acc[t][k]);
+                for (int k = 0; k < 8; ++k) cv[k] = ci[32 * k];
+#pragma unroll
+                for (int t = 0; t < FIX_ROWS; ++t) {
+                    const float xv = ii == 0 ? xq[t].x : (ii == 1 ? xq[t].y : (ii == 2 ? xq[t].z : xq[t].w));
+                    xn[t] = __fmaf_rn(xv, xv, xn[t]);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[t][k] = __fmaf_rn(xv, cv[k], acc[t][k]);
+                }
             }
         }
 #pragma unroll
