@@ -55,3 +55,18 @@ def test_benchmark_index_and_evaluate_recall():
 def _fitted(q, X):
     q.fit(X)
     return q
+
+
+def test_precompute_ground_truth_files(tmp_path):
+    from haag_vq.benchmarks.precompute_ground_truth import precompute_ground_truth
+    X = _data(3000, 24, 9)
+    np.save(tmp_path / "v.npy", X)
+    ids = precompute_ground_truth(str(tmp_path / "v.npy"), str(tmp_path / "out" / "gt.npy"), num_queries=40, k=7,
+                                  batch_size=16)
+    d2 = ((X[:40, None, :].astype(np.float64) - X[None].astype(np.float64)) ** 2).sum(-1)
+    assert np.array_equal(ids, np.argsort(d2, axis=1, kind="stable")[:, :7])
+    assert np.array_equal(np.load(tmp_path / "out" / "gt.npy"), ids)
+    dist = np.load(tmp_path / "out" / "gt.distances.npy")
+    assert dist.shape == (40, 7) and np.allclose(dist, np.sort(d2, axis=1)[:, :7], rtol=1e-4, atol=1e-4)
+    with pytest.raises(FileNotFoundError):
+        precompute_ground_truth(str(tmp_path / "nope.npy"), str(tmp_path / "x.npy"))
