@@ -121,25 +121,30 @@ __global__ void pq_decode_kernel(const uint8_t* __restrict__ codes, const int64_
     }
 }
 
-// 128-bit variant: one thread moves 4 consecutive floats of one sub-vector.
+// 128-bit variant: one warp per output row, a lane moves 4 consecutive floats of one sub-vector per step.
+// No 64-bit index arithmetic per element: the sub-quantizer of a 16-byte piece is a multiply-high by a
+// host-computed reciprocal (exact for the sizes here: piece index < 2^16, dsub / 4 <= 2^14).
 template <bool BY_ID>
-__global__ void pq_decode_v4_kernel(const uint8_t* __restrict__ codes,
-                                    const int64_t* __restrict__ ids, int64_t n,
-                                    const float* __restrict__ centroids, int M, int ksub, int dsub,
-                                    float* __restrict__ out, int64_t ldo) {
+__global__ void __launch_bounds__(256) pq_decode_v4_kernel(const uint8_t* __restrict__ codes,
+                                                           const int64_t* __restrict__ ids, int64_t n,
+                                                           const float* __restrict__ centroids, int M, int ksub,
+                                                           int dsub, uint32_t inv_dsub4, float* __restrict__ out,
+                                                           int64_t ldo) {
     const int D4 = (M * dsub) >> 2;
     const int dsub4 = dsub >> 2;
-    const int64_t total = n * (int64_t)D4;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t row = e / D4;
-        int c4 = (int)(e - row * D4);
-        int m = c4 / dsub4, i4 = c4 - m * dsub4;
-        int64_t src = BY_ID ? ids[row] : row;
-        int code = codes[src * M + m];
-        const float4* cp =
-            reinterpret_cast<const float4*>(centroids + ((size_t)m * ksub + code) * dsub) + i4;
-        reinterpret_cast<float4*>(out + row * ldo)[c4] = __ldg(cp);
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const float4* c4base = reinterpret_cast<const float4*>(centroids);
+    for (int64_t row = wid; row < n; row += nw) {
+        const uint8_t* code = codes + (BY_ID ? ids[row] : row) * M;
+        float4* o = reinterpret_cast<float4*>(out + row * ldo);
+#pragma unroll 4
+        for (int c4 = lane; c4 < D4; c4 += 32) {
+            const int m = (int)__umulhi((uint32_t)c4, inv_dsub4);
+            const int i4 = c4 - m * dsub4;
+            o[c4] = __ldg(c4base + ((size_t)m * ksub + code[m]) * dsub4 + i4);
+        }
     }
 }
 
@@ -370,6 +375,9 @@ static inline int grid_for(int64_t work, int block, int waves = 8) {
     return (int)g;
 }
 
+// ceil(2^32 / (dsub / 4)): __umulhi(c, inv) == c / (dsub / 4) for c < 2^16
+static uint32_t decode_inv(int dsub) { return (uint32_t)(((1ull << 32) + (uint64_t)(dsub >> 2) - 1) / (uint64_t)(dsub >> 2)); }
+
 extern "C" int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* centroids, int M,
                                 int ksub, int dsub, float* out, int64_t ldo, void* stream) {
     VQ_CHECK_ARG((codes || n == 0) && centroids && (out || n == 0) && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
@@ -379,9 +387,8 @@ extern "C" int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* ce
     bool v4 = (dsub % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
               (((uintptr_t)centroids & 15) == 0);
     if (v4) {
-        int64_t work = n * (int64_t)(M * dsub / 4);
-        pq_decode_v4_kernel<false><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
-            codes, nullptr, n, centroids, M, ksub, dsub, out, ldo);
+        pq_decode_v4_kernel<false><<<grid_for(n * 32, 256), 256, 0, as_stream(stream)>>>(
+            codes, nullptr, n, centroids, M, ksub, dsub, decode_inv(dsub), out, ldo);
     } else {
         int64_t work = n * (int64_t)(M * dsub);
         pq_decode_kernel<false><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
@@ -401,9 +408,8 @@ extern "C" int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, in
     bool v4 = (dsub % 4 == 0) && (ldo % 4 == 0) && (((uintptr_t)out & 15) == 0) &&
               (((uintptr_t)centroids & 15) == 0);
     if (v4) {
-        int64_t work = n_ids * (int64_t)(M * dsub / 4);
-        pq_decode_v4_kernel<true><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
-            codes, ids, n_ids, centroids, M, ksub, dsub, out, ldo);
+        pq_decode_v4_kernel<true><<<grid_for(n_ids * 32, 256), 256, 0, as_stream(stream)>>>(
+            codes, ids, n_ids, centroids, M, ksub, dsub, decode_inv(dsub), out, ldo);
     } else {
         int64_t work = n_ids * (int64_t)(M * dsub);
         pq_decode_kernel<true><<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(
