@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(256) pq_decode_v4_kernel(const uint8_t* __rest
         float4* o = reinterpret_cast<float4*>(out + row * ldo);
 #pragma unroll 4
         for (int c4 = lane; c4 < D4; c4 += 32) {
-            const int m = (int)__umulhi((uint32_t)c4, inv_dsub4);
+            const int m = dsub4 == 1 ? c4 : (int)__umulhi((uint32_t)c4, inv_dsub4);   // 2^32 / 1 does not fit the reciprocal
             const int i4 = c4 - m * dsub4;
             o[c4] = __ldg(c4base + ((size_t)m * ksub + code[m]) * dsub4 + i4);
         }
@@ -222,21 +222,24 @@ __global__ void pq_kmeans_finalize_kernel(const float* __restrict__ sums, int* _
     if (threadIdx.x == 0 && n_split && nsplit) atomicAdd(n_split, nsplit);
 }
 
-__global__ void pq_sse_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
-                              const uint8_t* __restrict__ codes,
-                              const float* __restrict__ centroids, int M, int ksub, int dsub,
-                              double* __restrict__ out) {
+// One warp per row: a lane walks the row's columns (no 64-bit index arithmetic per element), differences
+// in fp32, squares and sums in fp64.
+__global__ void __launch_bounds__(256) pq_sse_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
+                                                     const uint8_t* __restrict__ codes,
+                                                     const float* __restrict__ centroids, int M, int ksub, int dsub,
+                                                     double* __restrict__ out) {
     const int D = M * dsub;
-    const int64_t total = n * (int64_t)D;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
     double acc = 0.0;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t row = e / D;
-        int col = (int)(e - row * D);
-        int m = col / dsub, i = col - m * dsub;
-        int code = codes[row * M + m];
-        float d = x[row * ldx + col] - centroids[((size_t)m * ksub + code) * dsub + i];
-        acc += (double)d * (double)d;
+    for (int64_t row = wid; row < n; row += nw) {
+        const float* xr = x + row * ldx;
+        const uint8_t* code = codes + row * M;
+        for (int col = threadIdx.x & 31; col < D; col += 32) {
+            const int m = col / dsub, i = col - m * dsub;
+            const float d = xr[col] - centroids[((size_t)m * ksub + code[m]) * dsub + i];
+            acc += (double)d * (double)d;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
     __shared__ double part[32];
@@ -448,8 +451,7 @@ extern "C" int b200vq_pq_sse(const float* x, int64_t n, int64_t ldx, const uint8
     VQ_CHECK_ARG((x || n == 0) && (codes || n == 0) && centroids && (out || n == 0) && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
                  "pq_sse: bad args");
     if (n == 0) return B200VQ_OK;
-    int64_t work = n * (int64_t)(M * dsub);
-    pq_sse_kernel<<<grid_for(work, 256), 256, 0, as_stream(stream)>>>(x, n, ldx, codes, centroids,
+    pq_sse_kernel<<<grid_for(n * 32, 256), 256, 0, as_stream(stream)>>>(x, n, ldx, codes, centroids,
                                                                       M, ksub, dsub, out);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;

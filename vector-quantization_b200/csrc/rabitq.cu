@@ -319,76 +319,78 @@ __global__ void __launch_bounds__(256)
 
 // ======================================================= extended =========
 // One CTA per row (grid-stride). levels/bounds in shared memory.
-__global__ void erabitq_pack_kernel(const double* __restrict__ srot, const double* __restrict__ nrm,
-                                    int64_t n, int D, int B, const double* __restrict__ levels,
-                                    const double* __restrict__ bounds, uint8_t* __restrict__ codes) {
+// One warp per row (no CTA-wide barriers): level search for four elements per lane in flight, the row's
+// indices in a per-warp shared buffer, then one lane per output byte.
+__global__ void __launch_bounds__(256) erabitq_pack_kernel(const double* __restrict__ srot, const double* __restrict__ nrm,
+                                                           int64_t n, int D, int B, const double* __restrict__ levels,
+                                                           const double* __restrict__ bounds, uint8_t* __restrict__ codes) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* lv = reinterpret_cast<double*>(smem_raw);        // [2^B]
     double* bd = lv + (1 << B);                              // [2^B - 1] (padded to 2^B)
-    uint8_t* idx = reinterpret_cast<uint8_t*>(bd + (1 << B));  // [D]
-    __shared__ double red[2][32];
     const int L = 1 << B;
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5, nwarp = blockDim.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int dpad = (D + 15) & ~15;
+    uint8_t* idx = reinterpret_cast<uint8_t*>(bd + L) + (size_t)w * dpad;  // [warps][D]
     for (int i = tid; i < L; i += blockDim.x) lv[i] = levels[i];
     for (int i = tid; i < L - 1; i += blockDim.x) bd[i] = bounds[i];
     __syncthreads();
     const int ibytes = (D * B + 7) >> 3;
     const int code_size = ibytes + 8;
-    for (int64_t row = blockIdx.x; row < n; row += gridDim.x) {
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + tid) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = wid; row < n; row += nw) {
         const double* s = srot + row * (int64_t)D;
         double num = 0.0, den = 0.0;
-        for (int d = tid; d < D; d += blockDim.x) {
-            double v = s[d];
-            // np.searchsorted(bounds, v) (side='left'): number of bounds < v
-            int lo = 0, hi = L - 1;
-            while (lo < hi) {
-                int mid = (lo + hi) >> 1;
-                if (bd[mid] < v) lo = mid + 1;
-                else hi = mid;
+        for (int d0 = lane; d0 < D; d0 += 128) {
+            double v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = (d0 + 32 * u < D) ? s[d0 + 32 * u] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int d = d0 + 32 * u;
+                if (d < D) {
+                    // np.searchsorted(bounds, v) (side='left'): number of bounds < v
+                    int lo = 0, hi = L - 1;
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (bd[mid] < v[u]) lo = mid + 1;
+                        else hi = mid;
+                    }
+                    idx[d] = (uint8_t)lo;
+                    const double sh = lv[lo];
+                    num += v[u] * sh;
+                    den += sh * sh;
+                }
             }
-            idx[d] = (uint8_t)lo;
-            double sh = lv[lo];
-            num += v * sh;
-            den += sh * sh;
         }
         for (int o = 16; o > 0; o >>= 1) {
             num += __shfl_xor_sync(FULL_MASK, num, o);
             den += __shfl_xor_sync(FULL_MASK, den, o);
         }
-        if (lane == 0) {
-            red[0][w] = num;
-            red[1][w] = den;
-        }
-        __syncthreads();
+        __syncwarp();
         uint8_t* code = codes + row * (int64_t)code_size;
-        // MSB-first B-bit packing, one thread per output byte
-        for (int byte = tid; byte < ibytes; byte += blockDim.x) {
-            int b0 = byte * 8, b1 = b0 + 8;
+        // MSB-first B-bit packing, one lane per output byte
+        for (int byte = lane; byte < ibytes; byte += 32) {
+            const int b0 = byte * 8, b1 = b0 + 8;
             uint32_t acc = 0;
             for (int d = b0 / B; d < D && d * B < b1; ++d) {
-                int off = d * B;
-                int shift = b1 - (off + B);
-                uint32_t qv = idx[d];
+                const int shift = b1 - (d * B + B);
+                const uint32_t qv = idx[d];
                 acc |= ((shift >= 0) ? (qv << shift) : (qv >> (-shift))) & 0xffu;
             }
             code[byte] = (uint8_t)acc;
         }
-        if (tid == 0) {
-            double nsum = 0.0, dsum = 0.0;
-            for (int i = 0; i < nwarp; ++i) {
-                nsum += red[0][i];
-                dsum += red[1][i];
-            }
-            double t = (dsum > 1e-12) ? (nsum / dsum) : 1.0;
-            uint32_t u0 = __float_as_uint((float)nrm[row]);
-            uint32_t u1 = __float_as_uint((float)t);
+        if (lane == 0) {
+            const double t = (den > 1e-12) ? (num / den) : 1.0;
+            const uint32_t u0 = __float_as_uint((float)nrm[row]);
+            const uint32_t u1 = __float_as_uint((float)t);
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
                 code[ibytes + b] = (uint8_t)(u0 >> (8 * b));
                 code[ibytes + 4 + b] = (uint8_t)(u1 >> (8 * b));
             }
         }
-        __syncthreads();
+        __syncwarp();
     }
 }
 
@@ -400,22 +402,26 @@ __device__ __forceinline__ uint32_t erabitq_index(const uint8_t* code, int d, in
     return (wv >> shift) & ((1u << B) - 1u);
 }
 
-__global__ void erabitq_unpack_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
-                                      const double* __restrict__ levels, double* __restrict__ shat,
-                                      double* __restrict__ nrm_out) {
+// One warp per row; levels[i] / sqrt(D) is formed once per CTA (the same fp64 quotient the per-element form
+// computed 2^-B as often), t and nrm are read once per row.
+__global__ void __launch_bounds__(256) erabitq_unpack_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
+                                                             const double* __restrict__ levels, double* __restrict__ shat,
+                                                             double* __restrict__ nrm_out) {
+    __shared__ double lvs[256];
+    const double sqrt_d = sqrt((double)D);
+    for (int i = threadIdx.x; i < (1 << B); i += blockDim.x) lvs[i] = levels[i] / sqrt_d;
+    __syncthreads();
     const int ibytes = (D * B + 7) >> 3;
     const int code_size = ibytes + 8;
-    const double sqrt_d = sqrt((double)D);
-    const int64_t total = n * (int64_t)D;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t row = e / D;
-        int d = (int)(e - row * D);
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = wid; row < n; row += nw) {
         const uint8_t* code = codes + row * (int64_t)code_size;
-        uint32_t iv = erabitq_index(code, d, B, ibytes);
-        double t = (double)load_f32_unaligned(code + ibytes + 4);
-        shat[e] = (levels[iv] / sqrt_d) * t;
-        if (d == 0) nrm_out[row] = (double)load_f32_unaligned(code + ibytes);
+        const double t = (double)load_f32_unaligned(code + ibytes + 4);
+        double* o = shat + row * (int64_t)D;
+        for (int d = lane; d < D; d += 32) o[d] = lvs[erabitq_index(code, d, B, ibytes)] * t;
+        if (lane == 0) nrm_out[row] = (double)load_f32_unaligned(code + ibytes);
     }
 }
 
@@ -662,14 +668,14 @@ extern "C" int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_
                  "erabitq_pack: bad args");
     VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_pack: B must be in [1,8], got %d", B);
     if (n == 0) return B200VQ_OK;
-    size_t smem = (size_t)(2 << B) * sizeof(double) + (size_t)D + 16;
+    size_t smem = (size_t)(2 << B) * sizeof(double) + (size_t)8 * ((D + 15) & ~15) + 16;   // 8 warps' index buffers
     VQ_CHECK_ARG(smem <= 200 * 1024, "erabitq_pack: D too large");
     VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
-    int64_t g = n;
-    int64_t cap = (int64_t)device_sm_count() * 16;
+    int64_t g = (n + 7) / 8;
+    int64_t cap = (int64_t)device_sm_count() * 8;
     if (g > cap) g = cap;
-    erabitq_pack_kernel<<<(int)g, 128, smem, as_stream(stream)>>>(srot, nrm, n, D, B, levels, bounds,
+    erabitq_pack_kernel<<<(int)g, 256, smem, as_stream(stream)>>>(srot, nrm, n, D, B, levels, bounds,
                                                                  codes);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
@@ -681,7 +687,7 @@ extern "C" int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int
     VQ_CHECK_ARG((codes || n == 0) && levels && (shat || n == 0) && (nrm_out || n == 0) && n >= 0 && D > 0, "erabitq_unpack: bad args");
     VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_unpack: B must be in [1,8], got %d", B);
     if (n == 0) return B200VQ_OK;
-    int64_t g = (n * (int64_t)D + 255) / 256;
+    int64_t g = (n * 32 + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;
     if (g > cap) g = cap;
     erabitq_unpack_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, B, levels, shat,

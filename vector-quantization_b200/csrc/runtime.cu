@@ -100,17 +100,21 @@ __global__ void synth_rows_kernel(float* __restrict__ out, int64_t n, int64_t ld
     }
 }
 
-__global__ void sq_err_sum_kernel(const float* __restrict__ a, int64_t lda,
-                                  const float* __restrict__ b, int64_t ldb, int64_t n, int D,
-                                  double* __restrict__ out) {
-    const int64_t total = n * (int64_t)D;
+// One warp per row (no 64-bit index arithmetic per element): fp32 differences, fp64 squares and sums.
+__global__ void __launch_bounds__(256) sq_err_sum_kernel(const float* __restrict__ a, int64_t lda,
+                                                         const float* __restrict__ b, int64_t ldb, int64_t n, int D,
+                                                         double* __restrict__ out) {
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
     double acc = 0.0;
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (int64_t)gridDim.x * blockDim.x) {
-        int64_t row = e / D;
-        int c = (int)(e - row * D);
-        float d = a[row * lda + c] - b[row * ldb + c];
-        acc += (double)d * (double)d;
+    for (int64_t row = wid; row < n; row += nw) {
+        const float* ar = a + row * lda;
+        const float* br = b + row * ldb;
+#pragma unroll 4
+        for (int c = threadIdx.x & 31; c < D; c += 32) {
+            const float d = ar[c] - br[c];
+            acc += (double)d * (double)d;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
     __shared__ double part[32];
@@ -164,7 +168,7 @@ extern "C" int b200vq_sq_err_sum(const float* a, int64_t lda, const float* b, in
                                  int D, double* out, void* stream) {
     VQ_CHECK_ARG((a || n == 0) && (b || n == 0) && (out || n == 0) && n >= 0 && D > 0 && lda >= D && ldb >= D, "sq_err_sum: bad args");
     if (n == 0) return B200VQ_OK;
-    int64_t g = (n * (int64_t)D + 255) / 256;
+    int64_t g = (n * 32 + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 8;
     if (g > cap) g = cap;
     sq_err_sum_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(a, lda, b, ldb, n, D, out);
