@@ -42,6 +42,10 @@ def test_benchmark_index_and_evaluate_recall():
     assert row['method'] == 'FlatQuantizedIndex' and row['recall_at_k'] > 0.9 and row['qps'] > 0 and row['N'] == 4000
     df = sweep_bpd(lambda bpd: FlatQuantizedIndex(ScalarQuantizer(8 if bpd > 4.5 else 4)), [4.0, 8.0], X, Q, gt)
     assert list(df['bpd']) == [4.0, 8.0] and df['recall_at_k'][1] >= df['recall_at_k'][0]
+    from haag_vq.benchmarks.search_bench import compare_methods
+    from haag_vq.methods.search.rabitq_index import RaBitQIndex
+    cm = compare_methods({"sq8": FlatQuantizedIndex(ScalarQuantizer(8)), "rabitq": RaBitQIndex()}, X, Q, gt)
+    assert list(cm['method']) == ["sq8", "rabitq"] and cm['recall_at_k'][0] > cm['recall_at_k'][1] > 0.2
     ds = Dataset(X, queries=Q, num_queries=50)
     r = evaluate_recall(ds, _fitted(ScalarQuantizer(8), X), num_queries=50)
     assert r["recall@10"] > 0.9 and 0.9 < r["recall@100"] <= 1.0

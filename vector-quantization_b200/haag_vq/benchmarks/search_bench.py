@@ -97,3 +97,16 @@ def sweep_bpd(index_factory, bpd_values, X_train: np.ndarray, X_query: np.ndarra
         row['timestamp'] = stamp
         rows.append(row)
     return pd.DataFrame(rows)
+
+
+def compare_methods(method_configs: dict, X_train: np.ndarray, X_query: np.ndarray, gt_ids: np.ndarray, k: int = 10):
+    """One benchmark_index row per named (unfitted) index (search_bench.py:192-218); ``method`` = the dict key."""
+    import pandas as pd
+    stamp = _utc_timestamp()
+    rows = []
+    for name, index in method_configs.items():
+        row = benchmark_index(index, X_train, X_query, gt_ids, k=k)
+        row['method'] = name
+        row['timestamp'] = stamp
+        rows.append(row)
+    return pd.DataFrame(rows)
