@@ -227,7 +227,7 @@ __global__ void pq_kmeans_finalize_kernel(const float* __restrict__ sums, int* _
 __global__ void __launch_bounds__(256) pq_sse_kernel(const float* __restrict__ x, int64_t n, int64_t ldx,
                                                      const uint8_t* __restrict__ codes,
                                                      const float* __restrict__ centroids, int M, int ksub, int dsub,
-                                                     double* __restrict__ out) {
+                                                     uint32_t inv_dsub4, bool vec, double* __restrict__ out) {
     const int D = M * dsub;
     const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -235,10 +235,25 @@ __global__ void __launch_bounds__(256) pq_sse_kernel(const float* __restrict__ x
     for (int64_t row = wid; row < n; row += nw) {
         const float* xr = x + row * ldx;
         const uint8_t* code = codes + row * M;
-        for (int col = threadIdx.x & 31; col < D; col += 32) {
-            const int m = col / dsub, i = col - m * dsub;
-            const float d = xr[col] - centroids[((size_t)m * ksub + code[m]) * dsub + i];
-            acc += (double)d * (double)d;
+        if (vec) {   // 128-bit pieces, sub-quantizer by multiply-high (as pq_decode_v4_kernel)
+            const int D4 = D >> 2, dsub4 = dsub >> 2;
+            for (int c4 = threadIdx.x & 31; c4 < D4; c4 += 32) {
+                const int m = dsub4 == 1 ? c4 : (int)__umulhi((uint32_t)c4, inv_dsub4);
+                const float4 a = __ldg(reinterpret_cast<const float4*>(xr) + c4);
+                const float4 c = __ldg(reinterpret_cast<const float4*>(centroids) +
+                                       ((size_t)m * ksub + code[m]) * dsub4 + (c4 - m * dsub4));
+                const float d0 = a.x - c.x, d1 = a.y - c.y, d2 = a.z - c.z, d3 = a.w - c.w;
+                acc += (double)d0 * (double)d0;
+                acc += (double)d1 * (double)d1;
+                acc += (double)d2 * (double)d2;
+                acc += (double)d3 * (double)d3;
+            }
+        } else {
+            for (int col = threadIdx.x & 31; col < D; col += 32) {
+                const int m = col / dsub, i = col - m * dsub;
+                const float d = xr[col] - centroids[((size_t)m * ksub + code[m]) * dsub + i];
+                acc += (double)d * (double)d;
+            }
         }
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
@@ -451,8 +466,9 @@ extern "C" int b200vq_pq_sse(const float* x, int64_t n, int64_t ldx, const uint8
     VQ_CHECK_ARG((x || n == 0) && (codes || n == 0) && centroids && (out || n == 0) && M > 0 && ksub > 0 && dsub > 0 && n >= 0,
                  "pq_sse: bad args");
     if (n == 0) return B200VQ_OK;
-    pq_sse_kernel<<<grid_for(n * 32, 256), 256, 0, as_stream(stream)>>>(x, n, ldx, codes, centroids,
-                                                                      M, ksub, dsub, out);
+    const bool vec = dsub % 4 == 0 && ldx % 4 == 0 && (((uintptr_t)x | (uintptr_t)centroids) & 15) == 0;
+    pq_sse_kernel<<<grid_for(n * 32, 256), 256, 0, as_stream(stream)>>>(x, n, ldx, codes, centroids, M, ksub, dsub,
+                                                                        vec ? decode_inv(dsub) : 0u, vec, out);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
