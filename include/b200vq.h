@@ -128,6 +128,22 @@ int b200vq_adc_scan_topk(const uint8_t* codes, int64_t n, int M, int ksub, const
                          int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
                          void* scratch, size_t scratch_bytes, void* stream);
 
+/* Allocation-free variant of b200vq_adc_scan_topk for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). It has NO counterpart in the
+ * reference. Same inputs, outputs and results as
+ * b200vq_adc_scan_topk, but the partial top-k lists live in a file-scope `static __device__` array of
+ * B200VQ_ADC_STATIC_SCRATCH_BYTES (8 MiB, held by every GPU that loads the library until exit) whose
+ * device address the library resolves once per device with cudaGetSymbolAddress. The call performs no
+ * cudaMalloc / cudaFree / allocating library routine. Requests whose partial lists would not fit
+ * (b200vq_adc_scan_scratch_bytes(n, nq, k) > B200VQ_ADC_STATIC_SCRATCH_BYTES) are rejected with
+ * B200VQ_ERR_INVALID. All calls on a device share the array: calls that overlap on the GPU (different
+ * streams, no ordering) race; calls ordered on one stream do not. Nothing in it needs clearing between
+ * calls (every slot a call reads is written by that call first). */
+#define B200VQ_ADC_STATIC_SCRATCH_BYTES (8u << 20)
+int b200vq_adc_scan_topk_static(const uint8_t* codes, int64_t n, int M, int ksub, const float* lut,
+                                int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                                void* stream);
+
 /* Same scan over the conflict-free "scan layout" produced by
  * b200vq_pq_codes_to_scan_layout: blocks of 32 rows x groups of 32 sub-quantizers
  * (1 KiB each, row block major). Inside a block, lane i = row i of the block owns 32

@@ -42,6 +42,7 @@ SIGNATURES = {
     "b200vq_adc_lut": (_i, [_p, _i, _i64, _p, _i, _i, _i, _i, _p, _p]),
     "b200vq_adc_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_adc_scan_topk": (_i, [_p, _i64, _i, _i, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_adc_scan_topk_static": (_i, [_p, _i64, _i, _i, _p, _i, _i, _i, _p, _p, _p]),
     "b200vq_pq_codes_to_scan_layout": (_i, [_p, _i64, _i, _p, _p]),
     "b200vq_adc_scan_topk_rot": (_i, [_p, _i64, _i, _i, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_adc_scan_screen_scratch_bytes": (_sz, [_i64, _i, _i, _i]),

@@ -9,6 +9,8 @@
 //     sub-quantizer LUT entries equals the distance to the reconstruction.
 //   - bench/ffd_speed.cpp:87-127: score = sum_d LUT[d][code_d].
 //   - faiss IndexFlatL2/IP.search (benchmarks/exact_search.py:72-77).
+#include <mutex>
+
 #include "common.cuh"
 #include "topk.cuh"
 
@@ -822,4 +824,63 @@ extern "C" int b200vq_topk_merge(const float* in_vals, const int64_t* in_ids, in
         in_vals, in_ids, P, k, metric == B200VQ_METRIC_IP, out_vals, out_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
+}
+
+// ------------------------------------------- allocation-free ADC scan ---
+// b200vq_adc_scan_topk_static: b200vq_adc_scan_topk for callers that cannot allocate (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc). The per-(query, row chunk)
+// partial top-k lists live in a file-scope device array instead of a caller-owned buffer. The
+// array is part of the module image: every GPU that loads libb200vq.so holds its 8 MiB until exit.
+// No counterpart in the reference.
+//
+// In host code the NAME of a __device__ array is only a host-side stand-in for the symbol; the
+// device address is obtained once per device (that device current) with cudaGetSymbolAddress and
+// cached. Every call shares the array and finds the last call's partial lists in it: nothing has
+// to start at zero (each of the nq * nchunks * k slots a call reads is written by that call's
+// scan CTAs first), but two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) unsigned char g_adc_static_scratch[B200VQ_ADC_STATIC_SCRATCH_BYTES];
+
+static int adc_static_scratch_address(void** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static void* addr[MAX_DEV] = {};
+    int dev = -1;
+    VQ_CUDA(cudaGetDevice(&dev));
+    VQ_CHECK_ARG(dev >= 0 && dev < MAX_DEV, "adc_scan_topk_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        VQ_CUDA(cudaGetSymbolAddress(&p, g_adc_static_scratch));
+        VQ_CHECK_ARG(p != nullptr && ((uintptr_t)p & 255) == 0, "adc_scan_topk_static: bad symbol address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_adc_scan_topk_static(const uint8_t* codes, int64_t n, int M, int ksub, const float* lut,
+                                           int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
+                                           void* stream) {
+    VQ_CHECK_ARG(codes && lut && out_vals && out_ids, "adc_scan_topk_static: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && M > 0 && ksub > 0 && ksub <= 256 && nq >= 0,
+                 "adc_scan_topk_static: bad shape n=%lld M=%d ksub=%d nq=%d", (long long)n, M, ksub, nq);
+    VQ_CHECK_ARG(k > 0 && k <= 128, "adc_scan_topk_static: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "adc_scan_topk_static: bad metric");
+    if (nq == 0) return B200VQ_OK;
+    size_t need = partial_bytes(n, nq, k, nq);
+    VQ_CHECK_ARG(need <= (size_t)B200VQ_ADC_STATIC_SCRATCH_BYTES,
+                 "adc_scan_topk_static: n=%lld nq=%d k=%d needs %zu bytes of partial lists, the built-in scratch "
+                 "holds %zu; use b200vq_adc_scan_topk with caller-owned scratch",
+                 (long long)n, nq, k, need, (size_t)B200VQ_ADC_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    int rc = adc_static_scratch_address(&scratch);
+    if (rc != B200VQ_OK) return rc;
+    cudaStream_t st = as_stream(stream);
+    ScanPlan p = plan_scan(n, nq);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int negate = metric == B200VQ_METRIC_IP;
+    rc = (k <= 32) ? adc_scan_launch<128>(codes, n, M, ksub, lut, nq, k, negate, part, p, st)
+                   : adc_scan_launch<256>(codes, n, M, ksub, lut, nq, k, negate, part, p, st);
+    if (rc != B200VQ_OK) return rc;
+    return launch_merge<2048>(part, nq, p.nchunks, k, negate, out_vals, out_ids, st);
 }
