@@ -76,19 +76,19 @@ def random_rotation(D: int, seed: int) -> np.ndarray:
     return np.ascontiguousarray(Qm.astype(np.float32))
 
 
-_rot_cache: dict = {}
 TC_ROTATE_MIN_ROWS = 1024
 
 
 def _rotation_tc(A: torch.Tensor, transpose: bool) -> ops.RotationTC:
-    """RotationTC for y = x A^T (transpose) or y = x A, cached on the matrix's storage and version."""
-    key = (A.data_ptr(), A._version, tuple(A.shape), transpose)
-    r = _rot_cache.get(key)
-    if r is None:
-        if len(_rot_cache) > 8:
-            _rot_cache.clear()
-        r = _rot_cache[key] = ops.RotationTC(A if transpose else A.t().contiguous())
-    return r
+    """RotationTC for y = x A^T (transpose) or y = x A. The prepared operand split is owned by the
+    tensor OBJECT it was made from (an attribute on A, tagged with A's in-place version counter), so it
+    lives and dies with that matrix: a new matrix never finds another one's split, whatever address
+    the allocator hands it."""
+    slot = A.__dict__.setdefault("_b200vq_rotation_tc", {})
+    ent = slot.get(transpose)
+    if ent is None or ent[0] != A._version:
+        ent = slot[transpose] = (A._version, ops.RotationTC(A if transpose else A.t().contiguous()))
+    return ent[1]
 
 
 def rotate(x: torch.Tensor, A: torch.Tensor, transpose: bool = True, impl: str = "auto") -> torch.Tensor:
@@ -112,15 +112,17 @@ def rotate(x: torch.Tensor, A: torch.Tensor, transpose: bool = True, impl: str =
 
 
 def opq_train(x: torch.Tensor, M: int, nbits: int = 8, niter: int = 50, niter_pq: int = 4,
-              niter_pq_0: int = 40, seed: int = 123, A0: np.ndarray | None = None) -> torch.Tensor:
-    """OPQMatrix.train: alternate PQ training on rotated data with the Procrustes update."""
+              niter_pq_0: int = 40, seed: int = 123, A0: np.ndarray | None = None,
+              impl: str = "auto") -> torch.Tensor:
+    """OPQMatrix.train: alternate PQ training on rotated data with the Procrustes update.
+    impl selects the rotation GEMM (see rotate); every iterate A is a new tensor with its own split."""
     n, D = x.shape
     xt = _take_rows(x, subsample_ids(n, MAX_POINTS_PER_CENTROID * 256, seed))
     A = torch.from_numpy(random_rotation(D, seed) if A0 is None else np.asarray(A0, dtype=np.float32)).to(x.device)
     C = None
     xt64 = None
     for it in range(niter):
-        y = rotate(xt, A)
+        y = rotate(xt, A, impl=impl)
         if it == 0:
             C = pq_train(y, M, nbits, niter=niter_pq_0, seed=seed)
         else:
