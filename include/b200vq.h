@@ -210,6 +210,19 @@ int b200vq_rotate_tc_prepare(const float* w, int64_t ldw, int64_t N, int64_t K, 
 int b200vq_rotate_tc(const float* x, int64_t n, int64_t ldx, const void* wsplit, int64_t N, int64_t K,
                      float* y, int64_t ldy, void* stream);
 
+/* Same GEMM with the element-wise work around it fused in (the centring / scaling the reference does in
+ * separate numpy / Eigen passes): Y = row_scale[i] * ((X - x_sub) . W^T) + col_bias.
+ * x_sub (K, 16-byte aligned), row_scale (n), col_bias (N) are optional (NULL). transpose_out != 0 stores
+ * element (row, col) at y[col * ldy + row] (ldy >= n): the layout b200vq_caq_encode_t consumes
+ * (external/saq/include/saq/quantizer.h:66-72 rotates, caq_encoder.h walks the row). Used for the SAQ
+ * engine's PCA projection + segment rotations (external/saq/src/ivf_index.cpp:186-243), its inverse
+ * (ivf_index.cpp:296-374), and the rotations of ExtendedRaBitQuantizer
+ * (src/haag_vq/methods/extended_rabitq.py:140-170,180-198) and RankAwareQuantizer
+ * (rank_aware_quantization.py:195,218). */
+int b200vq_rotate_tc_ex(const float* x, int64_t n, int64_t ldx, const void* wsplit, int64_t N, int64_t K,
+                        const float* x_sub, const float* row_scale, const float* col_bias, int transpose_out,
+                        float* y, int64_t ldy, void* stream);
+
 /* Row squared norms (compute_exact_norms, exact_search.py:20-24, before the sqrt). */
 int b200vq_row_sqnorms(const float* x, int64_t n, int64_t ldx, int D, float* out, void* stream);
 
@@ -256,6 +269,22 @@ int b200vq_saq_decode(const uint8_t* codes, int64_t n, int D, const float* vmin,
 int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_t n, int D, int B,
                         const double* levels, const double* bounds, uint8_t* codes,
                         void* stream);
+/* The same encode with the O(n D^2) rotation on the tensor cores instead of an fp64 GEMM
+ * (extended_rabitq.py:134-149): nrm = |x - c| in fp64 (b200vq_resid_norms_f64; x fp32, or fp64 when x_is_f64),
+ * y (n, ldy) fp32 = (x - c32) P32 from b200vq_rotate_tc_ex, then b200vq_erabitq_pack_tc takes level indices from
+ * s = y sqrt(D) / nrm and recomputes, as exact fp64 dot products sum_k (x_k - c_k) PT[d][k] (PT = P^T, (D, D) fp64
+ * row-major), every coordinate within eps = (err_rel nrm + err_abs) sqrt(D) / nrm of a level mid-point, so the
+ * indices are those of the fp64 computation whenever |y - (x - c) P| <= err_rel |x - c| + err_abs. t uses the
+ * fp32-accurate s (the exact one where recomputed). y == NULL computes every coordinate exactly (SIMT fp64, for
+ * shapes the GEMM does not cover). stats (optional, device) += number of recomputed coordinates. */
+int b200vq_resid_norms_f64(const void* x, int x_is_f64, int64_t n, int64_t ldx, int D, const double* c,
+                           double* nrm, void* stream);
+int b200vq_erabitq_pack_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                           const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
+                           const double* levels, const double* bounds, double err_rel, double err_abs,
+                           uint8_t* codes, unsigned long long* stats, void* stream);
+/* a_i = nrm_i t_i / sqrt(D) read from the code trailers: the row scale of the code-domain estimator. */
+int b200vq_erabitq_rowscale(const uint8_t* codes, int64_t n, int D, int B, float* a, void* stream);
 /* Unpack: shat (n, D) fp64 = levels[idx]/sqrt(D)*t ; nrm_out (n) fp64. The caller
  * applies P^T, the norm and the centroid. */
 int b200vq_erabitq_unpack(const uint8_t* codes, int64_t n, int D, int B, const double* levels,
@@ -274,6 +303,41 @@ int b200vq_erabitq_scan_topk(const uint8_t* codes, int64_t n, int D, int B, cons
                              const float* qrot, const float* qconst, int nq, int metric, int k,
                              float* out_vals, uint32_t* out_ids, void* scratch,
                              size_t scratch_bytes, void* stream);
+
+/* ------------------------------------- code-domain estimator scan (tcgen05) ---
+ * Top-k of an estimator that is linear in per-dimension codes, scored straight from the packed codes (no
+ * decoded matrix in HBM). Serves (1) the SAQ engine's accurate estimator, external/saq/include/saq/
+ * caq_estimator.h:254-316 + saq_estimator.h:27-129,183-190 (GPU twin src/gpu/gpu_search.cu:37-99), and
+ * (2) extended RaBitQ searched through FlatQuantizedIndex (src/haag_vq/methods/extended_rabitq.py:173-198 +
+ * methods/search/flat_quantized_index.py:57-68), whose distance to the reconstruction is
+ * qc + a^2 sum(l^2) - 2 a <levels[idx], q_rot>.
+ *
+ * A stored row is nseg segments; segment s has seg_len[s] dimensions (multiple of 32) of seg_bits[s]-bit codes
+ * (1..13) in an MSB-first bit string at seg_codes[s] + row * seg_stride[s] (device pointers in HOST arrays;
+ * 4-byte aligned, stride % 4 == 0). A code means seg_table[s][code] (device table of 2^bits floats, bits <= 8)
+ * or, when seg_table[s] is NULL, code + seg_base[s]; the virtual row is x_i = concat_s seg_rowscale[s][i] *
+ * value (seg_rowscale[s] device (n) or NULL = 1). queries (nq, ldq) fp32 hold the matching concatenated query
+ * coordinates (sum of seg_len columns, 16-byte aligned, ldq % 4 == 0), qconst (nq, optional) is C_q,
+ * row_bias (n) is B_i and row_norm2 (n) = |x_i|^2 from b200vq_est_row_norms (it bounds the screen error).
+ *   L2 form: value = C_q + B_i - 2 <x_i, q>, ascending;   IP form: value = C_q + <x_i, q>, descending.
+ * Arithmetic of the returned values: per segment one fp32 FMA chain in dimension order, then
+ * acc = fma(rowscale, ip_s, acc) in segment order, value = fma(-2, acc, C_q + B_i) or C_q + acc. Rows are
+ * screened on the tensor cores (TF32, rigorous bound) and only survivors are scored; overflowing queries are
+ * redone exactly, so ids / values never depend on the screen. n < 16 384 is scored exactly without a screen.
+ * SAQ engine: seg_base = -(2^b - 1)/2, rowscale = rescale * 2/2^b, B_i = sum_s |o_s|^2, C_q = |q|^2.
+ * Extended RaBitQ: one segment, table = levels, rowscale = nrm t / sqrt(D), B_i = |x_i|^2, C_q = |q - c|^2.
+ * b200vq_est_row_norms needs 8192 bytes of scratch. */
+int b200vq_est_row_norms(int nseg, const int* seg_len, const int* seg_bits, const uint8_t* const* seg_codes,
+                         const int64_t* seg_stride, const float* const* seg_rowscale,
+                         const float* const* seg_table, const float* seg_base, int64_t n, float* norm2,
+                         void* scratch, size_t scratch_bytes, void* stream);
+size_t b200vq_est_scan_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_est_scan_topk(int nseg, const int* seg_len, const int* seg_bits, const uint8_t* const* seg_codes,
+                         const int64_t* seg_stride, const float* const* seg_rowscale,
+                         const float* const* seg_table, const float* seg_base, const float* row_norm2,
+                         const float* row_bias, int64_t n, const float* queries, int nq, int64_t ldq,
+                         const float* qconst, int metric, int k, float* out_vals, uint32_t* out_ids,
+                         void* scratch, size_t scratch_bytes, void* stream);
 
 /* ----------------------------------------------------------------- LVQ ---
  * Locally-adaptive vector quantization, single level: replaces the numpy code of

@@ -4,7 +4,7 @@
   * b200vq_caq_pack_t / b200vq_caq_decode round trip and dequantisation
   * oracle/caq.c pinned against the REFERENCE's own CUDA encoder (oracle/_ref/libsaq_ref_gpu.so =
     external/saq/src/gpu/gpu_encoder.cu compiled where it lies, caq_sequential = 1)
-  * SaqEngine.fit / reconstruct / accurate_dist vs the oracle pipeline on shared trained state
+  * SaqEngine.fit / reconstruct / search (code-domain estimator) vs the oracle pipeline on shared trained state
   * SaqEngineAdapter contract (reference tests/test_saq_engine_adapter.py:14-35)
 """
 import ctypes
@@ -178,10 +178,29 @@ def test_engine_fit_reconstruct_estimate_vs_oracle(T, D, avg_bits):
     mse_o = float(((R_o - X[ids]) ** 2).mean())
     mse_d = float(((R_d - X[ids]) ** 2).mean())
     assert abs(mse_o - mse_d) <= 1e-4 * mse_o
+    # accurate estimator, code domain: SaqEngine.search scores the packed codes on the tensor cores. Checked against
+    # the oracle's estimator on the rows whose codes are identical, and against a numpy evaluation of the same
+    # formula on the DEVICE's stored state for the top-k ids (rows whose codes moved by a near-tie flip included).
     Q = X[:7] + 0.05
-    est_o = ocaq.accurate_dist(st, Q, ids)
-    est_d = eng.accurate_dist(T.dev(Q), T.dev(ids.astype(np.int64))).cpu().numpy()
-    assert np.abs(est_d - est_o).max() <= 1e-4 * np.abs(est_o).max()
+    est_o = ocaq.accurate_dist(st, Q, None)
+    k = 25
+    vals, idsd = eng.search(T.dev(Q), k)
+    vals, idsd = vals.cpu().numpy(), idsd.cpu().numpy().view(np.uint32).astype(np.int64)
+    st_d = dict(st)
+    st_d["segs"] = []
+    for seg_o, seg_d in zip(st["segs"], eng.segs):
+        sd = dict(seg_o)
+        if seg_d["bits"]:
+            sd["codes"] = T.eng.caq_decode(seg_d["packed"], seg_d["len"], seg_d["bits"], None, None, mode=1).cpu().numpy()
+        for key in ("l2norm", "rescale"):
+            sd[key] = seg_d[key].cpu().numpy()
+        sd["c_rot"] = seg_d["c_rot"].cpu().numpy()
+        st_d["segs"].append(sd)
+    est_d = ocaq.accurate_dist(st_d, Q, None)
+    from parity import assert_topk_parity
+    assert_topk_parity(vals, idsd, est_d, k, 0, "saq_engine.search", gap_rel=1e-4, abs_tol=1e-5 * float(np.abs(est_d).max()))
+    sel = same[idsd]
+    assert np.abs(vals[sel] - np.take_along_axis(est_o, idsd, 1)[sel]).max() <= 1e-4 * np.abs(est_o).max()
 
 
 def test_engine_trains_its_own_state_and_mse_falls_with_bits(T):

@@ -55,6 +55,7 @@ SIGNATURES = {
     "b200vq_rotate_tc_scratch_bytes": (_sz, [_i64, _i64]),
     "b200vq_rotate_tc_prepare": (_i, [_p, _i64, _i64, _i64, _p, _sz, _p]),
     "b200vq_rotate_tc": (_i, [_p, _i64, _i64, _p, _i64, _i64, _p, _i64, _p]),
+    "b200vq_rotate_tc_ex": (_i, [_p, _i64, _i64, _p, _i64, _i64, _p, _p, _p, _i, _p, _i64, _p]),
     "b200vq_row_sqnorms": (_i, [_p, _i64, _i64, _i, _p, _p]),
     "b200vq_topk_merge": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "b200vq_sq_minmax": (_i, [_p, _i64, _i64, _i, _p, _p, _p]),
@@ -63,10 +64,18 @@ SIGNATURES = {
     "b200vq_saq_encode": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _i, _p, _p]),
     "b200vq_saq_decode": (_i, [_p, _i64, _i, _p, _p, _p, _p, _i, _p, _i64, _p]),
     "b200vq_erabitq_pack": (_i, [_p, _p, _i64, _i, _i, _p, _p, _p, _p]),
+    "b200vq_resid_norms_f64": (_i, [_p, _i, _i64, _i64, _i, _p, _p, _p]),
+    "b200vq_erabitq_pack_tc": (_i, [_p, _i64, _p, _i, _i64, _p, _p, _p, _i64, _i, _i, _p, _p, C.c_double, C.c_double,
+                                    _p, _p, _p]),
+    "b200vq_erabitq_rowscale": (_i, [_p, _i64, _i, _i, _p, _p]),
     "b200vq_erabitq_unpack": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p]),
     "b200vq_erabitq_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_erabitq_decode_f32": (_i, [_p, _i64, _i, _i, _p, _p, _i64, _p, _p]),
     "b200vq_erabitq_scan_topk": (_i, [_p, _i64, _i, _i, _p, _p, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_est_row_norms": (_i, [_i, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p]),
+    "b200vq_est_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
+    "b200vq_est_scan_topk": (_i, [_i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _i, _i64, _p, _i, _i, _p, _p,
+                                  _p, _sz, _p]),
     "b200vq_perdim_encode": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _p, _i, _p, _p]),
     "b200vq_perdim_decode": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p, _p, _i64, _p]),
     "b200vq_ffd_pack": (_i, [_p, _i64, _i, _p, _p, _i, _p, _p]),

@@ -247,17 +247,32 @@ class RotationTC:
         return bool(_lib.load().b200vq_rotate_tc_applies(n, ldx, self.N, self.K, (self.N + 3) // 4 * 4)) and \
             x.data_ptr() % 16 == 0
 
-    def __call__(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    def __call__(self, x: torch.Tensor, out: torch.Tensor | None = None, *, x_sub: torch.Tensor | None = None,
+                 row_scale: torch.Tensor | None = None, col_bias: torch.Tensor | None = None,
+                 transpose_out: bool = False) -> torch.Tensor:
+        """y = row_scale[:, None] * ((x - x_sub) W^T) + col_bias (each optional, fused into the GEMM).
+        transpose_out: the result is returned as a (N, n) tensor (row stride >= n) holding y^T."""
         x = _chk(x, torch.float32, "x")
         xptr, n, ldx, K = _rows(x, "x")
         if K != self.K:
             raise B200VQError(f"rotate_tc: x has {K} columns, W has {self.K}")
-        if out is None:
-            ldy = (self.N + 3) // 4 * 4
-            buf = torch.empty((n, ldy), dtype=torch.float32, device=x.device)
-            out = buf[:, :self.N]
-        yptr, _, ldy, _ = _rows(out, "out")
-        check(_lib.load().b200vq_rotate_tc(xptr, n, ldx, self.wsplit.data_ptr(), self.N, self.K, yptr, ldy, _stream()),
+        for t, m, name in ((x_sub, self.K, "x_sub"), (row_scale, n, "row_scale"), (col_bias, self.N, "col_bias")):
+            if t is not None and (_chk(t, torch.float32, name).numel() != m or not t.is_contiguous()):
+                raise B200VQError(f"rotate_tc: {name} must be a contiguous fp32 vector of {m} entries")
+        if transpose_out:
+            if out is None:
+                out = torch.empty((self.N, (n + 3) // 4 * 4), dtype=torch.float32, device=x.device)[:, :n]
+            if out.shape != (self.N, n) or (n > 1 and out.stride(1) != 1):
+                raise B200VQError("rotate_tc: transposed output must be (N, n) with unit column stride")
+            yptr, ldy = out.data_ptr(), (out.stride(0) if self.N > 1 else max(n, out.stride(0)))
+        else:
+            if out is None:
+                ldy = (self.N + 3) // 4 * 4
+                buf = torch.empty((n, ldy), dtype=torch.float32, device=x.device)
+                out = buf[:, :self.N]
+            yptr, _, ldy, _ = _rows(out, "out")
+        check(_lib.load().b200vq_rotate_tc_ex(xptr, n, ldx, self.wsplit.data_ptr(), self.N, self.K, _p(x_sub),
+                                              _p(row_scale), _p(col_bias), int(transpose_out), yptr, ldy, _stream()),
               "rotate_tc")
         return out
 

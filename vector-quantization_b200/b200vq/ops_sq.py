@@ -114,29 +114,94 @@ def erabitq_decode_f32(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Te
     return x, xn
 
 
+def resid_norms_f64(x: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
+    """|x_i - c| in fp64 (x fp32 or fp64 rows, c fp64)."""
+    _chk(c, torch.float64, "c")
+    if x.dtype not in (torch.float32, torch.float64) or not x.is_cuda:
+        raise B200VQError("resid_norms_f64: x must be a CUDA fp32 / fp64 matrix")
+    ptr, n, ld, D = _rows(x, "x")
+    out = torch.empty((n,), dtype=torch.float64, device=x.device)
+    check(_lib.load().b200vq_resid_norms_f64(ptr, int(x.dtype == torch.float64), n, ld, D, c.data_ptr(), out.data_ptr(),
+                                             _stream()), "resid_norms_f64")
+    return out
+
+
+def erabitq_rotation_error_bound(D: int, c_norm: float) -> tuple:
+    """(err_rel, err_abs): |y - (x - c) P| <= err_rel |x - c| + err_abs for y = rotate_tc_ex(x, P32^T, x_sub = c32).
+    Operand splits 3 * 2^-22, twelve TMEM accumulation steps per chunk (measured 2^-25.6 each, taken as 2^-25),
+    one round-to-nearest register add per 32-column chunk, fp32 rounding of x - c32, of P and of c; Cauchy-Schwarz
+    over the row (|P[:, d]| = 1), times 1.25."""
+    u = 2.0 ** -24
+    rel = 1.25 * (3 * 2.0 ** -22 + 12 * 2.0 ** -25 + (D // 32 + 2) * u)
+    return rel, 1.25 * u * float(c_norm)
+
+
+def erabitq_pack_tc(y: torch.Tensor | None, x: torch.Tensor, c: torch.Tensor, PT: torch.Tensor, nrm: torch.Tensor,
+                    B: int, levels: torch.Tensor, bounds: torch.Tensor, err_rel: float, err_abs: float,
+                    out: torch.Tensor | None = None, stats: torch.Tensor | None = None) -> torch.Tensor:
+    """Extended-RaBitQ codes from the fp32 rotated residuals y (or, y None, all-exact fp64) with exact fp64
+    re-evaluation of the coordinates inside the rotation's error bound of a level mid-point."""
+    for t, name in ((c, "c"), (PT, "PT"), (nrm, "nrm"), (levels, "levels"), (bounds, "bounds")):
+        _chk(t, torch.float64, name)
+    ptr, n, ldx, D = _rows(x, "x")
+    if PT.shape != (D, D) or not PT.is_contiguous():
+        raise B200VQError("erabitq_pack_tc: PT must be a contiguous (D, D) fp64 matrix")
+    yptr, ldy = None, 0
+    if y is not None:
+        _chk(y, torch.float32, "y")
+        yptr, ny, ldy, Dy = _rows(y, "y")
+        if (ny, Dy) != (n, D):
+            raise B200VQError("erabitq_pack_tc: y and x disagree")
+    if out is None:
+        out = torch.empty((n, (D * B + 7) // 8 + 8), dtype=torch.uint8, device=x.device)
+    check(_lib.load().b200vq_erabitq_pack_tc(yptr, ldy, ptr, int(x.dtype == torch.float64), ldx, c.data_ptr(),
+                                             PT.data_ptr(), nrm.data_ptr(), n, D, B, levels.data_ptr(), bounds.data_ptr(),
+                                             err_rel, err_abs, out.data_ptr(), _p(stats), _stream()), "erabitq_pack_tc")
+    return out
+
+
+def erabitq_rowscale(codes: torch.Tensor, D: int, B: int) -> torch.Tensor:
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    a = torch.empty((codes.shape[0],), dtype=torch.float32, device=codes.device)
+    check(_lib.load().b200vq_erabitq_rowscale(codes.data_ptr(), codes.shape[0], D, B, a.data_ptr(), _stream()),
+          "erabitq_rowscale")
+    return a
+
+
+class ERaBitQScanner:
+    """Extended-RaBitQ codes prepared for the code-domain estimator scan on the tensor cores (csrc/est_tc.cu):
+    row scales a_i and |x_i|^2 are extracted once, every search then reads only the code bytes."""
+
+    def __init__(self, codes: torch.Tensor, D: int, B: int, levels_f32: torch.Tensor):
+        from .ops_est import CodeSegments
+        _chk(codes, torch.uint8, "codes")
+        if D % 32 or codes.stride(0) % 4 or codes.data_ptr() % 4:
+            raise B200VQError("ERaBitQScanner: needs D % 32 == 0 and 4-byte aligned code rows")
+        self.codes, self.D, self.B = codes, D, B
+        self.a = erabitq_rowscale(codes, D, B)
+        self.segs = CodeSegments([D], [B], [codes], [self.a], [levels_f32.contiguous()], [0.0])
+        self.norm2 = self.segs.row_norms()
+
+    def search(self, qrot: torch.Tensor, qconst: torch.Tensor, k: int, metric):
+        return self.segs.scan_topk(self.norm2, self.norm2, qrot, qconst, k, metric)
+
+
 def erabitq_scan_topk(codes: torch.Tensor, D: int, B: int, levels_f32: torch.Tensor, qrot: torch.Tensor,
                       qconst: torch.Tensor, k: int, metric, impl: str = "auto"):
-    """Extended-RaBitQ estimator top-k. impl "simt": the code-domain kernel (one level look-up per dimension and
-    query); "tc" / "auto": decode once to fp32 rows, then the exact flat search on the tensor cores — the
-    estimator qc + a^2 sum l^2 - 2 a <l, q> is the squared distance between the decoded row and the rotated
-    query (inner-product form: qc + a <l, q>), with qc put back in place of ||q||^2. Same ranking and values up
-    to fp32 rounding of the differently associated sums (1e-5 relative)."""
-    from .ops import flat_topk, row_sqnorms, tc_available
+    """Extended-RaBitQ estimator top-k: qc + a^2 sum l^2 - 2 a <l, q> (L2) / qc + a <l, q> (IP), a = nrm t / sqrt(D).
+    impl "simt": one level look-up per (dimension, code, query); "tc" / "auto": the code-domain scan on the tensor
+    cores (TF32 screen straight from the code bytes + exact scoring of the survivors). Same arithmetic of the returned
+    values either way (one fp32 FMA chain in dimension order), hence the same ids and value bits."""
+    from .ops import tc_available
     _chk(codes, torch.uint8, "codes")
     codes = codes.contiguous()
     n = codes.shape[0]
     nq = qrot.shape[0]
     if impl not in ("auto", "tc", "simt"):
         raise B200VQError(f"erabitq_scan_topk: unknown impl {impl!r}")
-    if impl != "simt" and tc_available() and D % 32 == 0 and n >= 65536 and k <= 128:
-        x, xn = erabitq_decode_f32(codes, D, B, levels_f32)
-        q = qrot.contiguous()
-        vals, ids = flat_topk(x, q, k, metric, xnorm=xn)
-        if metric_id(metric) == 0:   # L2: the flat search used ||q||^2 where the estimator has qconst
-            vals = vals + (qconst - row_sqnorms(q))[:, None]
-        else:
-            vals = vals + qconst[:, None]
-        return vals, ids
+    if impl != "simt" and tc_available() and D % 32 == 0 and k <= 128 and (impl == "tc" or n >= 16384):
+        return ERaBitQScanner(codes, D, B, levels_f32).search(qrot.contiguous(), qconst, k, metric)
     lib = _lib.load()
     vals, ids = _topk_out(nq, k, codes.device)
     sc = scratch(lib.b200vq_erabitq_scan_scratch_bytes(n, nq, k), codes.device, "scan")

@@ -9,8 +9,12 @@ Pipeline (external/saq/src/ivf_index.cpp:186-243, saq_quantizer.h:49-83, quantiz
   bit-pack (b200vq_caq_pack_t). Codes stay in HBM segment by segment as MSB-first bit strings
   with three fp32 factors per (row, segment).
 
-The GEMMs (PCA projection, per-segment rotation, un-rotation) are plain library SGEMMs in
-strict fp32; everything per-row runs in libb200vq.so. There is no CPU fallback.
+Every GEMM runs in libb200vq.so's fp32-accurate tensor-core kernel (csrc/rotate_tc.cu): the PCA
+projection and the per-segment rotations are ONE composite matrix Wc = rot . blockdiag(P_s), so
+encode is a single GEMM with the mean subtraction, the rotated-centroid subtraction and the
+transposed store (the layout b200vq_caq_encode_t consumes) fused in; decode is the same matrix
+the other way with the bias fused; search is the code-domain estimator scan on the tensor cores
+(csrc/est_tc.cu) straight from the packed codes. There is no CPU fallback and no library GEMM.
 """
 from __future__ import annotations
 
@@ -20,7 +24,7 @@ from typing import List, Optional, Tuple
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, ops, ops_sq
 from ._lib import check
 from .ops import _stream, require_cuda
 
@@ -29,15 +33,6 @@ BLK = 64
 
 def pad64(d: int) -> int:
     return (d + BLK - 1) // BLK * BLK
-
-
-def _mm(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
-    prev = torch.backends.cuda.matmul.allow_tf32
-    torch.backends.cuda.matmul.allow_tf32 = False
-    try:
-        return torch.matmul(a, b)
-    finally:
-        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 def mt19937_first(seed: int) -> int:
@@ -55,14 +50,38 @@ def mt19937_first(seed: int) -> int:
     return x & 0xFFFFFFFF
 
 
+def mt19937_stream(seed: int):
+    """Outputs of std::mt19937(seed), one after another."""
+    mt = [seed & 0xFFFFFFFF]
+    for i in range(1, 624):
+        prev = mt[-1]
+        mt.append((1812433253 * (prev ^ (prev >> 30)) + i) & 0xFFFFFFFF)
+    idx = 624
+    while True:
+        if idx >= 624:
+            for i in range(624):
+                y = (mt[i] & 0x80000000) | (mt[(i + 1) % 624] & 0x7FFFFFFF)
+                mt[i] = mt[(i + 397) % 624] ^ (y >> 1) ^ (0x9908B0DF if (y & 1) else 0)
+            idx = 0
+        x = mt[idx]
+        idx += 1
+        x ^= x >> 11
+        x ^= (x << 7) & 0x9D2C5680
+        x ^= (x << 15) & 0xEFC60000
+        x ^= x >> 18
+        yield x & 0xFFFFFFFF
+
+
 def kmeans1_row(n: int, seed: int) -> int:
     """With K = 1 the engine's Lloyd loop (kmeans_eigen.cpp:40-56) exits before its first update
     (every assignment already is 0), so the centroid is the row drawn by
-    uniform_int_distribution<int>(0, n-1) from mt19937(seed): libstdc++'s multiply-shift."""
-    prod = mt19937_first(seed) * n
-    if (prod & 0xFFFFFFFF) < (((1 << 32) - n) % n):
-        raise NotImplementedError("first draw rejected; use another seed")
-    return prod >> 32
+    uniform_int_distribution<int>(0, n-1) from mt19937(seed): libstdc++'s multiply-shift with rejection
+    (a rejected draw takes the generator's next output)."""
+    thresh = ((1 << 32) - n) % n
+    for u in mt19937_stream(seed):
+        prod = u * n
+        if (prod & 0xFFFFFFFF) >= thresh:
+            return prod >> 32
 
 
 def plan_dp(variance: np.ndarray, avg_bits: float) -> List[Tuple[int, int]]:
@@ -116,13 +135,16 @@ def caq_pack_t(codesT: torch.Tensor, bits: int, out: Optional[torch.Tensor] = No
 
 
 def caq_decode(packed: torch.Tensor, ln: int, bits: int, l2norm: Optional[torch.Tensor],
-               ids: Optional[torch.Tensor] = None, mode: int = 0) -> torch.Tensor:
+               ids: Optional[torch.Tensor] = None, mode: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out (optional): an (m, ln) fp32 view with unit column stride (e.g. a column slice of a wider matrix)."""
     n_total = packed.shape[0]
     m = n_total if ids is None else int(ids.shape[0])
-    out = torch.empty((m, ln), dtype=torch.float32, device=packed.device)
+    if out is None:
+        out = torch.empty((m, ln), dtype=torch.float32, device=packed.device)
     check(_lib.load().b200vq_caq_decode(packed.data_ptr(), n_total, ids.data_ptr() if ids is not None else None, m,
                                         ln, bits, l2norm.data_ptr() if l2norm is not None else None, mode,
-                                        out.data_ptr(), ln, _stream()), "caq_decode")
+                                        out.data_ptr(), out.stride(0) if m > 1 else max(ln, out.stride(0)), _stream()),
+          "caq_decode")
     return out
 
 
@@ -136,15 +158,21 @@ class SaqEngine:
         self.n = self.D = self.d_pad = 0
         self.plan: List[Tuple[int, int]] = []
         self.segs: list = []
+        self._scanner = None
 
     # ---- training state
     def _pca(self, X: torch.Tensor):
+        """Mean (numpy's row-sequential fp32 order), covariance as a Gram matrix on the tensor cores
+        (X_c^T X_c = A A^T with A = X_c^T prepared as the GEMM's W operand), fp64 eigh (train time)."""
         n, D = X.shape
-        mean = X.mean(dim=0)
+        mean = ops_sq.col_mean_seq(X)
         cov = torch.zeros((D, D), dtype=torch.float32, device=X.device)
         for s in range(0, n, self.batch_rows):
-            xc = X[s:s + self.batch_rows] - mean
-            cov += _mm(xc.t(), xc)
+            xb = X[s:s + self.batch_rows]
+            rows = xb.shape[0]
+            xt = torch.zeros((D, (rows + 31) // 32 * 32), dtype=torch.float32, device=X.device)
+            xt[:, :rows] = (xb - mean).t()
+            cov += ops.RotationTC(xt)(xt)
         evals, evecs = torch.linalg.eigh(cov.double() / float(n - 1))
         return mean, evecs.flip(1).float().contiguous(), evals.flip(0).clamp_min(0).float()
 
@@ -176,11 +204,35 @@ class SaqEngine:
             Q, _r = torch.linalg.qr(torch.randn((ln, ln), generator=g, dtype=torch.float64))
             self.P.append(Q.t().float().contiguous().to(dev))
 
-    def _project(self, Xb: torch.Tensor) -> torch.Tensor:
-        Xp = _mm(Xb - self.mean, self.rot) if self.apply_pca else Xb
-        if self.d_pad != self.D:
-            Xp = torch.nn.functional.pad(Xp, (0, self.d_pad - self.D))
-        return Xp
+    def _compose(self, dev):
+        """Wc (Dk, d_pad) = [rot | 0] . blockdiag(P_s): projection and segment rotations as one matrix
+        (Dk = D rounded up to the GEMM's K granule, the extra rows are zero). Built with the same GEMM."""
+        D, d_pad = self.D, self.d_pad
+        self.Dk = (D + 31) // 32 * 32
+        rot_pad = torch.zeros((self.Dk, d_pad), dtype=torch.float32, device=dev)
+        rot_pad[:D, :D] = self.rot if self.apply_pca else torch.eye(D, device=dev)
+        Wc = torch.empty((self.Dk, d_pad), dtype=torch.float32, device=dev)
+        off = 0
+        for (ln, _), P in zip(self.plan, self.P):
+            # rot_pad[:, seg] . P_s  =  x W^T with W = P_s^T
+            ops.RotationTC(P.t().contiguous())(rot_pad[:, off:off + ln].contiguous(), out=Wc[:, off:off + ln])
+            off += ln
+        self.Wc = Wc
+        self.enc = ops.RotationTC(Wc.t().contiguous())     # o = (x - mean) Wc        (N = d_pad, K = Dk)
+        self.dec = ops.RotationTC(Wc[:D].contiguous())     # x = oa Wc^T + bias       (N = D, K = d_pad)
+        self.mean_k = torch.zeros(self.Dk, dtype=torch.float32, device=dev)
+        self.mean_k[:D] = self.mean if self.apply_pca else 0.0
+
+    def _pad_k(self, Xb: torch.Tensor) -> torch.Tensor:
+        if Xb.shape[1] == self.Dk and Xb.stride(0) % 4 == 0 and Xb.data_ptr() % 16 == 0 and Xb.stride(1) == 1:
+            return Xb
+        xp = torch.zeros((Xb.shape[0], self.Dk), dtype=torch.float32, device=Xb.device)
+        xp[:, :Xb.shape[1]] = Xb
+        return xp
+
+    def _project(self, Xb: torch.Tensor, transpose_out: bool = False) -> torch.Tensor:
+        """(x - mean) rot blockdiag(P) - c_rot for every row: (rows, d_pad), or its transpose."""
+        return self.enc(self._pad_k(Xb), x_sub=self.mean_k, col_bias=self.neg_c_rot, transpose_out=transpose_out)
 
     # ---- fit
     def fit(self, X: torch.Tensor, state: Optional[dict] = None) -> "SaqEngine":
@@ -191,12 +243,16 @@ class SaqEngine:
         self.n, self.D, self.d_pad = n, D, pad64(D)
         self._train(X, state)
         dev = X.device
-        cen = self._project(X[self.cent_row:self.cent_row + 1])[0]
-        self.centroid = cen
+        self._compose(dev)
+        # rotated centroid of every segment = the centroid row through the same composite matrix
+        self.neg_c_rot = None
+        c_rot_all = self._project(X[self.cent_row:self.cent_row + 1])[0].contiguous()
+        self.neg_c_rot = (-c_rot_all).contiguous()
+        # decode bias: (c_rot_s P_s^T)[:D] rot^T + mean = c_rot_all Wc^T + mean (ivf_index.cpp:296-374)
+        self.dec_bias = self.dec(c_rot_all.unsqueeze(0), col_bias=(self.mean if self.apply_pca else None))[0].contiguous()
         self.segs, off = [], 0
         for (ln, bits), P in zip(self.plan, self.P):
-            c_rot = _mm(cen[off:off + ln].unsqueeze(0), P)[0].contiguous()
-            self.segs.append(dict(len=ln, bits=bits, off=off, c_rot=c_rot,
+            self.segs.append(dict(len=ln, bits=bits, off=off, c_rot=c_rot_all[off:off + ln],
                                   packed=(torch.empty((n, ln * bits // 8), dtype=torch.uint8, device=dev)
                                           if bits else None),
                                   l2norm=torch.empty(n, device=dev), rescale=torch.empty(n, device=dev),
@@ -205,15 +261,15 @@ class SaqEngine:
             off += ln
         for s in range(0, n, self.batch_rows):
             e = min(n, s + self.batch_rows)
-            Xp = self._project(X[s:e])
-            for seg, P in zip(self.segs, self.P):
+            oT = self._project(X[s:e], transpose_out=True)          # (d_pad, rows): every segment, centred
+            for seg in self.segs:
                 ln, bits, o0 = seg["len"], seg["bits"], seg["off"]
-                oT = _mm(P.t(), Xp[:, o0:o0 + ln].t())          # (len, rows): rotated segment, transposed
-                codesT, outs = caq_encode_t(oT, bits, seg["c_rot"], self.rd_lmt, self.adj_eps)
+                codesT, outs = caq_encode_t(oT[o0:o0 + ln], bits, None, self.rd_lmt, self.adj_eps)
                 for key, o in zip(("l2norm", "rescale", "error", "mse", "cos"), outs):
                     seg[key][s:e] = o
                 if bits:
                     caq_pack_t(codesT, bits, out=seg["packed"][s:e])
+        self._scanner = None
         return self
 
     # ---- queries on the fitted index
@@ -228,39 +284,45 @@ class SaqEngine:
     def reconstruct(self, ids: torch.Tensor) -> torch.Tensor:
         """IVF::decompress (ivf_index.cpp:245-374): ids int64 on the device -> (m, D) fp32."""
         m = int(ids.shape[0])
-        o_rot = torch.empty((m, self.d_pad), dtype=torch.float32, device=ids.device)
-        for seg, P in zip(self.segs, self.P):
-            ln, bits, off = seg["len"], seg["bits"], seg["off"]
-            cen_unrot = _mm(seg["c_rot"].unsqueeze(0), P.t())[0]
-            if bits == 0:
-                o_rot[:, off:off + ln] = cen_unrot
-            else:
-                oa = caq_decode(seg["packed"], ln, bits, seg["l2norm"], ids, mode=0)
-                o_rot[:, off:off + ln] = _mm(oa, P.t()) + cen_unrot
-        o_rot = o_rot[:, :self.D]
-        return (_mm(o_rot, self.rot.t()) + self.mean) if self.apply_pca else o_rot.contiguous()
+        oa = torch.zeros((m, self.d_pad), dtype=torch.float32, device=ids.device)
+        for seg in self.segs:
+            if seg["bits"]:
+                caq_decode(seg["packed"], seg["len"], seg["bits"], seg["l2norm"], ids, mode=0,
+                           out=oa[:, seg["off"]:seg["off"] + seg["len"]])
+        return self.dec(oa, col_bias=self.dec_bias)
 
-    def accurate_dist(self, Q: torch.Tensor, ids: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Engine estimator (caq_estimator.h:254-283, saq_estimator.h:183-190), squared L2:
-        sum_s |o_s|^2 + |q_s|^2 - 2 rescale_s <q_s, oa_s>, q_s = Q_pca[:, seg] P_s - c_rot_s."""
-        Qp = self._project(Q)
-        m = self.n if ids is None else int(ids.shape[0])
-        out = torch.zeros((Q.shape[0], m), dtype=torch.float32, device=Q.device)
-        for seg, P in zip(self.segs, self.P):
-            ln, bits, off = seg["len"], seg["bits"], seg["off"]
-            q = _mm(Qp[:, off:off + ln], P) - seg["c_rot"]
-            q2 = (q * q).sum(1)
-            l2 = seg["l2norm"] if ids is None else seg["l2norm"][ids]
-            o2 = l2 * l2
-            if bits == 0:
-                out += o2[None, :] + q2[:, None]
-                continue
-            delta = 2.0 / (1 << bits)
-            codes = caq_decode(seg["packed"], ln, bits, None, ids, mode=1)
-            ip = _mm(q, codes.t()) * delta + (-1.0 + delta / 2) * q.sum(1)[:, None]
-            rs = seg["rescale"] if ids is None else seg["rescale"][ids]
-            out += o2[None, :] + q2[:, None] - 2.0 * rs[None, :] * ip
-        return out
+    def _scan_state(self):
+        """Per-index state of the code-domain scan: the coded segments, rowscale = rescale * Delta,
+        B_i = sum_s |o_s|^2 (all segments) and |x_i|^2 of the virtual rows."""
+        if self._scanner is None:
+            from .ops_est import CodeSegments
+            coded = [seg for seg in self.segs if seg["bits"] > 0]
+            bias = torch.zeros(self.n, dtype=torch.float32, device=self.segs[0]["l2norm"].device)
+            for seg in self.segs:
+                bias += seg["l2norm"] * seg["l2norm"]
+            if not coded:
+                self._scanner = dict(segs=None, bias=bias)
+                return self._scanner
+            scales = [(seg["rescale"] * (2.0 / (1 << seg["bits"]))).contiguous() for seg in coded]
+            cs = CodeSegments([seg["len"] for seg in coded], [seg["bits"] for seg in coded],
+                              [seg["packed"] for seg in coded], scales, [None] * len(coded),
+                              [-((1 << seg["bits"]) - 1) / 2.0 for seg in coded])
+            cols = torch.cat([torch.arange(seg["off"], seg["off"] + seg["len"], device=bias.device) for seg in coded])
+            self._scanner = dict(segs=cs, bias=bias, norm2=cs.row_norms(), cols=cols)
+        return self._scanner
+
+    def search(self, Q: torch.Tensor, k: int):
+        """Top-k by the engine's accurate estimator (caq_estimator.h:254-283, saq_estimator.h:183-190), squared L2:
+        sum_s |o_s|^2 + |q_s|^2 - 2 rescale_s (Delta_s <q_s, code> + (-1 + Delta_s / 2) sum(q_s)),
+        q_s = Q_pca[:, seg] P_s - c_rot_s, scored from the packed codes on the tensor cores (csrc/est_tc.cu).
+        Returns (dist (nq, k) fp32 ascending, ids (nq, k) int32-as-uint32)."""
+        sc = self._scan_state()
+        q_all = self._project(Q)                                # (nq, d_pad): every segment's query coordinates
+        qc = ops.row_sqnorms(q_all.contiguous() if q_all.stride(1) != 1 else q_all)
+        if sc["segs"] is None:
+            raise ValueError("SaqEngine.search: the plan has no coded segment")
+        qk = q_all.index_select(1, sc["cols"]) if sc["cols"].numel() != self.d_pad else q_all
+        return sc["segs"].scan_topk(sc["norm2"], sc["bias"], qk, qc, k, "l2")
 
     def export_state(self) -> dict:
         return dict(mean=self.mean.cpu().numpy(), rot=self.rot.cpu().numpy(), var=self.var.cpu().numpy(),

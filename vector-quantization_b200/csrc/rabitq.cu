@@ -394,6 +394,148 @@ __global__ void __launch_bounds__(256) erabitq_pack_kernel(const double* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Extended-RaBitQ encode with the rotation on the tensor cores (b200vq_erabitq_pack_tc).
+// The reference computes s = ((x - c) / |x - c|) P sqrt(D) in fp64 (extended_rabitq.py:140-149): an
+// O(n D^2) DGEMM. Here the rotation is the fp32-accurate tcgen05 GEMM (rotate_tc.cu, y = (x - c32) P32),
+// whose error is bounded by err_rel |x - c| + err_abs, and only the coordinates whose level index could
+// change inside that bound (|s - mid-point| < eps) are recomputed as exact fp64 dot products
+// sum_k (x_k - c_k) P[k][d] by the whole warp: the level indices are those of the fp64 computation.
+// y == nullptr: every coordinate is computed exactly (shapes the GEMM does not cover).
+template <typename T>
+__global__ void __launch_bounds__(256) resid_norm_kernel(const T* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                                         const double* __restrict__ c, double* __restrict__ nrm) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = wid; row < n; row += nw) {
+        const T* xr = x + row * ldx;
+        double acc = 0.0;
+        for (int d = lane; d < D; d += 32) {
+            const double r = (double)xr[d] - c[d];
+            acc = fma(r, r, acc);
+        }
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
+        if (lane == 0) nrm[row] = sqrt(acc);
+    }
+}
+
+__device__ __forceinline__ int erabitq_level_of(const double* bd, int L, double v) {
+    int lo = 0, hi = L - 1;          // np.searchsorted(bounds, v) (side='left'): number of bounds < v
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (bd[mid] < v) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
+                       const double* __restrict__ c, const double* __restrict__ PT, const double* __restrict__ nrm,
+                       int64_t n, int D, int B, const double* __restrict__ levels, const double* __restrict__ bounds,
+                       double err_rel, double err_abs, uint8_t* __restrict__ codes, unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* lv = reinterpret_cast<double*>(smem_raw);        // [2^B]
+    double* bd = lv + (1 << B);                              // [2^B - 1] (padded to 2^B)
+    const int L = 1 << B;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int dpad = (D + 15) & ~15;
+    uint8_t* idx = reinterpret_cast<uint8_t*>(bd + L) + (size_t)w * dpad * 3;  // [warps][D] indices
+    uint16_t* flist = reinterpret_cast<uint16_t*>(idx + dpad);                 // [warps][D] flagged coordinates
+    for (int i = tid; i < L; i += blockDim.x) lv[i] = levels[i];
+    for (int i = tid; i < L - 1; i += blockDim.x) bd[i] = bounds[i];
+    __syncthreads();
+    const int ibytes = (D * B + 7) >> 3;
+    const int code_size = ibytes + 8;
+    const double sqrt_d = sqrt((double)D);
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + tid) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long nfix_total = 0;
+    for (int64_t row = wid; row < n; row += nw) {
+        const double nr = nrm[row];
+        const double nsafe = fmax(nr, 1e-12);
+        const double sc = sqrt_d / nsafe;
+        const double eps_s = (err_rel * nr + err_abs) * sc;
+        const float* yr = y ? y + row * ldy : nullptr;
+        double num = 0.0, den = 0.0;
+        int nflag = 0;
+        for (int d0 = 0; d0 < D; d0 += 32) {
+            const int d = d0 + lane;
+            bool flag = false;
+            if (d < D) {
+                if (yr) {
+                    const double sv = (double)yr[d] * sc;
+                    const int lo = erabitq_level_of(bd, L, sv);
+                    flag = (lo > 0 && sv - bd[lo - 1] < eps_s) || (lo < L - 1 && bd[lo] - sv < eps_s);
+                    idx[d] = (uint8_t)lo;
+                    const double sh = lv[lo];
+                    num = fma(sv, sh, num);
+                    den = fma(sh, sh, den);
+                } else {
+                    flag = true;
+                }
+            }
+            const unsigned m = __ballot_sync(FULL_MASK, flag);
+            if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
+            nflag += __popc(m);
+        }
+        __syncwarp();
+        const T* xr = x + row * ldx;
+        for (int f = 0; f < nflag; ++f) {
+            const int d = flist[f];
+            const double* pt = PT + (int64_t)d * D;
+            double acc = 0.0;
+            for (int k = lane; k < D; k += 32) acc = fma((double)xr[k] - c[k], __ldg(pt + k), acc);
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
+            if (lane == 0) {
+                const double sv = (acc / nsafe) * sqrt_d;
+                const int lo = erabitq_level_of(bd, L, sv);
+                if (yr) {
+                    const double so = (double)yr[d] * sc;
+                    const double sho = lv[idx[d]];
+                    num -= so * sho;
+                    den -= sho * sho;
+                }
+                idx[d] = (uint8_t)lo;
+                const double sh = lv[lo];
+                num = fma(sv, sh, num);
+                den = fma(sh, sh, den);
+            }
+        }
+        nfix_total += (unsigned long long)nflag;
+        for (int o = 16; o > 0; o >>= 1) {
+            num += __shfl_xor_sync(FULL_MASK, num, o);
+            den += __shfl_xor_sync(FULL_MASK, den, o);
+        }
+        __syncwarp();
+        uint8_t* code = codes + row * (int64_t)code_size;
+        for (int byte = lane; byte < ibytes; byte += 32) {       // MSB-first B-bit packing, one lane per output byte
+            const int b0 = byte * 8, b1 = b0 + 8;
+            uint32_t acc = 0;
+            for (int d = b0 / B; d < D && d * B < b1; ++d) {
+                const int shift = b1 - (d * B + B);
+                const uint32_t qv = idx[d];
+                acc |= ((shift >= 0) ? (qv << shift) : (qv >> (-shift))) & 0xffu;
+            }
+            code[byte] = (uint8_t)acc;
+        }
+        if (lane == 0) {
+            const double t = (den > 1e-12) ? (num / den) : 1.0;
+            const uint32_t u0 = __float_as_uint((float)nr);
+            const uint32_t u1 = __float_as_uint((float)t);
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                code[ibytes + b] = (uint8_t)(u0 >> (8 * b));
+                code[ibytes + 4 + b] = (uint8_t)(u1 >> (8 * b));
+            }
+        }
+        __syncwarp();
+    }
+    if (stats && lane == 0 && nfix_total) atomicAdd(stats, nfix_total);
+}
+
 __device__ __forceinline__ uint32_t erabitq_index(const uint8_t* code, int d, int B, int ibytes) {
     int off = d * B;
     int byte = off >> 3;
@@ -460,6 +602,16 @@ __global__ void __launch_bounds__(256) erabitq_decode_f32_kernel(const uint8_t* 
     }
 }
 
+// a_i = nrm_i t_i / sqrt(D) (the row scale of the estimator), with the products of erabitq_scan_kernel
+__global__ void erabitq_rowscale_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B, float* __restrict__ a) {
+    const int ibytes = (D * B + 7) >> 3, code_size = ibytes + 8;
+    const float inv_sqrt_d = 1.0f / sqrtf((float)D);
+    for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t* code = codes + row * (int64_t)code_size;
+        a[row] = __fmul_rn(__fmul_rn(load_f32_unaligned(code + ibytes), load_f32_unaligned(code + ibytes + 4)), inv_sqrt_d);
+    }
+}
+
 template <int CAP>
 __global__ void __launch_bounds__(256)
     erabitq_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, int B,
@@ -503,9 +655,11 @@ __global__ void __launch_bounds__(256)
             }
             float nrm = load_f32_unaligned(code + ibytes);
             float t = load_f32_unaligned(code + ibytes + 4);
-            float a = nrm * t * inv_sqrt_d;
-            if (metric == B200VQ_METRIC_L2) est = qc + a * a * l2 - 2.f * a * dot;
-            else est = -(qc + a * dot);
+            // canonical arithmetic, shared with est_tc.cu (one segment): every operation rounded separately
+            const float a = __fmul_rn(__fmul_rn(nrm, t), inv_sqrt_d);
+            const float acc = __fmul_rn(a, dot);
+            if (metric == B200VQ_METRIC_L2) est = __fmaf_rn(-2.f, acc, __fadd_rn(qc, __fmul_rn(__fmul_rn(a, a), l2)));
+            else est = -__fadd_rn(qc, acc);
         }
         tk.offer(valid, est, (uint32_t)row);
     }
@@ -677,6 +831,60 @@ extern "C" int b200vq_erabitq_pack(const double* srot, const double* nrm, int64_
     if (g > cap) g = cap;
     erabitq_pack_kernel<<<(int)g, 256, smem, as_stream(stream)>>>(srot, nrm, n, D, B, levels, bounds,
                                                                  codes);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_resid_norms_f64(const void* x, int x_is_f64, int64_t n, int64_t ldx, int D, const double* c,
+                                      double* nrm, void* stream) {
+    VQ_CHECK_ARG((x || n == 0) && c && (nrm || n == 0) && n >= 0 && D > 0 && ldx >= D, "resid_norms_f64: bad args");
+    if (n == 0) return B200VQ_OK;
+    int64_t g = (n * 32 + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    if (x_is_f64)
+        resid_norm_kernel<double><<<(int)g, 256, 0, as_stream(stream)>>>(reinterpret_cast<const double*>(x), n, ldx, D, c, nrm);
+    else
+        resid_norm_kernel<float><<<(int)g, 256, 0, as_stream(stream)>>>(reinterpret_cast<const float*>(x), n, ldx, D, c, nrm);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_pack_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                                      const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
+                                      const double* levels, const double* bounds, double err_rel, double err_abs,
+                                      uint8_t* codes, unsigned long long* stats, void* stream) {
+    VQ_CHECK_ARG((x || n == 0) && c && PT && (nrm || n == 0) && levels && bounds && (codes || n == 0) && n >= 0 &&
+                     D > 0 && D < 65536 && ldx >= D && (!y || ldy >= D),
+                 "erabitq_pack_tc: bad args");
+    VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_pack_tc: B must be in [1,8], got %d", B);
+    VQ_CHECK_ARG(err_rel >= 0.0 && err_abs >= 0.0, "erabitq_pack_tc: negative error bound");
+    if (n == 0) return B200VQ_OK;
+    const size_t smem = (size_t)(2 << B) * sizeof(double) + (size_t)8 * 3 * ((D + 15) & ~15) + 16;
+    VQ_CHECK_ARG(smem <= 200 * 1024, "erabitq_pack_tc: D too large");
+    int64_t g = (n + 7) / 8;
+    const int64_t cap = (int64_t)device_sm_count() * 8;
+    if (g > cap) g = cap;
+    if (x_is_f64) {
+        VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        erabitq_pack_tc_kernel<double><<<(int)g, 256, smem, as_stream(stream)>>>(
+            y, ldy, reinterpret_cast<const double*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats);
+    } else {
+        VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        erabitq_pack_tc_kernel<float><<<(int)g, 256, smem, as_stream(stream)>>>(
+            y, ldy, reinterpret_cast<const float*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_erabitq_rowscale(const uint8_t* codes, int64_t n, int D, int B, float* a, void* stream) {
+    VQ_CHECK_ARG((codes || n == 0) && (a || n == 0) && n >= 0 && D > 0 && B >= 1 && B <= 8, "erabitq_rowscale: bad args");
+    if (n == 0) return B200VQ_OK;
+    int64_t g = (n + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    erabitq_rowscale_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, D, B, a);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

@@ -51,6 +51,10 @@ struct Params {
     int64_t n, ldy;
     int N, nchunk, ntn;       // output columns, K / 32, column tiles
     int64_t ntr;              // row tiles
+    const float* x_sub;       // (K) subtracted from every row of X before the split, or null
+    const float* col_bias;    // (N) added to every output row, or null
+    const float* row_scale;   // (n) output row i is multiplied by row_scale[i] (before the bias), or null
+    int transpose_out;        // 1: element (row, col) is stored at y[col * ldy + row]
 };
 
 // round-to-nearest (ties away) to 11 significant bits; the result is exactly representable in TF32
@@ -160,15 +164,25 @@ rotate_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         // ======================================================= converters ===
         asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
         const int tid = threadIdx.x - 128;     // 0..127
+        // float4 slot i * 128 + tid of the SWIZZLE_128B tile is row i * 16 + tid / 8, physical 16-byte chunk
+        // tid % 8, i.e. LOGICAL chunk (tid % 8) ^ (row % 8) = (tid & 7) ^ ((tid >> 3) & 7) for every i: a thread
+        // always sees the same four columns of the K chunk, so x_sub costs one float4 per chunk
+        const int lcol = 4 * ((tid & 7) ^ ((tid >> 3) & 7));
         uint32_t st = 0, phase = 0;
         for (int64_t unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
             for (int c = 0; c < p.nchunk; ++c) {
+                float4 sub = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p.x_sub) sub = __ldg(reinterpret_cast<const float4*>(p.x_sub + c * CH + lcol));
                 mbar_wait(bar(B_FULL + st), phase);
                 float4* xh = reinterpret_cast<float4*>(gbase + st * STAGE_BYTES + OFF_XH);
                 float4* xl = reinterpret_cast<float4*>(gbase + st * STAGE_BYTES + OFF_XL);
                 float4 v[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = xh[i * 128 + tid];
+                for (int i = 0; i < 8; ++i) {
+                    v[i] = xh[i * 128 + tid];
+                    v[i].x = __fsub_rn(v[i].x, sub.x); v[i].y = __fsub_rn(v[i].y, sub.y);
+                    v[i].z = __fsub_rn(v[i].z, sub.z); v[i].w = __fsub_rn(v[i].w, sub.w);
+                }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     float4 h, l;
@@ -214,10 +228,26 @@ rotate_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 if (lane == 0) mbar_arrive(bar(B_TEMPTY + acc));
                 if (++acc == 2) { acc = 0; t_phase ^= 1; }
             }
-            if (row < p.n) {
-                const int col0 = u * TILE_N + half * 128;
+            const int col0 = u * TILE_N + half * 128;
+            const int ncol = p.N - col0;                  // valid columns from col0 on (may exceed 128)
+            if (row < p.n && (p.row_scale || p.col_bias)) {
+                const float rs = p.row_scale ? __ldg(p.row_scale + row) : 1.f;
+#pragma unroll
+                for (int j = 0; j < 128; ++j) {
+                    float v = p.row_scale ? __fmul_rn(sum[j], rs) : sum[j];
+                    if (p.col_bias && j < ncol) v = __fadd_rn(v, __ldg(p.col_bias + col0 + j));
+                    sum[j] = v;
+                }
+            }
+            if (p.transpose_out) {
+                // lanes = 32 consecutive rows: every column is one coalesced 128-byte store
+                if (row < p.n) {
+#pragma unroll
+                    for (int j = 0; j < 128; ++j)
+                        if (j < ncol) p.y[(int64_t)(col0 + j) * p.ldy + row] = sum[j];
+                }
+            } else if (row < p.n) {
                 float* yr = p.y + row * p.ldy + col0;
-                const int ncol = p.N - col0;                  // valid columns from col0 on (may exceed 128)
 #pragma unroll
                 for (int j = 0; j < 128; j += 4) {
                     if (j + 3 < ncol) {
@@ -274,12 +304,22 @@ extern "C" int b200vq_rotate_tc_prepare(const float* w, int64_t ldw, int64_t N, 
 // Y (n x N, row stride ldy) = X (n x K, row stride ldx) . W^T with W prepared by b200vq_rotate_tc_prepare.
 extern "C" int b200vq_rotate_tc(const float* x, int64_t n, int64_t ldx, const void* wsplit, int64_t N, int64_t K,
                                 float* y, int64_t ldy, void* stream) {
-    VQ_CHECK_ARG(n >= 0 && N > 0 && K > 0 && ldx >= K && ldy >= N, "rotate_tc: bad shape");
+    return b200vq_rotate_tc_ex(x, n, ldx, wsplit, N, K, nullptr, nullptr, nullptr, 0, y, ldy, stream);
+}
+
+// Y = row_scale[i] * ((X - x_sub) . W^T) + col_bias, optionally stored transposed (y[col * ldy + row]).
+extern "C" int b200vq_rotate_tc_ex(const float* x, int64_t n, int64_t ldx, const void* wsplit, int64_t N, int64_t K,
+                                   const float* x_sub, const float* row_scale, const float* col_bias,
+                                   int transpose_out, float* y, int64_t ldy, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && N > 0 && K > 0 && ldx >= K && ldy >= (transpose_out ? n : N), "rotate_tc: bad shape");
     if (n == 0) return B200VQ_OK;
     VQ_CHECK_ARG(x && wsplit && y, "rotate_tc: null pointer");
-    VQ_CHECK_ARG(b200vq_rotate_tc_applies(n, ldx, N, K, ldy), "rotate_tc: shape not covered (K %% 32, ld %% 4)");
-    VQ_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
-                   reinterpret_cast<uintptr_t>(wsplit)) & 15) == 0, "rotate_tc: pointers must be 16-byte aligned");
+    VQ_CHECK_ARG(b200vq_rotate_tc_applies(n, ldx, N, K, transpose_out ? 4 : ldy),
+                 "rotate_tc: shape not covered (K %% 32, ld %% 4)");
+    VQ_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(wsplit)) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(y) & (transpose_out ? 3 : 15)) == 0 &&
+                     (reinterpret_cast<uintptr_t>(x_sub) & 15) == 0,
+                 "rotate_tc: pointers must be 16-byte aligned");
     const float* wh = reinterpret_cast<const float*>(wsplit);
     const float* wl = wh + (size_t)N * K;
     CUtensorMap map_x, map_wh, map_wl;
@@ -294,6 +334,7 @@ extern "C" int b200vq_rotate_tc(const float* x, int64_t n, int64_t ldx, const vo
     p.y = y; p.n = n; p.ldy = ldy; p.N = (int)N; p.nchunk = (int)(K / CH);
     p.ntn = (int)((N + TILE_N - 1) / TILE_N);
     p.ntr = (n + TILE_ROWS - 1) / TILE_ROWS;
+    p.x_sub = x_sub; p.col_bias = col_bias; p.row_scale = row_scale; p.transpose_out = transpose_out ? 1 : 0;
     const int64_t units = p.ntr * p.ntn;
     const int sms = device_sm_count();
     VQ_CUDA(cudaFuncSetAttribute(rotate_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));

@@ -39,6 +39,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes_dev: Optional[torch.Tensor] = None
         self._recon_dev: Optional[torch.Tensor] = None
         self._codes_rot: Optional[torch.Tensor] = None
+        self._erq_scanner = None
 
     def fit(self, X: np.ndarray, metric: Literal['l2', 'ip'] = 'l2') -> None:
         X = np.ascontiguousarray(X, dtype=np.float32)
@@ -49,6 +50,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes_dev = None
         self._recon_dev = None
         self._codes_rot = None
+        self._erq_scanner = None
 
     def attach_device_codes(self, codes_dev: torch.Tensor, D: int,
                             metric: Literal['l2', 'ip'] = 'l2') -> None:
@@ -63,6 +65,7 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes_dev = codes_dev
         self._recon_dev = None
         self._codes_rot = None
+        self._erq_scanner = None
 
     def search(self, Q: np.ndarray, k: int) -> np.ndarray:
         ids, _ = self.search_with_scores(Q, k)
@@ -109,9 +112,21 @@ class FlatQuantizedIndex(BaseSearchIndex):
                 vals, ids = codec.search(self._codes_rot, q_dev, k, self._metric, n=self._N, rot=True, m_pad=m_pad)
             else:
                 vals, ids = codec.search(self._codes_dev, q_dev, k, self._metric)
+        elif self._erabitq_ok():
+            # extended RaBitQ: |q - x^|^2 = |q - c|^2 + a^2 sum l^2 - 2 a <l, (q - c) P> (P orthonormal), scored from
+            # the packed codes on the tensor cores (csrc/est_tc.cu) - the reconstructions are never materialised
+            if self._erq_scanner is None:
+                self._erq_scanner = self._quantizer.device_scanner(self._codes)
+            qrot, qconst = self._quantizer.rotate_queries(q_dev, self._metric)
+            vals, ids = self._erq_scanner.search(qrot, qconst, k, self._metric)
         else:
             vals, ids = ops.flat_topk(self._reconstructions(), q_dev, k, self._metric)
         return host.to_host(ids).view(np.uint32), host.to_host(vals)
+
+    def _erabitq_ok(self) -> bool:
+        from haag_vq.methods.extended_rabitq import ExtendedRaBitQuantizer
+        q = self._quantizer
+        return isinstance(q, ExtendedRaBitQuantizer) and q.P is not None and q.D % 32 == 0 and self._codes is not None
 
     def memory_footprint(self) -> int:
         if self._codes is not None:
@@ -136,8 +151,11 @@ class FlatQuantizedIndex(BaseSearchIndex):
             quantizer_state = self._quantizer._state()
         else:
             quantizer_state = {'type': 'other', 'obj': self._quantizer}
+        codes = self._codes
+        if codes is None and self._codes_dev is not None:      # attach_device_codes: bring the codes back for the file
+            codes = host.to_host(self._codes_dev)
         with open(path, 'wb') as f:
-            pickle.dump({'quantizer_state': quantizer_state, 'codes': self._codes, 'metric': self._metric,
+            pickle.dump({'quantizer_state': quantizer_state, 'codes': codes, 'metric': self._metric,
                          'N': self._N, 'D': self._D}, f)
 
     def load(self, path: str | Path) -> None:
@@ -156,3 +174,4 @@ class FlatQuantizedIndex(BaseSearchIndex):
         self._codes_dev = None
         self._recon_dev = None
         self._codes_rot = None
+        self._erq_scanner = None
