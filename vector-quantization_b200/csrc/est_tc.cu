@@ -82,10 +82,20 @@ struct Params {
 // ------------------------------------------------------------------ decoding ---
 // One chunk = 32 fields of B bits = B 32-bit words of the big-endian bit stream.
 template <int B>
-__device__ __forceinline__ void load_words(const uint8_t* p, uint32_t (&w)[MAX_BITS]) {
+__device__ __forceinline__ void load_words_raw(const uint8_t* p, uint32_t (&w)[MAX_BITS]) {
     const uint32_t* q = reinterpret_cast<const uint32_t*>(p);
 #pragma unroll
-    for (int i = 0; i < B; ++i) w[i] = __byte_perm(__ldg(q + i), 0, 0x0123);
+    for (int i = 0; i < B; ++i) w[i] = __ldg(q + i);   // no use of the value here: the load stays in flight
+}
+template <int B>
+__device__ __forceinline__ void swap_words(uint32_t (&w)[MAX_BITS]) {
+#pragma unroll
+    for (int i = 0; i < B; ++i) w[i] = __byte_perm(w[i], 0, 0x0123);   // big-endian bit stream
+}
+template <int B>
+__device__ __forceinline__ void load_words(const uint8_t* p, uint32_t (&w)[MAX_BITS]) {
+    load_words_raw<B>(p, w);
+    swap_words<B>(w);
 }
 template <int B>
 __device__ __forceinline__ void zero_words(uint32_t (&w)[MAX_BITS]) {
@@ -154,6 +164,9 @@ __device__ __forceinline__ float sq_chunk(const uint32_t (&w)[MAX_BITS], const f
     }
 
 // ------------------------------------------------------------- screen kernel ---
+// FB > 0: every row is ONE segment of FB-bit codes with a value table (extended RaBitQ): the converters run
+// without per-chunk dispatch and keep two chunks of code words in flight. FB == 0: any segment list.
+template <int FB>
 __global__ void __launch_bounds__(THREADS, 1)
 est_screen_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ SegTable segs, const Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -244,47 +257,100 @@ est_screen_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         const int r = (cw & 3) * 32 + lane;
         const int r7 = r & 7;
         uint8_t* a_row0 = gbase + (uint32_t)(r >> 3) * 1024u + (uint32_t)r7 * 128u;
-        const int64_t my_units = (nunits - blockIdx.x + gridDim.x - 1) / gridDim.x;
-        const int64_t total = my_units * p.nchunk;
-        uint32_t cur[MAX_BITS], nxt[MAX_BITS];
-        float rs_cur = 0.f, rs_nxt = 0.f;
-        // position of chunk g of this CTA's sequence
-        auto fetch = [&](int64_t g, uint32_t (&w)[MAX_BITS], float& rs) {
-            const int64_t ul = g / p.nchunk;
-            const int c = (int)(g - ul * p.nchunk);
-            const int64_t unit = blockIdx.x + ul * gridDim.x;
-            const int64_t row = p.r0 + (unit / p.ntq) * TILE_ROWS + r;
-            const Seg& sg = segs.s[seg_of[c]];
-            if (row < p.r1) {
-                const uint8_t* src = sg.codes + row * sg.stride + (int64_t)(c - sg.chunk0) * (4 * sg.bits);
-                EST_SWITCH_BITS(sg.bits, load_words<BB>(src, w));
-                rs = sg.rowscale ? __ldg(sg.rowscale + row) : 1.f;
-            } else {
-                EST_SWITCH_BITS(sg.bits, zero_words<BB>(w));
-                rs = 0.f;
+        // (unit, row tile, chunk) cursors advance without divisions: a unit step adds gridDim.x units
+        const int dq = (int)(gridDim.x / (unsigned)p.ntq), dr = (int)(gridDim.x % (unsigned)p.ntq);
+        struct Cursor {
+            int64_t unit, t;
+            int u, c;
+        };
+        auto advance = [&](Cursor& k, int by) {
+            k.c += by;
+            while (k.c >= p.nchunk) {
+                k.c -= p.nchunk;
+                k.unit += gridDim.x;
+                k.t += dq;
+                k.u += dr;
+                if (k.u >= p.ntq) { k.u -= p.ntq; ++k.t; }
             }
         };
-        int64_t g = grp;
-        if (g < total) fetch(g, nxt, rs_nxt);
-        for (; g < total; g += 2) {
+        Cursor kc, kf;      // chunk being converted / chunk being fetched
+        kc.unit = blockIdx.x; kc.t = blockIdx.x / p.ntq; kc.u = (int)(blockIdx.x % p.ntq); kc.c = 0;
+        advance(kc, grp);
+        kf = kc;
+        if constexpr (FB > 0) {
+            const uint8_t* codes0 = segs.s[0].codes;
+            const float* rowscale0 = segs.s[0].rowscale;
+            const int64_t stride0 = segs.s[0].stride;
+            uint32_t w0[MAX_BITS], w1[MAX_BITS], w2[MAX_BITS];
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+            // raw words only: the byte swap happens at conversion time, so nothing waits on a load here
+            auto fetch1 = [&](const Cursor& k, uint32_t (&w)[MAX_BITS], float& rs) {
+                const int64_t row = p.r0 + k.t * TILE_ROWS + r;
+                if (k.unit < nunits && row < p.r1) {
+                    load_words_raw<FB>(codes0 + row * stride0 + (int64_t)k.c * (4 * FB), w);
+                    rs = rowscale0 ? __ldg(rowscale0 + row) : 1.f;
+                } else {
+                    zero_words<FB>(w);
+                    rs = 0.f;
+                }
+            };
+            fetch1(kf, w1, s1);
+            advance(kf, 2);
+            fetch1(kf, w2, s2);
+            for (uint32_t g = (uint32_t)grp; kc.unit < nunits; g += 2) {
 #pragma unroll
-            for (int i = 0; i < MAX_BITS; ++i) cur[i] = nxt[i];
-            rs_cur = rs_nxt;
-            if (g + 2 < total) fetch(g + 2, nxt, rs_nxt);
-            const uint32_t st = (uint32_t)(g % NST), phase = (uint32_t)((g / NST) & 1);
-            const int c = (int)(g % p.nchunk);
-            const Seg& sg = segs.s[seg_of[c]];
-            mbar_wait(bar(B_EMPTY + st), phase ^ 1);
-            uint8_t* a_row = a_row0 + st * STAGE_BYTES;
-            if (sg.tab_off >= 0) {
-                const float* tab = tab_s + sg.tab_off;
-                EST_SWITCH_BITS(sg.bits, (convert_chunk<(BB <= 8 ? BB : 8), true>(cur, rs_cur, tab, 0.f, a_row, r7)));
-            } else {
-                EST_SWITCH_BITS(sg.bits, (convert_chunk<BB, false>(cur, rs_cur, nullptr, sg.base, a_row, r7)));
+                for (int i = 0; i < FB; ++i) { w0[i] = w1[i]; w1[i] = w2[i]; }
+                s0 = s1; s1 = s2;
+                advance(kf, 2);
+                fetch1(kf, w2, s2);
+                const uint32_t st = g & (NST - 1), phase = (g / NST) & 1u;
+                mbar_wait(bar(B_EMPTY + st), phase ^ 1);
+                swap_words<FB>(w0);
+                convert_chunk<FB, true>(w0, s0, tab_s, 0.f, a_row0 + st * STAGE_BYTES, r7);
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(B_CONV + st));
+                advance(kc, 2);
             }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(B_CONV + st));
+        } else {
+            uint32_t cur[MAX_BITS], nxt[MAX_BITS];
+            float rs_cur = 0.f, rs_nxt = 0.f;
+            auto fetch = [&](const Cursor& k, uint32_t (&w)[MAX_BITS], float& rs) {
+                const int64_t row = p.r0 + k.t * TILE_ROWS + r;
+                const Seg& sg = segs.s[seg_of[k.c]];
+                if (k.unit < nunits && row < p.r1) {
+                    const uint8_t* src = sg.codes + row * sg.stride + (int64_t)(k.c - sg.chunk0) * (4 * sg.bits);
+                    EST_SWITCH_BITS(sg.bits, load_words_raw<BB>(src, w));
+                    rs = sg.rowscale ? __ldg(sg.rowscale + row) : 1.f;
+                } else {
+                    EST_SWITCH_BITS(sg.bits, zero_words<BB>(w));
+                    rs = 0.f;
+                }
+            };
+            fetch(kf, nxt, rs_nxt);
+            for (uint32_t g = (uint32_t)grp; kc.unit < nunits; g += 2) {
+#pragma unroll
+                for (int i = 0; i < MAX_BITS; ++i) cur[i] = nxt[i];
+                rs_cur = rs_nxt;
+                advance(kf, 2);
+                fetch(kf, nxt, rs_nxt);
+                const uint32_t st = g & (NST - 1), phase = (g / NST) & 1u;
+                const Seg& sg = segs.s[seg_of[kc.c]];
+                mbar_wait(bar(B_EMPTY + st), phase ^ 1);
+                uint8_t* a_row = a_row0 + st * STAGE_BYTES;
+                if (sg.tab_off >= 0) {
+                    const float* tab = tab_s + sg.tab_off;
+                    EST_SWITCH_BITS(sg.bits, (swap_words<(BB <= 8 ? BB : 8)>(cur),
+                                              convert_chunk<(BB <= 8 ? BB : 8), true>(cur, rs_cur, tab, 0.f, a_row, r7)));
+                } else {
+                    EST_SWITCH_BITS(sg.bits, (swap_words<BB>(cur),
+                                              convert_chunk<BB, false>(cur, rs_cur, nullptr, sg.base, a_row, r7)));
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(B_CONV + st));
+                advance(kc, 2);
+            }
         }
     } else {
         // ========================================================= epilogue ===
@@ -696,7 +762,15 @@ extern "C" int b200vq_est_scan_topk(int nseg, const int* seg_len, const int* seg
     if ((rc = encode_2d(&map_q, queries, (uint64_t)nq, (uint64_t)D, (uint64_t)ldq, TILE_Q, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
         return rc;
     const uint32_t smem = TAB_OFF + (uint32_t)ntab * 4 + 1024;
-    VQ_CUDA(cudaFuncSetAttribute(est_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    typedef void (*ScreenFn)(const CUtensorMap, const SegTable, const Params);
+    ScreenFn screen = est_screen_kernel<0>;
+    if (segs.nseg == 1 && segs.s[0].tab_off == 0) {   // one table segment (extended RaBitQ): width-specialised converters
+        static const ScreenFn fixed[9] = {nullptr, est_screen_kernel<1>, est_screen_kernel<2>, est_screen_kernel<3>,
+                                          est_screen_kernel<4>, est_screen_kernel<5>, est_screen_kernel<6>,
+                                          est_screen_kernel<7>, est_screen_kernel<8>};
+        screen = fixed[segs.s[0].bits];
+    }
+    VQ_CUDA(cudaFuncSetAttribute(screen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     Params p;
     p.norm2 = row_norm2; p.bias = row_bias; p.thr = thr; p.qstats = qstats; p.tables = tables; p.cand = cand;
     p.count = count; p.cap = fp.cap; p.nq = nq; p.nchunk = D / CH; p.ntq = fp.ntq; p.ntab = ntab; p.metric = metric;
@@ -708,7 +782,7 @@ extern "C" int b200vq_est_scan_topk(int nseg, const int* seg_len, const int* seg
         p.r0 = r; p.r1 = r1;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
-        est_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, smem, st>>>(map_q, segs, p);
+        screen<<<(unsigned)(units < sms ? units : sms), THREADS, smem, st>>>(map_q, segs, p);
         VQ_LAUNCH_CHECK();
         rc = EST_FINISH(r1 == n, 0, nullptr);
         if (rc != B200VQ_OK) return rc;

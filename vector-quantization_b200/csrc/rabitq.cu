@@ -431,7 +431,7 @@ __device__ __forceinline__ int erabitq_level_of(const double* bd, int L, double 
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
                        const double* __restrict__ c, const double* __restrict__ PT, const double* __restrict__ nrm,
                        int64_t n, int D, int B, const double* __restrict__ levels, const double* __restrict__ bounds,
@@ -461,47 +461,88 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
         const float* yr = y ? y + row * ldy : nullptr;
         double num = 0.0, den = 0.0;
         int nflag = 0;
-        for (int d0 = 0; d0 < D; d0 += 32) {
-            const int d = d0 + lane;
-            bool flag = false;
-            if (d < D) {
-                if (yr) {
-                    const double sv = (double)yr[d] * sc;
+        // pass 1: four consecutive coordinates per lane and step (one 128-bit load when the row allows it)
+        const bool vec4 = yr && ((reinterpret_cast<uintptr_t>(yr) & 15) == 0);
+        for (int d0 = 0; d0 < D; d0 += 128) {
+            const int db = d0 + 4 * lane;
+            float yv[4] = {0.f, 0.f, 0.f, 0.f};
+            if (yr) {
+                if (vec4 && db + 3 < D) {
+                    const float4 v = __ldg(reinterpret_cast<const float4*>(yr + db));
+                    yv[0] = v.x; yv[1] = v.y; yv[2] = v.z; yv[3] = v.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (db + e < D) yv[e] = __ldg(yr + db + e);
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int d = db + e;
+                bool flag = false;
+                if (d < D) {
+                    if (yr) {
+                        const double sv = (double)yv[e] * sc;
+                        const int lo = erabitq_level_of(bd, L, sv);
+                        flag = (lo > 0 && sv - bd[lo - 1] < eps_s) || (lo < L - 1 && bd[lo] - sv < eps_s);
+                        idx[d] = (uint8_t)lo;
+                        const double sh = lv[lo];
+                        num = fma(sv, sh, num);
+                        den = fma(sh, sh, den);
+                    } else {
+                        flag = true;
+                    }
+                }
+                const unsigned m = __ballot_sync(FULL_MASK, flag);
+                if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
+                nflag += __popc(m);
+            }
+        }
+        __syncwarp();
+        // pass 2: exact fp64 dot products, four flagged coordinates at a time (x - c is loaded once for the four)
+        const T* xr = x + row * ldx;
+        for (int f0 = 0; f0 < nflag; f0 += 4) {
+            int dd[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) dd[e] = flist[min(f0 + e, nflag - 1)];
+            const double* pt0 = PT + (int64_t)dd[0] * D;
+            const double* pt1 = PT + (int64_t)dd[1] * D;
+            const double* pt2 = PT + (int64_t)dd[2] * D;
+            const double* pt3 = PT + (int64_t)dd[3] * D;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+            for (int k = lane; k < D; k += 32) {
+                const double rk = (double)xr[k] - c[k];
+                a0 = fma(rk, __ldg(pt0 + k), a0);
+                a1 = fma(rk, __ldg(pt1 + k), a1);
+                a2 = fma(rk, __ldg(pt2 + k), a2);
+                a3 = fma(rk, __ldg(pt3 + k), a3);
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                a0 += __shfl_xor_sync(FULL_MASK, a0, o);
+                a1 += __shfl_xor_sync(FULL_MASK, a1, o);
+                a2 += __shfl_xor_sync(FULL_MASK, a2, o);
+                a3 += __shfl_xor_sync(FULL_MASK, a3, o);
+            }
+            if (lane == 0) {
+                const double av[4] = {a0, a1, a2, a3};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (f0 + e >= nflag) break;
+                    const int d = dd[e];
+                    const double sv = (av[e] / nsafe) * sqrt_d;
                     const int lo = erabitq_level_of(bd, L, sv);
-                    flag = (lo > 0 && sv - bd[lo - 1] < eps_s) || (lo < L - 1 && bd[lo] - sv < eps_s);
+                    if (yr) {
+                        const double so = (double)yr[d] * sc;
+                        const double sho = lv[idx[d]];
+                        num -= so * sho;
+                        den -= sho * sho;
+                    }
                     idx[d] = (uint8_t)lo;
                     const double sh = lv[lo];
                     num = fma(sv, sh, num);
                     den = fma(sh, sh, den);
-                } else {
-                    flag = true;
                 }
-            }
-            const unsigned m = __ballot_sync(FULL_MASK, flag);
-            if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
-            nflag += __popc(m);
-        }
-        __syncwarp();
-        const T* xr = x + row * ldx;
-        for (int f = 0; f < nflag; ++f) {
-            const int d = flist[f];
-            const double* pt = PT + (int64_t)d * D;
-            double acc = 0.0;
-            for (int k = lane; k < D; k += 32) acc = fma((double)xr[k] - c[k], __ldg(pt + k), acc);
-            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
-            if (lane == 0) {
-                const double sv = (acc / nsafe) * sqrt_d;
-                const int lo = erabitq_level_of(bd, L, sv);
-                if (yr) {
-                    const double so = (double)yr[d] * sc;
-                    const double sho = lv[idx[d]];
-                    num -= so * sho;
-                    den -= sho * sho;
-                }
-                idx[d] = (uint8_t)lo;
-                const double sh = lv[lo];
-                num = fma(sv, sh, num);
-                den = fma(sh, sh, den);
             }
         }
         nfix_total += (unsigned long long)nflag;
