@@ -65,6 +65,8 @@ def parse_args():
                     help="screen = four-queries-per-lookup screened scan (scan layout only), same results")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1-C4 kernel table (N = 1 only)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed result check of the scan / NCCL merge")
     return ap.parse_args()
 
 
@@ -401,6 +403,8 @@ def run_b200(args):
             traffic = rec["dram_bytes_per_launch"]
     except (OSError, ValueError, KeyError):
         traffic = None
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    lds_floor_ms = float(n) * M * nq / q_tile / 32.0 / (148 * sm_mhz * 1e6) * 1e3
     line = {
         "metric": METRIC, "value": enc_vps, "unit": "vectors/s",
         "adc": {"value": adc_cps, "unit": "codes/s"},
@@ -413,7 +417,15 @@ def run_b200(args):
                      "achieved": scan_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": scan_gbs / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peaks["source"],
                      "algorithmic_bytes_per_launch": scan_bytes, "query_tile": q_tile,
-                     "table_lookups_per_s": float(n) * M * nq / (knl / steps * 1e-3)},
+                     "table_lookups_per_s": float(n) * M * nq / (knl / steps * 1e-3),
+                     # what the number is and is not: the query passes are served by L2, so DRAM sees `traffic`
+                     # bytes per call (dram_gbs); the kernel's own ceiling is the shared-memory look-up rate:
+                     # lookups / (4 queries per LDS) / 32 lanes per warp-LDS / (SMs x clock) = lds_floor_ms
+                     "dram_gbs": (traffic / (knl / steps * 1e-3) / 1e9) if traffic else None,
+                     "dram_frac": (traffic / (knl / steps * 1e-3) / 1e9 / peaks["hbm_gbs"]) if traffic else None,
+                     "lds_floor_ms": lds_floor_ms, "lds_frac": lds_floor_ms / (knl / steps),
+                     "bound_note": "hbm per SURVEY 8(d) accounting (algorithmic code bytes x query-tile passes); "
+                                   "actual limiter = shared-memory LUT look-ups (lds_frac), DRAM at dram_frac"},
         "roofline_assign": {"kernel": "pq_assign_tc_kernel" if impl == "tc" else "pq_assign_simt_kernel",
                             "bound": "tensor", "achieved": assign_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
                             "frac": assign_tflops / tf32_peak,
@@ -422,8 +434,40 @@ def run_b200(args):
         "gpu_launches": int(n_calls + steps),  # every ABI call is >= 1 kernel; the scan call adds its merge kernel
         "clocks": clocks,
     }
-    return line, dict(torch=torch, tdist=tdist, codec=codec, codes=codes, C=C, Qd=Qd, world=world, rank=rank,
-                      dev=dev, n=n, nq=nq, row_offset=row_offset, col_scale=col_scale, xbuf=xbuf)
+    ctx = dict(torch=torch, tdist=tdist, codec=codec, codes=codes, C=C, Qd=Qd, world=world, rank=rank,
+               dev=dev, n=n, nq=nq, row_offset=row_offset, col_scale=col_scale, xbuf=xbuf, step=step, scan=scan,
+               codes_rot=codes_rot, layout=layout)
+    if not args.no_parity:
+        line["parity_check"] = parity_check(ctx)
+    return line, ctx
+
+
+def parity_check(ctx):
+    """Untimed result check on hardware. N = 1: the screened scan against the exact row-layout kernel (ids and value
+    bits). N > 1: every rank's codes are all-gathered (53 M x 32 B = 1.7 GB at N = 8), rank 0 scans them as ONE shard
+    and the NCCL-merged (value, global id) lists must equal that single-GPU answer bit for bit."""
+    torch, tdist = ctx["torch"], ctx["tdist"]
+    from b200vq import ops
+    codec, codes, Qd, world, rank, n = ctx["codec"], ctx["codes"], ctx["Qd"], ctx["world"], ctx["rank"], ctx["n"]
+    vals, ids = ctx["step"](0, False)
+    if world == 1:
+        lut = codec.luts(Qd, "l2")
+        v0, i0 = ops.adc_scan_topk(codes, lut, K, "l2")
+        ok = bool(torch.equal(ids.view(torch.int32), i0.view(torch.int32))) and \
+            bool(torch.equal(vals.view(torch.int32), v0.view(torch.int32)))
+        return "ok (N=1: scan path == exact row-layout scan, ids and value bits)" if ok else "MISMATCH (N=1)"
+    allc = torch.empty((world * n, M), dtype=torch.uint8, device=ctx["dev"])
+    tdist.all_gather_into_tensor(allc, codes)
+    res = "ok"
+    if rank == 0:
+        v1, i1 = codec.search(allc, Qd, K, "l2")                      # exact row-layout scan of the whole corpus
+        same = bool(torch.equal(ids.to(torch.int64), i1.view(torch.int32).to(torch.int64) & 0xFFFFFFFF)) and \
+            bool(torch.equal(vals.view(torch.int32), v1.view(torch.int32)))
+        res = (f"ok (N={world}: NCCL all-gather + merge == single-GPU scan of all {world * n} codes, ids and value bits)"
+               if same else f"MISMATCH (N={world})")
+    del allc
+    tdist.barrier()
+    return res
 
 
 def run_e2e(args, ctx):
@@ -447,41 +491,82 @@ def run_e2e(args, ctx):
     torch.cuda.synchronize()
     Xh, Qh = xh.numpy(), qh.numpy()
 
-    def one():
+    def sync_all():
         torch.cuda.synchronize()
+        if world > 1:
+            tdist.barrier()           # the two legs are timed separately: no rank's H2D skew leaks into the search leg
+            torch.cuda.synchronize()
+
+    def one():
+        sync_all()
         a = time.perf_counter()
         codes_h = pq.compress(Xh)
         torch.cuda.synchronize()
         b = time.perf_counter()
+        sync_all()
+        c = time.perf_counter()
         ids, sc = index.search_with_scores(Qh, K)
         if world > 1:
             v, i = vdist.sharded_topk(host.to_device(sc), host.to_device(ids.view(np.int32)),
                                       ctx["row_offset"], K, "l2")
             sc, ids = host.to_host(v), host.to_host(i)
         torch.cuda.synchronize()
-        c = time.perf_counter()
+        d = time.perf_counter()
         assert codes_h.shape == (rows, M) and ids.shape == (nq, K)
-        return b - a, c - b
+        return b - a, d - c
 
     one()
     reps = max(1, min(args.steps, 3))
-    if world > 1:
-        tdist.barrier()
     te = ts = 0.0
     for _ in range(reps):
         a, b = one()
         te += a
         ts += b
+    mine = te
     t = torch.tensor([te, ts], dtype=torch.float64, device=dev)
     if world > 1:
         tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
     te, ts = (float(v) for v in t.tolist())
+    h2d = rows * D * 4
+    per_rank = torch.tensor([h2d * reps / mine / 1e9], dtype=torch.float64, device=dev)
+    gathered = [torch.zeros_like(per_rank) for _ in range(world)]
+    if world > 1:
+        tdist.all_gather(gathered, per_rank)
+    else:
+        gathered = [per_rank]
     return {"value": rows * world * reps / te, "unit": "vectors/s",
             "adc": {"value": float(ctx["n"]) * world * nq * reps / ts, "unit": "codes/s"},
             "h2d_bytes_per_step": rows * D * 4 + nq * D * 4, "d2h_bytes_per_step": rows * M + nq * K * 8,
+            "h2d_gbs_per_rank": [round(float(g.item()), 2) for g in gathered],
             "api": "haag_vq ProductQuantizer.compress(X) + FlatQuantizedIndex.search_with_scores(Q, 10); "
                    f"pinned host X ({rows}x{D}) and Q, numpy results; codes of the shard resident in HBM",
-            "timing": "host perf_counter around the call, device synchronised both sides, max over ranks"}
+            "timing": "host perf_counter around each call, device synchronised and ranks aligned by a barrier before "
+                      "each of the two legs, max over ranks; the encode leg is bound by the host link (h2d_gbs_per_rank: "
+                      "input bytes / encode time of every rank; all GPUs of the box share the host's PCIe / DRAM)"}
+
+
+def run_configs(ctx):
+    """C1-C4 + SAQ-engine kernel table (tools/config_bench.py), CUDA-event timed on this box, outside the timed
+    region of the headline: one row per kernel with its algorithmic bytes / FLOP and fraction of the measured peak."""
+    torch = ctx["torch"]
+    for key in ("codes", "codes_rot", "xbuf"):
+        ctx[key] = None                      # free the C5 shard before the 1M x 1536 / 3072 configs
+    ctx["step"] = ctx["scan"] = None
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    try:
+        import config_bench
+        rows = config_bench.run(("c1", "c2", "c3", "c4", "saq"), device=ctx["dev"], quick=True)
+        for r in rows:
+            for k, v in list(r.items()):
+                if isinstance(v, float):
+                    r[k] = float(f"{v:.5g}")
+        return {"peaks": config_bench.peaks, "timing": "CUDA events, 3 warm-ups, inputs resident in HBM and larger than L2",
+                "rows": rows}
+    except Exception as e:  # the headline line must still print
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def main():
@@ -502,6 +587,8 @@ def main():
     if not args.no_e2e:
         line["e2e"] = run_e2e(args, ctx)
     if ctx["rank"] == 0:
+        if ctx["world"] == 1 and not args.no_configs:
+            line["configs"] = run_configs(ctx)
         if ctx["world"] == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg()
         print_line(line)

@@ -1,7 +1,7 @@
-"""Per-config kernel table: every hot-path kernel of SURVEY 8(a) at its BASELINE config shape, timed on
-one B200 with CUDA events (inputs resident, > L2, 3 warm-ups), with the algorithmic bytes / FLOP of
-SURVEY 8(d) against MEASURED_PEAKS.json. Writes one JSON document (default profiles/r1_configs.json).
-Diagnostic companion of bench.py (which carries the C5 headline); no oracle, no CPU path."""
+"""Per-config kernel table: every hot-path kernel of SURVEY 8(a) at its BASELINE config shape (C1-C4), timed on
+one B200 with CUDA events (inputs resident, > L2, warm-ups first), with the algorithmic bytes / FLOP of
+SURVEY 8(d) against MEASURED_PEAKS.json. bench.py imports run() and prints the rows as "configs" in its JSON line
+(N = 1, rank 0, outside the timed region); run as a script it writes one JSON document. No oracle, no CPU path."""
 import json
 import os
 import sys
@@ -13,7 +13,7 @@ import torch
 
 from b200vq import ops, ops_sq, pq as dpq
 
-dev = torch.device("cuda")
+dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cuda")
 peaks = {"hbm_gbps": 6551.0, "tf32_tflops": 695.0}
 try:
     mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -22,6 +22,7 @@ try:
 except Exception:
     pass
 rows = []
+QUICK = False   # bench.py: skip the rows that only time a replaced (SIMT / library) path
 
 
 def timed(fn, reps=5, warm=3):
@@ -50,7 +51,8 @@ def add(config, kernel, ms, units, unit_name, bytes_=None, flops=None, note=""):
     rows.append(r)
     tail = (f" {r['GBps']:8.0f} GB/s ({r['frac_hbm']:.2f} of HBM)" if bytes_ is not None else "") + \
            (f" {r['TFLOPs']:7.1f} TFLOP/s ({r['frac_tf32']:.2f} of TF32)" if flops is not None else "")
-    print(f"{config:3s} {kernel:34s} {ms:9.3f} ms {r['units_per_s']:.3e} {unit_name}/s{tail}  {note}", flush=True)
+    print(f"{config:3s} {kernel:34s} {ms:9.3f} ms {r['units_per_s']:.3e} {unit_name}/s{tail}  {note}", flush=True,
+          file=sys.stderr)
 
 
 def data(n, D, seed=1234, normalize=True):
@@ -80,7 +82,8 @@ def c1():
     xn = ops.row_sqnorms(x)
     add("C1", "flat_topk_tc k=100 (ground truth)", timed(lambda: ops.flat_topk(x, q, 100, "l2", xnorm=xn)), n * nq,
         "pairs", flops=2.0 * n * nq * D)
-    add("C1", "flat_topk simt k=100", timed(lambda: ops.flat_topk(x, q, 100, "l2", xnorm=xn, impl="simt"), reps=2, warm=1),
+    if not QUICK:
+      add("C1", "flat_topk simt k=100", timed(lambda: ops.flat_topk(x, q, 100, "l2", xnorm=xn, impl="simt"), reps=2, warm=1),
         n * nq, "pairs", flops=2.0 * n * nq * D)
 
 
@@ -94,7 +97,8 @@ def c2():
     codes = codec.encode(x)
     add("C2", "rotate_tc 1536x1536 (3xTF32)", timed(lambda: dpq.rotate(x, A, impl="tc")), n, "vectors",
         bytes_=n * 8 * D, flops=2.0 * n * D * D, note="issued tensor work is 3x")
-    add("C2", "library sgemm rotation (replaced)", timed(lambda: dpq.rotate(x, A, impl="lib")), n, "vectors",
+    if not QUICK:
+      add("C2", "library sgemm rotation (replaced)", timed(lambda: dpq.rotate(x, A, impl="lib")), n, "vectors",
         flops=2.0 * n * D * D)
     add("C2", "pq_assign_tc dsub=48", timed(lambda: ops.pq_assign(y, C, codec.cnorm, out=codes)), n, "vectors",
         bytes_=n * (4 * D + M), flops=2.0 * n * D * 256)
@@ -143,6 +147,7 @@ def c4():
     x = data(n, D)
     q = data(nq, D, seed=1235)
     cen = x[:65536].mean(0).contiguous()
+    xn = ops.row_sqnorms(x)
     codes = ops_sq.rabitq1_encode(x, cen, "l2")
     add("C4", "rabitq1_encode", timed(lambda: ops_sq.rabitq1_encode(x, cen, "l2")), n, "vectors",
         bytes_=n * (4 * D + D // 8 + 8))
@@ -152,50 +157,102 @@ def c4():
     add("C4", "rabitq1_scan_topk_tc qb=4 k=10", timed(lambda: ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2")),
         n * nq, "codes", bytes_=float(n) * (D // 8 + 8) * ((nq + 255) // 256), flops=2.0 * n * nq * D,
         note="query tile 256; FLOP = FP8 tensor work, fraction quoted against TF32 peak/1 (FP8 peak is 4x)")
-    add("C4", "rabitq1_scan_topk simt qb=4 k=10",
+    if not QUICK:
+      add("C4", "rabitq1_scan_topk simt qb=4 k=10",
         timed(lambda: ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2", impl="simt"), reps=2, warm=1),
         n * nq, "codes", bytes_=float(n) * (D // 8 + 8) * nq, note="query tile 1")
-    del x
-    # extended RaBitQ, B = 4: pack / unpack on fp64 rotated rows (the rotation itself is an fp64 library GEMM)
+    # extended RaBitQ, B = 4 (registry method "rabitq"): encode = residual norms + rotation GEMM on the tensor cores
+    # (centroid subtraction fused) + level search with exact fp64 re-evaluation near the mid-points
+    from haag_vq.methods.extended_rabitq import ExtendedRaBitQuantizer
     nb, B = 131_072, 4
-    g = torch.Generator(device=dev).manual_seed(5)
-    srot = torch.randn((nb, D), generator=g, device=dev, dtype=torch.float64)
-    nrm = torch.rand((nb,), generator=g, device=dev, dtype=torch.float64) + 0.5
-    from haag_vq.methods.extended_rabitq import _lloyd_1d_normal
-    levels = torch.from_numpy(np.asarray(_lloyd_1d_normal(1 << B, 0), dtype=np.float64)).to(dev)
-    bounds = (0.5 * (levels[:-1] + levels[1:])).contiguous()
-    ecodes = ops_sq.erabitq_pack(srot, nrm, B, levels, bounds)
-    add("C4", "erabitq_pack B=4 (fp64 in)", timed(lambda: ops_sq.erabitq_pack(srot, nrm, B, levels, bounds)), nb,
-        "vectors", bytes_=nb * (8 * D + D * B // 8 + 8))
-    add("C4", "erabitq_unpack B=4 (fp64 out)", timed(lambda: ops_sq.erabitq_unpack(ecodes, D, B, levels)), nb, "vectors",
-        bytes_=nb * (8 * D + D * B // 8 + 8))
-    # extended RaBitQ estimator scan in the code domain (BASELINE config 4): <levels[idx], q P> per (code, query)
-    qrot = torch.randn((nq, D), generator=g, device=dev, dtype=torch.float32)
-    qconst = torch.rand((nq,), generator=g, device=dev, dtype=torch.float32)
-    lv32 = levels.to(torch.float32).contiguous()
-    add("C4", f"erabitq_scan_topk simt B=4 k=10 ({nb} codes)",
-        timed(lambda: ops_sq.erabitq_scan_topk(ecodes, D, B, lv32, qrot, qconst, 10, "l2", impl="simt"), reps=1, warm=1),
-        nb * nq, "codes", bytes_=float(nb) * (D * B // 8 + 8) * nq, note="query tile 1")
-    add("C4", f"erabitq_scan_topk tc B=4 k=10 ({nb} codes; decode + flat search)",
-        timed(lambda: ops_sq.erabitq_scan_topk(ecodes, D, B, lv32, qrot, qconst, 10, "l2", impl="tc"), reps=3, warm=2),
-        nb * nq, "codes", bytes_=float(nb) * (D * B // 8 + 8) * ((nq + 255) // 256), flops=2.0 * nb * nq * D,
-        note="query tile 256")
-    big = ecodes.repeat(8, 1)[:1_000_000].contiguous()
-    add("C4", "erabitq_scan_topk tc B=4 k=10 (1M codes; decode + flat search)",
-        timed(lambda: ops_sq.erabitq_scan_topk(big, D, B, lv32, qrot, qconst, 10, "l2", impl="tc"), reps=3, warm=2),
-        1_000_000 * nq, "codes", bytes_=1e6 * (D * B // 8 + 8) * ((nq + 255) // 256), flops=2.0 * 1e6 * nq * D,
-        note="query tile 256")
-    del big
-    P = torch.randn((D, D), generator=g, device=dev, dtype=torch.float64)
-    add("C4", "fp64 rotation GEMM (library)", timed(lambda: torch.matmul(srot, P), reps=2, warm=1), nb, "vectors",
+    eq = ExtendedRaBitQuantizer(B, seed=0)
+    eq.fit(x[:4096].cpu().numpy())
+    st = eq._state()
+    ecodes = torch.empty((n, eq.code_size), dtype=torch.uint8, device=dev)
+
+    def enc(s, e):
+        xs = x[s:e]
+        nrm = ops_sq.resid_norms_f64(xs, st["c"])
+        y = st["fwd"](xs, x_sub=st["c32"])
+        ops_sq.erabitq_pack_tc(y, xs, st["c"], st["PT"], nrm, B, st["levels"], st["bounds"], st["err_rel"],
+                               2 * st["err_abs"], out=ecodes[s:e], stats=st["nfix"])
+    add("C4", "extended RaBitQ encode B=4 (norms + rotate_tc + pack with fp64 fix-up)", timed(lambda: enc(0, nb)), nb,
+        "vectors", bytes_=nb * (4 * D + eq.code_size), flops=2.0 * nb * D * D, note="fp64 indices; issued tensor work is 3x")
+    xb = x[:nb]
+    nrm = ops_sq.resid_norms_f64(xb, st["c"])
+    yb = st["fwd"](xb, x_sub=st["c32"])
+    add("C4", "  rotate_tc_ex 1536x1536 (x - c fused)", timed(lambda: st["fwd"](xb, x_sub=st["c32"])), nb, "vectors",
         flops=2.0 * nb * D * D)
+    add("C4", "  erabitq_pack_tc B=4", timed(lambda: ops_sq.erabitq_pack_tc(yb, xb, st["c"], st["PT"], nrm, B, st["levels"],
+                                                                         st["bounds"], st["err_rel"], 2 * st["err_abs"],
+                                                                         out=ecodes[:nb])), nb, "vectors",
+        bytes_=nb * (4 * D + eq.code_size))
+    for s0 in range(0, n, nb):
+        enc(s0, min(n, s0 + nb))
+    add("C4", "extended RaBitQ decode B=4 (decode_f32 + rotate_tc_ex)",
+        timed(lambda: st["rev"](ops_sq.erabitq_decode_f32(ecodes[:nb], D, B, st["levels32"])[0], col_bias=st["c32d"])), nb,
+        "vectors", flops=2.0 * nb * D * D)
+    sc = ops_sq.ERaBitQScanner(ecodes, D, B, st["levels32"])
+    qrot, qconst = eq.rotate_queries(q, "l2")
+    add("C4", "extended RaBitQ estimator scan B=4 k=10 (1M codes; code-domain, tcgen05)",
+        timed(lambda: sc.search(qrot, qconst, 10, "l2"), reps=3, warm=2), n * nq, "codes",
+        bytes_=float(n) * eq.code_size * ((nq + 255) // 256), flops=2.0 * n * nq * D, note="query tile 256; codes only")
+    add("C4", "exact ground truth flat_topk_tc k=10 (1M x 1536)", timed(lambda: ops.flat_topk(x, q, 10, "l2", xnorm=xn), reps=3, warm=2),
+        n * nq, "pairs", flops=2.0 * n * nq * D)
+    ev, ei = sc.search(qrot, qconst, 10, "l2")
+    gv, gi = ops.flat_topk(x, q, 10, "l2", xnorm=xn)
+    rec = float(np.mean([len(set(a) & set(b)) / 10 for a, b in zip(ei.cpu().numpy().tolist(), gi.cpu().numpy().tolist())]))
+    rows.append({"config": "C4", "kernel": "recall@10 of the extended RaBitQ B=4 scan vs exact search", "value": rec})
+    rv, ri = ops_sq.rabitq1_scan_topk(codes, D, planes, qfac, 4, 10, "l2")
+    rec1 = float(np.mean([len(set(a) & set(b)) / 10 for a, b in zip(ri.cpu().numpy().tolist(), gi.cpu().numpy().tolist())]))
+    rows.append({"config": "C4", "kernel": "recall@10 of the 1-bit RaBitQ scan (qb=4) vs exact search", "value": rec1})
+    del x, ecodes, sc
+
+
+def saq_engine():
+    """SAQ engine (registry "saq_paper") at the reference's own recorded size 99 000 x 1536, avg 4 bits."""
+    from b200vq import saq_engine as E
+    n, D, nq = 99_000, 1536, 1000
+    x = data(n, D)
+    q = data(nq, D, seed=1235)
+    eng = E.SaqEngine(4.0).fit(x)
+    add("SAQ", "engine projection + segment rotations (one GEMM, transposed store)",
+        timed(lambda: eng._project(x, transpose_out=True)), n, "vectors", flops=2.0 * n * D * D)
+    oT = eng._project(x, transpose_out=True)
+
+    def encode_all():
+        for seg in eng.segs:
+            codesT, _ = E.caq_encode_t(oT[seg["off"]:seg["off"] + seg["len"]], seg["bits"], None)
+            if seg["bits"]:
+                E.caq_pack_t(codesT, seg["bits"], out=seg["packed"])
+    bits_total = sum(ln * b for ln, b in eng.plan)
+    add("SAQ", f"CAQ encode + pack, plan {eng.plan}", timed(encode_all), n, "vectors",
+        bytes_=n * (4 * D + bits_total / 8 + 16 * len(eng.plan)), note="sequential code adjustment = CPU-identical codes")
+    eng.search(q, 10)
+    add("SAQ", "engine estimator search k=10 (code-domain, tcgen05)", timed(lambda: eng.search(q, 10)), n * nq, "codes",
+        flops=2.0 * n * nq * (D - 192))
+    ids = torch.arange(n, device=dev)
+    add("SAQ", "engine reconstruct (decode + one GEMM, bias fused)", timed(lambda: eng.reconstruct(ids)), n, "vectors",
+        flops=2.0 * n * D * D)
+
+
+def run(which=("c1", "c2", "c3", "c4", "saq"), device=None, quick=False):
+    """Run the named config groups; returns the list of rows (and leaves it in `rows`)."""
+    global dev, QUICK
+    QUICK = bool(quick)
+    if device is not None:
+        dev = device
+    rows.clear()
+    fns = {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "saq": saq_engine}
+    for w in which:
+        fns[w]()
+        torch.cuda.empty_cache()
+    return list(rows)
 
 
 if __name__ == "__main__":
-    which = sys.argv[1].split(",") if len(sys.argv) > 1 else ["c1", "c2", "c3", "c4"]
-    out_path = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "r1_configs.json")
-    for w in which:
-        {"c1": c1, "c2": c2, "c3": c3, "c4": c4}[w]()
-        torch.cuda.empty_cache()
+    which = sys.argv[1].split(",") if len(sys.argv) > 1 else ["c1", "c2", "c3", "c4", "saq"]
+    out_path = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "r2_configs.json")
+    run(which)
     os.makedirs(os.path.dirname(out_path), exist_ok=True)
     json.dump({"peaks": peaks, "rows": rows}, open(out_path, "w"), indent=1)
