@@ -441,6 +441,14 @@ int b200vq_saq_plan_dp(const float* variance, int d_pad, float avg_bits, int* se
 int b200vq_caq_encode_t(const float* oT, int64_t n, int64_t ld, int len, const float* c_rot, int bits,
                         int rd_lmt, float adj_eps, uint16_t* codesT, int64_t ldc, float* l2norm,
                         float* rescale, float* error, float* mse, float* cosv, void* stream);
+/* Every segment of the plan in one launch (blockIdx.y = segment, longest first), so the latency-bound per-row
+ * chains of different segments overlap: oT (d_pad, ld) holds all segments stacked (segment s = rows
+ * seg_off[s] .. seg_off[s] + seg_len[s]), already centred; codesT (d_pad, ldc) likewise; the five factor outputs
+ * are (nseg, n) row-major. seg_* are HOST arrays. Same codes and factors as one b200vq_caq_encode_t per segment. */
+int b200vq_caq_encode_t_segments(const float* oT, int64_t n, int64_t ld, int nseg, const int* seg_off,
+                                 const int* seg_len, const int* seg_bits, int rd_lmt, float adj_eps,
+                                 uint16_t* codesT, int64_t ldc, float* l2norm, float* rescale, float* error,
+                                 float* mse, float* cosv, void* stream);
 int b200vq_caq_pack_t(const uint16_t* codesT, int64_t n, int64_t ldc, int len, int bits, uint8_t* packed,
                       void* stream);
 int b200vq_caq_decode(const uint8_t* packed, int64_t n_total, const int64_t* ids, int64_t m, int len,

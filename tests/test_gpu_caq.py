@@ -71,6 +71,21 @@ def test_caq_encode_subtracts_the_rotated_centroid_and_handles_strides(T):
     assert e0.shape == (ln, 0)
 
 
+def test_caq_encode_all_segments_in_one_launch_equals_per_segment_calls(T):
+    """b200vq_caq_encode_t_segments (blockIdx.y = segment) against one b200vq_caq_encode_t per segment."""
+    plan = [(128, 4), (64, 0), (192, 6), (64, 1), (64, 9)]
+    n, d = 777, sum(a for a, _ in plan)
+    oT = T.dev(_rows(n, d, 3).T.copy())
+    codesT, outs = T.eng.caq_encode_t_segments(oT, plan)
+    off = 0
+    for si, (ln, bits) in enumerate(plan):
+        c1, o1 = T.eng.caq_encode_t(oT[off:off + ln], bits)
+        assert T.torch.equal(codesT[off:off + ln], c1), (si, "codes")
+        for a, b in zip(outs, o1):
+            assert T.torch.equal(a[si].view(T.torch.int32), b.view(T.torch.int32)), (si, "factors")
+        off += ln
+
+
 @pytest.mark.parametrize("ln,bits", [(64, 1), (128, 3), (192, 4), (64, 13), (320, 7), (1024, 5)])
 def test_pack_decode_round_trip(T, ln, bits):
     n = 1237

@@ -221,10 +221,10 @@ def saq_engine():
     oT = eng._project(x, transpose_out=True)
 
     def encode_all():
+        codesT, _ = E.caq_encode_t_segments(oT, eng.plan)
         for seg in eng.segs:
-            codesT, _ = E.caq_encode_t(oT[seg["off"]:seg["off"] + seg["len"]], seg["bits"], None)
             if seg["bits"]:
-                E.caq_pack_t(codesT, seg["bits"], out=seg["packed"])
+                E.caq_pack_t(codesT[seg["off"]:seg["off"] + seg["len"]], seg["bits"], out=seg["packed"])
     bits_total = sum(ln * b for ln, b in eng.plan)
     add("SAQ", f"CAQ encode + pack, plan {eng.plan}", timed(encode_all), n, "vectors",
         bytes_=n * (4 * D + bits_total / 8 + 16 * len(eng.plan)), note="sequential code adjustment = CPU-identical codes")

@@ -92,6 +92,7 @@ SIGNATURES = {
     "b200vq_rabitq1_scan_topk_tc": (_i, [_p, _i64, _i, _p, _p, _i, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_saq_plan_dp": (_i, [_p, _i, C.c_float, _p, _p, _p]),
     "b200vq_caq_encode_t": (_i, [_p, _i64, _i64, _i, _p, _i, _i, C.c_float, _p, _i64, _p, _p, _p, _p, _p, _p]),
+    "b200vq_caq_encode_t_segments": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, C.c_float, _p, _i64, _p, _p, _p, _p, _p, _p]),
     "b200vq_caq_pack_t": (_i, [_p, _i64, _i64, _i, _i, _p, _p]),
     "b200vq_caq_decode": (_i, [_p, _i64, _p, _i64, _i, _i, _p, _i, _p, _i64, _p]),
     "b200vq_synth_rows": (_i, [_p, _i64, _i64, _i, _i64, _u64, _p, _i, _p]),

@@ -125,6 +125,26 @@ def caq_encode_t(oT: torch.Tensor, bits: int, c_rot: Optional[torch.Tensor] = No
     return codesT, outs
 
 
+def caq_encode_t_segments(oT: torch.Tensor, plan, rd_lmt: int = 6, adj_eps: float = 1e-8):
+    """Every segment of `plan` ((len, bits) pairs, stacked in oT (d_pad, n), already centred) in one launch.
+    Returns codesT (d_pad, n) uint16-as-int16 and five (nseg, n) fp32 factor arrays."""
+    require_cuda()
+    d_pad, n = oT.shape
+    ns = len(plan)
+    lens = [int(a) for a, _ in plan]
+    offs = list(np.cumsum([0] + lens[:-1]))
+    if sum(lens) != d_pad or (n > 1 and oT.stride(1) != 1):
+        raise ValueError("caq_encode_t_segments: oT must be (sum of segment lengths, n) row-major")
+    codesT = torch.empty((d_pad, n), dtype=torch.int16, device=oT.device)
+    outs = [torch.empty((ns, n), dtype=torch.float32, device=oT.device) for _ in range(5)]
+    arr = lambda v: (C.c_int * ns)(*[int(x) for x in v])
+    check(_lib.load().b200vq_caq_encode_t_segments(oT.data_ptr(), n, oT.stride(0), ns, arr(offs), arr(lens),
+                                                   arr([b for _, b in plan]), rd_lmt, C.c_float(adj_eps),
+                                                   codesT.data_ptr(), n, *[o.data_ptr() for o in outs], _stream()),
+          "caq_encode_t_segments")
+    return codesT, outs
+
+
 def caq_pack_t(codesT: torch.Tensor, bits: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     ln, n = codesT.shape
     if out is None:
@@ -262,13 +282,12 @@ class SaqEngine:
         for s in range(0, n, self.batch_rows):
             e = min(n, s + self.batch_rows)
             oT = self._project(X[s:e], transpose_out=True)          # (d_pad, rows): every segment, centred
-            for seg in self.segs:
-                ln, bits, o0 = seg["len"], seg["bits"], seg["off"]
-                codesT, outs = caq_encode_t(oT[o0:o0 + ln], bits, None, self.rd_lmt, self.adj_eps)
+            codesT, outs = caq_encode_t_segments(oT, self.plan, self.rd_lmt, self.adj_eps)
+            for si, seg in enumerate(self.segs):
                 for key, o in zip(("l2norm", "rescale", "error", "mse", "cos"), outs):
-                    seg[key][s:e] = o
-                if bits:
-                    caq_pack_t(codesT, bits, out=seg["packed"][s:e])
+                    seg[key][s:e] = o[si]
+                if seg["bits"]:
+                    caq_pack_t(codesT[seg["off"]:seg["off"] + seg["len"]], seg["bits"], out=seg["packed"][s:e])
         self._scanner = None
         return self
 

@@ -30,14 +30,12 @@ __device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a,
 __device__ __forceinline__ double dsub(double a, double b) { return __dsub_rn(a, b); }
 
 // One thread = one row of the segment. oT: (len, ld) with element (j, row) at oT[j * ld + row].
-__global__ void __launch_bounds__(128)
-caq_encode_t_kernel(const float* __restrict__ oT, int64_t n, int64_t ld, int len,
-                    const float* __restrict__ c_rot, int bits, int rd_lmt, float adj_eps,
-                    uint16_t* __restrict__ codesT, int64_t ldc, float* __restrict__ l2norm,
-                    float* __restrict__ rescale, float* __restrict__ error, float* __restrict__ mse,
-                    float* __restrict__ cosv) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+__device__ __forceinline__ void
+caq_encode_row(const int64_t i, const float* __restrict__ oT, int64_t ld, int len,
+               const float* __restrict__ c_rot, int bits, int rd_lmt, float adj_eps,
+               uint16_t* __restrict__ codesT, int64_t ldc, float* __restrict__ l2norm,
+               float* __restrict__ rescale, float* __restrict__ error, float* __restrict__ mse,
+               float* __restrict__ cosv) {
     const float* op = oT + i;
     uint16_t* cp = codesT + i;
     auto O = [&](int j) -> float {
@@ -148,6 +146,38 @@ caq_encode_t_kernel(const float* __restrict__ oT, int64_t n, int64_t ld, int len
     error[i] = (float)fac_error;
 }
 
+__global__ void __launch_bounds__(128)
+caq_encode_t_kernel(const float* __restrict__ oT, int64_t n, int64_t ld, int len,
+                    const float* __restrict__ c_rot, int bits, int rd_lmt, float adj_eps,
+                    uint16_t* __restrict__ codesT, int64_t ldc, float* __restrict__ l2norm,
+                    float* __restrict__ rescale, float* __restrict__ error, float* __restrict__ mse,
+                    float* __restrict__ cosv) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    caq_encode_row(i, oT, ld, len, c_rot, bits, rd_lmt, adj_eps, codesT, ldc, l2norm, rescale, error, mse, cosv);
+}
+
+// Every segment of the plan in ONE grid (blockIdx.y = segment, longest first): the rows of a segment are a
+// latency-bound fp64 chain each, so the segments' chains overlap instead of running one launch after another.
+constexpr int CAQ_MAX_SEGS = 64;
+struct CaqSegs {
+    int nseg;
+    int off[CAQ_MAX_SEGS], len[CAQ_MAX_SEGS], bits[CAQ_MAX_SEGS], slot[CAQ_MAX_SEGS];
+};
+__global__ void __launch_bounds__(128)
+caq_encode_t_segments_kernel(const float* __restrict__ oT, int64_t n, int64_t ld, const __grid_constant__ CaqSegs segs,
+                             int rd_lmt, float adj_eps, uint16_t* __restrict__ codesT, int64_t ldc,
+                             float* __restrict__ l2norm, float* __restrict__ rescale, float* __restrict__ error,
+                             float* __restrict__ mse, float* __restrict__ cosv) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int s = blockIdx.y;
+    const int off = segs.off[s], slot = segs.slot[s];
+    const int64_t fo = (int64_t)slot * n;
+    caq_encode_row(i, oT + (int64_t)off * ld, ld, segs.len[s], nullptr, segs.bits[s], rd_lmt, adj_eps,
+                   codesT + (int64_t)off * ldc, ldc, l2norm + fo, rescale + fo, error + fo, mse + fo, cosv + fo);
+}
+
 // codesT (len, ldc) uint16 -> packed (n, row_bytes): MSB-first bit string, `bits` per dimension.
 // Block = 32 rows x a 256-byte slice of the row; reads are coalesced over rows, the tile is
 // turned in shared memory and written out row-contiguous.
@@ -237,6 +267,39 @@ extern "C" int b200vq_caq_encode_t(const float* oT, int64_t n, int64_t ld, int l
     const int block = 128;
     caq_encode_t_kernel<<<(unsigned)((n + block - 1) / block), block, 0, as_stream(stream)>>>(
         oT, n, ld, len, c_rot, bits, rd_lmt, adj_eps, codesT, ldc, l2norm, rescale, error, mse, cosv);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_caq_encode_t_segments(const float* oT, int64_t n, int64_t ld, int nseg, const int* seg_off,
+                                            const int* seg_len, const int* seg_bits, int rd_lmt, float adj_eps,
+                                            uint16_t* codesT, int64_t ldc, float* l2norm, float* rescale,
+                                            float* error, float* mse, float* cosv, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && nseg >= 1 && nseg <= CAQ_MAX_SEGS && seg_off && seg_len && seg_bits && ld >= n && ldc >= n &&
+                     rd_lmt >= 0,
+                 "caq_encode_t_segments: bad args (1 <= nseg <= %d)", CAQ_MAX_SEGS);
+    VQ_CHECK_ARG(n == 0 || (oT && codesT && l2norm && rescale && error && mse && cosv), "caq_encode_t_segments: null pointer");
+    if (n == 0) return B200VQ_OK;
+    CaqSegs segs;
+    segs.nseg = nseg;
+    std::vector<int> order(nseg);
+    for (int s = 0; s < nseg; ++s) {
+        VQ_CHECK_ARG(seg_len[s] > 1 && seg_bits[s] >= 0 && seg_bits[s] <= 13 && seg_off[s] >= 0,
+                     "caq_encode_t_segments: bad segment %d", s);
+        order[s] = s;
+    }
+    // longest chains first: cost ~ len * (1 + sweeps), sweeps only when bits > 0
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+        return (long long)seg_len[a] * (seg_bits[a] ? 8 : 1) > (long long)seg_len[b] * (seg_bits[b] ? 8 : 1);
+    });
+    for (int k = 0; k < nseg; ++k) {
+        const int s = order[k];
+        segs.off[k] = seg_off[s]; segs.len[k] = seg_len[s]; segs.bits[k] = seg_bits[s]; segs.slot[k] = s;
+    }
+    const int block = 128;
+    dim3 grid((unsigned)((n + block - 1) / block), (unsigned)nseg);
+    caq_encode_t_segments_kernel<<<grid, block, 0, as_stream(stream)>>>(oT, n, ld, segs, rd_lmt, adj_eps, codesT, ldc,
+                                                                       l2norm, rescale, error, mse, cosv);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

@@ -321,6 +321,89 @@ __global__ void saq_encode_kernel(const float* __restrict__ x, int64_t n, int64_
     }
 }
 
+// Aligned input rows: four consecutive dimensions per thread with their constants in registers, rows strided over
+// grid.y, four 128-bit loads in flight (the structure of sq_encode_vec_kernel). A thread's four fields are one
+// run of W <= 32 bits at the row-independent bit offset o. The thread OWNS every output byte whose first bit lies
+// in [o, o + W): bytes that lie wholly inside the run come straight from the run (for the usual plans - widths
+// from {0, 2, 4, 6, 8}, segment lengths a multiple of 4 - every run is whole bytes and nothing else happens);
+// an owned byte that extends past the run takes the missing bits from the following dimensions, quantised here
+// with the same arithmetic (any widths, any segment boundaries; rare, and only that one byte per thread).
+__global__ void __launch_bounds__(128)
+saq_encode_vec_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D, const float* __restrict__ vmin,
+                      const float* __restrict__ vmax, const int* __restrict__ dim_bits,
+                      const int* __restrict__ bit_offset, int code_bytes, uint8_t* __restrict__ codes, int word_ok) {
+    const int c4 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c4 * 4 >= D) return;
+    const float4 mn = *reinterpret_cast<const float4*>(vmin + c4 * 4);
+    const float4 mx = *reinterpret_cast<const float4*>(vmax + c4 * 4);
+    const int4 nb = *reinterpret_cast<const int4*>(dim_bits + c4 * 4);
+    const DivConst d0 = make_div(sq_range(mn.x, mx.x)), d1 = make_div(sq_range(mn.y, mx.y)),
+                   d2 = make_div(sq_range(mn.z, mx.z)), d3 = make_div(sq_range(mn.w, mx.w));
+    const float l0 = (float)((1 << nb.x) - 1), l1 = (float)((1 << nb.y) - 1), l2 = (float)((1 << nb.z) - 1),
+                l3 = (float)((1 << nb.w) - 1);
+    const int o = bit_offset[c4 * 4], W = nb.x + nb.y + nb.z + nb.w, end = o + W;
+    const int total_bits = bit_offset[D];
+    const int fo = (o + 7) >> 3;                              // first owned byte
+    const int nfull = W > 0 && (end >> 3) > fo ? (end >> 3) - fo : 0;     // owned bytes wholly inside the run
+    const bool tail = W > 0 && (end & 7) != 0 && (end >> 3) >= fo;        // owned byte end/8 extends past the run
+    const bool pad = total_bits == 0 && c4 == 0;              // empty plan: the single pad byte
+    const bool word = word_ok && nfull == 4 && !tail && (fo & 3) == 0;
+    const bool half_ok = word_ok != 0;                        // rows start on a 4-byte boundary   // 8-bit runs on a word boundary: one 32-bit store
+    auto put = [&](int64_t row, const float4& v) {
+        uint32_t V = 0;
+        if (nb.x) V = sq_quant_c(v.x, mn.x, d0, l0);
+        if (nb.y) V = (V << nb.y) | sq_quant_c(v.y, mn.y, d1, l1);
+        if (nb.z) V = (V << nb.z) | sq_quant_c(v.z, mn.z, d2, l2);
+        if (nb.w) V = (V << nb.w) | sq_quant_c(v.w, mn.w, d3, l3);
+        uint8_t* out = codes + row * (int64_t)code_bytes;
+        if (word) {
+            *reinterpret_cast<uint32_t*>(out + fo) = __byte_perm(V, 0, 0x0123);
+            return;
+        }
+        if (nfull) {
+            // the run's whole bytes, most significant first, as the widest naturally aligned stores
+            const uint32_t B = V >> (end - 8 * (fo + nfull));          // nfull bytes, big-endian in the low bits
+            if (half_ok && nfull == 2 && !(fo & 1)) {
+                *reinterpret_cast<uint16_t*>(out + fo) = (uint16_t)__byte_perm(B, 0, 0x4401);
+            } else if (half_ok && nfull == 3) {
+                if (fo & 1) {
+                    out[fo] = (uint8_t)(B >> 16);
+                    *reinterpret_cast<uint16_t*>(out + fo + 1) = (uint16_t)__byte_perm(B, 0, 0x4401);
+                } else {
+                    *reinterpret_cast<uint16_t*>(out + fo) = (uint16_t)__byte_perm(B, 0, 0x4412);
+                    out[fo + 2] = (uint8_t)B;
+                }
+            } else {
+#pragma unroll 4
+                for (int j = 0; j < nfull; ++j) out[fo + j] = (uint8_t)(B >> (8 * (nfull - 1 - j)));
+            }
+        }
+        if (tail) {
+            const int b = end >> 3, b1 = 8 * b + 8;
+            uint32_t acc = (V << (b1 - end)) & 0xffu;
+            for (int d = c4 * 4 + 4; d < D && bit_offset[d] < b1; ++d) {
+                const int w = dim_bits[d];
+                if (w == 0) continue;
+                const uint32_t q = sq_quant(x[row * ldx + d], vmin[d], sq_range(vmin[d], vmax[d]), (float)((1 << w) - 1));
+                const int shift = b1 - (bit_offset[d] + w);
+                acc |= ((shift >= 0) ? (q << shift) : (q >> (-shift))) & 0xffu;
+            }
+            out[b] = (uint8_t)acc;
+        }
+        if (pad) out[0] = 0;
+    };
+    const int64_t step = gridDim.y;
+    int64_t row = blockIdx.y;
+    for (; row + 3 * step < n; row += 4 * step) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = ld_stream_f4(reinterpret_cast<const float4*>(x + (row + u * step) * ldx) + c4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) put(row + u * step, v[u]);
+    }
+    for (; row < n; row += step) put(row, ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4));
+}
+
 __global__ void saq_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
                                   const float* __restrict__ vmin, const float* __restrict__ vmax,
                                   const int* __restrict__ dim_bits,
@@ -546,6 +629,18 @@ extern "C" int b200vq_saq_encode(const float* x, int64_t n, int64_t ldx, int D, 
                      ldx >= D && code_bytes > 0,
                  "saq_encode: bad args");
     if (n == 0) return B200VQ_OK;
+    if ((D % 4 == 0) && (ldx % 4 == 0) && (((uintptr_t)x | (uintptr_t)vmin | (uintptr_t)vmax | (uintptr_t)dim_bits) & 15) == 0 &&
+        true) {
+        const int word_ok = (code_bytes % 4 == 0) && (((uintptr_t)codes & 3) == 0);
+        int gx = (D / 4 + 127) / 128;
+        int64_t gy = ((int64_t)device_sm_count() * 16 + gx - 1) / gx;
+        if (gy > n) gy = n;
+        if (gy > 65535) gy = 65535;
+        saq_encode_vec_kernel<<<dim3(gx, (unsigned)gy), 128, 0, as_stream(stream)>>>(
+            x, n, ldx, D, vmin, vmax, dim_bits, bit_offset, code_bytes, codes, word_ok);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     saq_encode_kernel<<<sq_grid(n * (int64_t)code_bytes, 256), 256, 0, as_stream(stream)>>>(
         x, n, ldx, D, vmin, vmax, dim_bits, bit_offset, code_bytes, codes);
     VQ_LAUNCH_CHECK();
