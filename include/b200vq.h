@@ -378,6 +378,20 @@ int b200vq_perdim_decode(const uint8_t* codes, int64_t n, int code_size, int D, 
                          const int* bitpos, const double* cb, const int* cb_off, double* yhat, int64_t ldy,
                          void* stream);
 
+/* The same data path with the O(n D^2) PCA projection on the tensor cores (rank_aware_quantization.py:246-250 and
+ * :318-320 project in float64): y (n, ldy) fp32 = (x - mu32) V32 from b200vq_rotate_tc_ex, nrm (n) = |x - mu| from
+ * b200vq_resid_norms_f64; every coordinate within err_rel * nrm + err_abs of one of its mid-points is recomputed as
+ * the exact fp64 dot product sum_k (x_k - mu_k) VT[d][k] (VT = V^T, (D, D) fp64), so the indices are the fp64 ones.
+ * stats (optional) += recomputed coordinates. _decode_f32 gathers fp32 levels (cb fp32) for the inverse GEMM. */
+int b200vq_perdim_encode_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                            const double* mu, const double* VT, const double* nrm, int64_t n, int D,
+                            const double* bounds, const int* bound_off, const uint8_t* bits, const int* bitpos,
+                            int code_size, double err_rel, double err_abs, uint8_t* codes,
+                            unsigned long long* stats, void* stream);
+int b200vq_perdim_decode_f32(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits,
+                             const int* bitpos, const float* cb, const int* cb_off, float* yhat, int64_t ldy,
+                             void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):

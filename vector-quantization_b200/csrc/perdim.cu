@@ -55,6 +55,138 @@ __global__ void __launch_bounds__(256) perdim_encode_kernel(const double* __rest
     }
 }
 
+// The same encode with the O(n D^2) PCA projection on the tensor cores instead of an fp64 GEMM
+// (rank_aware_quantization.py:246-250 projects in float64): y (fp32) = (x - mu32) V32 from rotate_tc.cu with
+// |y - (x - mu) V| <= err_rel |x - mu| + err_abs. A coordinate whose y lies within that bound of one of its
+// codebook's mid-points is recomputed as the exact fp64 dot product sum_k (x_k - mu_k) VT[d][k] by the whole
+// warp (four flagged coordinates per pass), so the level indices are those of the fp64 computation.
+template <typename T>
+__global__ void __launch_bounds__(256, 4)
+perdim_encode_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
+                        const double* __restrict__ mu, const double* __restrict__ VT, const double* __restrict__ nrm,
+                        int64_t n, int D, const double* __restrict__ bounds, const int* __restrict__ bound_off,
+                        const uint8_t* __restrict__ bits, const int* __restrict__ bitpos, int code_size,
+                        double err_rel, double err_abs, uint8_t* __restrict__ codes,
+                        unsigned long long* __restrict__ stats) {
+    extern __shared__ uint32_t pd_smem[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int words = (code_size + 1 + 3) >> 2;
+    const int fwords = (D + 1) >> 1;                                  // flagged list: uint16 per dimension
+    uint32_t* buf = pd_smem + (size_t)w * (words + fwords);
+    uint16_t* flist = reinterpret_cast<uint16_t*>(buf + words);
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long nfix_total = 0;
+    auto level_of = [&](const double* bd, int b, double v) {
+        int lo = 0, hi = (1 << b) - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (bd[mid] < v) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+    };
+    auto put = [&](int d, int b, int lo) {
+        const int pos = bitpos[d], byte = pos >> 3;
+        const uint32_t v16 = (uint32_t)lo << (16 - b - (pos & 7));
+        const uint32_t hi8 = v16 >> 8, lo8 = v16 & 0xFFu;
+        if (hi8) atomicOr(buf + (byte >> 2), hi8 << (8 * (byte & 3)));
+        if (lo8) atomicOr(buf + ((byte + 1) >> 2), lo8 << (8 * ((byte + 1) & 3)));
+    };
+    for (int64_t row = wid; row < n; row += nw) {
+        for (int i = lane; i < words; i += 32) buf[i] = 0u;
+        __syncwarp();
+        const float* yr = y + row * ldy;
+        const double eps = err_rel * nrm[row] + err_abs;
+        int nflag = 0;
+        for (int d0 = 0; d0 < D; d0 += 32) {
+            const int d = d0 + lane;
+            bool flag = false;
+            if (d < D) {
+                const int b = bits[d];
+                if (b) {
+                    const double v = (double)yr[d];
+                    const double* bd = bounds + bound_off[d];
+                    const int lo = level_of(bd, b, v), L = 1 << b;
+                    flag = (lo > 0 && v - bd[lo - 1] < eps) || (lo < L - 1 && bd[lo] - v < eps);
+                    if (!flag) put(d, b, lo);
+                }
+            }
+            const unsigned m = __ballot_sync(FULL_MASK, flag);
+            if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
+            nflag += __popc(m);
+        }
+        __syncwarp();
+        const T* xr = x + row * ldx;
+        for (int f0 = 0; f0 < nflag; f0 += 4) {
+            int dd[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) dd[e] = flist[min(f0 + e, nflag - 1)];
+            const double* p0 = VT + (int64_t)dd[0] * D;
+            const double* p1 = VT + (int64_t)dd[1] * D;
+            const double* p2 = VT + (int64_t)dd[2] * D;
+            const double* p3 = VT + (int64_t)dd[3] * D;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+            for (int k = lane; k < D; k += 32) {
+                const double rk = (double)xr[k] - mu[k];
+                a0 = fma(rk, __ldg(p0 + k), a0);
+                a1 = fma(rk, __ldg(p1 + k), a1);
+                a2 = fma(rk, __ldg(p2 + k), a2);
+                a3 = fma(rk, __ldg(p3 + k), a3);
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                a0 += __shfl_xor_sync(FULL_MASK, a0, o);
+                a1 += __shfl_xor_sync(FULL_MASK, a1, o);
+                a2 += __shfl_xor_sync(FULL_MASK, a2, o);
+                a3 += __shfl_xor_sync(FULL_MASK, a3, o);
+            }
+            if (lane == 0) {
+                const double av[4] = {a0, a1, a2, a3};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (f0 + e >= nflag) break;
+                    const int d = dd[e], b = bits[d];
+                    put(d, b, level_of(bounds + bound_off[d], b, av[e]));
+                }
+            }
+        }
+        nfix_total += (unsigned long long)nflag;
+        __syncwarp();
+        uint8_t* o = codes + row * (int64_t)code_size;
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(buf);
+        for (int i = lane; i < code_size; i += 32) o[i] = src[i];
+        __syncwarp();
+    }
+    if (stats && lane == 0 && nfix_total) atomicAdd(stats, nfix_total);
+}
+
+// decode to fp32 (the operand of the inverse projection GEMM)
+__global__ void __launch_bounds__(256) perdim_decode_f32_kernel(const uint8_t* __restrict__ codes, int64_t n, int code_size,
+                                                                int D, const uint8_t* __restrict__ bits,
+                                                                const int* __restrict__ bitpos,
+                                                                const float* __restrict__ cb,
+                                                                const int* __restrict__ cb_off, float* __restrict__ yhat,
+                                                                int64_t ldy) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = wid; row < n; row += nw) {
+        const uint8_t* c = codes + row * (int64_t)code_size;
+        float* o = yhat + row * ldy;
+        for (int d = lane; d < D; d += 32) {
+            const int b = bits[d];
+            float r = 0.f;
+            if (b) {
+                const int pos = bitpos[d], byte = pos >> 3;
+                const uint32_t v16 = ((uint32_t)c[byte] << 8) | (byte + 1 < code_size ? (uint32_t)c[byte + 1] : 0u);
+                const uint32_t idx = (v16 >> (16 - b - (pos & 7))) & ((1u << b) - 1u);
+                r = cb[cb_off[d] + idx];
+            }
+            o[d] = r;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) perdim_decode_kernel(const uint8_t* __restrict__ codes, int64_t n, int code_size,
                                                             int D, const uint8_t* __restrict__ bits,
                                                             const int* __restrict__ bitpos,
@@ -115,6 +247,47 @@ extern "C" int b200vq_perdim_decode(const uint8_t* codes, int64_t n, int code_si
     VQ_CHECK_ARG(bits && bitpos && cb && cb_off && yhat && (codes || code_size == 0), "perdim_decode: null pointer");
     perdim_decode_kernel<<<perdim_grid(n), 256, 0, as_stream(stream)>>>(codes, n, code_size, D, bits, bitpos, cb, cb_off,
                                                                       yhat, ldy);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_perdim_encode_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                                       const double* mu, const double* VT, const double* nrm, int64_t n, int D,
+                                       const double* bounds, const int* bound_off, const uint8_t* bits,
+                                       const int* bitpos, int code_size, double err_rel, double err_abs, uint8_t* codes,
+                                       unsigned long long* stats, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && D > 0 && D < 65536 && ldy >= D && ldx >= D && code_size >= 0 && err_rel >= 0.0 && err_abs >= 0.0,
+                 "perdim_encode_tc: bad shape");
+    if (n == 0 || code_size == 0) return B200VQ_OK;
+    VQ_CHECK_ARG(y && x && mu && VT && nrm && bounds && bound_off && bits && bitpos && codes, "perdim_encode_tc: null pointer");
+    const size_t smem = (size_t)8 * (((code_size + 4) / 4) + ((D + 1) / 2)) * 4;
+    VQ_CHECK_ARG(smem <= 200 * 1024, "perdim_encode_tc: row too large");
+    int64_t g = (n + 7) / 8;
+    const int64_t cap = (int64_t)device_sm_count() * 8;
+    if (g > cap) g = cap;
+    if (x_is_f64) {
+        VQ_CUDA(cudaFuncSetAttribute(perdim_encode_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        perdim_encode_tc_kernel<double><<<(int)g, 256, smem, as_stream(stream)>>>(
+            y, ldy, reinterpret_cast<const double*>(x), ldx, mu, VT, nrm, n, D, bounds, bound_off, bits, bitpos, code_size,
+            err_rel, err_abs, codes, stats);
+    } else {
+        VQ_CUDA(cudaFuncSetAttribute(perdim_encode_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        perdim_encode_tc_kernel<float><<<(int)g, 256, smem, as_stream(stream)>>>(
+            y, ldy, reinterpret_cast<const float*>(x), ldx, mu, VT, nrm, n, D, bounds, bound_off, bits, bitpos, code_size,
+            err_rel, err_abs, codes, stats);
+    }
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_perdim_decode_f32(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits,
+                                        const int* bitpos, const float* cb, const int* cb_off, float* yhat, int64_t ldy,
+                                        void* stream) {
+    VQ_CHECK_ARG(n >= 0 && D > 0 && ldy >= D && code_size >= 0, "perdim_decode_f32: bad shape");
+    if (n == 0) return B200VQ_OK;
+    VQ_CHECK_ARG(bits && bitpos && cb && cb_off && yhat && (codes || code_size == 0), "perdim_decode_f32: null pointer");
+    perdim_decode_f32_kernel<<<perdim_grid(n), 256, 0, as_stream(stream)>>>(codes, n, code_size, D, bits, bitpos, cb, cb_off,
+                                                                          yhat, ldy);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

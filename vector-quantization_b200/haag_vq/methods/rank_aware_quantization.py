@@ -6,9 +6,10 @@ var_d^(1+alpha) * (Dg[b] - Dg[b+1]); codes are per-row bit strings (``packing="d
 byte layouts (``packing="ffd"``). Same constructor, public state (mu, V, var, bits, cb, D, code_size) and
 errors as the reference.
 
-Device work: mean / covariance (fp64 accumulation) and the eigendecomposition in ``fit``; the fp64
-projection GEMMs; nearest-level search + packing (``b200vq_perdim_encode``) and the inverse gather
-(``b200vq_perdim_decode``). The 1-D Lloyd-Max tables for N(0,1) and the greedy allocation are host
+Device work: mean / covariance (fp64 accumulation) and the eigendecomposition in ``fit`` (train time); the
+projection GEMMs on the tensor cores (``b200vq_rotate_tc_ex``, fp32-accurate) with the level search finished in
+exact fp64 wherever the GEMM's error bound reaches a codebook mid-point (``b200vq_perdim_encode_tc``), and the
+inverse gather + GEMM (``b200vq_perdim_decode_f32``). The 1-D Lloyd-Max tables for N(0,1) and the greedy allocation are host
 training logic (a few thousand scalar steps). ``codebook="gaussian"`` only: the data-fit codebooks
 ('lloyd', 'exact') come from the SAQ engine's C++ builders (external/saq), which are not built here.
 Given the same trained state, codes are identical to the reference's wherever a projected coordinate is
@@ -160,6 +161,7 @@ class RankAwareQuantizer(BaseQuantizer):
     # -------------------------------------------------------------- device tables
     def _tables(self):
         if self._dev is None:
+            from b200vq import ops, ops_sq
             D = self.D
             bits = self.bits
             if self.packing == "ffd":
@@ -170,32 +172,65 @@ class RankAwareQuantizer(BaseQuantizer):
             boff = np.concatenate(([0], np.cumsum([len(x) for x in bounds])))[:-1]
             cboff = np.concatenate(([0], np.cumsum([len(c) for c in self.cb])))[:-1]
             t = lambda a, dt: host.to_device(np.ascontiguousarray(a, dtype=dt))
+            Dp = (D + 31) // 32 * 32              # the GEMM wants K % 32 == 0: zero columns are exact
+            V32 = self.V.astype(np.float32)
+            Wf = np.zeros((D, Dp), np.float32)    # y = (x - mu) V: W[d][k] = V[k][d]
+            Wf[:, :D] = V32.T
+            Wr = np.zeros((D, Dp), np.float32)    # x^ = y^ V^T: W[j][d] = V[j][d]
+            Wr[:, :D] = V32
+            mu32 = np.zeros(Dp, np.float32)
+            mu32[:D] = self.mu.astype(np.float32)
+            err_rel, err_abs = ops_sq.erabitq_rotation_error_bound(Dp, float(np.linalg.norm(self.mu)))
             self._dev = {
-                "mu": t(self.mu, np.float64), "V": t(self.V, np.float64),
+                "mu": t(self.mu, np.float64), "VT": t(self.V.T, np.float64),
                 "bits": t(bits, np.uint8), "pos": t(pos, np.int32),
                 "bounds": t(np.concatenate(bounds + [np.zeros(1)]), np.float64), "boff": t(boff, np.int32),
-                "cb": t(np.concatenate(list(self.cb)), np.float64), "cboff": t(cboff, np.int32),
+                "cb32": t(np.concatenate(list(self.cb)), np.float32), "cboff": t(cboff, np.int32),
+                "fwd": ops.RotationTC(host.to_device(Wf)), "rev": ops.RotationTC(host.to_device(Wr)),
+                "mu32": host.to_device(mu32), "mu32d": host.to_device(mu32[:D].copy()), "Dp": Dp,
+                "err_rel": err_rel, "err_abs": err_abs,
+                "nfix": torch.zeros(1, dtype=torch.int64, device=host.device()),
             }
         return self._dev
 
+    @staticmethod
+    def _pad_cols(xb: torch.Tensor, Dp: int) -> torch.Tensor:
+        if xb.shape[1] == Dp and xb.stride(0) % 4 == 0 and xb.data_ptr() % 16 == 0:
+            return xb
+        xp = torch.zeros((xb.shape[0], Dp), dtype=torch.float32, device=xb.device)
+        xp[:, :xb.shape[1]] = xb
+        return xp
+
     # ------------------------------------------------------------- compress
     def compress(self, X: np.ndarray) -> np.ndarray:
+        """Projection on the tensor cores (fp32-accurate 3xTF32 GEMM, mean subtraction fused) + nearest-level search
+        with an exact fp64 re-evaluation of every coordinate inside the GEMM's error bound of a codebook mid-point
+        (b200vq_perdim_encode_tc): the level indices are those of the reference's float64 projection."""
         if self.V is None:
             raise RuntimeError("Quantizer must be fit before compress().")
-        X = np.asarray(X)
+        from b200vq import ops_sq
+        X = np.ascontiguousarray(X)
         N, D = X.shape
         if D != self.D:
             raise ValueError(f"compress() got D={D}, but fit() saw D={self.D}")
+        if X.dtype not in (np.float32, np.float64):
+            X = X.astype(np.float64)
         T = self._tables()
         out = torch.empty((N, self.code_size), dtype=torch.uint8, device=host.device())
-        rows = max(1, min(max(N, 1), (1 << 28) // max(1, 8 * D)))
         lib = _lib.load()
-        for s in range(0, N, rows):
-            e = min(N, s + rows)
-            Y = (host.to_device(np.ascontiguousarray(X[s:e])).to(torch.float64) - T["mu"]) @ T["V"]
-            check(lib.b200vq_perdim_encode(Y.data_ptr(), e - s, Y.stride(0), D, T["bounds"].data_ptr(),
-                                           T["boff"].data_ptr(), T["bits"].data_ptr(), T["pos"].data_ptr(),
-                                           self.code_size, out[s:e].data_ptr(), _stream()), "perdim_encode")
+
+        def f(xb, s, e):
+            nrm = ops_sq.resid_norms_f64(xb, T["mu"])
+            x32 = xb if xb.dtype == torch.float32 else xb.to(torch.float32)
+            y = T["fwd"](self._pad_cols(x32, T["Dp"]), x_sub=T["mu32"])
+            rel = T["err_rel"] + (2.0 ** -24 if xb.dtype == torch.float64 else 0.0)
+            check(lib.b200vq_perdim_encode_tc(y.data_ptr(), y.stride(0), xb.data_ptr(), int(xb.dtype == torch.float64),
+                                              xb.stride(0), T["mu"].data_ptr(), T["VT"].data_ptr(), nrm.data_ptr(), e - s, D,
+                                              T["bounds"].data_ptr(), T["boff"].data_ptr(), T["bits"].data_ptr(),
+                                              T["pos"].data_ptr(), self.code_size, rel, 2.0 * T["err_abs"],
+                                              out[s:e].data_ptr(), T["nfix"].data_ptr(), _stream()), "perdim_encode_tc")
+        if N:
+            host.stream_rows(X, f, batch_rows=host.batch_rows_for(D * 4 * 4, N))
         return host.to_host(out)
 
     # ----------------------------------------------------------- decompress
@@ -211,11 +246,11 @@ class RankAwareQuantizer(BaseQuantizer):
         for s in range(0, N, rows):
             e = min(N, s + rows)
             c = host.to_device(codes[s:e])
-            Yh = torch.empty((e - s, D), dtype=torch.float64, device=c.device)
-            check(lib.b200vq_perdim_decode(c.data_ptr(), e - s, self.code_size, D, T["bits"].data_ptr(),
-                                           T["pos"].data_ptr(), T["cb"].data_ptr(), T["cboff"].data_ptr(),
-                                           Yh.data_ptr(), Yh.stride(0), _stream()), "perdim_decode")
-            out[s:e] = host.to_host((Yh @ T["V"].t() + T["mu"]).to(torch.float32))
+            Yh = torch.zeros((e - s, T["Dp"]), dtype=torch.float32, device=c.device)
+            check(lib.b200vq_perdim_decode_f32(c.data_ptr(), e - s, self.code_size, D, T["bits"].data_ptr(),
+                                               T["pos"].data_ptr(), T["cb32"].data_ptr(), T["cboff"].data_ptr(),
+                                               Yh.data_ptr(), Yh.stride(0), _stream()), "perdim_decode_f32")
+            out[s:e] = host.to_host(T["rev"](Yh, col_bias=T["mu32d"]))       # y^ V^T + mu on the tensor cores
         return out
 
     def get_compression_ratio(self, X: np.ndarray) -> float:
