@@ -392,6 +392,21 @@ int b200vq_perdim_decode_f32(const uint8_t* codes, int64_t n, int code_size, int
                              const int* bitpos, const float* cb, const int* cb_off, float* yhat, int64_t ldy,
                              void* stream);
 
+/* Data-fit per-dimension codebooks: 1-D k-means (k-means++ seeding with std::mt19937_64(seed), Lloyd over the sorted
+ * column with prefix sums, one empty-cell repair per iteration) = the SAQ engine's build_codebook_lloyd
+ * (external/saq/src/preprocessing/codebook_builder.cpp:341-420 with :146-188 and :64-128; LloydOpts defaults
+ * max_iters 50, tol 1e-6, seed 0), called per dimension by rank_aware_quantization.py:189-214 (codebook="lloyd") and
+ * by quantization_plan.cpp:21-51 (MSE table of the greedy allocator). sorted_cols (D, ld) fp32: row d = the sorted
+ * sample of dimension d (n values); ps / psq (D, n + 1) fp64: exclusive prefix sums of the values / their squares.
+ * dim_bits (D, device, optional): bit-rate b_d in [0, 8] of every dimension (NULL: fixed_bits for all). Outputs:
+ * centroids (D, 256) fp32, the first sizes[d] entries valid (2^b, or the distinct values when there are fewer
+ * than 2^b); costs (D) = MSE on the sample. scratch: b200vq_codebook_lloyd_scratch_bytes(n, D). */
+size_t b200vq_codebook_lloyd_scratch_bytes(int64_t n, int D);
+int b200vq_codebook_lloyd(const float* sorted_cols, int64_t ld, const double* ps, const double* psq, int64_t n,
+                          int D, const int* dim_bits, int fixed_bits, unsigned long long seed, int max_iters,
+                          float tol, float* centroids, int* sizes, float* costs, void* scratch,
+                          size_t scratch_bytes, void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):

@@ -47,7 +47,10 @@ def test_codes_match_reference_given_shared_state(golden_dir):
                         near |= np.min(np.abs(mid - Y[r, d])) <= 1e-12 * max(1.0, abs(Y[r, d]))
                 assert near
         rec = q.decompress(ref)
-        assert rec.dtype == np.float32 and np.allclose(rec, g[f"rec_{packing}"], rtol=2e-6, atol=1e-6)
+        # the inverse projection is the fp32-accurate tensor-core GEMM (the reference: float64, then a cast):
+        # reconstructions agree to fp32 rounding of the row, far inside north_star's 1e-4
+        ref_rec = g[f"rec_{packing}"]
+        assert rec.dtype == np.float32 and np.abs(rec - ref_rec).max() <= 2e-6 * np.abs(ref_rec).max()
 
 
 def test_fit_and_reference_properties():
@@ -76,7 +79,7 @@ def test_fit_and_reference_properties():
     with pytest.raises(ValueError):
         q.compress(X[:, :10])
     with pytest.raises(NotImplementedError):
-        _Q(avg_bits=4, codebook="lloyd")
+        _Q(avg_bits=4, codebook="exact")
 
 
 def test_ffd_is_lossless_relayout():

@@ -3,11 +3,12 @@
 Mirrors src/haag_vq/benchmarks/method_registry_saq.py:17-74 for the methods on
 the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)) and
 ``saq_paper`` -> SaqEngineAdapter(CAQ, DP allocation) (SURVEY.md §8 rows a9-a11,
-a16) and ``lvq`` -> LVQQuantizer(num_bits=round(bpd)) (reference :49-52). The other
-names of SAQ_METHODS (ours*, rankaware*, perdim_mse*) need the SAQ engine's greedy allocator / data-fit
-codebook builders (RankAwareQuantizer itself is built with codebook="gaussian", haag_vq/methods/
-rank_aware_quantization.py); they are the studies SURVEY.md §8(f) ranks as
-"next"; they raise NotImplementedError here instead of silently falling back.
+a16), ``lvq`` -> LVQQuantizer(num_bits=round(bpd)) (reference :49-52), and the per-dimension family
+``rankaware`` (the proposed method: var^0.5-weighted greedy) / ``perdim_mse`` (alpha = 0) ->
+RankAwareQuantizer(packing="ffd", codebook="lloyd") (reference :58-65), whose data-fit codebooks come from
+b200vq_codebook_lloyd. Still not built: ``ours`` / ``ours_exact`` (engine-side greedy allocation + codebook-aware
+CAQ encoder) and the ``*_exact`` variants (optimal-DP codebooks); they raise NotImplementedError instead of
+silently falling back.
 """
 from __future__ import annotations
 
@@ -31,6 +32,11 @@ def build_saq_quantizer(method: str, bpd: float, D: int):
         from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
         from haag_vq.methods.lvq_quantization import LVQQuantizer
         return FaissQuantizerAdapter(LVQQuantizer(num_bits=b))
+    if method in ("rankaware", "perdim_mse"):
+        from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter
+        from haag_vq.methods.rank_aware_quantization import RankAwareQuantizer
+        return FaissQuantizerAdapter(RankAwareQuantizer(avg_bits=bpd, alpha=0.5 if method == "rankaware" else 0.0,
+                                                        packing="ffd", codebook="lloyd"))
     if method in SAQ_METHODS:
         raise NotImplementedError(
             f"method {method!r} is not built on the B200 path yet (SURVEY.md §8f); no fallback is provided")

@@ -66,10 +66,10 @@ class RankAwareQuantizer(BaseQuantizer):
             raise ValueError("packing must be 'dense' or 'ffd'")
         if codebook not in ("gaussian", "lloyd", "exact"):
             raise ValueError("codebook must be 'gaussian', 'lloyd', or 'exact'")
-        if codebook != "gaussian":
+        if codebook == "exact":
             raise NotImplementedError(
-                f"codebook={codebook!r} needs the SAQ engine's codebook builders, which are not built on the "
-                "B200 path yet (SURVEY.md 8f); no fallback is provided")
+                "codebook='exact' (the engine's optimal-DP 1-D k-means, build_codebook_exact) is not built on the "
+                "B200 path; 'lloyd' (the method's production codebook) and 'gaussian' are. No fallback is provided")
         self.codebook = codebook
         self.avg_bits = float(avg_bits)
         self.alpha = float(alpha)
@@ -118,8 +118,48 @@ class RankAwareQuantizer(BaseQuantizer):
         self._Dg = Dg
         self.bits = self._allocate(self.var, Dg, int(round(self.avg_bits * D)))
         scale = np.sqrt(self.var)
-        self.cb = [self._levels[int(b)] * scale[d] for d, b in enumerate(self.bits)]
+        if self.codebook == "gaussian":
+            self.cb = [self._levels[int(b)] * scale[d] for d, b in enumerate(self.bits)]
+        else:
+            self.cb = self._fit_lloyd_codebooks(X)
         self._finish_layout()
+
+    CB_SAMPLE = 200_000
+
+    def _fit_lloyd_codebooks(self, X: np.ndarray):
+        """Per-dimension data-fit codebooks (rank_aware_quantization.py:189-214): the engine's build_codebook_lloyd on
+        the projected column of a fixed ~200k-row sample at the dimension's own bit-rate. Projection on the tensor
+        cores, then one CTA per dimension (b200vq_codebook_lloyd: k-means++ seeding with mt19937_64(0), Lloyd over
+        the sorted column). The codebooks are trained state (the fp32-accurate projection differs from the
+        reference's float64-then-cast in the last bit of some sample values)."""
+        from b200vq import ops, ops_sq
+        N, D = X.shape
+        if N > self.CB_SAMPLE:
+            idx = np.sort(np.random.default_rng(0).choice(N, self.CB_SAMPLE, replace=False))
+            Xs = np.ascontiguousarray(X[idx], dtype=np.float32)
+        else:
+            Xs = np.ascontiguousarray(X, dtype=np.float32)
+        Dp = (D + 31) // 32 * 32
+        Wf = np.zeros((D, Dp), np.float32)
+        Wf[:, :D] = self.V.astype(np.float32).T
+        mu32 = np.zeros(Dp, np.float32)
+        mu32[:D] = self.mu.astype(np.float32)
+        fwd = ops.RotationTC(host.to_device(Wf))
+        xd = self._pad_cols(host.to_device(Xs), Dp)
+        yT = fwd(xd, x_sub=host.to_device(mu32), transpose_out=True).contiguous()      # (D, n): one sample column per row
+        bits = host.to_device(self.bits.astype(np.int32))
+        cen, sizes, _ = ops_sq.codebook_lloyd(yT, bits, seed=0)
+        cen_h, sizes_h = host.to_host(cen), host.to_host(sizes)
+        cb = []
+        for d, b in enumerate(self.bits):
+            if int(b) == 0:
+                cb.append(np.array([0.0], dtype=np.float64))
+                continue
+            c = np.sort(cen_h[d, :sizes_h[d]].astype(np.float64))
+            if c.size < (1 << int(b)):        # fewer distinct sample values than levels: pad like the reference's encoders need
+                c = np.concatenate([c, np.full((1 << int(b)) - c.size, c[-1])])
+            cb.append(c)
+        return cb
 
     def _allocate(self, var: np.ndarray, Dg: np.ndarray, total: int) -> np.ndarray:
         """Greedy of rank_aware_quantization.py:148-181: one bit at a time to the dimension with the largest
