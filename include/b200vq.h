@@ -85,6 +85,12 @@ int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const float* cen
 int b200vq_pq_decode(const uint8_t* codes, int64_t n, const float* centroids, int M, int ksub,
                      int dsub, float* out, int64_t ldo, void* stream);
 
+/* Sub-byte code layout of faiss ProductQuantizer for nbits != 8 (the reference passes any B to faiss,
+ * product_quantization.py:67-73; faiss PQEncoderGeneric / PQDecoderGeneric): the M indices of a row as a
+ * little-endian bit stream of ceil(M nbits / 8) bytes. codes (n, M) uint8 <-> packed (n, ceil(M nbits / 8)). */
+int b200vq_pq_pack_bits(const uint8_t* codes, int64_t n, int M, int nbits, uint8_t* packed, void* stream);
+int b200vq_pq_unpack_bits(const uint8_t* packed, int64_t n, int M, int nbits, uint8_t* codes, void* stream);
+
 /* Decode selected rows: out[j] = decode(codes[ids[j]]) — the adapter's
  * reconstruct(ids) (src/haag_vq/benchmarks/quantizer_adapters.py:48-54). */
 int b200vq_pq_decode_ids(const uint8_t* codes, const int64_t* ids, int64_t n_ids,
@@ -398,13 +404,14 @@ int b200vq_perdim_decode_f32(const uint8_t* codes, int64_t n, int code_size, int
  * max_iters 50, tol 1e-6, seed 0), called per dimension by rank_aware_quantization.py:189-214 (codebook="lloyd") and
  * by quantization_plan.cpp:21-51 (MSE table of the greedy allocator). sorted_cols (D, ld) fp32: row d = the sorted
  * sample of dimension d (n values); ps / psq (D, n + 1) fp64: exclusive prefix sums of the values / their squares.
- * dim_bits (D, device, optional): bit-rate b_d in [0, 8] of every dimension (NULL: fixed_bits for all). Outputs:
- * centroids (D, 256) fp32, the first sizes[d] entries valid (2^b, or the distinct values when there are fewer
- * than 2^b); costs (D) = MSE on the sample. scratch: b200vq_codebook_lloyd_scratch_bytes(n, D). */
+ * dim_bits (D, device, optional): bit-rate b_d in [0, max_bits] of every dimension (NULL: fixed_bits for all),
+ * max_bits <= 13 (the engine's kMaxQuantBit). Outputs: centroids (D, 2^max_bits) fp32, the first sizes[d] entries
+ * valid (2^b, or the distinct values when there are fewer than 2^b); costs (D) = MSE on the sample.
+ * scratch: b200vq_codebook_lloyd_scratch_bytes(n, D). */
 size_t b200vq_codebook_lloyd_scratch_bytes(int64_t n, int D);
 int b200vq_codebook_lloyd(const float* sorted_cols, int64_t ld, const double* ps, const double* psq, int64_t n,
-                          int D, const int* dim_bits, int fixed_bits, unsigned long long seed, int max_iters,
-                          float tol, float* centroids, int* sizes, float* costs, void* scratch,
+                          int D, const int* dim_bits, int fixed_bits, int max_bits, unsigned long long seed,
+                          int max_iters, float tol, float* centroids, int* sizes, float* costs, void* scratch,
                           size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------- 1-bit RaBitQ ---

@@ -254,4 +254,4 @@ def test_saq_engine_adapter_contract(T):
         assert q.code_bytes() == int(1200 * 128 * bpd / 8.0) + 4 * 1200
     assert out[8] < out[2]
     with pytest.raises(NotImplementedError):
-        build_quantizer("ours", 4, 128)
+        build_quantizer("rankaware_exact", 4, 128)

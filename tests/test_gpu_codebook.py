@@ -97,3 +97,36 @@ def test_rank_aware_lloyd_codebooks_and_registry():
         assert R.shape == (100, d) and float(np.mean((R - X[:100]) ** 2)) < float(np.mean(X[:100] ** 2))
     with pytest.raises(NotImplementedError):
         build_quantizer("rankaware_exact", 3.0, d)
+
+
+def test_engine_greedy_allocator_and_ours_registry_name():
+    """Method ``ours``: the engine with the greedy allocator on the per-dimension Lloyd MSE table (bit-rates 0..13).
+    The device table against the pinned oracle builder on a few dimensions, the plan against the oracle's
+    restatement of BitAllocatorGreedy on the SAME table, and the adapter contract."""
+    import torch
+    from b200vq import saq_engine as E
+    from haag_vq.benchmarks.method_registry import build_quantizer
+    rng = np.random.default_rng(3)
+    n, D = 3000, 128
+    X = (rng.standard_normal((n, D)) * np.linspace(3.0, 0.05, D)).astype(np.float32)
+    eng = E.SaqEngine(3.0, allocator="greedy").fit(torch.from_numpy(X).cuda())
+    tab = eng.mse_table
+    assert tab.shape == (128, 14) and np.all(np.diff(tab, axis=1) <= 1e-6 * tab[:, :1] + 1e-12)
+    Y = ((X - eng.mean.cpu().numpy()) @ eng.rot.cpu().numpy()).astype(np.float32)
+    for d in (0, 5, 60):
+        oc, _ = ocb.build_codebook_lloyd(Y[:, d], 13)
+        # the device projects with the 3xTF32 GEMM: sample values differ from numpy's in the last bit
+        assert np.allclose(tab[d, :9], oc[:9], rtol=2e-3, atol=1e-9), d
+        # at hundreds of centroids on 3000 points a last-bit change of a sample value moves the local optimum
+        assert np.allclose(tab[d, 9:12], oc[9:12], rtol=0.25, atol=1e-9), d
+    plan = ocb.allocate_greedy(tab, 64, 13, int(3.0 * 128) + 64, 64)
+    assert eng.plan == [(int(a), int(b)) for a, b in plan]
+    assert sum(a * b + (64 if b else 0) for a, b in eng.plan) <= int(3.0 * 128) + 64
+    R = eng.reconstruct(torch.arange(n, device="cuda")).cpu().numpy()
+    dp = E.SaqEngine(3.0).fit(torch.from_numpy(X).cuda())
+    Rd = dp.reconstruct(torch.arange(n, device="cuda")).cpu().numpy()
+    assert float(((R - X) ** 2).mean()) < 1.5 * float(((Rd - X) ** 2).mean())
+    for name in ("ours", "ours_exact"):
+        q = build_quantizer(name, 3.0, D)
+        q.fit(X)
+        assert q.reconstruct(np.arange(10)).shape == (10, D)

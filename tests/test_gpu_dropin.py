@@ -43,7 +43,7 @@ def test_registry_errors_and_constants():
     with pytest.raises(ValueError):
         mr.build_quantizer("nope", 4.0, 48)
     with pytest.raises(NotImplementedError):
-        mr.build_quantizer("ours", 4.0, 48)          # greedy allocation + derived codebooks: SURVEY §8f
+        mr.build_quantizer("perdim_mse_exact", 4.0, 48)          # optimal-DP codebooks: not built
     from haag_vq.benchmarks.quantizer_adapters import SaqEngineAdapter
     assert isinstance(mr.build_quantizer("saq_paper", 4.0, 48), SaqEngineAdapter)
 
@@ -199,3 +199,35 @@ def test_scalar_and_saq_quantizer_surface():
     s.fit(X)
     # 132 bits round up to 17 bytes per row: ratio = 4*33/17
     assert int(s.bit_offset[-1]) <= 33 * 4 and s.get_compression_ratio(X) >= 4 * 33 / 17 - 1e-9
+
+
+@pytest.mark.parametrize("B,M", [(4, 8), (6, 5), (1, 16), (7, 3)])
+def test_sub_byte_pq_codes_use_the_faiss_bit_stream_layout(B, M):
+    """ProductQuantizer(M, B < 8): faiss packs the M indices as a little-endian bit stream of ceil(M B / 8) bytes
+    (the reference forwards any B: product_quantization.py:67-73); indices, decode and search agree with the oracle."""
+    from haag_vq.methods.product_quantization import ProductQuantizer
+    from haag_vq.methods.search.flat_quantized_index import FlatQuantizedIndex
+    rng = np.random.default_rng(B * 10 + M)
+    D = M * 6
+    X = rng.standard_normal((1500, D)).astype(np.float32)
+    pq = ProductQuantizer(M=M, B=B)
+    pq.fit(X)
+    assert pq.num_clusters == 1 << B and pq.pq.code_size == (M * B + 7) // 8
+    codes = pq.compress(X)
+    assert codes.shape == (1500, (M * B + 7) // 8) and codes.dtype == np.uint8
+    C = pq.pq.centroids.reshape(M, 1 << B, D // M)
+    ref, d1, d2 = opq.pq_assign(X, C, return_gap=True)
+    # unpack the little-endian bit stream on the host: index m = bits [m B, (m + 1) B)
+    bits = np.unpackbits(codes, axis=1, bitorder="little")[:, :M * B].reshape(1500, M, B)
+    idx = (bits.astype(np.int64) << np.arange(B)).sum(-1)
+    bad = (idx != ref) & ((d2 - d1) > 1e-6 * np.maximum(d1, 1e-30))
+    assert not bad.any()
+    assert np.array_equal(pq.decompress(codes), opq.pq_decode(idx.astype(np.uint8), C))
+    assert pq.get_compression_ratio(X) == pytest.approx(D * 4 / ((M * B + 7) // 8))
+    index = FlatQuantizedIndex(ProductQuantizer(M=M, B=B))
+    index.fit(X, metric="l2")
+    ids, d = index.search_with_scores(X[:5], 3)
+    assert ids.shape == (5, 3) and np.all(np.diff(d, axis=1) >= 0)
+    Xhat = index._quantizer.decompress(index._codes)
+    true = ((X[:5, None, :] - Xhat[None]) ** 2).sum(-1)
+    assert np.allclose(d[:, 0], true.min(1), rtol=1e-4, atol=1e-5)

@@ -35,6 +35,8 @@ SIGNATURES = {
     "b200vq_pq_assign_tc_scratch_bytes2": (_sz, [_i64, _i, _i]),
     "b200vq_pq_assign_tc": (_i, [_p, _i64, _i64, _p, _p, _i, _i, _i, _p, _p, _sz, _p, _p]),
     "b200vq_pq_decode": (_i, [_p, _i64, _p, _i, _i, _i, _p, _i64, _p]),
+    "b200vq_pq_pack_bits": (_i, [_p, _i64, _i, _i, _p, _p]),
+    "b200vq_pq_unpack_bits": (_i, [_p, _i64, _i, _i, _p, _p]),
     "b200vq_pq_decode_ids": (_i, [_p, _p, _i64, _p, _i, _i, _i, _p, _i64, _p]),
     "b200vq_pq_kmeans_accumulate": (_i, [_p, _i64, _i64, _p, _i, _i, _i, _p, _p, _p]),
     "b200vq_pq_kmeans_finalize": (_i, [_p, _p, _i, _i, _i, _p, _p, _p]),
@@ -82,7 +84,7 @@ SIGNATURES = {
                                      C.c_double, _p, _p, _p]),
     "b200vq_perdim_decode_f32": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p, _p, _i64, _p]),
     "b200vq_codebook_lloyd_scratch_bytes": (_sz, [_i64, _i]),
-    "b200vq_codebook_lloyd": (_i, [_p, _i64, _p, _p, _i64, _i, _p, _i, _u64, _i, C.c_float, _p, _p, _p, _p, _sz, _p]),
+    "b200vq_codebook_lloyd": (_i, [_p, _i64, _p, _p, _i64, _i, _p, _i, _i, _u64, _i, C.c_float, _p, _p, _p, _p, _sz, _p]),
     "b200vq_ffd_pack": (_i, [_p, _i64, _i, _p, _p, _i, _p, _p]),
     "b200vq_ffd_unpack": (_i, [_p, _i64, _i, _p, _p, _p, _i, _p, _p]),
     "b200vq_lvq_encode": (_i, [_p, _i64, _i64, _i, _p, _i, _p, _p]),

@@ -226,6 +226,27 @@ def pq_codes_to_scan_layout(codes: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def pq_pack_bits(codes: torch.Tensor, nbits: int) -> torch.Tensor:
+    """(n, M) uint8 indices -> faiss' packed layout for nbits < 8: (n, ceil(M nbits / 8)) little-endian bit stream."""
+    _chk(codes, torch.uint8, "codes")
+    codes = codes.contiguous()
+    n, M = codes.shape
+    out = torch.empty((n, (M * nbits + 7) // 8), dtype=torch.uint8, device=codes.device)
+    check(_lib.load().b200vq_pq_pack_bits(codes.data_ptr(), n, M, nbits, out.data_ptr(), _stream()), "pq_pack_bits")
+    return out
+
+
+def pq_unpack_bits(packed: torch.Tensor, M: int, nbits: int) -> torch.Tensor:
+    _chk(packed, torch.uint8, "packed")
+    packed = packed.contiguous()
+    n = packed.shape[0]
+    if packed.shape[1] != (M * nbits + 7) // 8:
+        raise B200VQError(f"pq_unpack_bits: rows have {packed.shape[1]} bytes, expected {(M * nbits + 7) // 8}")
+    out = torch.empty((n, M), dtype=torch.uint8, device=packed.device)
+    check(_lib.load().b200vq_pq_unpack_bits(packed.data_ptr(), n, M, nbits, out.data_ptr(), _stream()), "pq_unpack_bits")
+    return out
+
+
 class RotationTC:
     """W (N, K) prepared for y = x W^T on the tensor cores (three TF32 passes over hi/lo operand
     splits, fp32-accurate; csrc/rotate_tc.cu). The split of W is made once and reused."""

@@ -328,13 +328,8 @@ def sq_err_sum(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------ data-fit per-dimension codebooks
-def codebook_lloyd(cols: torch.Tensor, bits, seed: int = 0, max_iters: int = 50, tol: float = 1e-6):
-    """1-D k-means codebooks (the SAQ engine's build_codebook_lloyd) for every row of ``cols`` (D, n) fp32 = the sample
-    of one dimension each. bits: an int (same bit-rate for all) or a (D,) int32 device tensor of per-dimension
-    bit-rates in [0, 8]. Returns (centroids (D, 256) fp32, sizes (D,) int32, costs (D,) fp32 = MSE on the sample).
-    The sort and the fp64 prefix sums are library calls (train time); the seeding and the Lloyd iterations are
-    b200vq_codebook_lloyd."""
-    _chk(cols, torch.float32, "cols")
+def codebook_prefix(cols: torch.Tensor):
+    """(sorted columns, prefix sums, prefix sums of squares) of the (D, n) sample columns (library sort / scan)."""
     D, n = cols.shape
     srt = torch.sort(cols, dim=1)[0].contiguous()
     v = srt.to(torch.float64)
@@ -342,8 +337,21 @@ def codebook_lloyd(cols: torch.Tensor, bits, seed: int = 0, max_iters: int = 50,
     psq = torch.zeros((D, n + 1), dtype=torch.float64, device=cols.device)
     torch.cumsum(v, dim=1, out=ps[:, 1:])
     torch.cumsum(v * v, dim=1, out=psq[:, 1:])
-    del v
-    cen = torch.zeros((D, 256), dtype=torch.float32, device=cols.device)
+    return srt, ps, psq
+
+
+def codebook_lloyd(cols: torch.Tensor, bits, seed: int = 0, max_iters: int = 50, tol: float = 1e-6, max_bits: int = 8,
+                   presorted=None):
+    """1-D k-means codebooks (the SAQ engine's build_codebook_lloyd) for every row of ``cols`` (D, n) fp32 = the sample
+    of one dimension each. bits: an int (same bit-rate for all) or a (D,) int32 device tensor of per-dimension
+    bit-rates in [0, max_bits] (max_bits <= 13). Returns (centroids (D, 2^max_bits) fp32, sizes (D,) int32, costs (D,)
+    fp32 = MSE on the sample). presorted: the (sorted, ps, psq) triple of an earlier call on the same columns.
+    The sort and the fp64 prefix sums are library calls (train time); the seeding and the Lloyd iterations are
+    b200vq_codebook_lloyd."""
+    _chk(cols, torch.float32, "cols")
+    D, n = cols.shape
+    srt, ps, psq = presorted if presorted is not None else codebook_prefix(cols)
+    cen = torch.zeros((D, 1 << max_bits), dtype=torch.float32, device=cols.device)
     sizes = torch.zeros((D,), dtype=torch.int32, device=cols.device)
     costs = torch.zeros((D,), dtype=torch.float32, device=cols.device)
     lib = _lib.load()
@@ -353,7 +361,7 @@ def codebook_lloyd(cols: torch.Tensor, bits, seed: int = 0, max_iters: int = 50,
         bptr, fixed = bits.data_ptr(), 0
     else:
         bptr, fixed = None, int(bits)
-    check(lib.b200vq_codebook_lloyd(srt.data_ptr(), srt.stride(0), ps.data_ptr(), psq.data_ptr(), n, D, bptr, fixed, seed,
-                                    max_iters, tol, cen.data_ptr(), sizes.data_ptr(), costs.data_ptr(), sc.data_ptr(),
+    check(lib.b200vq_codebook_lloyd(srt.data_ptr(), srt.stride(0), ps.data_ptr(), psq.data_ptr(), n, D, bptr, fixed,
+                                    max_bits, seed, max_iters, tol, cen.data_ptr(), sizes.data_ptr(), costs.data_ptr(), sc.data_ptr(),
                                     sc.numel(), _stream()), "codebook_lloyd")
     return cen, sizes, costs

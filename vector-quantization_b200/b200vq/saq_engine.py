@@ -96,6 +96,51 @@ def plan_dp(variance: np.ndarray, avg_bits: float) -> List[Tuple[int, int]]:
     return [(int(seg_len[i]), int(seg_bits[i])) for i in range(ns.value)]
 
 
+MAX_QUANT_BIT = 13          # kMaxQuantBit
+NUM_BIT_FACTORS = 64        # kNumShortFactors * sizeof(float) * 8
+
+
+def allocate_greedy(mse_table: np.ndarray, avg_bits: float, dim_padding: int = BLK, max_bits: int = MAX_QUANT_BIT,
+                    num_bit_factors: int = NUM_BIT_FACTORS) -> List[Tuple[int, int]]:
+    """BitAllocatorGreedy::AllocateJoint (external/saq/src/bit_allocator_greedy.cpp:11-116) driven as in
+    quantization_plan.h:246-266: every 64-dimension block starts at 0 bits; the block with the largest marginal MSE
+    drop (first index wins ties) is bumped by one bit until the bump would exceed the budget
+    avg_bits * d_pad + 64 (bits of all dimensions + 64 factor bits per coded segment, segments = runs of equal
+    widths); runs of equal widths are merged into the plan. mse_table: (d_pad, max_bits + 1) host fp32."""
+    d_pad = int(mse_table.shape[0])
+    nb = d_pad // dim_padding
+    total_bits = int(avg_bits * d_pad) + num_bit_factors
+    block = np.zeros((nb, max_bits + 1), dtype=np.float64)
+    for k in range(dim_padding):                      # s += mse_table(i * pad + k, b), k ascending, in double
+        block += mse_table[k::dim_padding].astype(np.float64)[:nb]
+
+    def usage(bits):
+        segs = sum(1 for i in range(nb) if bits[i] > 0 and (i == 0 or bits[i - 1] != bits[i]))
+        return int(sum(bits)) * dim_padding + segs * num_bit_factors
+    bits = [0] * nb
+    while True:
+        best_i, best_drop = -1, -np.inf
+        for i in range(nb):
+            if bits[i] < max_bits:
+                drop = block[i, bits[i]] - block[i, bits[i] + 1]
+                if drop > best_drop:
+                    best_drop, best_i = drop, i
+        if best_i < 0:
+            break
+        bits[best_i] += 1
+        if usage(bits) > total_bits:
+            bits[best_i] -= 1
+            break
+    plan, i = [], 0
+    while i < nb:
+        j = i + 1
+        while j < nb and bits[j] == bits[i]:
+            j += 1
+        plan.append(((j - i) * dim_padding, int(bits[i])))
+        i = j
+    return plan
+
+
 def equal_segmentation(d_pad: int, avg_bits: float, num_segs: int) -> List[Tuple[int, int]]:
     """quantization_plan.cpp:125-138."""
     plan, d = [], 0
@@ -172,7 +217,12 @@ class SaqEngine:
     """Device-resident single-cluster SAQ index (the K = 1 configuration SaqEngineAdapter uses)."""
 
     def __init__(self, avg_bits: float, apply_pca: bool = True, seed: int = 0, rot_seed: int = 20240607,
-                 rd_lmt: int = 6, adj_eps: float = 1e-8, seg_eqseg: int = 0, batch_rows: int = 1 << 17):
+                 rd_lmt: int = 6, adj_eps: float = 1e-8, seg_eqseg: int = 0, batch_rows: int = 1 << 17,
+                 allocator: str = "dp"):
+        if allocator not in ("dp", "greedy"):
+            raise ValueError("allocator must be 'dp' or 'greedy'")
+        self.allocator = allocator
+        self.mse_table = None
         self.avg_bits, self.apply_pca, self.seed, self.rot_seed = float(avg_bits), bool(apply_pca), seed, rot_seed
         self.rd_lmt, self.adj_eps, self.seg_eqseg, self.batch_rows = rd_lmt, adj_eps, seg_eqseg, batch_rows
         self.n = self.D = self.d_pad = 0
@@ -216,13 +266,43 @@ class SaqEngine:
         self.cent_row = kmeans1_row(n, self.seed)
         var_pad = np.zeros(self.d_pad, np.float32)
         var_pad[:D] = self.var.cpu().numpy()
-        self.plan = (equal_segmentation(self.d_pad, self.avg_bits, self.seg_eqseg) if self.seg_eqseg > 0
-                     else plan_dp(var_pad, self.avg_bits))
+        if self.seg_eqseg > 0:
+            self.plan = equal_segmentation(self.d_pad, self.avg_bits, self.seg_eqseg)
+        elif self.allocator == "greedy":
+            self.mse_table = self._mse_table(X)
+            self.plan = allocate_greedy(self.mse_table, self.avg_bits)
+        else:
+            self.plan = plan_dp(var_pad, self.avg_bits)
         g = torch.Generator(device="cpu").manual_seed(self.rot_seed)
         self.P = []
         for ln, _ in self.plan:   # P = Q^T of a QR of a Gaussian matrix (rotator.h:43-48)
             Q, _r = torch.linalg.qr(torch.randn((ln, ln), generator=g, dtype=torch.float64))
             self.P.append(Q.t().float().contiguous().to(dev))
+
+    def _mse_table(self, X: torch.Tensor) -> np.ndarray:
+        """build_mse_table_for_allocation (external/saq/src/quantization_plan.cpp:21-51): per PCA dimension the MSE of
+        its 1-D Lloyd codebook (k-means++ seeding, seed 0) at every bit-rate 0..13, on the PCA-projected data
+        (every row while n <= recommended_sample_size = 4 096 000). (d_pad, 14) host fp32; padding dimensions
+        are constant columns (cost 0)."""
+        n, D = X.shape
+        if n > 500 * (1 << MAX_QUANT_BIT):
+            raise NotImplementedError("greedy allocation samples the column beyond 4 096 000 rows (not built)")
+        Dk = (D + 31) // 32 * 32
+        W = torch.zeros((self.d_pad, Dk), dtype=torch.float32, device=X.device)      # y = (x - mean) rot: W = rot^T
+        W[:D, :D] = (self.rot if self.apply_pca else torch.eye(D, device=X.device)).t()
+        mean_k = torch.zeros(Dk, dtype=torch.float32, device=X.device)
+        mean_k[:D] = self.mean if self.apply_pca else 0.0
+        xp = X
+        if D != Dk or X.stride(0) % 4 or X.data_ptr() % 16:
+            xp = torch.zeros((n, Dk), dtype=torch.float32, device=X.device)
+            xp[:, :D] = X
+        colsT = ops.RotationTC(W)(xp, x_sub=mean_k, transpose_out=True).contiguous()   # (d_pad, n)
+        pre = ops_sq.codebook_prefix(colsT)
+        table = np.zeros((self.d_pad, MAX_QUANT_BIT + 1), dtype=np.float32)
+        for b in range(MAX_QUANT_BIT + 1):
+            _, _, costs = ops_sq.codebook_lloyd(colsT, b, seed=0, max_bits=max(b, 1), presorted=pre)
+            table[:, b] = costs.cpu().numpy()
+        return table
 
     def _compose(self, dev):
         """Wc (Dk, d_pad) = [rot | 0] . blockdiag(P_s): projection and segment rotations as one matrix
@@ -345,4 +425,5 @@ class SaqEngine:
 
     def export_state(self) -> dict:
         return dict(mean=self.mean.cpu().numpy(), rot=self.rot.cpu().numpy(), var=self.var.cpu().numpy(),
-                    cent_row=self.cent_row, plan=list(self.plan), P=[p.cpu().numpy() for p in self.P])
+                    cent_row=self.cent_row, plan=list(self.plan), P=[p.cpu().numpy() for p in self.P],
+                    mse_table=self.mse_table)

@@ -21,7 +21,7 @@ namespace b200vq {
 namespace cbk {
 
 constexpr int THREADS = 256;
-constexpr int MAXK = 256;
+constexpr int MAXK = 8192;      // 13 bits: the engine's kMaxQuantBit (the greedy allocator's MSE table goes that far)
 
 struct Mt64 {
     unsigned long long mt[312];
@@ -80,7 +80,22 @@ __device__ void nudge(double* c, int k) {
     for (int i = 1; i < k; ++i)
         if (c[i] <= c[i - 1]) c[i] = __dadd_rn(c[i - 1], fmax(1e-9, __dmul_rn(fabs(c[i - 1]), 1e-6)));
 }
-__device__ void sort_small(double* c, int k) {      // insertion sort, k <= 256, one thread
+// bitonic sort of k = 2^b doubles in shared memory by the whole CTA (ends with a barrier)
+__device__ void sort_block(double* c, int k) {
+    for (int size = 2; size <= k; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            __syncthreads();
+            for (int t = threadIdx.x; t < (k >> 1); t += blockDim.x) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const double a = c[lo], b = c[hi];
+                if ((a > b) == up) { c[lo] = b; c[hi] = a; }
+            }
+        }
+    }
+    __syncthreads();
+}
+__device__ void sort_small(double* c, int k) {      // insertion sort of a nearly sorted array, one thread
     for (int i = 1; i < k; ++i) {
         const double v = c[i];
         int j = i - 1;
@@ -101,10 +116,9 @@ __global__ void __launch_bounds__(THREADS)
 codebook_lloyd_kernel(const float* __restrict__ cols, int64_t ld, const double* __restrict__ ps_all,
                       const double* __restrict__ psq_all, int64_t n, const int* __restrict__ dim_bits, int fixed_bits,
                       unsigned long long seed, int max_iters, float tol_f, double* __restrict__ d2_all,
-                      float* __restrict__ centroids, int* __restrict__ sizes, float* __restrict__ costs) {
+                      float* __restrict__ centroids, int* __restrict__ sizes, float* __restrict__ costs, int kmax) {
+    extern __shared__ __align__(16) unsigned char cb_smem[];
     __shared__ Mt64 rng;
-    __shared__ double c[MAXK];
-    __shared__ int64_t bnd[MAXK + 1];
     __shared__ double part[THREADS];
     __shared__ double sh_d[4];
     __shared__ int64_t sh_i[4];
@@ -114,8 +128,10 @@ codebook_lloyd_kernel(const float* __restrict__ cols, int64_t ld, const double* 
     const double* ps = ps_all + (int64_t)dim * (n + 1);
     const double* psq = psq_all + (int64_t)dim * (n + 1);
     double* d2 = d2_all + (int64_t)dim * n;
-    float* out = centroids + (int64_t)dim * MAXK;
+    float* out = centroids + (int64_t)dim * kmax;
     const int k = 1 << bits;
+    double* c = reinterpret_cast<double*>(cb_smem);                         // [kmax]
+    int64_t* bnd = reinterpret_cast<int64_t*>(c + kmax);                    // [kmax + 1]
     if (bits == 0) {
         if (tid == 0) {
             out[0] = (float)seg_mean(ps, 0, n - 1);
@@ -216,10 +232,8 @@ codebook_lloyd_kernel(const float* __restrict__ cols, int64_t ld, const double* 
         part[tid] = acc;
         __syncthreads();
     }
-    if (tid == 0) {
-        sort_small(c, k);
-        nudge(c, k);
-    }
+    sort_block(c, k);
+    if (tid == 0) nudge(c, k);
     __syncthreads();
     // ---------------------------------------------------------------- Lloyd iterations
     const double tol = (double)tol_f;
@@ -284,17 +298,11 @@ codebook_lloyd_kernel(const float* __restrict__ cols, int64_t ld, const double* 
         if (state == 1) break;
     }
     assign();
-    {
-        double e = 0.0;
-        for (int i = tid; i < k; i += THREADS)
-            if (bnd[i + 1] > bnd[i]) e += seg_sse(ps, psq, bnd[i], bnd[i + 1] - 1);
-        part[tid] = e;
-        __syncthreads();
-    }
     if (tid == 0) {
-        // the reference adds the cells' SSE in index order; with k <= 256 = THREADS every thread holds one cell
+        // the reference adds the cells' SSE in index order
         double sse = 0.0;
-        for (int i = 0; i < k; ++i) sse = __dadd_rn(sse, part[i]);
+        for (int i = 0; i < k; ++i)
+            if (bnd[i + 1] > bnd[i]) sse = __dadd_rn(sse, seg_sse(ps, psq, bnd[i], bnd[i + 1] - 1));
         float* o = out;
         int m = 0;
         // float(c) sorted, duplicates dropped, padded with the last value up to 2^bits
@@ -319,17 +327,21 @@ extern "C" size_t b200vq_codebook_lloyd_scratch_bytes(int64_t n, int D) {
 }
 
 extern "C" int b200vq_codebook_lloyd(const float* sorted_cols, int64_t ld, const double* ps, const double* psq, int64_t n,
-                                     int D, const int* dim_bits, int fixed_bits, unsigned long long seed, int max_iters,
-                                     float tol, float* centroids, int* sizes, float* costs, void* scratch,
+                                     int D, const int* dim_bits, int fixed_bits, int max_bits, unsigned long long seed,
+                                     int max_iters, float tol, float* centroids, int* sizes, float* costs, void* scratch,
                                      size_t scratch_bytes, void* stream) {
     VQ_CHECK_ARG(sorted_cols && ps && psq && centroids && sizes && costs && n >= 1 && D >= 1 && ld >= n && max_iters >= 0,
                  "codebook_lloyd: bad args");
-    VQ_CHECK_ARG(dim_bits || (fixed_bits >= 0 && fixed_bits <= 8), "codebook_lloyd: bits must be in [0, 8]");
+    VQ_CHECK_ARG(max_bits >= 0 && max_bits <= 13 && (dim_bits || (fixed_bits >= 0 && fixed_bits <= max_bits)),
+                 "codebook_lloyd: bits must be in [0, max_bits], max_bits <= 13");
+    const int kmax = 1 << max_bits;
+    const size_t smem = (size_t)kmax * 8 + (size_t)(kmax + 1) * 8;
+    VQ_CUDA(cudaFuncSetAttribute(cbk::codebook_lloyd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     VQ_CHECK_ARG(scratch && scratch_bytes >= b200vq_codebook_lloyd_scratch_bytes(n, D),
                  "codebook_lloyd: scratch too small (%zu < %zu)", scratch_bytes, b200vq_codebook_lloyd_scratch_bytes(n, D));
-    cbk::codebook_lloyd_kernel<<<D, cbk::THREADS, 0, as_stream(stream)>>>(
+    cbk::codebook_lloyd_kernel<<<D, cbk::THREADS, smem, as_stream(stream)>>>(
         sorted_cols, ld, ps, psq, n, dim_bits, fixed_bits, seed, max_iters, tol, reinterpret_cast<double*>(scratch), centroids,
-        sizes, costs);
+        sizes, costs, kmax);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

@@ -344,9 +344,64 @@ adc_lut_batched_kernel(const float* __restrict__ queries, int nq, int64_t ldq, c
     }
 }
 
+// faiss packs sub-quantizer indices of nbits != 8 into a little-endian bit stream (PQEncoderGeneric /
+// PQDecoderGeneric: index m occupies stream bits [m nbits, (m + 1) nbits), stream bit i = bit i % 8 of byte i / 8).
+// One thread per packed byte (pack) / per index (unpack); nbits < 8, so an index spans at most two bytes.
+__global__ void pq_pack_bits_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int nbits, int code_size,
+                                    uint8_t* __restrict__ packed) {
+    const int64_t total = n * (int64_t)code_size;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = e / code_size;
+        const int byte = (int)(e - row * code_size);
+        const int b0 = byte * 8, b1 = b0 + 8;
+        uint32_t acc = 0;
+        for (int m = b0 / nbits; m < M && m * nbits < b1; ++m) {
+            const int sh = m * nbits - b0;                 // stream position of the index's bit 0 relative to the byte
+            const uint32_t q = codes[row * M + m];
+            acc |= (sh >= 0) ? (q << sh) : (q >> (-sh));
+        }
+        packed[e] = (uint8_t)acc;
+    }
+}
+__global__ void pq_unpack_bits_kernel(const uint8_t* __restrict__ packed, int64_t n, int M, int nbits, int code_size,
+                                      uint8_t* __restrict__ codes) {
+    const int64_t total = n * (int64_t)M;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = e / M;
+        const int m = (int)(e - row * M);
+        const int bit = m * nbits, byte = bit >> 3;
+        const uint8_t* p = packed + row * code_size;
+        const uint32_t w = (uint32_t)p[byte] | (byte + 1 < code_size ? (uint32_t)p[byte + 1] << 8 : 0u);
+        codes[e] = (uint8_t)((w >> (bit & 7)) & ((1u << nbits) - 1u));
+    }
+}
+
 }  // namespace b200vq
 
 using namespace b200vq;
+
+extern "C" int b200vq_pq_pack_bits(const uint8_t* codes, int64_t n, int M, int nbits, uint8_t* packed, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && M > 0 && nbits >= 1 && nbits <= 8 && (n == 0 || (codes && packed)), "pq_pack_bits: bad args");
+    if (n == 0) return B200VQ_OK;
+    const int code_size = (M * nbits + 7) / 8;
+    int64_t g = (n * code_size + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    pq_pack_bits_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, M, nbits, code_size, packed);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+extern "C" int b200vq_pq_unpack_bits(const uint8_t* packed, int64_t n, int M, int nbits, uint8_t* codes, void* stream) {
+    VQ_CHECK_ARG(n >= 0 && M > 0 && nbits >= 1 && nbits <= 8 && (n == 0 || (codes && packed)), "pq_unpack_bits: bad args");
+    if (n == 0) return B200VQ_OK;
+    const int code_size = (M * nbits + 7) / 8;
+    int64_t g = (n * M + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (g > cap) g = cap;
+    pq_unpack_bits_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(packed, n, M, nbits, code_size, codes);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
 
 extern "C" int b200vq_pq_centroid_norms(const float* centroids, int M, int ksub, int dsub,
                                         float* cnorm, void* stream) {

@@ -848,13 +848,20 @@ extern "C" int b200vq_pq_assign_tc(const float* x, int64_t n, int64_t ldx, const
     if (tpi > 64) tpi = 64;
     p.tiles_per_item = tpi;
     p.nitems = (int64_t)p.groups * ((p.ntiles + tpi - 1) / tpi);
+    p.debug = 0;
+#ifdef B200VQ_DEBUG_BUILD   // tools/ A/B builds only: the debug bits change results, so release builds never read them
     {
         const char* dbg = getenv("B200VQ_TC_DEBUG");
         p.debug = dbg ? atoi(dbg) : 0;
     }
+#endif
     int grid = (int)(p.nitems < sms ? p.nitems : sms);
     const size_t smem = ts.sp.total + 1024;
+#ifdef B200VQ_DEBUG_BUILD
     auto kern = p.debug ? assign_tc_kernel<true> : assign_tc_kernel<false>;
+#else
+    auto kern = assign_tc_kernel<false>;
+#endif
     VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, THREADS, smem, st>>>(map_x, map_b, map_bx, map_ax, p);
     VQ_LAUNCH_CHECK();

@@ -573,7 +573,11 @@ extern "C" int b200vq_rabitq1_scan_topk_tc(const uint8_t* codes, int64_t n, int 
     p.codes = codes; p.rowinfo = rowinfo; p.qscreen = qscreen; p.cand = cand; p.count = count; p.cap = fp.cap;
     p.code_size = D / 8 + 8; p.nchunk = fp.Dp / CHB; p.ntq = fp.ntq; p.D = D;
     p.dbg = nullptr;
+#ifdef B200VQ_DEBUG_BUILD   // wait-cycle counters of the MMA thread (tools/ builds only)
     const bool debug = getenv("B200VQ_RQ_DEBUG") != nullptr;
+#else
+    const bool debug = false;
+#endif
     unsigned long long* dbg_dev = reinterpret_cast<unsigned long long*>(amax + 8);   // inside the 256-byte amax slot
     for (int64_t r = 0; r < n;) {
         int64_t r1 = r == 0 ? SEED_ROWS : r * 4;   // x4: about 3k expected survivors per query and stage

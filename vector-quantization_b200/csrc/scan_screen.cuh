@@ -31,6 +31,7 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
                       int negate, uint8_t* __restrict__ qlut4, int* __restrict__ thr) {
     __shared__ float red[8], redx[8];
     __shared__ float lo_s[96];
+    __shared__ float amax_s[96];
     __shared__ int active_s;
     __shared__ float step_s;
     const int q = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -55,6 +56,7 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
                 mx = fmaxf(mx, redx[i]);
             }
             lo_s[m] = mn;
+            amax_s[m] = fmaxf(fabsf(mn), fabsf(mx));
             // constant tables (the all-zero tables of sub-quantizers added by padding M to the scan layout's
             // group width) always contribute exactly lo: they take no share of the budget
             if (mx > mn) ++active_s;
@@ -62,8 +64,8 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
         __syncthreads();
     }
     if (t == 0) {
-        double sum_lo = 0.0, sum_abs = 0.0;
-        for (int m = 0; m < M; ++m) { sum_lo += lo_s[m]; sum_abs += fabs((double)lo_s[m]); }
+        double sum_lo = 0.0, sum_abs = 0.0, sum_amax = 0.0;
+        for (int m = 0; m < M; ++m) { sum_lo += lo_s[m]; sum_abs += fabs((double)lo_s[m]); sum_amax += (double)amax_s[m]; }
         const float tv = sample_vals[(size_t)q * k + (k - 1)];
         int th;
         float step;
@@ -72,8 +74,12 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
             th = 65535;
         } else {
             const double tau = (double)(sgn * tv);
-            // slack for the fp32 summation error of the sample's and the candidates' exact scores
-            const double margin = 7.63e-6 * (fabs(tau) + sum_abs) + 1e-30;
+            // slack for the fp32 summation error of the sample's and the candidates' exact scores: an M-term fp32 sum
+            // is off by at most (M - 1) 2^-24 sum_m |T[m][c]| <= (M - 1) 2^-24 sum_m max|T[m]| (mixed-sign inner-product
+            // tables included), once for the threshold row and once for the candidate
+            const double worst = 2.0 * (double)M * 5.9604645e-8 * 1.01 * sum_amax;
+            double margin = 7.63e-6 * (fabs(tau) + sum_abs) + 1e-30;
+            if (worst > margin) margin = worst;
             double budget = tau - sum_lo;
             if (budget < 0) budget = 0;
             // clip level of one table entry = 6x the mean budget per (non-constant) sub-quantizer of a threshold row

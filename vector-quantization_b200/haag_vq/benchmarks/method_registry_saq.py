@@ -6,9 +6,10 @@ the hot path: ``rabitq`` -> ExtendedRaBitQuantizer(num_bits=round(bpd)) and
 a16), ``lvq`` -> LVQQuantizer(num_bits=round(bpd)) (reference :49-52), and the per-dimension family
 ``rankaware`` (the proposed method: var^0.5-weighted greedy) / ``perdim_mse`` (alpha = 0) ->
 RankAwareQuantizer(packing="ffd", codebook="lloyd") (reference :58-65), whose data-fit codebooks come from
-b200vq_codebook_lloyd. Still not built: ``ours`` / ``ours_exact`` (engine-side greedy allocation + codebook-aware
-CAQ encoder) and the ``*_exact`` variants (optimal-DP codebooks); they raise NotImplementedError instead of
-silently falling back.
+b200vq_codebook_lloyd, and ``ours`` / ``ours_exact`` -> SaqEngineAdapter(greedy=True, derive_codebooks=True[,
+exact_codebooks=True]) (reference :34-47; see the adapter for what the codebook flags do in the CPU engine).
+Still not built: ``rankaware_exact`` / ``perdim_mse_exact`` (optimal-DP 1-D codebooks, build_codebook_exact); they
+raise NotImplementedError instead of silently falling back.
 """
 from __future__ import annotations
 
@@ -23,6 +24,12 @@ def build_saq_quantizer(method: str, bpd: float, D: int):
         from haag_vq.benchmarks.quantizer_adapters import SaqEngineAdapter
         # VQ_SAQ_APPLY_PCA=0 skips the internal PCA for already-rotated inputs (reference :24-27)
         return SaqEngineAdapter(quant_type="CAQ", avg_bits=bpd, greedy=False, derive_codebooks=False,
+                                apply_pca=os.environ.get("VQ_SAQ_APPLY_PCA", "1") != "0")
+    if method in ("ours", "ours_exact"):
+        import os
+        from haag_vq.benchmarks.quantizer_adapters import SaqEngineAdapter
+        return SaqEngineAdapter(quant_type="CAQ", avg_bits=bpd, greedy=True, derive_codebooks=True,
+                                exact_codebooks=(method == "ours_exact"),
                                 apply_pca=os.environ.get("VQ_SAQ_APPLY_PCA", "1") != "0")
     if method == "rabitq":
         from haag_vq.benchmarks.quantizer_adapters import FaissQuantizerAdapter

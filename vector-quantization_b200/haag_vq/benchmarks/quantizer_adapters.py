@@ -57,10 +57,13 @@ class SaqEngineAdapter:
 
     Mirrors src/haag_vq/benchmarks/quantizer_adapters.py:62-135 (same constructor keywords, same
     errors, same code_bytes formula). The engine itself (`saq.IVF(n, D, K, cfg).fit / .decompress`)
-    is b200vq.saq_engine.SaqEngine on the device. Built here: quant_type "CAQ" with the DP
-    allocator and the engine's default uniform codebook (method ``saq_paper``). The greedy
-    allocator and derived per-dimension codebooks (methods ``ours`` / ``ours_exact``) are
-    SURVEY.md §8(f) items and raise NotImplementedError - there is no fallback.
+    is b200vq.saq_engine.SaqEngine on the device: quant_type "CAQ" with the DP allocator (method
+    ``saq_paper``) or the greedy allocator on the per-dimension Lloyd MSE table (``greedy=True``, methods ``ours`` /
+    ``ours_exact``: external/saq/include/saq/quantization_plan.h:246-266, src/bit_allocator_greedy.cpp:11-116).
+    ``derive_codebooks`` / ``exact_codebooks``: the reference's CPU engine (the `saq.IVF` this adapter drives) builds
+    per-dimension codebooks in construct() (src/ivf_index.cpp:50-121) but only its CUDA construct path consumes
+    them (segment_codebooks is read in src/gpu/gpu_ivf_construct.cpp alone); the CPU encoder stays CAQ's uniform
+    grid, so the flags change no code and no reconstruction there, and none here.
     """
 
     def __init__(self, *, quant_type: str = "CAQ", avg_bits: float = 4.0, greedy: bool = False,
@@ -68,9 +71,8 @@ class SaqEngineAdapter:
                  K: int = 1, num_threads: int = 8, seed: int = 0, max_bits: int = 13) -> None:
         if quant_type != "CAQ":
             raise ValueError(f"SaqEngineAdapter: unsupported quant_type {quant_type!r} (CAQ only)")
-        if greedy or derive_codebooks or exact_codebooks:
-            raise NotImplementedError("greedy allocation / derived codebooks are not built on the B200 path yet "
-                                      "(SURVEY.md §8f); no fallback is provided")
+        self._greedy = bool(greedy)
+        self._derive_codebooks, self._exact_codebooks = bool(derive_codebooks), bool(exact_codebooks)
         if K != 1:
             raise NotImplementedError("SaqEngineAdapter on the B200 path is the K = 1 (flat) configuration")
         self._avg_bits = float(avg_bits)
@@ -85,7 +87,8 @@ class SaqEngineAdapter:
         from b200vq.saq_engine import SaqEngine
         X = np.ascontiguousarray(X, dtype=np.float32)
         self._n, self._D = X.shape
-        eng = SaqEngine(self._avg_bits, apply_pca=self._apply_pca, seed=self._seed)
+        eng = SaqEngine(self._avg_bits, apply_pca=self._apply_pca, seed=self._seed,
+                        allocator="greedy" if self._greedy else "dp")
         eng.fit(torch.from_numpy(X).cuda())
         self._index = eng
 

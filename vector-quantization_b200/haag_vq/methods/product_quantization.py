@@ -26,9 +26,9 @@ class DevicePQ:
     def __init__(self, d: int, M: int, nbits: int):
         if nbits < 1 or nbits > 8:
             raise ValueError("b200vq ProductQuantizer supports 1 <= B <= 8")
-        if nbits != 8:
-            # faiss packs sub-8-bit indices into a bit string; only the byte layout is built.
-            raise NotImplementedError("only B = 8 (one byte per sub-quantizer) is supported")
+        # nbits < 8: faiss packs the indices into a little-endian bit stream of ceil(M nbits / 8) bytes
+        # (PQEncoderGeneric); the kernels work on one byte per index and b200vq_pq_pack_bits / _unpack_bits convert.
+        # nbits > 8 (up to 65 536 centroids per sub-quantizer) is not built: the kernels keep ksub <= 256.
         self.d, self.M, self.nbits = int(d), int(M), int(nbits)
         self.ksub = 1 << self.nbits
         self.dsub = self.d // self.M
@@ -64,13 +64,19 @@ class DevicePQ:
         n = X.shape[0]
         out = torch.empty((n, self.M), dtype=torch.uint8, device=host.device())
         host.stream_rows(X, lambda xb, s, e: self.codec.encode(xb, out=out[s:e]))
+        if self.nbits != 8:
+            out = ops.pq_pack_bits(out, self.nbits)
         return host.to_host(out)
+
+    def unpack_codes(self, codes_dev: torch.Tensor) -> torch.Tensor:
+        """(n, code_size) stored codes -> (n, M) one byte per index (identity for nbits = 8)."""
+        return codes_dev if self.nbits == 8 else ops.pq_unpack_bits(codes_dev, self.M, self.nbits)
 
     def decode(self, codes: np.ndarray) -> np.ndarray:
         codes = np.ascontiguousarray(codes, dtype=np.uint8)
-        if codes.ndim != 2 or codes.shape[1] != self.M:
-            raise ValueError(f"decode: codes must be (n, {self.M})")
-        return host.to_host(self.codec.decode(host.to_device(codes)))
+        if codes.ndim != 2 or codes.shape[1] != self.code_size:
+            raise ValueError(f"decode: codes must be (n, {self.code_size})")
+        return host.to_host(self.codec.decode(self.unpack_codes(host.to_device(codes))))
 
 
 class ProductQuantizer(BaseQuantizer):

@@ -100,7 +100,9 @@ class FlatQuantizedIndex(BaseSearchIndex):
         codec = self._pq_codec()
         if codec is not None:
             if self._codes_dev is None:
-                self._codes_dev = host.to_device(np.ascontiguousarray(self._codes, dtype=np.uint8))
+                # stored codes -> one byte per sub-quantizer index (sub-byte PQ codes are a packed bit stream)
+                self._codes_dev = self._quantizer.pq.unpack_codes(
+                    host.to_device(np.ascontiguousarray(self._codes, dtype=np.uint8)))
             if codec.ksub == 256 and codec.M <= 96 and (codec.M % 32 == 0 or (codec.M % 16 == 0 and self._N >= 65536)):
                 # conflict-free scan layout (b200vq_pq_codes_to_scan_layout), built once per fit/load; M is
                 # padded to the layout's group width of 32 with all-zero tables (same scores bit for bit; M % 16 keeps
