@@ -414,6 +414,18 @@ int b200vq_codebook_lloyd(const float* sorted_cols, int64_t ld, const double* ps
                           int max_iters, float tol, float* centroids, int* sizes, float* costs, void* scratch,
                           size_t scratch_bytes, void* stream);
 
+/* ADC scan directly on the packed per-dimension layout (dense or FFD) with a top-k: the reference's micro-kernel
+ * bench/ffd_speed.cpp:87-127 (score = sum_d LUT[d][code_d], LUT[d][c] = q_d cb_d[c]; :119-123 is the FFD-packed
+ * variant), without decoding the rows to HBM. Layout arguments as b200vq_perdim_decode_f32 (cb fp32). queries
+ * (nq, ldq) fp32 are the PROJECTED query coordinates; value = C_q + B_i - 2 <y^_i, q> (L2; row_bias = B_i = |y^_i|^2,
+ * qconst = C_q = |q|^2; both optional) or C_q + <y^_i, q> (IP). One fp32 FMA chain per (row, query) in dimension
+ * order. k <= 128; scratch: b200vq_perdim_scan_scratch_bytes(n, nq, k). */
+size_t b200vq_perdim_scan_scratch_bytes(int64_t n, int nq, int k);
+int b200vq_perdim_scan_topk(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits,
+                            const int* bitpos, const float* cb, const int* cb_off, const float* row_bias,
+                            const float* queries, int nq, int64_t ldq, const float* qconst, int metric, int k,
+                            float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream);
+
 /* ------------------------------------------------------- 1-bit RaBitQ ---
  * faiss RaBitQuantizer / IndexRaBitQ semantics (src/haag_vq/methods/
  * rabit_quantization.py:20-29, methods/search/rabitq_index.py:42-70):

@@ -92,3 +92,25 @@ def test_ffd_is_lossless_relayout():
     np.testing.assert_array_equal(xf, xd)
     assert qd.code_size <= qf.code_size <= 64
     assert qf.get_compression_ratio(X) == pytest.approx(64 * 4 / qf.code_size)
+
+
+@pytest.mark.parametrize("packing", ["dense", "ffd"])
+@pytest.mark.parametrize("metric", ["l2", "ip"])
+def test_adc_scan_on_the_packed_layout_equals_search_on_reconstructions(packing, metric):
+    """b200vq_perdim_scan_topk (the ADC loop of bench/ffd_speed.cpp:87-127 on the dense / FFD layout) against the
+    distance to the reconstruction, the definition of FlatQuantizedIndex.search_with_scores (:57-68)."""
+    from parity import assert_topk_parity
+    X = _data(n=5000)
+    Q = _data(seed=3, n=13)
+    q = _Q(avg_bits=4, alpha=0.5, packing=packing, codebook="lloyd")
+    q.fit(X)
+    codes = q.compress(X)
+    ids, vals = q.adc_search(codes, Q, 10, metric)
+    Xhat = q.decompress(codes).astype(np.float64)
+    if metric == "l2":
+        true = ((Q[:, None, :].astype(np.float64) - Xhat[None]) ** 2).sum(-1)
+    else:
+        true = Q.astype(np.float64) @ Xhat.T
+    scale = float(np.abs(true).max())
+    assert_topk_parity(vals, ids, true.astype(np.float32), 10, 0 if metric == "l2" else 1, "perdim_scan", gap_rel=1e-5,
+                       val_rel=1e-4, abs_tol=2e-6 * scale)

@@ -1,0 +1,49 @@
+"""Profiling drivers for ncu (one short workload per mode, warmed): scan = the bench's screened ADC scan over one
+C5 shard; rotate = rotate_tc 262144 x 1536; caq = all-segment CAQ encode at 99 000 x 1536. Diagnostic."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "vector-quantization_b200"), ROOT]
+import torch
+
+from b200vq import ops, ops_sq, pq as dpq, saq_engine as E
+
+mode = sys.argv[1]
+dev = torch.device("cuda")
+
+
+def data(n, D, seed=1234, row0=0):
+    return ops_sq.synth_rows(n, D, row0, seed, torch.linspace(4.0, 0.2, D, device=dev), True, device=dev)
+
+
+if mode == "scan":
+    n, D, M, nq = 6_625_000, 1024, 32, 1000
+    C = dpq.pq_train(data(65536, D, row0=1 << 40), M, 8, niter=4, seed=1234)
+    codec = dpq.PQCodec(C)
+    codes = torch.empty((n, M), dtype=torch.uint8, device=dev)
+    for s in range(0, n, 1 << 20):
+        e = min(n, s + (1 << 20))
+        codec.encode(data(e - s, D, row0=s), out=codes[s:e])
+    rot = ops.pq_codes_to_scan_layout(codes)
+    Q = data(nq, D, seed=4321, row0=1 << 41)
+    lut = codec.luts(Q, "l2")
+    for _ in range(2):
+        v, i = ops.adc_scan_topk(rot, lut, 10, "l2", n=n, rot=True, screen=True)
+elif mode == "rotate":
+    n, D = 262_144, 1536
+    x = data(n, D)
+    A = torch.from_numpy(dpq.random_rotation(D, 5)).to(dev)
+    for _ in range(2):
+        v = dpq.rotate(x, A, impl="tc")
+elif mode == "caq":
+    n, D = 99_000, 1536
+    x = data(n, D)
+    eng = E.SaqEngine(4.0).fit(x)
+    oT = eng._project(x, transpose_out=True)
+    for _ in range(2):
+        v, _ = E.caq_encode_t_segments(oT, eng.plan)
+else:
+    raise SystemExit("mode: scan | rotate | caq")
+torch.cuda.synchronize()
+print("ok", mode)

@@ -85,6 +85,8 @@ SIGNATURES = {
     "b200vq_perdim_decode_f32": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p, _p, _i64, _p]),
     "b200vq_codebook_lloyd_scratch_bytes": (_sz, [_i64, _i]),
     "b200vq_codebook_lloyd": (_i, [_p, _i64, _p, _p, _i64, _i, _p, _i, _i, _u64, _i, C.c_float, _p, _p, _p, _p, _sz, _p]),
+    "b200vq_perdim_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
+    "b200vq_perdim_scan_topk": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p, _p, _p, _i, _i64, _p, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_ffd_pack": (_i, [_p, _i64, _i, _p, _p, _i, _p, _p]),
     "b200vq_ffd_unpack": (_i, [_p, _i64, _i, _p, _p, _p, _i, _p, _p]),
     "b200vq_lvq_encode": (_i, [_p, _i64, _i64, _i, _p, _i, _p, _p]),

@@ -10,6 +10,7 @@
 // packed bytes are integer work: bit-identical for identical inputs.
 // HBM-bound: 8 D bytes in + code_size out per vector (encode), the reverse for decode.
 #include "common.cuh"
+#include "topk.cuh"
 
 namespace b200vq {
 
@@ -213,6 +214,87 @@ __global__ void __launch_bounds__(256) perdim_decode_kernel(const uint8_t* __res
     }
 }
 
+// ADC scan straight on the packed per-dimension layout (dense or FFD) = the reference's micro-benchmark loop
+// bench/ffd_speed.cpp:87-127 (score = sum_d LUT[d][code_d], LUT[d][c] = q_d * cb_d[c]) with a running top-k:
+// thread = row, PD_QT queries per pass so that a field is extracted and its level fetched once for all of them;
+// per query one fp32 FMA chain in dimension order (the arithmetic of the exact flat search over the decoded rows).
+// value(q, i) = C_q + B_i - 2 <y^_i, q> (L2, ascending) or C_q + <y^_i, q> (IP, descending).
+constexpr int PD_QT = 4;
+struct PdMeta {
+    uint16_t pos;      // MSB-first bit position of the field in the row
+    uint8_t bits, pad;
+    int32_t cb_off;
+};
+template <int CAP>
+__global__ void __launch_bounds__(256)
+perdim_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int code_size, int D, const uint8_t* __restrict__ bits,
+                   const int* __restrict__ bitpos, const float* __restrict__ cb, const int* __restrict__ cb_off,
+                   const float* __restrict__ row_bias, const float* __restrict__ queries, int nq, int64_t ldq,
+                   const float* __restrict__ qconst, int metric, int k, int64_t chunk_rows, uint64_t* __restrict__ part) {
+    extern __shared__ __align__(16) unsigned char pds[];
+    const int qt = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* qs = reinterpret_cast<float*>(pds);                                  // [PD_QT][D]
+    PdMeta* meta = reinterpret_cast<PdMeta*>(qs + (size_t)PD_QT * D);           // [D]
+    uint64_t* wbuf = reinterpret_cast<uint64_t*>(meta + D);                     // [8 warps][PD_QT][CAP]
+    const int n2 = next_pow2(8 * k);
+    uint64_t* mbuf = wbuf + 8 * PD_QT * CAP;
+    for (int i = threadIdx.x; i < PD_QT * D; i += blockDim.x) {
+        const int t = i / D, d = i - t * D, q = qt * PD_QT + t;
+        qs[i] = q < nq ? queries[(int64_t)q * ldq + d] : 0.f;
+    }
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        PdMeta m;
+        m.pos = (uint16_t)bitpos[d]; m.bits = bits[d]; m.pad = 0; m.cb_off = cb_off[d];
+        meta[d] = m;
+    }
+    __syncthreads();
+    WarpTopK<CAP> tk[PD_QT];
+#pragma unroll
+    for (int t = 0; t < PD_QT; ++t) tk[t].init(wbuf + ((size_t)w * PD_QT + t) * CAP, k);
+    float cq[PD_QT];
+#pragma unroll
+    for (int t = 0; t < PD_QT; ++t) cq[t] = (qconst && qt * PD_QT + t < nq) ? qconst[qt * PD_QT + t] : 0.f;
+    const int64_t r0 = (int64_t)chunk * chunk_rows;
+    int64_t r1 = r0 + chunk_rows;
+    if (r1 > n) r1 = n;
+    for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += 256) {
+        const int64_t row = base + lane;
+        const bool valid = row < r1;
+        float acc[PD_QT];
+#pragma unroll
+        for (int t = 0; t < PD_QT; ++t) acc[t] = 0.f;
+        if (valid) {
+            const uint8_t* c = codes + row * (int64_t)code_size;
+            for (int d = 0; d < D; ++d) {
+                const PdMeta m = meta[d];
+                if (m.bits == 0) continue;
+                const int byte = m.pos >> 3;
+                const uint32_t v16 = ((uint32_t)c[byte] << 8) | (byte + 1 < code_size ? (uint32_t)c[byte + 1] : 0u);
+                const uint32_t idx = (v16 >> (16 - m.bits - (m.pos & 7))) & ((1u << m.bits) - 1u);
+                const float val = __ldg(cb + m.cb_off + idx);
+#pragma unroll
+                for (int t = 0; t < PD_QT; ++t) acc[t] = __fmaf_rn(qs[t * D + d], val, acc[t]);
+            }
+        }
+        const float bi = (valid && row_bias) ? row_bias[row] : 0.f;
+#pragma unroll
+        for (int t = 0; t < PD_QT; ++t) {
+            const float key = metric == B200VQ_METRIC_L2 ? __fmaf_rn(-2.f, acc[t], __fadd_rn(cq[t], bi))
+                                                        : -__fadd_rn(cq[t], acc[t]);
+            tk[t].offer(valid, key, (uint32_t)row);
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < PD_QT; ++t) {
+        const int q = qt * PD_QT + t;
+        uint64_t* dst = part + ((size_t)(q < nq ? q : 0) * nchunks + chunk) * k;
+        // queries past nq (tile padding) write nothing: their lists are emitted into a scratch slot of the tile buffer
+        block_emit_topk<CAP>(tk[t], mbuf, n2, k, q < nq ? dst : mbuf + n2);
+        __syncthreads();
+    }
+}
+
 }  // namespace b200vq
 
 using namespace b200vq;
@@ -288,6 +370,74 @@ extern "C" int b200vq_perdim_decode_f32(const uint8_t* codes, int64_t n, int cod
     VQ_CHECK_ARG(bits && bitpos && cb && cb_off && yhat && (codes || code_size == 0), "perdim_decode_f32: null pointer");
     perdim_decode_f32_kernel<<<perdim_grid(n), 256, 0, as_stream(stream)>>>(codes, n, code_size, D, bits, bitpos, cb, cb_off,
                                                                           yhat, ldy);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+static void pd_plan(int64_t n, int nq, int64_t* chunk_rows, int* nchunks) {
+    const int64_t unit = 2048;
+    const int qtiles = (nq + PD_QT - 1) / PD_QT;
+    int64_t want = ((int64_t)device_sm_count() * 4 + qtiles - 1) / (qtiles > 0 ? qtiles : 1);
+    int64_t maxc = (n + unit - 1) / unit;
+    if (maxc < 1) maxc = 1;
+    if (want < 1) want = 1;
+    if (want > maxc) want = maxc;
+    if (want > 65535) want = 65535;
+    int64_t rows = (n + want - 1) / want;
+    rows = (rows + unit - 1) / unit * unit;
+    *chunk_rows = rows;
+    *nchunks = (int)((n + rows - 1) / rows);
+    if (*nchunks < 1) *nchunks = 1;
+}
+
+extern "C" size_t b200vq_perdim_scan_scratch_bytes(int64_t n, int nq, int k) {
+    if (n < 0 || nq <= 0 || k <= 0) return 0;
+    int64_t cr;
+    int nc;
+    pd_plan(n, nq, &cr, &nc);
+    return (size_t)nq * nc * k * sizeof(uint64_t);
+}
+
+template <int CAP>
+static int pd_scan_launch(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits, const int* bitpos,
+                          const float* cb, const int* cb_off, const float* row_bias, const float* queries, int nq,
+                          int64_t ldq, const float* qconst, int metric, int k, int64_t cr, int nc, uint64_t* part,
+                          cudaStream_t st) {
+    const int n2 = next_pow2(8 * k);
+    const size_t smem = (size_t)PD_QT * D * 4 + (size_t)D * sizeof(PdMeta) + (size_t)(8 * PD_QT * CAP + n2 + k) * 8;
+    VQ_CHECK_ARG(smem <= 220 * 1024, "perdim_scan_topk: D = %d needs %zu bytes of shared memory", D, smem);
+    VQ_CUDA(cudaFuncSetAttribute(perdim_scan_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((nq + PD_QT - 1) / PD_QT), (unsigned)nc);
+    perdim_scan_kernel<CAP><<<grid, 256, smem, st>>>(codes, n, code_size, D, bits, bitpos, cb, cb_off, row_bias, queries, nq,
+                                                    ldq, qconst, metric, k, cr, part);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+extern "C" int b200vq_perdim_scan_topk(const uint8_t* codes, int64_t n, int code_size, int D, const uint8_t* bits,
+                                       const int* bitpos, const float* cb, const int* cb_off, const float* row_bias,
+                                       const float* queries, int nq, int64_t ldq, const float* qconst, int metric, int k,
+                                       float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                                       void* stream) {
+    VQ_CHECK_ARG(codes && bits && bitpos && cb && cb_off && queries && out_vals && out_ids, "perdim_scan_topk: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && code_size > 0 && code_size < 8192 && nq >= 0 && ldq >= D,
+                 "perdim_scan_topk: bad shape");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "perdim_scan_topk: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "perdim_scan_topk: bad metric");
+    if (nq == 0) return B200VQ_OK;
+    int64_t cr;
+    int nc;
+    pd_plan(n, nq, &cr, &nc);
+    const size_t need = (size_t)nq * nc * k * sizeof(uint64_t);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "perdim_scan_topk: scratch too small (%zu < %zu)", scratch_bytes, need);
+    cudaStream_t st = as_stream(stream);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32) ? pd_scan_launch<64>(codes, n, code_size, D, bits, bitpos, cb, cb_off, row_bias, queries, nq, ldq,
+                                            qconst, metric, k, cr, nc, part, st)
+                       : pd_scan_launch<256>(codes, n, code_size, D, bits, bitpos, cb, cb_off, row_bias, queries, nq, ldq,
+                                             qconst, metric, k, cr, nc, part, st);
+    if (rc != B200VQ_OK) return rc;
+    merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, nc, k, metric == B200VQ_METRIC_IP, out_vals, out_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

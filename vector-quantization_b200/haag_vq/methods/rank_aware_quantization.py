@@ -293,5 +293,53 @@ class RankAwareQuantizer(BaseQuantizer):
             out[s:e] = host.to_host(T["rev"](Yh, col_bias=T["mu32d"]))       # y^ V^T + mu on the tensor cores
         return out
 
+    # ---- code-domain search (not part of the reference surface; the ADC loop of bench/ffd_speed.cpp:87-127)
+    def adc_search(self, codes, Q: np.ndarray, k: int, metric: str = "l2"):
+        """Top-k of |q - x^_i|^2 (l2) or q . x^_i (ip) straight from the packed codes (dense or FFD layout):
+        with y^ the decoded PCA coordinates and V orthonormal, |q - x^|^2 = |(q - mu) V - y^|^2 and
+        q . x^ = (q V) . y^ + q . mu. codes: (n, code_size) uint8 numpy array or device tensor.
+        Returns (ids uint32 (nq, k), values fp32 (nq, k))."""
+        from b200vq import ops
+        from b200vq.ops import _topk_out, metric_id, scratch
+        T = self._tables()
+        cd = codes if isinstance(codes, torch.Tensor) else host.to_device(np.ascontiguousarray(codes, dtype=np.uint8))
+        n, D = int(cd.shape[0]), self.D
+        qd = host.to_device(np.ascontiguousarray(Q, dtype=np.float32))
+        nq = int(qd.shape[0])
+        lib = _lib.load()
+        if metric == "l2":
+            qp = T["fwd"](self._pad_cols(qd, T["Dp"]), x_sub=T["mu32"]).contiguous()
+            qc = ops.row_sqnorms(qp)
+            bias = self._row_sqnorms(cd)
+        else:
+            qp = T["fwd"](self._pad_cols(qd, T["Dp"])).contiguous()
+            qc = (qd * T["mu32d"]).sum(1).contiguous()
+            bias = None
+        vals, ids = _topk_out(nq, k, cd.device)
+        sc = scratch(lib.b200vq_perdim_scan_scratch_bytes(n, nq, k), cd.device, "scan")
+        check(lib.b200vq_perdim_scan_topk(cd.data_ptr(), n, self.code_size, D, T["bits"].data_ptr(), T["pos"].data_ptr(),
+                                          T["cb32"].data_ptr(), T["cboff"].data_ptr(),
+                                          bias.data_ptr() if bias is not None else None, qp.data_ptr(), nq, qp.stride(0),
+                                          qc.data_ptr(), metric_id(metric), k, vals.data_ptr(), ids.data_ptr(),
+                                          sc.data_ptr(), sc.numel(), _stream()), "perdim_scan_topk")
+        return host.to_host(ids).view(np.uint32), host.to_host(vals)
+
+    def _row_sqnorms(self, cd: torch.Tensor) -> torch.Tensor:
+        """|y^_i|^2 of every stored row (decode in row batches + b200vq_row_sqnorms)."""
+        from b200vq import ops
+        T = self._tables()
+        n = int(cd.shape[0])
+        out = torch.empty((n,), dtype=torch.float32, device=cd.device)
+        step = max(1, (1 << 28) // max(1, 4 * self.D))
+        lib = _lib.load()
+        for s in range(0, n, step):
+            e = min(n, s + step)
+            yh = torch.empty((e - s, self.D), dtype=torch.float32, device=cd.device)
+            check(lib.b200vq_perdim_decode_f32(cd[s:e].data_ptr(), e - s, self.code_size, self.D, T["bits"].data_ptr(),
+                                               T["pos"].data_ptr(), T["cb32"].data_ptr(), T["cboff"].data_ptr(),
+                                               yh.data_ptr(), yh.stride(0), _stream()), "perdim_decode_f32")
+            out[s:e] = ops.row_sqnorms(yh)
+        return out
+
     def get_compression_ratio(self, X: np.ndarray) -> float:
         return float(int(X.shape[1]) * 4 / self.code_size)
