@@ -161,11 +161,12 @@ def caq_encode_t(oT: torch.Tensor, bits: int, c_rot: Optional[torch.Tensor] = No
     ln, n = oT.shape
     if oT.stride(1) != 1:
         raise ValueError("caq_encode_t: oT must be row-major (len, n)")
-    codesT = torch.empty((ln, n), dtype=torch.int16, device=oT.device)
+    ldc = (n + 1) // 2 * 2
+    codesT = torch.empty((ln, ldc), dtype=torch.int16, device=oT.device)[:, :n]
     outs = [torch.empty((n,), dtype=torch.float32, device=oT.device) for _ in range(5)]
     check(_lib.load().b200vq_caq_encode_t(oT.data_ptr(), n, oT.stride(0), ln,
                                           c_rot.data_ptr() if c_rot is not None else None, bits, rd_lmt,
-                                          C.c_float(adj_eps), codesT.data_ptr(), n,
+                                          C.c_float(adj_eps), codesT.data_ptr(), ldc,
                                           *[o.data_ptr() for o in outs], _stream()), "caq_encode_t")
     return codesT, outs
 
@@ -180,12 +181,13 @@ def caq_encode_t_segments(oT: torch.Tensor, plan, rd_lmt: int = 6, adj_eps: floa
     offs = list(np.cumsum([0] + lens[:-1]))
     if sum(lens) != d_pad or (n > 1 and oT.stride(1) != 1):
         raise ValueError("caq_encode_t_segments: oT must be (sum of segment lengths, n) row-major")
-    codesT = torch.empty((d_pad, n), dtype=torch.int16, device=oT.device)
+    ldc = (n + 1) // 2 * 2          # even row stride: the encoder brings two codes per 4-byte cp.async
+    codesT = torch.empty((d_pad, ldc), dtype=torch.int16, device=oT.device)[:, :n]
     outs = [torch.empty((ns, n), dtype=torch.float32, device=oT.device) for _ in range(5)]
     arr = lambda v: (C.c_int * ns)(*[int(x) for x in v])
     check(_lib.load().b200vq_caq_encode_t_segments(oT.data_ptr(), n, oT.stride(0), ns, arr(offs), arr(lens),
                                                    arr([b for _, b in plan]), rd_lmt, C.c_float(adj_eps),
-                                                   codesT.data_ptr(), n, *[o.data_ptr() for o in outs], _stream()),
+                                                   codesT.data_ptr(), ldc, *[o.data_ptr() for o in outs], _stream()),
           "caq_encode_t_segments")
     return codesT, outs
 

@@ -146,15 +146,209 @@ caq_encode_row(const int64_t i, const float* __restrict__ oT, int64_t ld, int le
     error[i] = (float)fac_error;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Warp-tiled form of the same encoder. The per-row arithmetic (order, rounding) is caq_encode_row's, but the
+// residuals and working codes of a warp's 32 rows stream through shared memory in tiles of 32 dimensions,
+// brought in by cp.async one tile ahead: the sweep is a latency-bound fp64 chain, and with the loads issued
+// from inside it (the store of dimension j may alias the load of j + 1 as far as the compiler knows) every
+// step used to wait on L2 / DRAM (ncu: 36 % of the samples on the code load alone). The exact re-accumulation of
+// <o, oa> and |oa|^2 that follows every sweep is folded into the sweep (dimension j's code is final once its
+// step is done, and the sums run over j in the same order), which saves a pass over the segment per round.
+constexpr int CW_TILE = 16;
+struct CaqWarpTile {
+    float o[2][CW_TILE][32];
+    uint16_t c[2][CW_TILE][32];
+};
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, bool valid) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    const int sz = valid ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// One warp = rows i0 .. i0 + 31 of one segment (i0 % 32 == 0). Lanes past n run on row n - 1's data and store nothing.
+__device__ void caq_encode_rows_warp(CaqWarpTile& T, const int64_t i0, const int64_t n, const float* __restrict__ oT,
+                                     int64_t ld, int len, const float* __restrict__ c_rot, int bits, int rd_lmt,
+                                     float adj_eps, uint16_t* __restrict__ codesT, int64_t ldc,
+                                     float* __restrict__ l2norm, float* __restrict__ rescale, float* __restrict__ error,
+                                     float* __restrict__ mse, float* __restrict__ cosv) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = i0 + lane;
+    const bool live = i < n;
+    const int ntile = (len + CW_TILE - 1) / CW_TILE;
+    const bool pair_codes = ((ldc & 1) == 0) && ((reinterpret_cast<uintptr_t>(codesT) & 3) == 0);
+    // tile t of the residuals (and, with_codes, of the working codes) -> buffer t & 1, as one cp.async group
+    auto load_tile = [&](int t, bool with_codes) {
+        const int buf = t & 1;
+        if (t < ntile) {
+            const int j0 = t * CW_TILE;
+            const int nj = min(CW_TILE, len - j0);
+            for (int jj = 0; jj < nj; ++jj) {
+                cp_async4(&T.o[buf][jj][lane], oT + (int64_t)(j0 + jj) * ld + (live ? i : n - 1), true);
+                if (with_codes && pair_codes && lane < 16)
+                    cp_async4(&T.c[buf][jj][2 * lane], codesT + (int64_t)(j0 + jj) * ldc + i0 + 2 * lane,
+                              i0 + 2 * lane < ldc);
+            }
+        }
+        cp_async_commit();
+    };
+    auto finish_tile_load = [&](int t, bool with_codes) {     // codes of an odd-stride scratch: plain loads
+        if (with_codes && !pair_codes) {
+            const int buf = t & 1, j0 = t * CW_TILE, nj = min(CW_TILE, len - j0);
+            for (int jj = 0; jj < nj; ++jj) T.c[buf][jj][lane] = live ? codesT[(int64_t)(j0 + jj) * ldc + i] : (uint16_t)0;
+        }
+    };
+    auto store_codes = [&](int t) {
+        const int buf = t & 1, j0 = t * CW_TILE, nj = min(CW_TILE, len - j0);
+        if (live)
+            for (int jj = 0; jj < nj; ++jj) codesT[(int64_t)(j0 + jj) * ldc + i] = T.c[buf][jj][lane];
+    };
+    // walk the segment: body(j, o_j, code slot) for j = 0 .. len-1 in order
+    auto walk = [&](bool read_codes, bool write_codes, auto&& body) {
+        __syncwarp();
+        load_tile(0, read_codes);
+        for (int t = 0; t < ntile; ++t) {
+            load_tile(t + 1, read_codes);
+            cp_async_wait<1>();
+            __syncwarp();
+            finish_tile_load(t, read_codes);
+            const int buf = t & 1, j0 = t * CW_TILE, nj = min(CW_TILE, len - j0);
+            for (int jj = 0; jj < nj; ++jj) {
+                float v = T.o[buf][jj][lane];
+                if (c_rot) v = __fsub_rn(v, __ldg(c_rot + j0 + jj));
+                body(j0 + jj, v, T.c[buf][jj][lane]);
+            }
+            if (write_codes) store_codes(t);
+            __syncwarp();
+        }
+        cp_async_wait<0>();
+    };
+
+    float mx = 0.f, mn = 0.f, fsum = 0.f, fsq = 0.f;
+    walk(false, false, [&](int j, float v, uint16_t&) {
+        if (j == 0) { mx = v; mn = v; }
+        mx = fmaxf(mx, v);
+        mn = fminf(mn, v);
+        fsum = __fadd_rn(fsum, v);
+        fsq = __fadd_rn(fsq, __fmul_rn(v, v));
+    });
+    const double o_l2sqr = (double)fsq;
+    if (bits == 0) {
+        if (live) {
+            for (int j = 0; j < len; ++j) codesT[(int64_t)j * ldc + i] = 0;
+            l2norm[i] = (float)sqrt(o_l2sqr);
+            rescale[i] = 0.f;
+            error[i] = 0.f;
+            mse[i] = __fdiv_rn(fsq, (float)len);
+            cosv[i] = 0.f;
+        }
+        return;
+    }
+    const int code_max = (1 << bits) - 1;
+    const double v_mx = (double)((mx > -mn) ? mx : -mn);
+    const double v_mi = -v_mx;
+    const double delta = dsub(v_mx, v_mi) / (double)(code_max + 1);
+    const float fmi = (float)v_mi, fdelta = (float)delta;
+    double ip_o_code = 0.0;
+    unsigned long long code_l2sqr = 0;
+    uint32_t code_sum = 0;
+    walk(false, true, [&](int, float v, uint16_t& slot) {
+        float cf = 0.f;
+        if (delta != 0.0) {
+            cf = floorf(__fdiv_rn(__fsub_rn(v, fmi), fdelta));
+            if (cf > (float)code_max) cf = (float)code_max;
+        }
+        ip_o_code = dadd(ip_o_code, (double)__fmul_rn(cf, v));
+        const int c = (int)cf;
+        slot = (uint16_t)c;
+        code_l2sqr += (unsigned long long)(c * c);
+        code_sum += (uint32_t)c;
+    });
+    const double dd = dmul(delta, delta);
+    double ip = dadd(dmul(ip_o_code, delta), dmul(dadd(v_mi, dmul(0.5, delta)), (double)fsum));
+    double oa2 = dadd(dmul(dd, (double)code_l2sqr),
+                      dmul(dadd(dd, dmul(dmul(2.0, delta), v_mi)), (double)code_sum));
+    oa2 = dadd(oa2, dmul(dadd(dadd(dmul(0.25, dd), dmul(delta, v_mi)), dmul(v_mi, v_mi)), (double)len));
+
+    // lanes leave the adjustment at different rounds; the warp keeps walking (cooperative loads) while any lane is in
+    bool adjusting = live && rd_lmt && oa2 != 0.0;
+    const double re_eps = dmul((double)adj_eps, oa2);
+    for (int round = 1; __any_sync(FULL_MASK, adjusting); ++round) {
+        int adj_cnt = 0;
+        double cl2 = 0.0, cip = 0.0;
+        walk(true, true, [&](int, float of, uint16_t& slot) {
+            if (!adjusting) return;
+            const int c0 = slot;
+            int c = c0, curr = 0;
+            double oa = dadd(dmul(dadd((double)c0, 0.5), delta), v_mi);
+            const double tmp = dsub(oa2, dmul(oa, oa));
+            const double ip_delta = dmul(delta, (double)of);
+            while (c < code_max) {
+                const double nq = dadd(oa, delta);
+                const double nl = dadd(tmp, dmul(nq, nq));
+                const double nip = dadd(ip, ip_delta);
+                if (dmul(dadd(dmul(ip, ip), re_eps), nl) >= dmul(dmul(nip, nip), oa2)) break;
+                c++; ip = nip; oa = nq; oa2 = nl; curr++;
+            }
+            while (c > 0) {
+                const double nq = dsub(oa, delta);
+                const double nl = dadd(tmp, dmul(nq, nq));
+                const double nip = dsub(ip, ip_delta);
+                if (dmul(dadd(dmul(ip, ip), re_eps), nl) >= dmul(dmul(nip, nip), oa2)) break;
+                c--; ip = nip; oa = nq; oa2 = nl; curr++;
+            }
+            if (c != c0) {
+                slot = (uint16_t)c;
+                adj_cnt += curr;
+            }
+            // exact re-accumulation over the round's final codes (the reference's separate pass, same order)
+            const double q = dadd(dmul(dadd((double)c, 0.5), delta), v_mi);
+            cip = dadd(cip, dmul(q, (double)of));
+            cl2 = dadd(cl2, dmul(q, q));
+        });
+        if (adjusting) {
+            if (rd_lmt && round >= rd_lmt) {
+                adjusting = false;
+            } else {
+                oa2 = cl2;
+                ip = cip;
+                if (adj_cnt == 0) adjusting = false;
+            }
+        }
+    }
+    const double o_l2norm = sqrt(o_l2sqr);
+    double fac_rescale = (ip != 0.0) ? o_l2sqr / ip : 0.0;
+    const double fac_error =
+        dmul(dmul(o_l2sqr, (double)1.9f), sqrt(dsub(dmul(o_l2sqr, oa2) / dmul(ip, ip), 1.0) / (double)(len - 1)));
+    float diff = 0.f;
+    walk(true, false, [&](int, float ov, uint16_t& slot) {
+        const float oa = __fadd_rn(__fmul_rn((float)slot, (float)delta), (float)v_mi);
+        const float d = __fsub_rn(ov, oa);
+        diff = __fadd_rn(diff, __fmul_rn(d, d));
+    });
+    if (live) {
+        mse[i] = __fdiv_rn(diff, (float)len);
+        cosv[i] = (bits > 1) ? (float)((ip / o_l2norm) / sqrt(oa2)) : 0.f;
+        if (v_mx != 0.0) fac_rescale = dmul(fac_rescale, v_mx);
+        l2norm[i] = (float)o_l2norm;
+        rescale[i] = (float)fac_rescale;
+        error[i] = (float)fac_error;
+    }
+}
+
 __global__ void __launch_bounds__(128)
 caq_encode_t_kernel(const float* __restrict__ oT, int64_t n, int64_t ld, int len,
                     const float* __restrict__ c_rot, int bits, int rd_lmt, float adj_eps,
                     uint16_t* __restrict__ codesT, int64_t ldc, float* __restrict__ l2norm,
                     float* __restrict__ rescale, float* __restrict__ error, float* __restrict__ mse,
                     float* __restrict__ cosv) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    caq_encode_row(i, oT, ld, len, c_rot, bits, rd_lmt, adj_eps, codesT, ldc, l2norm, rescale, error, mse, cosv);
+    extern __shared__ __align__(16) unsigned char caq_smem[];
+    CaqWarpTile& T = reinterpret_cast<CaqWarpTile*>(caq_smem)[threadIdx.x >> 5];
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~(int64_t)31;
+    if (i0 >= n) return;
+    caq_encode_rows_warp(T, i0, n, oT, ld, len, c_rot, bits, rd_lmt, adj_eps, codesT, ldc, l2norm, rescale, error, mse, cosv);
 }
 
 // Every segment of the plan in ONE grid (blockIdx.y = segment, longest first): the rows of a segment are a
@@ -169,13 +363,15 @@ caq_encode_t_segments_kernel(const float* __restrict__ oT, int64_t n, int64_t ld
                              int rd_lmt, float adj_eps, uint16_t* __restrict__ codesT, int64_t ldc,
                              float* __restrict__ l2norm, float* __restrict__ rescale, float* __restrict__ error,
                              float* __restrict__ mse, float* __restrict__ cosv) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    extern __shared__ __align__(16) unsigned char caq_smem[];
+    CaqWarpTile& T = reinterpret_cast<CaqWarpTile*>(caq_smem)[threadIdx.x >> 5];
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~(int64_t)31;
+    if (i0 >= n) return;
     const int s = blockIdx.y;
     const int off = segs.off[s], slot = segs.slot[s];
     const int64_t fo = (int64_t)slot * n;
-    caq_encode_row(i, oT + (int64_t)off * ld, ld, segs.len[s], nullptr, segs.bits[s], rd_lmt, adj_eps,
-                   codesT + (int64_t)off * ldc, ldc, l2norm + fo, rescale + fo, error + fo, mse + fo, cosv + fo);
+    caq_encode_rows_warp(T, i0, n, oT + (int64_t)off * ld, ld, segs.len[s], nullptr, segs.bits[s], rd_lmt, adj_eps,
+                         codesT + (int64_t)off * ldc, ldc, l2norm + fo, rescale + fo, error + fo, mse + fo, cosv + fo);
 }
 
 // codesT (len, ldc) uint16 -> packed (n, row_bytes): MSB-first bit string, `bits` per dimension.
@@ -265,7 +461,9 @@ extern "C" int b200vq_caq_encode_t(const float* oT, int64_t n, int64_t ld, int l
     VQ_CHECK_ARG(n == 0 || (oT && codesT && l2norm && rescale && error && mse && cosv), "caq_encode_t: null pointer");
     if (n == 0) return B200VQ_OK;
     const int block = 128;
-    caq_encode_t_kernel<<<(unsigned)((n + block - 1) / block), block, 0, as_stream(stream)>>>(
+    const size_t smem = (block / 32) * sizeof(caq::CaqWarpTile);
+    VQ_CUDA(cudaFuncSetAttribute(caq::caq_encode_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    caq_encode_t_kernel<<<(unsigned)((n + block - 1) / block), block, smem, as_stream(stream)>>>(
         oT, n, ld, len, c_rot, bits, rd_lmt, adj_eps, codesT, ldc, l2norm, rescale, error, mse, cosv);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
@@ -298,7 +496,9 @@ extern "C" int b200vq_caq_encode_t_segments(const float* oT, int64_t n, int64_t 
     }
     const int block = 128;
     dim3 grid((unsigned)((n + block - 1) / block), (unsigned)nseg);
-    caq_encode_t_segments_kernel<<<grid, block, 0, as_stream(stream)>>>(oT, n, ld, segs, rd_lmt, adj_eps, codesT, ldc,
+    const size_t smem = (block / 32) * sizeof(caq::CaqWarpTile);
+    VQ_CUDA(cudaFuncSetAttribute(caq::caq_encode_t_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    caq_encode_t_segments_kernel<<<grid, block, smem, as_stream(stream)>>>(oT, n, ld, segs, rd_lmt, adj_eps, codesT, ldc,
                                                                        l2norm, rescale, error, mse, cosv);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
