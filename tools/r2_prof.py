@@ -43,7 +43,27 @@ elif mode == "caq":
     oT = eng._project(x, transpose_out=True)
     for _ in range(2):
         v, _ = E.caq_encode_t_segments(oT, eng.plan)
+elif mode == "assign":
+    # C5 shape: 1 Mi x 1024, M = 32; prints the screen's statistics and the event time of the whole call
+    n, D, M = 1 << 20, 1024, int(sys.argv[2]) if len(sys.argv) > 2 else 32
+    x = data(n, D)
+    C = dpq.pq_train(data(65536, D, row0=1 << 40), M, 8, niter=4, seed=1234)
+    cn = ops.pq_centroid_norms(C)
+    st = torch.zeros(8, dtype=torch.int64, device=dev)
+    out = ops.pq_assign(x, C, cn, impl="tc", stats=st)
+    torch.cuda.synchronize()
+    print("stats pairs / candidates / fix-up entries:", st[:3].tolist(), "of", n * M)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):
+        ops.pq_assign(x, C, cn, out=out, impl="tc")
+    a.record()
+    for _ in range(10):
+        ops.pq_assign(x, C, cn, out=out, impl="tc")
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 10
+    print(f"assign_tc {ms:.3f} ms  {2.0 * n * D * 256 / ms / 1e9:.1f} TFLOP/s")
 else:
-    raise SystemExit("mode: scan | rotate | caq")
+    raise SystemExit("mode: scan | rotate | caq | assign")
 torch.cuda.synchronize()
 print("ok", mode)
