@@ -44,6 +44,57 @@ __device__ __forceinline__ int lvq_load8(const float* __restrict__ xr, const flo
     return cnt;
 }
 
+// clip(rint(a / delta), 0, levels) with the reference's IEEE division and half-to-even rounding (the exact form).
+__device__ __forceinline__ unsigned lvq_quant_exact(float a, float delta, int levels) {
+    const int q = __float2int_rn(__fdiv_rn(a, delta));
+    return (unsigned)(q < 0 ? 0 : (q > levels ? levels : q));
+}
+// The same eight indices without the division in the common case. t = a * (1 / delta) is within 1.8e-7 t of the true
+// quotient, and so is the rounded quotient, so both round to the same integer unless a half-integer lies within
+// 6e-7 t <= 1.6e-4 of t (levels <= 255); t + 1.5 * 2^23 rounds t to the nearest even integer and leaves it in the low
+// mantissa bits, which IMAD shifts into the packed word (the exponent bits are a constant, subtracted once). 0 <= a <=
+// span gives 0 <= rint <= levels, so nothing is clipped here. A thread whose group has a value within 2e-4 of a
+// half-integer, or a NaN, redoes the group with the exact form (about 0.3 % of the groups).
+// hi = indices 0..3, lo = indices 4..7, each MSB first in 4 B bits.
+__device__ __forceinline__ void lvq_quant8(const float (&v)[8], float lo_v, float delta, float inv, int B, int levels,
+                                           uint32_t& hi, uint32_t& lo) {
+    const uint32_t mul = 1u << B;
+    uint32_t w[2] = {0u, 0u};
+    bool risky = false;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float t = __fmul_rn(__fsub_rn(v[k], lo_v), inv);
+        const float tr = __fadd_rn(t, 12582912.f);
+        const float d = __fsub_rn(t, __fsub_rn(tr, 12582912.f));
+        risky |= !(fabsf(d) <= 0.4998f);
+        w[k >> 2] = w[k >> 2] * mul + __float_as_uint(tr);
+    }
+    const uint32_t bias = 0x4B400000u * (1u + mul + mul * mul + mul * mul * mul);   // mod 2^32, like the sums
+    hi = w[0] - bias;
+    lo = w[1] - bias;
+    if (risky) {
+        hi = lo = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            hi = (hi << B) | lvq_quant_exact(__fsub_rn(v[k], lo_v), delta, levels);
+            lo = (lo << B) | lvq_quant_exact(__fsub_rn(v[4 + k], lo_v), delta, levels);
+        }
+    }
+}
+// B bytes of one group, most significant first
+__device__ __forceinline__ void lvq_store_group(uint8_t* o, uint32_t hi, uint32_t lo, int B, bool wide) {
+    if (wide && B == 8) {
+        *reinterpret_cast<uint2*>(o) = make_uint2(__byte_perm(hi, 0, 0x0123), __byte_perm(lo, 0, 0x0123));
+    } else if (wide && B == 4) {
+        *reinterpret_cast<uint32_t*>(o) = __byte_perm((hi << 16) | lo, 0, 0x0123);
+    } else if (wide && B == 2) {
+        *reinterpret_cast<uint16_t*>(o) = (uint16_t)__byte_perm((hi << 8) | lo, 0, 0x3201);
+    } else {
+        const unsigned long long acc = ((unsigned long long)hi << (4 * B)) | lo;
+        for (int b = 0; b < B; ++b) o[b] = (uint8_t)(acc >> (8 * (B - 1 - b)));
+    }
+}
+
 __global__ void __launch_bounds__(256) lvq_encode_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
                                                          const float* __restrict__ mu, int B,
                                                          uint8_t* __restrict__ codes) {
@@ -54,10 +105,14 @@ __global__ void __launch_bounds__(256) lvq_encode_kernel(const float* __restrict
     const int levels = (1 << B) - 1;
     const bool vec = (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(mu) & 15) == 0);
+    // a lane's B bytes go out in one store when the row pitch keeps them aligned (B = 8, 4, 2)
+    const bool wide = (B == 8 || B == 4 || B == 2) && code_size % B == 0 &&
+                      (reinterpret_cast<uintptr_t>(codes) % B) == 0;
     for (int64_t row = wid; row < n; row += nw) {
         const float* xr = x + row * ldx;
         uint8_t* code = codes + row * (int64_t)code_size;
         float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+#pragma unroll 4
         for (int j = 8 * lane; j < D; j += 256) {
             float r[8];
             const int cnt = lvq_load8(xr, mu, j, D, vec, r);
@@ -75,24 +130,113 @@ __global__ void __launch_bounds__(256) lvq_encode_kernel(const float* __restrict
         }
         const float span = __fsub_rn(hi, lo);
         const float delta = span == 0.0f ? 1.17549435e-38f : __fdiv_rn(span, (float)levels);
+        const float inv = __fdiv_rn(1.0f, delta);
+        // second read of the row: L1 / L2
+#pragma unroll 2
         for (int j = 8 * lane; j < D; j += 256) {
             float r[8];
             const int cnt = lvq_load8(xr, mu, j, D, vec, r);
-            unsigned long long acc = 0ull;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                int q = 0;
-                if (k < cnt) {
-                    q = __float2int_rn(__fdiv_rn(__fsub_rn(r[k], lo), delta));   // rint: half to even, as np.round
-                    q = q < 0 ? 0 : (q > levels ? levels : q);
-                }
-                acc = (acc << B) | (unsigned long long)q;
-            }
-            // 8 B bits, most significant first; a ragged last group keeps ceil(cnt B / 8) bytes
-            const int nb = (cnt * B + 7) >> 3;
             uint8_t* o = code + (j >> 3) * B;
-            for (int b = 0; b < nb; ++b) o[b] = (uint8_t)(acc >> (8 * (B - 1 - b)));
+            if (cnt == 8) {
+                uint32_t h32, l32;
+                lvq_quant8(r, lo, delta, inv, B, levels, h32, l32);
+                lvq_store_group(o, h32, l32, B, wide);
+            } else {
+                // ragged last group: ceil(cnt B / 8) bytes
+                unsigned long long acc = 0ull;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    acc = (acc << B) | (unsigned long long)(k < cnt ? lvq_quant_exact(__fsub_rn(r[k], lo), delta, levels) : 0u);
+                const int nb = (cnt * B + 7) >> 3;
+                for (int b = 0; b < nb; ++b) o[b] = (uint8_t)(acc >> (8 * (B - 1 - b)));
+            }
         }
+        if (lane == 0) {
+            lvq_store_f32(code + index_bytes, lo);
+            lvq_store_f32(code + index_bytes + 4, delta);
+        }
+    }
+}
+
+// Four indices (MSB first, 4 B bits) by the scheme of lvq_quant8.
+__device__ __forceinline__ uint32_t lvq_quant4(const float4& v, float lo_v, float delta, float inv, int B, int levels) {
+    const uint32_t mul = 1u << B;
+    const float e[4] = {v.x, v.y, v.z, v.w};
+    uint32_t w = 0u;
+    bool risky = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float t = __fmul_rn(__fsub_rn(e[k], lo_v), inv);
+        const float tr = __fadd_rn(t, 12582912.f);
+        const float d = __fsub_rn(t, __fsub_rn(tr, 12582912.f));
+        risky |= !(fabsf(d) <= 0.4998f);
+        w = w * mul + __float_as_uint(tr);
+    }
+    w -= 0x4B400000u * (1u + mul + mul * mul + mul * mul * mul);
+    if (risky) {
+        w = 0u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) w = (w << B) | lvq_quant_exact(__fsub_rn(e[k], lo_v), delta, levels);
+    }
+    return w;
+}
+
+// Aligned rows, D % 4 == 0, D <= 128 NK, even B: the row lives in registers. Lane l owns the 4-dimension groups
+// 32 k + l (every 128-bit load instruction of the warp is one contiguous 512-byte run; a lane owning 8 consecutive
+// dimensions would touch every 32-byte sector twice), so x is read from HBM once with the whole row in flight and the
+// second pass costs no loads. A group is 4 B bits = B / 2 whole bytes, stored by its lane (contiguous over the warp).
+// Same arithmetic as lvq_encode_kernel.
+template <int NK>
+__global__ void __launch_bounds__(128, NK <= 8 ? 6 : (NK <= 16 ? 4 : (NK <= 24 ? 3 : 2))) lvq_encode_reg_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                                                             const float* __restrict__ mu, int B,
+                                                             uint8_t* __restrict__ codes) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int index_bytes = (D * B) >> 3, code_size = index_bytes + 8;
+    const int levels = (1 << B) - 1;
+    const int ngroups = D >> 2, gb = B >> 1;                      // bytes per group
+    const bool wide = (code_size % gb) == 0 && (reinterpret_cast<uintptr_t>(codes) % gb) == 0;
+    extern __shared__ __align__(16) float4 lvq_mu_s[];            // the mean, staged once per CTA
+    for (int i = threadIdx.x; i < ngroups; i += blockDim.x) lvq_mu_s[i] = __ldg(reinterpret_cast<const float4*>(mu) + i);
+    __syncthreads();
+    for (int64_t row = wid; row < n; row += nw) {
+        const float4* xr = reinterpret_cast<const float4*>(x + row * ldx) + lane;
+        const float4* mr = lvq_mu_s + lane;
+        uint8_t* code = codes + row * (int64_t)code_size;
+        float4 r[NK];
+#pragma unroll
+        for (int k = 0; k < NK; ++k)
+            if (32 * k + lane < ngroups) r[k] = ld_stream_f4(xr + 32 * k);
+        asm volatile("" ::: "memory");     // every load of the row is issued before the first use of one
+        float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+#pragma unroll
+        for (int k = 0; k < NK; ++k)
+            if (32 * k + lane < ngroups) {
+                const float4 m = mr[32 * k];
+                r[k] = make_float4(__fsub_rn(r[k].x, m.x), __fsub_rn(r[k].y, m.y), __fsub_rn(r[k].z, m.z),
+                                   __fsub_rn(r[k].w, m.w));
+                lo = fminf(fminf(fminf(lo, r[k].x), fminf(r[k].y, r[k].z)), r[k].w);
+                hi = fmaxf(fmaxf(fmaxf(hi, r[k].x), fmaxf(r[k].y, r[k].z)), r[k].w);
+            }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(FULL_MASK, lo, o));
+            hi = fmaxf(hi, __shfl_xor_sync(FULL_MASK, hi, o));
+        }
+        const float span = __fsub_rn(hi, lo);
+        const float delta = span == 0.0f ? 1.17549435e-38f : __fdiv_rn(span, (float)levels);
+        const float inv = __fdiv_rn(1.0f, delta);
+#pragma unroll
+        for (int k = 0; k < NK; ++k)
+            if (32 * k + lane < ngroups) {
+                const uint32_t w = lvq_quant4(r[k], lo, delta, inv, B, levels);
+                uint8_t* o = code + (32 * k + lane) * gb;
+                if (wide && B == 8) *reinterpret_cast<uint32_t*>(o) = __byte_perm(w, 0, 0x0123);
+                else if (wide && B == 4) *reinterpret_cast<uint16_t*>(o) = (uint16_t)__byte_perm(w, 0, 0x3201);
+                else
+                    for (int b = 0; b < gb; ++b) o[b] = (uint8_t)(w >> (8 * (gb - 1 - b)));
+            }
         if (lane == 0) {
             lvq_store_f32(code + index_bytes, lo);
             lvq_store_f32(code + index_bytes + 4, delta);
@@ -110,6 +254,8 @@ __global__ void __launch_bounds__(256) lvq_decode_kernel(const uint8_t* __restri
     const unsigned levels = (1u << B) - 1u;
     const bool vec = (ldo % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(mu) & 15) == 0);
+    const bool wide = (B == 8 || B == 4 || B == 2) && code_size % B == 0 &&
+                      (reinterpret_cast<uintptr_t>(codes) % B) == 0;
     for (int64_t row = wid; row < n; row += nw) {
         const uint8_t* code = codes + row * (int64_t)code_size;
         const float lo = lvq_load_f32(code + index_bytes), delta = lvq_load_f32(code + index_bytes + 4);
@@ -119,7 +265,18 @@ __global__ void __launch_bounds__(256) lvq_decode_kernel(const uint8_t* __restri
             const int nb = (cnt * B + 7) >> 3;
             const uint8_t* c = code + (j >> 3) * B;
             unsigned long long acc = 0ull;
-            for (int b = 0; b < B; ++b) acc = (acc << 8) | (unsigned long long)(b < nb ? __ldg(c + b) : 0);
+            if (wide && cnt == 8) {
+                if (B == 8) {
+                    const uint2 w = __ldg(reinterpret_cast<const uint2*>(c));
+                    acc = ((unsigned long long)__byte_perm(w.x, 0, 0x0123) << 32) | __byte_perm(w.y, 0, 0x0123);
+                } else if (B == 4) {
+                    acc = __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(c)), 0, 0x0123);
+                } else {
+                    acc = __byte_perm((uint32_t)__ldg(reinterpret_cast<const uint16_t*>(c)), 0, 0x3201) & 0xFFFFu;
+                }
+            } else {
+                for (int b = 0; b < B; ++b) acc = (acc << 8) | (unsigned long long)(b < nb ? __ldg(c + b) : 0);
+            }
             float r[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
@@ -178,6 +335,19 @@ extern "C" int b200vq_lvq_encode(const float* x, int64_t n, int64_t ldx, int D, 
     VQ_CHECK_ARG(num_bits >= 1 && num_bits <= 8, "lvq_encode: num_bits must be in [1, 8], got %d", num_bits);
     if (n == 0) return B200VQ_OK;
     VQ_CHECK_ARG(x && mu && codes, "lvq_encode: null pointer");
+    const bool reg_ok = D % 4 == 0 && D <= 4096 && num_bits % 2 == 0 && ldx % 4 == 0 && ((uintptr_t)x & 15) == 0 &&
+                        ((uintptr_t)mu & 15) == 0;
+    if (reg_ok) {
+        int64_t g = (n * 32 + 127) / 128;
+        const int64_t cap = (int64_t)device_sm_count() * 32;
+        if (g > cap) g = cap;
+        const int nk = (D + 127) / 128;
+        auto k = nk <= 8 ? lvq_encode_reg_kernel<8> : nk <= 16 ? lvq_encode_reg_kernel<16>
+                 : nk <= 24 ? lvq_encode_reg_kernel<24> : lvq_encode_reg_kernel<32>;
+        k<<<(int)g, 128, (size_t)D * sizeof(float), as_stream(stream)>>>(x, n, ldx, D, mu, num_bits, codes);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     lvq_encode_kernel<<<lvq_grid(n), 256, 0, as_stream(stream)>>>(x, n, ldx, D, mu, num_bits, codes);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;

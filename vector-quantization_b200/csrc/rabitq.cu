@@ -99,6 +99,100 @@ __global__ void rabitq1_encode_kernel(const float* __restrict__ x, int64_t n, in
     }
 }
 
+// The same encoder for 16-byte aligned rows with D % 4 == 0: a lane owns 4 consecutive dimensions of every
+// 128-dimension block (one 128-bit load of x and of the centroid), its 4 sign bits are merged with the neighbours'
+// by three xor-shuffles into the block's four 32-bit words, and the three sums run on four independent chains.
+// (The reference's sums are numpy / faiss reductions in their own order; parity on the two factors is to 1e-6.)
+__global__ void __launch_bounds__(256)
+rabitq1_encode_vec_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
+                          const float* __restrict__ centroid, int metric, uint8_t* __restrict__ codes) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int nbytes = (D + 7) >> 3;
+    const int code_size = nbytes + 8;
+    const float inv_d_sqrt = 1.0f / sqrtf((float)D);
+    const bool word_rows = (code_size & 3) == 0 && ((reinterpret_cast<uintptr_t>(codes) & 3) == 0);
+    for (int64_t row = wid; row < n; row += nw) {
+        const float* xr = x + row * ldx;
+        uint8_t* code = codes + row * (int64_t)code_size;
+        float nr[4] = {0.f, 0.f, 0.f, 0.f}, o2[4] = {0.f, 0.f, 0.f, 0.f}, ad[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int j0 = 0; j0 < D; j0 += 256) {
+            // two 128-dimension blocks per step: four 128-bit loads in flight per lane
+            float4 v[2], c[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int j = j0 + 128 * u + 4 * lane;
+                v[u] = j < D ? ld_stream_f4(reinterpret_cast<const float4*>(xr + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                c[u] = (j < D && centroid) ? __ldg(reinterpret_cast<const float4*>(centroid + j))
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (j0 + 128 * u >= D) break;     // warp-uniform
+                const float o0 = v[u].x - c[u].x, o1 = v[u].y - c[u].y, o2_ = v[u].z - c[u].z, o3 = v[u].w - c[u].w;
+                nr[0] = __fmaf_rn(o0, o0, nr[0]);
+                nr[1] = __fmaf_rn(o1, o1, nr[1]);
+                nr[2] = __fmaf_rn(o2_, o2_, nr[2]);
+                nr[3] = __fmaf_rn(o3, o3, nr[3]);
+                o2[0] = __fmaf_rn(v[u].x, v[u].x, o2[0]);
+                o2[1] = __fmaf_rn(v[u].y, v[u].y, o2[1]);
+                o2[2] = __fmaf_rn(v[u].z, v[u].z, o2[2]);
+                o2[3] = __fmaf_rn(v[u].w, v[u].w, o2[3]);
+                ad[0] += fabsf(o0);
+                ad[1] += fabsf(o1);
+                ad[2] += fabsf(o2_);
+                ad[3] += fabsf(o3);
+                // bit j % 8 of byte j / 8: nibble -> byte -> half word -> word (held by lanes 0, 8, 16, 24)
+                unsigned w = (o0 > 0.f ? 1u : 0u) | (o1 > 0.f ? 2u : 0u) | (o2_ > 0.f ? 4u : 0u) | (o3 > 0.f ? 8u : 0u);
+                w |= __shfl_xor_sync(FULL_MASK, w, 1) << 4;
+                w |= __shfl_xor_sync(FULL_MASK, w, 2) << 8;
+                w |= __shfl_xor_sync(FULL_MASK, w, 4) << 16;
+                const int byte0 = ((j0 + 128 * u) >> 3) + (lane >> 1);
+                if ((lane & 7) == 0 && byte0 < nbytes) {
+                    if (word_rows && byte0 + 4 <= nbytes) {
+                        *reinterpret_cast<uint32_t*>(code + byte0) = w;
+                    } else {
+#pragma unroll
+                        for (int b = 0; b < 4; ++b)
+                            if (byte0 + b < nbytes) code[byte0 + b] = (uint8_t)(w >> (8 * b));
+                    }
+                }
+            }
+        }
+        float norm = (nr[0] + nr[1]) + (nr[2] + nr[3]), orl2 = (o2[0] + o2[1]) + (o2[2] + o2[3]);
+        float dp = (ad[0] + ad[1]) + (ad[2] + ad[3]);
+        for (int o = 16; o > 0; o >>= 1) {
+            norm += __shfl_xor_sync(FULL_MASK, norm, o);
+            orl2 += __shfl_xor_sync(FULL_MASK, orl2, o);
+            dp += __shfl_xor_sync(FULL_MASK, dp, o);
+        }
+        if (lane == 0) {
+            const float eps = 1.1920929e-07f;  // std::numeric_limits<float>::epsilon()
+            float sq = sqrtf(norm);
+            float inv_norm = (fabsf(norm) < eps) ? 1.0f : (1.0f / sq);
+            float dpn = dp * inv_norm;
+            dpn *= inv_d_sqrt;
+            float inv_dp = (fabsf(dpn) < eps) ? 1.0f : (1.0f / dpn);
+            float f0 = norm;
+            if (metric == B200VQ_METRIC_IP) f0 -= orl2;
+            float f1 = inv_dp * sq;
+            uint32_t u0 = __float_as_uint(f0), u1 = __float_as_uint(f1);
+            uint8_t* f = code + nbytes;
+            if (word_rows && (nbytes & 3) == 0) {
+                reinterpret_cast<uint32_t*>(f)[0] = u0;
+                reinterpret_cast<uint32_t*>(f)[1] = u1;
+            } else {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    f[b] = (uint8_t)(u0 >> (8 * b));
+                    f[4 + b] = (uint8_t)(u1 >> (8 * b));
+                }
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ float load_f32_unaligned(const uint8_t* p) {
     uint32_t u = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) |
                  ((uint32_t)p[3] << 24);
@@ -754,8 +848,11 @@ extern "C" int b200vq_rabitq1_encode(const float* x, int64_t n, int64_t ldx, int
     int64_t g = (n * 32 + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;
     if (g > cap) g = cap;
-    rabitq1_encode_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, ldx, D, centroid, metric,
-                                                                 codes);
+    const bool vec = D % 4 == 0 && ldx % 4 == 0 && ((uintptr_t)x & 15) == 0 && (!centroid || ((uintptr_t)centroid & 15) == 0);
+    if (vec)
+        rabitq1_encode_vec_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, ldx, D, centroid, metric, codes);
+    else
+        rabitq1_encode_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(x, n, ldx, D, centroid, metric, codes);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

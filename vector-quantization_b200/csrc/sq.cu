@@ -394,6 +394,43 @@ saq_encode_vec_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D
     };
     const int64_t step = gridDim.y;
     int64_t row = blockIdx.y;
+    // The usual plans (one even width w for the thread's four dimensions, run on a byte boundary): the run is
+    // exactly w / 2 bytes and the row loop is straight-line code; zero-width groups read nothing at all.
+    const bool uniform = nb.x == nb.y && nb.y == nb.z && nb.z == nb.w && d0.fast && d1.fast && d2.fast && d3.fast &&
+                         (o & 7) == 0 && !pad && half_ok;
+    if (W == 0 && !pad) return;
+    if (uniform && (nb.x == 8 || nb.x == 6 || nb.x == 4 || nb.x == 2) && (nb.x != 8 || (fo & 3) == 0) &&
+        (nb.x != 4 || (fo & 1) == 0)) {
+        const int w = nb.x;
+        auto fast = [&](int64_t r, const float4& v) {
+            const uint32_t V = (((((sq_quant_c(v.x, mn.x, d0, l0) << w) | sq_quant_c(v.y, mn.y, d1, l1)) << w) |
+                                 sq_quant_c(v.z, mn.z, d2, l2)) << w) | sq_quant_c(v.w, mn.w, d3, l3);
+            uint8_t* out = codes + r * (int64_t)code_bytes + fo;
+            if (w == 8) {
+                *reinterpret_cast<uint32_t*>(out) = __byte_perm(V, 0, 0x0123);
+            } else if (w == 4) {
+                *reinterpret_cast<uint16_t*>(out) = (uint16_t)__byte_perm(V, 0, 0x4401);
+            } else if (w == 2) {
+                out[0] = (uint8_t)V;
+            } else if (fo & 1) {          // w == 6: three bytes
+                out[0] = (uint8_t)(V >> 16);
+                *reinterpret_cast<uint16_t*>(out + 1) = (uint16_t)__byte_perm(V, 0, 0x4401);
+            } else {
+                *reinterpret_cast<uint16_t*>(out) = (uint16_t)__byte_perm(V, 0, 0x4412);
+                out[2] = (uint8_t)V;
+            }
+        };
+        for (; row + 7 * step < n; row += 8 * step) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                v[u] = ld_stream_f4(reinterpret_cast<const float4*>(x + (row + u * step) * ldx) + c4);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) fast(row + u * step, v[u]);
+        }
+        for (; row < n; row += step) fast(row, ld_stream_f4(reinterpret_cast<const float4*>(x + row * ldx) + c4));
+        return;
+    }
     for (; row + 3 * step < n; row += 4 * step) {
         float4 v[4];
 #pragma unroll
