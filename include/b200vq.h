@@ -190,6 +190,32 @@ int b200vq_flat_topk(const float* x, int64_t n, int64_t ldx, int D, const float*
                      int metric, int k, float* out_vals, uint32_t* out_ids, void* scratch,
                      size_t scratch_bytes, void* stream);
 
+/* Continuation of b200vq_flat_topk: the best k rows AFTER (after_vals[q], after_ids[q]) in its (key, id) order, i.e.
+ * ranks r+1 .. r+k when given every query's rank-r entry. Chained calls lift the k <= 128 limit of one launch
+ * (nprobe = 200 of the reference's IVF shell, ivf_quantized_index.py:87-90). Scratch as b200vq_flat_topk. */
+int b200vq_flat_topk_after(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                           const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
+                           int k, const float* after_vals, const uint32_t* after_ids, float* out_vals,
+                           uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------ IVF search ---
+ * Exact top-k over the reconstructions of the clusters each query probes: the result of the per-query loop of
+ * src/haag_vq/methods/search/ivf_quantized_index.py:98-146 (decompress the probed clusters, exact distance, top-k).
+ * recon (N, ldr): reconstructions decompress(codes_c) + centroid_c of all rows, sorted by cluster; rnorm (N) their
+ * squared norms (L2); gid (N) the rows' global ids; row_off (K + 1) int64 CSR offsets of the clusters;
+ * probe (nq, nprobe) uint32 cluster ids per query (ids >= K are skipped). Values as b200vq_flat_topk (squared L2,
+ * or the inner product), ids = global ids, (inf, 0xffffffff) where fewer than k rows were probed. The scan is
+ * cluster-major (csrc/ivf.cu): a row is read once per 64 probing queries. k <= 128. */
+/* Row-wise arg-min (lowest index on ties) of an (n, K) score matrix: the assignment step of the coarse k-means
+ * (faiss.Kmeans.train / km.index.search(X, 1), ivf_quantized_index.py:52-57) on scores |c|^2 - 2 x.c produced by
+ * b200vq_rotate_tc_ex with a column bias. val (n, optional) receives the minima. */
+int b200vq_row_argmin(const float* y, int64_t n, int64_t ld, int K, uint32_t* idx, float* val, void* stream);
+size_t b200vq_ivf_search_scratch_bytes(int nq, int nprobe, int K, int k);
+int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
+                      const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
+                      const uint32_t* probe, int nprobe, int metric, int k, float* out_vals, uint32_t* out_ids,
+                      void* scratch, size_t scratch_bytes, void* stream);
+
 /* Same search, same results (ids and values are those of b200vq_flat_topk's fp32 arithmetic), with the
  * tensor cores as a screen: TF32 tcgen05 products of 128 rows x 256 queries give a rigorous lower
  * bound of every exact key; rows are processed in geometric stages against the thresholds of the

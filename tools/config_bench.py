@@ -236,6 +236,46 @@ def saq_engine():
         flops=2.0 * n * D * D)
 
 
+def ivf_group():
+    """IVF shell at the reference's ratios: 256 rows per cluster, ~5 % of the clusters probed."""
+    import time
+    from haag_vq.methods.scalar_quantization import ScalarQuantizer
+    from haag_vq.methods.search.ivf_quantized_index import IvfQuantizedIndex
+    from b200vq import host, ivf as divf
+    n, D, K, nprobe, nq, k = 262144, 1536, 1024, 50, 1000, 10
+    xd = data(n, D)
+    qd = data(nq, D, seed=99)
+    X, Q = xd.cpu().numpy(), qd.cpu().numpy()
+    t0 = time.perf_counter()
+    C = divf.kmeans(xd, K, seed=0)
+    torch.cuda.synchronize()
+    t_km = time.perf_counter() - t0
+    rows.append({"config": "IVF", "kernel": f"coarse k-means K={K}, 20 iterations, {n} x {D} (tensor-core assignment)",
+                 "ms": round(t_km * 1e3, 1), "units_per_s": n * 20 / t_km, "unit": "point-iterations",
+                 "TFLOPs": 2.0 * n * K * D * 20 / t_km / 1e12})
+    print(f"IVF kmeans {t_km:.2f} s", file=sys.stderr, flush=True)
+    idx = IvfQuantizedIndex(lambda: ScalarQuantizer(num_bits=8), K=K, nprobe=nprobe)
+    t0 = time.perf_counter()
+    idx.fit(X, "l2", centroids=C.cpu().numpy())
+    t_fit = time.perf_counter() - t0
+    rows.append({"config": "IVF", "kernel": f"assign + {K} per-cluster SQ8 fit/compress/decompress (host loop)",
+                 "ms": round(t_fit * 1e3, 1), "units_per_s": n / t_fit, "unit": "vectors"})
+    d = idx._dev
+    probe = idx._probe(qd)
+    ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2"))
+    frac = nprobe / K
+    add("IVF", f"ivf_search nprobe={nprobe}/{K} k={k} (cluster-major exact scan of reconstructions)", ms, nq, "queries",
+        flops=2.0 * nq * n * frac * D, note=f"{frac:.3f} of the rows per query")
+    ms_p = timed(lambda: idx._probe(qd))
+    add("IVF", "probe lists: exact flat search over the centroids", ms_p, nq, "queries", flops=2.0 * nq * K * D)
+    ids, _ = idx.search_with_scores(Q, k)
+    _, gt = ops.flat_topk(xd, qd, k, "l2")
+    gt = gt.cpu().numpy().view(np.uint32)
+    rec = float(np.mean([len(set(ids[i]) & set(gt[i])) / k for i in range(nq)]))
+    rows.append({"config": "IVF", "kernel": f"recall@{k} of the IVF-SQ8 search vs exact search", "value": rec})
+    print(f"IVF recall@{k} {rec:.4f}", file=sys.stderr, flush=True)
+
+
 def run(which=("c1", "c2", "c3", "c4", "saq"), device=None, quick=False):
     """Run the named config groups; returns the list of rows (and leaves it in `rows`)."""
     global dev, QUICK
@@ -243,7 +283,7 @@ def run(which=("c1", "c2", "c3", "c4", "saq"), device=None, quick=False):
     if device is not None:
         dev = device
     rows.clear()
-    fns = {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "saq": saq_engine}
+    fns = {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "saq": saq_engine, "ivf": ivf_group}
     for w in which:
         fns[w]()
         torch.cuda.empty_cache()

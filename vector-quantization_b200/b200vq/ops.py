@@ -321,9 +321,28 @@ def flat_topk(x: torch.Tensor, queries: torch.Tensor, k: int, metric, xnorm: tor
     if mid == METRIC_L2 and xnorm is None:
         xnorm = row_sqnorms(x)
     lib = _lib.load()
-    vals, ids = _topk_out(nq, k, x.device)
     if impl not in ("auto", "tc", "simt"):
         raise B200VQError(f"flat_topk: unknown impl {impl!r}")
+    if k > 128:
+        # one launch ranks at most 128 rows per query: chain continuations, each starting after the last entry of
+        # the previous one in the same (key, id) order -- the concatenation is the exact top-k
+        vals, ids = _topk_out(nq, k, x.device)
+        v0, i0 = flat_topk(x, queries, 128, metric, xnorm, row_scale, impl)
+        vals[:, :128], ids[:, :128] = v0, i0
+        nbytes = lib.b200vq_flat_topk_scratch_bytes(n, nq, 128)
+        sc = scratch(nbytes, x.device, "scan")
+        done = 128
+        while done < k:
+            kk = min(128, k - done)
+            av, ai = vals[:, done - 1].contiguous(), ids[:, done - 1].contiguous()
+            v1, i1 = _topk_out(nq, kk, x.device)
+            check(lib.b200vq_flat_topk_after(ptr, n, ld, D, _p(xnorm), _p(row_scale), qptr, nq, ldq, mid, kk,
+                                             av.data_ptr(), ai.data_ptr(), v1.data_ptr(), i1.data_ptr(), sc.data_ptr(),
+                                             sc.numel(), _stream()), "flat_topk_after")
+            vals[:, done:done + kk], ids[:, done:done + kk] = v1, i1
+            done += kk
+        return vals, ids
+    vals, ids = _topk_out(nq, k, x.device)
     if impl != "simt" and tc_available() and k <= 128:
         if xnorm is None:
             xnorm = row_sqnorms(x)

@@ -230,7 +230,8 @@ __global__ void __launch_bounds__(FT_THREADS)
     flat_topk_kernel(const float* __restrict__ x, int64_t n, int64_t ldx, int D,
                      const float* __restrict__ xnorm, const float* __restrict__ row_scale,
                      const float* __restrict__ queries, int nq, int64_t ldq, int metric, int k,
-                     int64_t chunk_rows, uint64_t* __restrict__ part, const uint32_t* __restrict__ gate = nullptr) {
+                     int64_t chunk_rows, uint64_t* __restrict__ part, const uint32_t* __restrict__ gate = nullptr,
+                     const float* __restrict__ after_vals = nullptr, const uint32_t* __restrict__ after_ids = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     if (gate) {   // gated launch (fallback of the tensor-core search): skip tiles without a flagged query
         int any = 0;
@@ -246,10 +247,15 @@ __global__ void __launch_bounds__(FT_THREADS)
     int* s_cnt = reinterpret_cast<int*>(s_thr + FT_Q);         // [FT_Q]
     uint64_t* lists = reinterpret_cast<uint64_t*>(
         (reinterpret_cast<uintptr_t>(s_cnt + FT_Q) + 15) & ~(uintptr_t)15);  // [FT_Q][CAP]
+    uint64_t* s_after = lists + (size_t)FT_Q * CAP;            // [FT_Q] continuation floor (see b200vq_flat_topk_after)
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int ty = tid >> 4, tx = tid & 15;
     const int q0 = blockIdx.x * FT_Q;
+    if (after_vals && tid < FT_Q && q0 + tid < nq) {
+        const float av = after_vals[q0 + tid];
+        s_after[tid] = make_key(metric == B200VQ_METRIC_IP ? -av : av, after_ids[q0 + tid]);
+    }
     const int chunk = blockIdx.y, nchunks = gridDim.y;
     const int64_t r0 = (int64_t)chunk * chunk_rows;
     int64_t r1 = r0 + chunk_rows;
@@ -342,7 +348,10 @@ __global__ void __launch_bounds__(FT_THREADS)
             for (int c = 0; c < FT_N / 32; ++c) {
                 int rl = c * 32 + lane;
                 int64_t row = t0 + rl;
-                tk.offer(row < r1, ds[ql * (FT_N + 1) + rl], (uint32_t)row);
+                const float dv = ds[ql * (FT_N + 1) + rl];
+                bool ok = row < r1;
+                if (after_vals) ok = ok && make_key(dv, (uint32_t)row) > s_after[ql];
+                tk.offer(ok, dv, (uint32_t)row);
             }
             if (lane == 0) {
                 s_cnt[ql] = tk.count;
@@ -759,14 +768,16 @@ template <int CAP>
 static int flat_launch(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
                        const float* row_scale, const float* queries, int nq, int64_t ldq,
                        int metric, int k, uint64_t* part, const ScanPlan& p, cudaStream_t st,
-                       const uint32_t* gate = nullptr) {
+                       const uint32_t* gate = nullptr, const float* after_vals = nullptr,
+                       const uint32_t* after_ids = nullptr) {
     size_t smem = (size_t)(FT_K * (FT_Q + 4) + FT_K * (FT_N + 4) + FT_Q * (FT_N + 1) + 3 * FT_Q) * 4 +
-                  16 + (size_t)FT_Q * CAP * sizeof(uint64_t);
+                  16 + (size_t)FT_Q * (CAP + 1) * sizeof(uint64_t);
     VQ_CUDA(cudaFuncSetAttribute(flat_topk_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
     dim3 grid((unsigned)((nq + FT_Q - 1) / FT_Q), (unsigned)p.nchunks);
     flat_topk_kernel<CAP><<<grid, FT_THREADS, smem, st>>>(x, n, ldx, D, xnorm, row_scale, queries,
-                                                          nq, ldq, metric, k, p.chunk_rows, part, gate);
+                                                          nq, ldq, metric, k, p.chunk_rows, part, gate, after_vals,
+                                                          after_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -811,6 +822,33 @@ extern "C" int b200vq_flat_topk(const float* x, int64_t n, int64_t ldx, int D, c
     if (rc != B200VQ_OK) return rc;
     return launch_merge<2048>(part, nq, p.nchunks, k, metric == B200VQ_METRIC_IP, out_vals, out_ids,
                               st);
+}
+
+// Continuation of an exact search: the best k rows AFTER (after_vals[q], after_ids[q]) in the (key, id) order of
+// b200vq_flat_topk, i.e. its ranks r+1 .. r+k when called with the rank-r entry of every query. Callers chain calls
+// to lift the k <= 128 limit of one launch (haag_vq uses it for IVF probe lists longer than 128).
+extern "C" int b200vq_flat_topk_after(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                                      const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
+                                      int k, const float* after_vals, const uint32_t* after_ids, float* out_vals,
+                                      uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(x && queries && out_vals && out_ids && after_vals && after_ids, "flat_topk_after: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && ldx >= D && ldq >= D && nq >= 0, "flat_topk_after: bad shape");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "flat_topk_after: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "flat_topk_after: bad metric");
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_IP || xnorm, "flat_topk_after: L2 needs xnorm");
+    if (nq == 0) return B200VQ_OK;
+    int nqc = (nq + FT_Q - 1) / FT_Q;
+    size_t need = partial_bytes(n, nq, k, nqc);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "flat_topk_after: scratch too small (%zu < %zu)", scratch_bytes, need);
+    cudaStream_t st = as_stream(stream);
+    ScanPlan p = plan_scan(n, nqc);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32) ? flat_launch<64>(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, part, p, st,
+                                         nullptr, after_vals, after_ids)
+                       : flat_launch<256>(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, part, p, st,
+                                          nullptr, after_vals, after_ids);
+    if (rc != B200VQ_OK) return rc;
+    return launch_merge<2048>(part, nq, p.nchunks, k, metric == B200VQ_METRIC_IP, out_vals, out_ids, st);
 }
 
 extern "C" int b200vq_topk_merge(const float* in_vals, const int64_t* in_ids, int nq, int P, int k,
