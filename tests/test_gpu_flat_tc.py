@@ -72,3 +72,38 @@ def test_tc_overflow_falls_back_to_simt(T):
     a = T.ops.flat_topk(X, Q, k, "l2", impl="simt")
     b = T.ops.flat_topk(X, Q, k, "l2", impl="tc")
     assert T.torch.equal(a[1], b[1]) and T.torch.equal(a[0], b[0])
+
+
+def test_flat_topk_beyond_128_is_the_exact_ranking_and_index_accepts_large_k():
+    """k > 128: chained continuations (b200vq_flat_topk_after) concatenate to the exact (value, id) ranking."""
+    import numpy as np
+    import torch
+    from b200vq import ops
+    from haag_vq.methods.scalar_quantization import ScalarQuantizer
+    from haag_vq.methods.search.flat_quantized_index import FlatQuantizedIndex
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((3000, 40)).astype(np.float32)
+    X[100:140] = X[50]                      # 41 identical rows: ties across a continuation boundary
+    Q = rng.standard_normal((9, 40)).astype(np.float32)
+    Q[0] = X[50]
+    xd, qd = torch.from_numpy(X).cuda(), torch.from_numpy(Q).cuda()
+    for metric in ("l2", "ip"):
+        for k in (129, 300, 3000):
+            v, i = ops.flat_topk(xd, qd, k, metric, impl="simt")
+            v1, i1 = ops.flat_topk(xd, qd, 128, metric, impl="simt")
+            assert torch.equal(v[:, :128], v1) and torch.equal(i[:, :128], i1)
+            vh, ih = v.cpu().numpy(), i.cpu().numpy().view(np.uint32)
+            # a permutation prefix, sorted by (value, id) with the kernel's own values
+            sgn = -1.0 if metric == "ip" else 1.0
+            for q in range(9):
+                assert len(set(ih[q])) == k
+                key = list(zip((sgn * vh[q]).tolist(), ih[q].tolist()))
+                assert key == sorted(key)
+            if k == 3000:
+                assert (np.sort(ih, axis=1) == np.arange(3000, dtype=np.uint32)).all()
+    idx = FlatQuantizedIndex(ScalarQuantizer(num_bits=8))
+    idx.fit(X, "l2")
+    ids, d = idx.search_with_scores(Q, 200)
+    assert ids.shape == (9, 200) and (np.diff(d, axis=1) >= 0).all()
+    ids128, _ = idx.search_with_scores(Q, 128)
+    assert np.array_equal(ids[:, :128], ids128)

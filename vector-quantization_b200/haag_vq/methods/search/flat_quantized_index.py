@@ -92,13 +92,17 @@ class FlatQuantizedIndex(BaseSearchIndex):
         k = min(k, self._N)
         if k <= 0:
             return np.empty((nq, 0), dtype=np.uint32), np.empty((nq, 0), dtype=np.float32)
-        if k > MAX_K:
-            raise ValueError(f"k={k} exceeds the device top-k limit ({MAX_K})")
         if Q.shape[1] != self._D:
             raise ValueError(f"query dimension {Q.shape[1]} != index dimension {self._D}")
         q_dev = host.to_device(Q)
         codec = self._pq_codec()
-        if codec is not None:
+        if k > MAX_K:
+            # one scan launch ranks at most 128 rows per query: beyond that the reference's own route (decompress,
+            # exact distance to the reconstructions) with the chained exact search of ops.flat_topk
+            if self._codes is None:
+                raise ValueError(f"k={k} exceeds the device top-k limit ({MAX_K}) of an index built from device codes")
+            vals, ids = ops.flat_topk(self._reconstructions(), q_dev, k, self._metric)
+        elif codec is not None:
             if self._codes_dev is None:
                 # stored codes -> one byte per sub-quantizer index (sub-byte PQ codes are a packed bit stream)
                 self._codes_dev = self._quantizer.pq.unpack_codes(
