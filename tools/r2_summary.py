@@ -49,6 +49,9 @@ for name in sorted(glob.glob(os.path.join(P, "r2_bench_*.json"))):
 cfg = os.path.join(P, "r2_configs.json")
 if os.path.exists(cfg):
     d = json.load(open(cfg))
+    ivfj = os.path.join(P, "r2_ivf.json")
+    if os.path.exists(ivfj):
+        d["rows"] = d["rows"] + json.load(open(ivfj))["rows"]
     w("## Per-config kernel table (`tools/config_bench.py`, BASELINE C1-C4 shapes at full size)\n")
     w("| config | kernel | ms | units/s | GB/s (frac HBM) | TFLOP/s (frac TF32) | note |")
     w("|---|---|---:|---:|---:|---:|---|")
@@ -57,7 +60,7 @@ if os.path.exists(cfg):
             w(f"| {r['config']} | {r['kernel']} | | {r.get('value', 0):.4f} | | | |")
             continue
         gb = f"{r['GBps']:.0f} ({r['frac_hbm']:.2f})" if "GBps" in r else ""
-        tf = f"{r['TFLOPs']:.0f} ({r['frac_tf32']:.2f})" if "TFLOPs" in r else ""
+        tf = (f"{r['TFLOPs']:.0f} ({r['frac_tf32']:.2f})" if "frac_tf32" in r else f"{r['TFLOPs']:.0f}") if "TFLOPs" in r else ""
         w(f"| {r['config']} | {r['kernel']} | {r['ms']:.3f} | {r['units_per_s']:.3g} {r['unit']} | {gb} | {tf} | "
           f"{r.get('note', '')} |")
     w("")
