@@ -12,15 +12,18 @@
 //   |P (1 + 2^-10) - x_i.q| <= E_i = (2^-10 * 1.02 + 3 D 2^-24) |x_i| max_q|q|  (truncation is
 //   one-sided, hence the centring factor; the D 2^-24 terms cover both fp32 accumulations),
 //   so LB = a_i P + b_i is a rigorous lower bound of the exact key of (row i, query q) and the
-//   row can only enter the top-k if LB <= T_q (T_q from the current exact k-th best).
+//   row can only enter the top-k if LB <= T_q. The same bound gives UB = LB + 4 E_i (L2) / LB + 2 E_i (IP).
 //
-// Rows are processed in geometric stages (the first 1024 rows scored exactly, then x3 per stage):
-// each stage screens its rows against the thresholds of the exact top-k so far, appends the
-// survivors to per-query lists, and flat_finish_kernel scores them exactly and merges them
-// into the running top-k, which tightens the thresholds for the next, twice as large,
-// stage. A query whose list overflows is flagged and redone by the SIMT kernel (gated launch)
-// at the end, so the result never depends on the screen. x is read from HBM once (the query
-// tiles of a row tile are consumed back to back, out of L2).
+// Rows are processed in geometric stages (2048 rows, then x8 per stage). Each stage screens its rows against T_q and
+// appends the survivors WITH their lower bounds to per-query lists; flat_pool_kernel merges them into the query's
+// candidate pool = every row seen so far with LB <= U_q, where U_q = the k-th smallest UB (an upper bound of the final
+// k-th best key), and U_q becomes T_q of the next stage. No row is re-read between the stages (round 1 scored every
+// survivor exactly after every stage: k ln(growth) rows of 6 KB per query and stage, 25 % of the search at 1M rows and
+// 75 % at 100K). After the last stage flat_finish_kernel scores the pool rows - k plus the few whose [LB, UB]
+// straddles U_q - exactly, once, and ranks them in (key, id) order. A query whose list or pool overflows (thousands
+// of rows within the TF32 uncertainty of its k-th best) is flagged and redone by the SIMT kernel (gated launch), so
+// the result never depends on the screen. x is read from HBM once (the query tiles of a row tile are consumed back to
+// back, out of L2).
 #include "tc_common.cuh"
 #include "topk.cuh"
 
@@ -48,6 +51,7 @@ struct Params {
     const float* thr;         // (ntq * 256) T_q, NaN for padding queries
     const float* qstats;      // [0] = max_q |q|^2
     uint32_t* cand;           // (nq, cap)
+    float* cand_lb;           // (nq, cap) the survivors' lower bounds
     uint32_t* count;          // (nq)
     uint32_t cap;
     int64_t r0, r1;           // rows of this stage
@@ -55,6 +59,7 @@ struct Params {
     int64_t ntr;              // row tiles of this stage
     int metric;
     float ebound;             // 2^-10 * 1.02 + 3 D 2^-24
+    int dense;                // stage 0: every row is a survivor, slot = row - r0 (no counters, no atomics)
 };
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -178,10 +183,19 @@ flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float lb = __fmaf_rn(a, v[4 * j4 + e], b);
-                        if (live && lb <= th[e]) {
+                        if (p.dense) {
+                            const int q = u * TILE_Q + cb * 64 + 4 * j4 + e;
+                            if (live && q < p.nq) {
+                                p.cand[(size_t)q * p.cap + (uint32_t)(row - p.r0)] = (uint32_t)row;
+                                p.cand_lb[(size_t)q * p.cap + (uint32_t)(row - p.r0)] = lb;
+                            }
+                        } else if (live && lb <= th[e]) {
                             const int q = u * TILE_Q + cb * 64 + 4 * j4 + e;
                             const uint32_t pos = atomicAdd(p.count + q, 1u);
-                            if (pos < p.cap) p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
+                            if (pos < p.cap) {
+                                p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
+                                p.cand_lb[(size_t)q * p.cap + pos] = lb;
+                            }
                         }
                     }
                 }
@@ -202,7 +216,7 @@ flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 
 // |q|^2 of every query with the SIMT kernel's arithmetic (lane-strided FMA chain + xor tree), and their maximum.
 __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, int64_t ldq, int D, float* __restrict__ qn,
-                                   float* __restrict__ qstats) {
+                                   float* __restrict__ qstats, float* __restrict__ thr) {
     const int lane = threadIdx.x & 31;
     const int q = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (q >= nq) return;
@@ -212,7 +226,104 @@ __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, in
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
     if (lane == 0) {
         qn[q] = acc;
+        thr[q] = __int_as_float(0x7f800000);    // first stage: every row passes (padding queries keep their NaN)
         atomicMax(reinterpret_cast<int*>(qstats), __float_as_int(acc));   // non-negative floats order as ints
+    }
+}
+
+// ---------------------------------------------------------------- candidate pool ---
+// Between the stages NO row is re-read. Every survivor of a screen carries its rigorous lower bound lb of the exact
+// key; the same error bound gives ub = lb + 4E (L2) / lb + 2E (IP) >= exact key. Per query the pool keeps every row
+// seen so far that can still be in the top-k: with U = the k-th smallest ub (an upper bound of the final k-th best
+// key), exactly the rows with lb <= U. U is the next stage's screening threshold. After the last stage
+// flat_finish_kernel scores the pool rows (k plus the few rows whose interval straddles U) exactly, once.
+// One CTA per query; pool arrays are double-buffered by stage parity. A pool or entry overflow (thousands of rows
+// within the TF32 uncertainty of the k-th best: duplicated rows) flags the query for the gated exact SIMT search.
+constexpr int POOL_CAP = 1024;
+constexpr int POOL_MAX_ENTRIES = 8192;
+__global__ void __launch_bounds__(256)
+flat_pool_kernel(const float* __restrict__ xnorm, const float* __restrict__ row_scale, const float* __restrict__ qstats,
+                 float ebound, int metric, int k, const uint32_t* __restrict__ cand, const float* __restrict__ cand_lb,
+                 float* __restrict__ cand_ub, uint32_t* __restrict__ count, uint32_t cap,
+                 const uint32_t* __restrict__ prow_in, const float* __restrict__ plb_in, const float* __restrict__ pub_in,
+                 uint32_t* __restrict__ prow_out, float* __restrict__ plb_out, float* __restrict__ pub_out,
+                 uint32_t* __restrict__ pool_cnt, float* __restrict__ thr, uint32_t* __restrict__ flags,
+                 uint32_t dense_count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ uint32_t s_np;
+    const int q = blockIdx.x;
+    uint32_t cnt = dense_count ? dense_count : count[q];
+    bool overflow = false;
+    if (cnt > cap) {
+        cnt = cap;
+        overflow = true;
+    }
+    const uint32_t pc = pool_cnt[q];
+    uint32_t total = pc + cnt;
+    if (total > POOL_MAX_ENTRIES) {
+        total = POOL_MAX_ENTRIES;
+        overflow = true;
+    }
+    const int n2 = next_pow2((int)(total < 2 ? 2 : total));
+    const float qn_max = qstats[0], q_max = sqrtf(qn_max) * 1.0000005f;
+    const uint32_t* list = cand + (size_t)q * cap;
+    const float* llb = cand_lb + (size_t)q * cap;
+    float* lub = cand_ub + (size_t)q * cap;
+    const size_t pq = (size_t)q * POOL_CAP;
+    if (threadIdx.x == 0) s_np = 0;
+    for (int e = threadIdx.x; e < n2; e += blockDim.x) {
+        uint64_t key = KEY_INF;
+        if ((uint32_t)e < pc) {
+            key = make_key(pub_in[pq + e], (uint32_t)e);
+        } else if ((uint32_t)e < total) {
+            const uint32_t row = list[e - pc];
+            const float xn = xnorm[row];
+            const float rs = row_scale ? row_scale[row] : 1.f;
+            const float nrm = sqrtf(xn) * fabsf(rs) * 1.0000005f;
+            const float slack = 2.4e-7f * (xn * rs * rs + qn_max);
+            const float E = ebound * nrm * q_max + slack;      // the screen's own bound (flat_screen_kernel)
+            const float ub = llb[e - pc] + (metric == B200VQ_METRIC_L2 ? 4.f : 2.f) * E + slack;
+            lub[e - pc] = ub;
+            key = make_key(ub, (uint32_t)e);
+        }
+        keys[e] = key;
+    }
+    block_bitonic_sort(keys, n2);
+    const float U = ((uint32_t)k <= total) ? key_value(keys[k - 1]) : __int_as_float(0x7f800000);
+    __syncthreads();
+    for (uint32_t e = threadIdx.x; e < total; e += blockDim.x) {
+        uint32_t row;
+        float lb, ub;
+        if (e < pc) {
+            row = prow_in[pq + e];
+            lb = plb_in[pq + e];
+            ub = pub_in[pq + e];
+        } else {
+            row = list[e - pc];
+            lb = llb[e - pc];
+            ub = lub[e - pc];
+        }
+        if (lb <= U) {
+            const uint32_t pos = atomicAdd(&s_np, 1u);
+            if (pos < POOL_CAP) {
+                prow_out[pq + pos] = row;
+                plb_out[pq + pos] = lb;
+                pub_out[pq + pos] = ub;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t np = s_np;
+        if (np > POOL_CAP) {
+            np = POOL_CAP;
+            overflow = true;
+        }
+        pool_cnt[q] = np;
+        thr[q] = U;
+        count[q] = 0;
+        if (overflow) flags[q] = 1;     // redone by the gated SIMT launch
     }
 }
 
@@ -354,14 +465,16 @@ using namespace b200vq;
 using namespace b200vq::ftc;
 
 namespace {
-constexpr int64_t FLAT_STAGE_GROWTH = 3;   // rows seen after a stage / rows seen before it (measured: 2 -> 8.2 ms,
-                                          // 3 -> 7.7 ms, 4 -> 7.8 ms, 8 -> 8.1 ms at 1M x 1536 x 1000 queries, k = 100)
-constexpr int64_t SEED_ROWS = 1024;   // scored exactly by flat_finish_kernel (identity list); stages grow x3 from here
+constexpr int64_t FLAT_STAGE_GROWTH = 8;   // rows seen after a stage / rows seen before it. With the candidate pool a stage costs a
+                                          // screen launch + a 30 us pool kernel and k ln(growth) appended survivors per query:
+                                          // 3 -> 5.14 / 1.69 ms, 8 -> 4.64 / 1.43 ms (1M x 1536 k = 10 / 100K x 1536 k = 100, 1000 queries)
+constexpr int64_t FIRST_ROWS = 2048;  // stage 0 (infinite threshold: every row enters the pool kernel, dense slots, no atomics)
 constexpr int64_t MIN_ROWS = 65536;   // below this the SIMT kernel alone is as fast
 struct FlatPlan {
     uint32_t cap;
     int ntq;
-    size_t off_simt, off_running, off_thr, off_count, off_flags, off_qn, off_qstats, off_cand, total;
+    size_t off_simt, off_running, off_thr, off_count, off_flags, off_qn, off_qstats, off_cand, off_cand_lb, off_cand_ub,
+        off_pool, off_pool_cnt, total;
 };
 FlatPlan plan_flat(int64_t n, int nq, int k) {
     FlatPlan f;
@@ -379,6 +492,10 @@ FlatPlan plan_flat(int64_t n, int nq, int k) {
     f.off_qn = o;      o = up(o + (size_t)nq * 4);
     f.off_qstats = o;  o = up(o + 16);
     f.off_cand = o;    o = up(o + (size_t)nq * f.cap * 4);
+    f.off_cand_lb = o; o = up(o + (size_t)nq * f.cap * 4);
+    f.off_cand_ub = o; o = up(o + (size_t)nq * f.cap * 4);
+    f.off_pool = o;    o = up(o + (size_t)nq * POOL_CAP * 4 * 6);     // rows, lb, ub: two generations
+    f.off_pool_cnt = o; o = up(o + (size_t)nq * 4);
     f.total = o;
     return f;
 }
@@ -437,47 +554,66 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     float* qstats = reinterpret_cast<float*>(sb + fp.off_qstats);
     uint32_t* cand = reinterpret_cast<uint32_t*>(sb + fp.off_cand);
 
-    // query norms and their maximum; exact top-k of the first rows (finish kernel on the identity list)
+    float* cand_lb = reinterpret_cast<float*>(sb + fp.off_cand_lb);
+    float* cand_ub = reinterpret_cast<float*>(sb + fp.off_cand_ub);
+    uint32_t* pool_cnt = reinterpret_cast<uint32_t*>(sb + fp.off_pool_cnt);
+    const size_t pstride = (size_t)nq * POOL_CAP;
+    uint32_t* prow[2] = {reinterpret_cast<uint32_t*>(sb + fp.off_pool), reinterpret_cast<uint32_t*>(sb + fp.off_pool) + pstride};
+    float* plb[2] = {reinterpret_cast<float*>(sb + fp.off_pool) + 2 * pstride, reinterpret_cast<float*>(sb + fp.off_pool) + 3 * pstride};
+    float* pub[2] = {reinterpret_cast<float*>(sb + fp.off_pool) + 4 * pstride, reinterpret_cast<float*>(sb + fp.off_pool) + 5 * pstride};
+
+    // query norms and their maximum; thresholds +inf (NaN for the padding queries: they never pass)
     VQ_CUDA(cudaMemsetAsync(qstats, 0, 16, st));
-    flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats);
-    VQ_LAUNCH_CHECK();
-    VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)fp.ntq * TILE_Q * 4, st));   // NaN: padding queries never pass
+    VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)fp.ntq * TILE_Q * 4, st));
     VQ_CUDA(cudaMemsetAsync(running, 0xFF, (size_t)nq * k * 8, st));        // KEY_INF
     VQ_CUDA(cudaMemsetAsync(flags, 0, (size_t)nq * 4, st));
-    int rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
-                                           running, thr, flags, 0, out_vals, out_ids, st, (uint32_t)SEED_ROWS)
-                       : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
-                                            running, thr, flags, 0, out_vals, out_ids, st, (uint32_t)SEED_ROWS);
-    if (rc != B200VQ_OK) return rc;
+    VQ_CUDA(cudaMemsetAsync(count, 0, (size_t)nq * 4, st));
+    VQ_CUDA(cudaMemsetAsync(pool_cnt, 0, (size_t)nq * 4, st));
+    flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats, thr);
+    VQ_LAUNCH_CHECK();
 
     CUtensorMap map_x, map_q;
+    int rc;
     if ((rc = encode_2d(&map_x, x, (uint64_t)n, (uint64_t)D, (uint64_t)ldx, TILE_ROWS, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
         return rc;
     if ((rc = encode_2d(&map_q, queries, (uint64_t)nq, (uint64_t)D, (uint64_t)ldq, TILE_Q, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
         return rc;
     VQ_CUDA(cudaFuncSetAttribute(flat_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    const size_t pool_smem = (size_t)POOL_MAX_ENTRIES * 8;
+    VQ_CUDA(cudaFuncSetAttribute(flat_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pool_smem));
     Params p;
-    p.xnorm = xnorm; p.row_scale = row_scale; p.thr = thr; p.qstats = qstats; p.cand = cand; p.count = count;
+    p.xnorm = xnorm; p.row_scale = row_scale; p.thr = thr; p.qstats = qstats; p.cand = cand; p.cand_lb = cand_lb;
+    p.count = count;
     p.cap = fp.cap; p.nq = nq; p.nchunk = D / CH; p.ntq = fp.ntq; p.metric = metric;
     p.ebound = 0.0009765625f * 1.02f + 3.0f * (float)D * 5.9604645e-8f;
     const int sms = device_sm_count();
     const int64_t growth = FLAT_STAGE_GROWTH;
-    for (int64_t r = SEED_ROWS; r < n;) {
-        int64_t r1 = r * growth;
-        if (r1 > n || n - r1 < r / 2) r1 = n;  // fold a short tail into the last stage
+    int gen = 0;
+    // Stage 0 covers rows [0, FIRST_ROWS) with an infinite threshold (all of them enter the pool kernel, which keeps
+    // the k + few that matter); later stages grow x3. No row is re-read until the single exact pass at the end.
+    for (int64_t r = 0; r < n;) {
+        int64_t r1 = r == 0 ? FIRST_ROWS : r * growth;
+        if (r1 > n || n - r1 < r1 / 4) r1 = n;  // fold a short tail into the last stage
         p.r0 = r; p.r1 = r1;
+        p.dense = r == 0;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
         flat_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, SMEM_BYTES, st>>>(map_x, map_q, p);
         VQ_LAUNCH_CHECK();
-        const int last = r1 == n;
-        rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
-                                           running, thr, flags, last, out_vals, out_ids, st)
-                       : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, cand, count, fp.cap,
-                                            running, thr, flags, last, out_vals, out_ids, st);
-        if (rc != B200VQ_OK) return rc;
+        flat_pool_kernel<<<nq, 256, pool_smem, st>>>(xnorm, row_scale, qstats, p.ebound, metric, k, cand, cand_lb, cand_ub,
+                                                     count, fp.cap, prow[gen], plb[gen], pub[gen], prow[gen ^ 1],
+                                                     plb[gen ^ 1], pub[gen ^ 1], pool_cnt, thr, flags,
+                                                     r == 0 ? (uint32_t)(r1 - r) : 0u);
+        VQ_LAUNCH_CHECK();
+        gen ^= 1;
         r = r1;
     }
+    // exact keys of the pool rows, top-k in (key, id) order
+    rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, prow[gen], pool_cnt,
+                                       (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st)
+                   : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, prow[gen], pool_cnt,
+                                        (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st);
+    if (rc != B200VQ_OK) return rc;
     // queries whose survivor list overflowed in some stage: exact SIMT search, gated per query
     return flat_topk_gated(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids,
                            sb + fp.off_simt, flags, st);
