@@ -216,12 +216,27 @@ int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const float* rnorm
                       const uint32_t* probe, int nprobe, int metric, int k, float* out_vals, uint32_t* out_ids,
                       void* scratch, size_t scratch_bytes, void* stream);
 
+/* The same search on the tensor cores: the screen / candidate-pool machinery of b200vq_flat_topk_tc over the
+ * cluster-sorted reconstructions, where a row only counts for the queries whose probe list holds its cluster
+ * (rowcluster (N): cluster of every row; the probe lists become one K-bit mask per query). Same values and ids as
+ * b200vq_ivf_search. Needs N >= 1024, D % 32 == 0, 16-byte aligned rows (else an error: use b200vq_ivf_search).
+ * flags_out (nq): 1 for a query whose candidate lists overflowed - its output row is undefined and the caller redoes
+ * it with b200vq_ivf_search. init_vals (nq, optional): an upper bound of every query's k-th best value (e.g. the exact
+ * k-th best over its nearest cluster, from b200vq_ivf_search with nprobe = 1): the screen then starts with finite
+ * thresholds instead of admitting every probed row until k of them have been seen. */
+size_t b200vq_ivf_search_tc_scratch_bytes(int64_t n, int nq, int K, int k);
+int b200vq_ivf_search_tc(const float* recon, int64_t n, int64_t ldr, int D, const float* rnorm,
+                         const uint32_t* gid, const uint32_t* rowcluster, int K, const float* queries, int nq,
+                         int64_t ldq, const uint32_t* probe, int nprobe, int metric, int k, float* out_vals,
+                         uint32_t* out_ids, uint32_t* flags_out, const float* init_vals, void* scratch,
+                         size_t scratch_bytes, void* stream);
+
 /* Same search, same results (ids and values are those of b200vq_flat_topk's fp32 arithmetic), with the
  * tensor cores as a screen: TF32 tcgen05 products of 128 rows x 256 queries give a rigorous lower
  * bound of every exact key; rows are processed in geometric stages against the thresholds of the
  * exact top-k so far and only the survivors are scored exactly. xnorm (n) = squared norms of the
  * RAW rows is required (it also bounds the screen error). Falls back to b200vq_flat_topk for
- * n < 65 536, D % 32 != 0, unaligned rows, or L2 with row_scale. */
+ * n < 1024, D % 32 != 0, unaligned rows, or L2 with row_scale. */
 size_t b200vq_flat_topk_tc_scratch_bytes(int64_t n, int nq, int k);
 int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
                         const float* row_scale, const float* queries, int nq, int64_t ldq,

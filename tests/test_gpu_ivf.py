@@ -145,3 +145,36 @@ def test_ivf_nprobe_above_128_pq_clusters_and_recall():
     ids, d = pq.search_with_scores(Q, 10)
     recall = np.mean([len(set(ids[i]) & set(gt[i])) / 10 for i in range(100)])
     assert recall > 0.3, recall
+
+
+@pytest.mark.parametrize("metric", ["l2", "ip"])
+def test_ivf_tensor_core_search_equals_the_simt_kernel(metric):
+    """b200vq_ivf_search_tc (screen + candidate pool with the probe lists as a mask) == b200vq_ivf_search, bit for bit."""
+    import torch
+    from b200vq import host, ivf, ops
+    X, Q = _data(70000, 64, 300, 7)
+    rng = np.random.default_rng(8)
+    K, nprobe = 64, 8
+    C = X[rng.choice(70000, K, replace=False)].copy()
+    xd, qd, cd = host.to_device(X), host.to_device(Q), host.to_device(C)
+    a = ivf.CoarseAssigner(cd, metric == "ip")(xd).long()
+    order = torch.argsort(a, stable=True)
+    recon = xd[order].contiguous()                    # "reconstructions" = the rows themselves
+    rowc = a[order].int().contiguous()
+    gid = order.int().contiguous()
+    row_off = torch.zeros(K + 1, dtype=torch.int64, device=xd.device)
+    row_off[1:] = torch.cumsum(torch.bincount(a, minlength=K), 0)
+    rnorm = ops.row_sqnorms(recon)
+    _, probe = ops.flat_topk(cd, qd, nprobe, metric, impl="simt")
+    for k in (1, 10, 100):
+        v0, i0 = ivf.ivf_search(recon, rnorm, gid, row_off, K, qd, probe, k, metric, impl="simt")
+        v1, i1 = ivf.ivf_search(recon, rnorm, gid, row_off, K, qd, probe, k, metric, rowcluster=rowc, impl="tc")
+        assert torch.equal(i0, i1), (metric, k, (i0 != i1).sum().item())
+        assert torch.equal(v0.view(torch.int32), v1.view(torch.int32))
+    # every returned row belongs to a probed cluster
+    ids = i1.cpu().numpy().view(np.uint32)
+    assign = a.cpu().numpy()
+    pr = probe.cpu().numpy()
+    for q in range(0, 300, 17):
+        got = ids[q][ids[q] != np.iinfo(np.uint32).max]
+        assert np.isin(assign[got], pr[q]).all()

@@ -262,10 +262,14 @@ def ivf_group():
                  "ms": round(t_fit * 1e3, 1), "units_per_s": n / t_fit, "unit": "vectors"})
     d = idx._dev
     probe = idx._probe(qd)
-    ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2"))
+    ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2", impl="simt"))
     frac = nprobe / K
-    add("IVF", f"ivf_search nprobe={nprobe}/{K} k={k} (cluster-major exact scan of reconstructions)", ms, nq, "queries",
+    add("IVF", f"ivf_search simt nprobe={nprobe}/{K} k={k} (cluster-major exact scan of reconstructions)", ms, nq, "queries",
         flops=2.0 * nq * n * frac * D, note=f"{frac:.3f} of the rows per query")
+    ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2",
+                                       rowcluster=d["rowcluster"], impl="tc"))
+    add("IVF", f"ivf_search tc nprobe={nprobe}/{K} k={k} (tcgen05 screen of all rows, probe lists as a mask; default)", ms,
+        nq, "queries", flops=2.0 * nq * n * D, note="FLOP = issued (all rows); same results as the simt kernel")
     ms_p = timed(lambda: idx._probe(qd))
     add("IVF", "probe lists: exact flat search over the centroids", ms_p, nq, "queries", flops=2.0 * nq * K * D)
     ids, _ = idx.search_with_scores(Q, k)

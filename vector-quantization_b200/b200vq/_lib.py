@@ -53,6 +53,8 @@ SIGNATURES = {
     "b200vq_flat_topk": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_flat_topk_after": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "b200vq_row_argmin": (_i, [_p, _i64, _i64, _i, _p, _p, _p]),
+    "b200vq_ivf_search_tc_scratch_bytes": (_sz, [_i64, _i, _i, _i]),
+    "b200vq_ivf_search_tc": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _p, _i, _i64, _p, _i, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "b200vq_ivf_search_scratch_bytes": (_sz, [_i, _i, _i, _i]),
     "b200vq_ivf_search": (_i, [_p, _i64, _i, _p, _p, _p, _i, _p, _i, _i64, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_flat_topk_tc_scratch_bytes": (_sz, [_i64, _i, _i]),

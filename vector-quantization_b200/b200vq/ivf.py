@@ -104,21 +104,45 @@ def kmeans(x: torch.Tensor, K: int, niter: int = NITER, seed: int = 0, spherical
 
 
 def ivf_search(recon: torch.Tensor, rnorm: torch.Tensor | None, gid: torch.Tensor, row_off: torch.Tensor, K: int,
-               queries: torch.Tensor, probe: torch.Tensor, k: int, metric):
-    """Exact top-k of every query over the rows of the clusters it probes (b200vq_ivf_search). recon (N, D) fp32
-    sorted by cluster, gid (N) int32 global ids, row_off (K + 1) int64, probe (nq, nprobe) int32."""
+               queries: torch.Tensor, probe: torch.Tensor, k: int, metric, rowcluster: torch.Tensor | None = None,
+               impl: str = "auto"):
+    """Exact top-k of every query over the rows of the clusters it probes. recon (N, D) fp32 sorted by cluster,
+    gid (N) int32 global ids, row_off (K + 1) int64, probe (nq, nprobe) int32, rowcluster (N) int32 (tensor-core path).
+    impl: "simt" = cluster-major exact kernel (b200vq_ivf_search); "tc" / "auto" = tensor-core screen with the probe
+    lists as a mask (b200vq_ivf_search_tc, same results), queries it flags are redone by the SIMT kernel."""
     rptr, N, ldr, D = _rows(recon, "recon")
     qptr, nq, ldq, Dq = _rows(queries, "queries")
     if D != Dq:
         raise B200VQError(f"ivf_search: dimension mismatch {D} vs {Dq}")
     if row_off.dtype != torch.int64 or row_off.numel() != K + 1:
         raise B200VQError("ivf_search: row_off must be int64 with K + 1 entries")
+    if impl not in ("auto", "tc", "simt"):
+        raise B200VQError(f"ivf_search: unknown impl {impl!r}")
     probe = probe.contiguous()
     nprobe = probe.shape[1]
     mid = metric_id(metric)
     lib = _lib.load()
     vals = torch.empty((nq, k), dtype=torch.float32, device=recon.device)
     ids = torch.empty((nq, k), dtype=torch.int32, device=recon.device)
+    tc_ok = (rowcluster is not None and N >= 1024 and D % 32 == 0 and ldr % 4 == 0 and ldq % 4 == 0 and
+             rptr % 16 == 0 and qptr % 16 == 0 and ops.tc_available() and nq > 0)
+    if impl == "tc" and not tc_ok:
+        raise B200VQError("ivf_search(impl='tc'): needs N >= 1024, D % 32 == 0, aligned rows and the row -> cluster map")
+    if impl != "simt" and tc_ok:
+        if rnorm is None:
+            rnorm = ops.row_sqnorms(recon)
+        flags = torch.empty((nq,), dtype=torch.int32, device=recon.device)
+        sc = scratch(lib.b200vq_ivf_search_tc_scratch_bytes(N, nq, K, k), recon.device, "ivf_tc")
+        check(lib.b200vq_ivf_search_tc(rptr, N, ldr, D, rnorm.data_ptr(), gid.data_ptr(), rowcluster.data_ptr(), K, qptr,
+                                       nq, ldq, probe.data_ptr(), nprobe, mid, k, vals.data_ptr(), ids.data_ptr(),
+                                       flags.data_ptr(), None, sc.data_ptr(), sc.numel(), _stream()),
+              "ivf_search_tc")
+        redo = torch.nonzero(flags, as_tuple=False).flatten()      # host sync; the results go to the host anyway
+        if redo.numel():
+            v2, i2 = ivf_search(recon, rnorm, gid, row_off, K, queries[redo].contiguous(), probe[redo].contiguous(), k,
+                                metric, impl="simt")
+            vals[redo], ids[redo] = v2, i2
+        return vals, ids
     sc = scratch(lib.b200vq_ivf_search_scratch_bytes(nq, nprobe, K, k), recon.device, "ivf")
     check(lib.b200vq_ivf_search(rptr, ldr, D, _p(rnorm), gid.data_ptr(), row_off.data_ptr(), K, qptr, nq, ldq,
                                 probe.data_ptr(), nprobe, mid, k, vals.data_ptr(), ids.data_ptr(), sc.data_ptr(),

@@ -60,6 +60,9 @@ struct Params {
     int metric;
     float ebound;             // 2^-10 * 1.02 + 3 D 2^-24
     int dense;                // stage 0: every row is a survivor, slot = row - r0 (no counters, no atomics)
+    const uint32_t* rowcluster;   // IVF mode (b200vq_ivf_search_tc): cluster of every row, or null
+    const uint32_t* probe_bits;   // IVF mode: (nq, kwords) bitmap of the clusters each query probes
+    int kwords;
 };
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -152,6 +155,7 @@ flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const int64_t row = p.r0 + t * TILE_ROWS + q4 * 32 + lane;
             const bool live = row < p.r1;
             float a = 0.f, b = 0.f;
+            const uint32_t rc = (live && p.rowcluster) ? p.rowcluster[row] : 0u;
             if (live) {
                 const float xn = p.xnorm[row];
                 const float rs = p.row_scale ? p.row_scale[row] : 1.f;
@@ -191,6 +195,9 @@ flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                             }
                         } else if (live && lb <= th[e]) {
                             const int q = u * TILE_Q + cb * 64 + 4 * j4 + e;
+                            // IVF mode: the row only counts for queries that probe its cluster (tested on the few
+                            // survivors, not on every accumulator value)
+                            if (p.probe_bits && !((p.probe_bits[(size_t)q * p.kwords + (rc >> 5)] >> (rc & 31u)) & 1u)) continue;
                             const uint32_t pos = atomicAdd(p.count + q, 1u);
                             if (pos < p.cap) {
                                 p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
@@ -216,7 +223,8 @@ flat_screen_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 
 // |q|^2 of every query with the SIMT kernel's arithmetic (lane-strided FMA chain + xor tree), and their maximum.
 __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, int64_t ldq, int D, float* __restrict__ qn,
-                                   float* __restrict__ qstats, float* __restrict__ thr) {
+                                   float* __restrict__ qstats, float* __restrict__ thr,
+                                   const float* __restrict__ init_vals, int metric) {
     const int lane = threadIdx.x & 31;
     const int q = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (q >= nq) return;
@@ -226,7 +234,11 @@ __global__ void flat_qstats_kernel(const float* __restrict__ queries, int nq, in
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL_MASK, acc, o);
     if (lane == 0) {
         qn[q] = acc;
-        thr[q] = __int_as_float(0x7f800000);    // first stage: every row passes (padding queries keep their NaN)
+        // first stage: every row passes (padding queries keep their NaN), unless the caller knows an upper bound of
+        // the k-th best value already (IVF mode: the exact k-th best of the nearest cluster)
+        float t = __int_as_float(0x7f800000);
+        if (init_vals && init_vals[q] < t && init_vals[q] > -t) t = metric == B200VQ_METRIC_L2 ? init_vals[q] - acc : -init_vals[q];
+        thr[q] = t;
         atomicMax(reinterpret_cast<int*>(qstats), __float_as_int(acc));   // non-negative floats order as ints
     }
 }
@@ -336,7 +348,8 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
                    const float* __restrict__ row_scale, const float* __restrict__ queries, int64_t ldq, int metric, int k,
                    const uint32_t* __restrict__ cand, uint32_t* __restrict__ count, uint32_t cap,
                    uint64_t* __restrict__ running, float* __restrict__ thr, uint32_t* __restrict__ flags, int last,
-                   float* __restrict__ out_vals, uint32_t* __restrict__ out_ids, uint32_t seed_rows) {
+                   float* __restrict__ out_vals, uint32_t* __restrict__ out_ids, uint32_t seed_rows,
+                   const uint32_t* __restrict__ idmap = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint64_t best[128];
     __shared__ float qn_s;
@@ -427,7 +440,7 @@ flat_finish_kernel(const float* __restrict__ x, int64_t ldx, int D, const float*
         float key;
         if (metric == B200VQ_METRIC_L2) key = fmaxf(__fmaf_rn(-2.f, acc, __fadd_rn(qn, valid ? xnorm[row] : 0.f)), 0.f);
         else key = -acc;
-        tk.offer(valid, key, row);
+        tk.offer(valid, key, (idmap && valid) ? idmap[row] : row);    // IVF mode: ranked and reported by global id
     }
     block_emit_topk<CAP>(tk, mbuf, n2, k, best);
     __syncthreads();
@@ -469,7 +482,7 @@ constexpr int64_t FLAT_STAGE_GROWTH = 8;   // rows seen after a stage / rows see
                                           // screen launch + a 30 us pool kernel and k ln(growth) appended survivors per query:
                                           // 3 -> 5.14 / 1.69 ms, 8 -> 4.64 / 1.43 ms (1M x 1536 k = 10 / 100K x 1536 k = 100, 1000 queries)
 constexpr int64_t FIRST_ROWS = 2048;  // stage 0 (infinite threshold: every row enters the pool kernel, dense slots, no atomics)
-constexpr int64_t MIN_ROWS = 65536;   // below this the SIMT kernel alone is as fast
+constexpr int64_t MIN_ROWS = 1024;    // below this the SIMT kernel alone is as fast (one dense stage covers up to 2048 rows)
 struct FlatPlan {
     uint32_t cap;
     int ntq;
@@ -516,22 +529,42 @@ template <int CAP>
 static int finish_launch(const float* x, int64_t ldx, int D, const float* xnorm, const float* row_scale,
                          const float* queries, int nq, int64_t ldq, int metric, int k, const uint32_t* cand,
                          uint32_t* count, uint32_t cap, uint64_t* running, float* thr, uint32_t* flags, int last,
-                         float* out_vals, uint32_t* out_ids, cudaStream_t st, uint32_t seed_rows = 0) {
+                         float* out_vals, uint32_t* out_ids, cudaStream_t st, uint32_t seed_rows = 0,
+                         const uint32_t* idmap = nullptr) {
     const int n2 = next_pow2((FIN_THREADS / 32) * k);
     const size_t smem = (((size_t)D * 4 + 15) & ~(size_t)15) + (size_t)((FIN_THREADS / 32) * CAP + n2) * 8 +
                         (size_t)(FIN_THREADS / 32) * 32 * FIN_TILE_LD * 4;
     VQ_CUDA(cudaFuncSetAttribute(flat_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     flat_finish_kernel<CAP><<<nq, FIN_THREADS, smem, st>>>(x, ldx, D, xnorm, row_scale, queries, ldq, metric, k, cand,
                                                          count, cap, running, thr, flags, last, out_vals, out_ids,
-                                                         seed_rows);
+                                                         seed_rows, idmap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
 
-extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
-                                   const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
-                                   int k, float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes,
-                                   void* stream) {
+// IVF mode of the same search (b200vq_ivf_search_tc): rows = cluster-sorted reconstructions, a row only counts for the
+// queries whose probe list holds its cluster, ids are mapped to global ids, flagged queries are reported to the caller.
+struct IvfMode {
+    const uint32_t* rowcluster;
+    const uint32_t* probe;     // (nq, nprobe)
+    int nprobe, K;
+    const uint32_t* gid;
+    uint32_t* flags_out;       // (nq)
+    uint32_t* bits;            // (nq, kwords) scratch
+    const float* init_vals;    // (nq) or null: an upper bound of every query's k-th best value
+};
+__global__ void ivf_bits_kernel(const uint32_t* __restrict__ probe, int64_t total, int nprobe, int K, int kwords,
+                                uint32_t* __restrict__ bits) {
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t c = probe[e];
+        if (c < (uint32_t)K) atomicOr(bits + (e / nprobe) * kwords + (c >> 5), 1u << (c & 31u));
+    }
+}
+
+static int flat_tc_run(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                       const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
+                       int k, float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                       void* stream, const IvfMode* ivf) {
     VQ_CHECK_ARG(x && queries && out_vals && out_ids, "flat_topk_tc: null pointer");
     VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && ldx >= D && ldq >= D && nq >= 0, "flat_topk_tc: bad shape");
     VQ_CHECK_ARG(k > 0 && k <= 128, "flat_topk_tc: k must be in [1,128], got %d", k);
@@ -542,7 +575,10 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     VQ_CHECK_ARG(scratch && scratch_bytes >= fp.total, "flat_topk_tc: scratch too small (%zu < %zu)", scratch_bytes,
                  fp.total);
     uint8_t* sb = reinterpret_cast<uint8_t*>(scratch);
-    if (!tc_applies(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k))   // shapes the screen does not cover
+    if (ivf) {
+        VQ_CHECK_ARG(tc_applies(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k),
+                     "ivf_search_tc: shape not covered by the tensor-core screen (n >= 65536, D %% 32 == 0, aligned rows)");
+    } else if (!tc_applies(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k))   // shapes the screen does not cover
         return b200vq_flat_topk(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids,
                                 sb + fp.off_simt, fp.off_running - fp.off_simt, stream);
     cudaStream_t st = as_stream(stream);
@@ -569,7 +605,8 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     VQ_CUDA(cudaMemsetAsync(flags, 0, (size_t)nq * 4, st));
     VQ_CUDA(cudaMemsetAsync(count, 0, (size_t)nq * 4, st));
     VQ_CUDA(cudaMemsetAsync(pool_cnt, 0, (size_t)nq * 4, st));
-    flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats, thr);
+    flat_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qn, qstats, thr,
+                                                                                   ivf ? ivf->init_vals : nullptr, metric);
     VQ_LAUNCH_CHECK();
 
     CUtensorMap map_x, map_q;
@@ -586,8 +623,21 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
     p.count = count;
     p.cap = fp.cap; p.nq = nq; p.nchunk = D / CH; p.ntq = fp.ntq; p.metric = metric;
     p.ebound = 0.0009765625f * 1.02f + 3.0f * (float)D * 5.9604645e-8f;
+    p.rowcluster = nullptr; p.probe_bits = nullptr; p.kwords = 0;
+    if (ivf) {
+        p.kwords = (ivf->K + 31) / 32;
+        VQ_CUDA(cudaMemsetAsync(ivf->bits, 0, (size_t)nq * p.kwords * 4, st));
+        const int64_t total = (int64_t)nq * ivf->nprobe;
+        ivf_bits_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
+            ivf->probe, total, ivf->nprobe, ivf->K, p.kwords, ivf->bits);
+        VQ_LAUNCH_CHECK();
+        p.rowcluster = ivf->rowcluster;
+        p.probe_bits = ivf->bits;
+    }
     const int sms = device_sm_count();
-    const int64_t growth = FLAT_STAGE_GROWTH;
+    // IVF mode: a query admits every probed row until k of them have been seen, so the stages grow slowly (x3): a
+    // stage of S rows appends nprobe / K * S rows to such a query's list (4096 slots)
+    const int64_t growth = ivf ? 3 : FLAT_STAGE_GROWTH;
     int gen = 0;
     // Stage 0 covers rows [0, FIRST_ROWS) with an infinite threshold (all of them enter the pool kernel, which keeps
     // the k + few that matter); later stages grow x3. No row is re-read until the single exact pass at the end.
@@ -595,7 +645,7 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
         int64_t r1 = r == 0 ? FIRST_ROWS : r * growth;
         if (r1 > n || n - r1 < r1 / 4) r1 = n;  // fold a short tail into the last stage
         p.r0 = r; p.r1 = r1;
-        p.dense = r == 0;
+        p.dense = r == 0 && !ivf;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
         flat_screen_kernel<<<(unsigned)(units < sms ? units : sms), THREADS, SMEM_BYTES, st>>>(map_x, map_q, p);
@@ -603,18 +653,55 @@ extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D
         flat_pool_kernel<<<nq, 256, pool_smem, st>>>(xnorm, row_scale, qstats, p.ebound, metric, k, cand, cand_lb, cand_ub,
                                                      count, fp.cap, prow[gen], plb[gen], pub[gen], prow[gen ^ 1],
                                                      plb[gen ^ 1], pub[gen ^ 1], pool_cnt, thr, flags,
-                                                     r == 0 ? (uint32_t)(r1 - r) : 0u);
+                                                     p.dense ? (uint32_t)(r1 - r) : 0u);
         VQ_LAUNCH_CHECK();
         gen ^= 1;
         r = r1;
     }
     // exact keys of the pool rows, top-k in (key, id) order
+    const uint32_t* idmap = ivf ? ivf->gid : nullptr;
     rc = (k <= 32) ? finish_launch<64>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, prow[gen], pool_cnt,
-                                       (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st)
+                                       (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st, 0, idmap)
                    : finish_launch<256>(x, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, prow[gen], pool_cnt,
-                                        (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st);
+                                        (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st, 0, idmap);
     if (rc != B200VQ_OK) return rc;
+    if (ivf) {   // the caller redoes flagged queries with the exact cluster-major kernel (b200vq_ivf_search)
+        VQ_CUDA(cudaMemcpyAsync(ivf->flags_out, flags, (size_t)nq * 4, cudaMemcpyDeviceToDevice, st));
+        return B200VQ_OK;
+    }
     // queries whose survivor list overflowed in some stage: exact SIMT search, gated per query
     return flat_topk_gated(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids,
                            sb + fp.off_simt, flags, st);
+}
+
+extern "C" int b200vq_flat_topk_tc(const float* x, int64_t n, int64_t ldx, int D, const float* xnorm,
+                                   const float* row_scale, const float* queries, int nq, int64_t ldq, int metric,
+                                   int k, float* out_vals, uint32_t* out_ids, void* scratch, size_t scratch_bytes,
+                                   void* stream) {
+    return flat_tc_run(x, n, ldx, D, xnorm, row_scale, queries, nq, ldq, metric, k, out_vals, out_ids, scratch,
+                       scratch_bytes, stream, nullptr);
+}
+
+extern "C" size_t b200vq_ivf_search_tc_scratch_bytes(int64_t n, int nq, int K, int k) {
+    if (n < 0 || nq <= 0 || k <= 0 || K <= 0) return 0;
+    return plan_flat(n, nq, k).total + 256 + (size_t)nq * ((K + 31) / 32) * 4;
+}
+
+extern "C" int b200vq_ivf_search_tc(const float* recon, int64_t n, int64_t ldr, int D, const float* rnorm,
+                                    const uint32_t* gid, const uint32_t* rowcluster, int K, const float* queries, int nq,
+                                    int64_t ldq, const uint32_t* probe, int nprobe, int metric, int k, float* out_vals,
+                                    uint32_t* out_ids, uint32_t* flags_out, const float* init_vals, void* scratch,
+                                    size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(gid && rowcluster && probe && flags_out && rnorm, "ivf_search_tc: null pointer");
+    VQ_CHECK_ARG(K > 0 && nprobe > 0 && nq >= 0, "ivf_search_tc: bad shape");
+    if (nq == 0) return B200VQ_OK;
+    const size_t base = plan_flat(n, nq, k).total;
+    const size_t need = b200vq_ivf_search_tc_scratch_bytes(n, nq, K, k);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "ivf_search_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
+    IvfMode m;
+    m.rowcluster = rowcluster; m.probe = probe; m.nprobe = nprobe; m.K = K; m.gid = gid; m.flags_out = flags_out;
+    m.init_vals = init_vals;
+    m.bits = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + ((base + 255) & ~(size_t)255));
+    return flat_tc_run(recon, n, ldr, D, rnorm, nullptr, queries, nq, ldq, metric, k, out_vals, out_ids, scratch, base,
+                       stream, &m);
 }

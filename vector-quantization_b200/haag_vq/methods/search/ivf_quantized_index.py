@@ -83,6 +83,7 @@ class IvfQuantizedIndex(BaseSearchIndex):
         recon = torch.empty((N, D), dtype=torch.float32, device=dev)
         gid = np.empty(N, dtype=np.uint32)
         row_off = np.zeros(K + 1, dtype=np.int64)
+        rowc = np.empty(N, dtype=np.uint32)
         pos = 0
         for c in range(K):
             vid = self._cluster_ids[c]
@@ -91,6 +92,7 @@ class IvfQuantizedIndex(BaseSearchIndex):
                 r = q.decompress(self._cluster_codes[c]).astype(np.float32) + self._centroids[c]
                 recon[pos:pos + vid.size] = host.to_device(np.ascontiguousarray(r))
                 gid[pos:pos + vid.size] = vid
+                rowc[pos:pos + vid.size] = c
                 pos += vid.size
             row_off[c + 1] = pos
         recon = recon[:pos]
@@ -100,6 +102,7 @@ class IvfQuantizedIndex(BaseSearchIndex):
             'rnorm': ops.row_sqnorms(recon) if pos else torch.empty(0, dtype=torch.float32, device=dev),
             'gid': host.to_device(gid[:pos]),
             'row_off': torch.from_numpy(row_off).to(dev),
+            'rowcluster': host.to_device(rowc[:pos]),
         }
 
     # --------------------------------------------------------------- search
@@ -109,7 +112,7 @@ class IvfQuantizedIndex(BaseSearchIndex):
         return host.to_host(probe).astype(np.int64)
 
     def _probe(self, qd: torch.Tensor) -> torch.Tensor:
-        _, ids = ops.flat_topk(self._dev['centroids'], qd, min(self._nprobe, self._K), self._metric, impl="simt")
+        _, ids = ops.flat_topk(self._dev['centroids'], qd, min(self._nprobe, self._K), self._metric)
         return ids
 
     def search(self, Q: np.ndarray, k: int) -> np.ndarray:
@@ -133,7 +136,7 @@ class IvfQuantizedIndex(BaseSearchIndex):
         qd = host.to_device(Q)
         d = self._dev
         vals, ids = ivf.ivf_search(d['recon'], d['rnorm'], d['gid'], d['row_off'], self._K, qd, self._probe(qd), k,
-                                   self._metric)
+                                   self._metric, rowcluster=d['rowcluster'])
         ids_h = host.to_host(ids).view(np.uint32)
         dists = host.to_host(vals)
         if self._metric == 'ip':
