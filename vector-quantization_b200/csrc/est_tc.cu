@@ -70,8 +70,10 @@ struct Params {
     const float* qstats;      // [0] = max_q |q|^2, [1] = max_q |C_q|
     const float* tables;      // concatenated value tables
     uint32_t* cand;           // (nq, cap)
+    float* cand_lb;           // (nq, cap) the survivors' lower bounds
     uint32_t* count;          // (nq)
     uint32_t cap;
+    int dense;                // stage 0: every row is a survivor, slot = row - r0 (no counters, no atomics)
     int64_t r0, r1;           // rows of this stage
     int nq, nchunk, ntq, ntab;
     int64_t ntr;
@@ -402,10 +404,19 @@ est_screen_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float lb = __fmaf_rn(a, v[4 * j4 + e], b);
-                        if (live && lb <= th[e]) {
+                        if (p.dense) {
+                            const int q = u * TILE_Q + cb * 32 + 4 * j4 + e;
+                            if (live && q < p.nq) {
+                                p.cand[(size_t)q * p.cap + (uint32_t)(row - p.r0)] = (uint32_t)row;
+                                p.cand_lb[(size_t)q * p.cap + (uint32_t)(row - p.r0)] = lb;
+                            }
+                        } else if (live && lb <= th[e]) {
                             const int q = u * TILE_Q + cb * 32 + 4 * j4 + e;
                             const uint32_t pos = atomicAdd(p.count + q, 1u);
-                            if (pos < p.cap) p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
+                            if (pos < p.cap) {
+                                p.cand[(size_t)q * p.cap + pos] = (uint32_t)row;
+                                p.cand_lb[(size_t)q * p.cap + pos] = lb;
+                            }
                         }
                     }
                 }
@@ -491,7 +502,7 @@ __global__ void __launch_bounds__(256) est_rownorm_kernel(const __grid_constant_
 
 // max_q |q|^2 (lane-strided chain + tree; only bounds the screen error) and max_q |C_q|
 __global__ void est_qstats_kernel(const float* __restrict__ queries, int nq, int64_t ldq, int D, const float* __restrict__ qconst,
-                                  float* __restrict__ qstats) {
+                                  float* __restrict__ qstats, float* __restrict__ thr) {
     const int lane = threadIdx.x & 31;
     const int q = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (q >= nq) return;
@@ -502,6 +513,97 @@ __global__ void est_qstats_kernel(const float* __restrict__ queries, int nq, int
     if (lane == 0) {
         atomicMax(reinterpret_cast<int*>(qstats), __float_as_int(acc));   // non-negative floats order as ints
         atomicMax(reinterpret_cast<int*>(qstats) + 1, __float_as_int(fabsf(qconst ? qconst[q] : 0.f)));
+        thr[q] = __int_as_float(0x7f800000);    // first stage: every row passes (padding queries keep their NaN)
+    }
+}
+
+// Candidate pool between the stages (the scheme of flat_tc.cu: flat_pool_kernel): no code row is decoded again until
+// the one exact pass at the end. UB = LB + 4E (L2) / LB + 2E (IP) with the screen's own E; U = k-th smallest UB over
+// pool and new survivors bounds the final k-th best key from above, the pool keeps the rows with LB <= U and U is the
+// next stage's threshold. One CTA per query; pool arrays double-buffered by stage parity.
+constexpr int POOL_CAP = 1024;
+constexpr int POOL_MAX_ENTRIES = 8192;
+__global__ void __launch_bounds__(256)
+est_pool_kernel(const float* __restrict__ norm2, const float* __restrict__ bias, const float* __restrict__ qstats,
+                float ebound, int metric, int k, const uint32_t* __restrict__ cand, const float* __restrict__ cand_lb,
+                float* __restrict__ cand_ub, uint32_t* __restrict__ count, uint32_t cap,
+                const uint32_t* __restrict__ prow_in, const float* __restrict__ plb_in, const float* __restrict__ pub_in,
+                uint32_t* __restrict__ prow_out, float* __restrict__ plb_out, float* __restrict__ pub_out,
+                uint32_t* __restrict__ pool_cnt, float* __restrict__ thr, uint32_t* __restrict__ flags,
+                uint32_t dense_count) {
+    extern __shared__ __align__(16) unsigned char pool_smem[];
+    uint64_t* keys = reinterpret_cast<uint64_t*>(pool_smem);
+    __shared__ uint32_t s_np;
+    const int q = blockIdx.x;
+    uint32_t cnt = dense_count ? dense_count : count[q];
+    bool overflow = false;
+    if (cnt > cap) {
+        cnt = cap;
+        overflow = true;
+    }
+    const uint32_t pc = pool_cnt[q];
+    uint32_t total = pc + cnt;
+    if (total > POOL_MAX_ENTRIES) {
+        total = POOL_MAX_ENTRIES;
+        overflow = true;
+    }
+    const int n2 = next_pow2((int)(total < 2 ? 2 : total));
+    const float qn_max = qstats[0], qc_max = qstats[1], q_max = sqrtf(qn_max) * 1.0000005f;
+    const uint32_t* list = cand + (size_t)q * cap;
+    const float* llb = cand_lb + (size_t)q * cap;
+    float* lub = cand_ub + (size_t)q * cap;
+    const size_t pq = (size_t)q * POOL_CAP;
+    if (threadIdx.x == 0) s_np = 0;
+    for (int e = threadIdx.x; e < n2; e += blockDim.x) {
+        uint64_t key = KEY_INF;
+        if ((uint32_t)e < pc) {
+            key = make_key(pub_in[pq + e], (uint32_t)e);
+        } else if ((uint32_t)e < total) {
+            const uint32_t row = list[e - pc];
+            const float xn = norm2[row];
+            const float slack = 2.4e-7f * (xn + fabsf(bias[row]) + qn_max + qc_max);
+            const float E = ebound * (sqrtf(xn) * 1.0000005f) * q_max + slack;     // est_screen_kernel's bound
+            const float ub = llb[e - pc] + (metric == B200VQ_METRIC_L2 ? 4.f : 2.f) * E + slack;
+            lub[e - pc] = ub;
+            key = make_key(ub, (uint32_t)e);
+        }
+        keys[e] = key;
+    }
+    block_bitonic_sort(keys, n2);
+    const float U = ((uint32_t)k <= total) ? key_value(keys[k - 1]) : __int_as_float(0x7f800000);
+    __syncthreads();
+    for (uint32_t e = threadIdx.x; e < total; e += blockDim.x) {
+        uint32_t row;
+        float lb, ub;
+        if (e < pc) {
+            row = prow_in[pq + e];
+            lb = plb_in[pq + e];
+            ub = pub_in[pq + e];
+        } else {
+            row = list[e - pc];
+            lb = llb[e - pc];
+            ub = lub[e - pc];
+        }
+        if (lb <= U) {
+            const uint32_t pos = atomicAdd(&s_np, 1u);
+            if (pos < POOL_CAP) {
+                prow_out[pq + pos] = row;
+                plb_out[pq + pos] = lb;
+                pub_out[pq + pos] = ub;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t np = s_np;
+        if (np > POOL_CAP) {
+            np = POOL_CAP;
+            overflow = true;
+        }
+        pool_cnt[q] = np;
+        thr[q] = U;
+        count[q] = 0;
+        if (overflow) flags[q] = 1;     // redone exactly by the gated launch
     }
 }
 
@@ -597,13 +699,14 @@ using namespace b200vq;
 using namespace b200vq::est;
 
 namespace {
-constexpr int64_t STAGE_GROWTH = 3;
-constexpr int64_t SEED_ROWS = 1024;
+constexpr int64_t STAGE_GROWTH = 8;     // as flat_tc.cu: a stage costs a screen launch and a 30 us pool kernel
+constexpr int64_t FIRST_ROWS = 2048;    // stage 0: infinite threshold, dense slots
 constexpr int64_t MIN_SCREEN_ROWS = 16384;   // below this the exact kernel alone scores every row
 struct EstPlan {
     uint32_t cap;
     int ntq;
-    size_t off_running, off_thr, off_count, off_flags, off_qstats, off_tables, off_cand, total;
+    size_t off_running, off_thr, off_count, off_flags, off_qstats, off_tables, off_cand, off_cand_lb, off_cand_ub, off_pool,
+        off_pool_cnt, total;
 };
 EstPlan plan_est(int nq, int k) {
     EstPlan f;
@@ -620,6 +723,10 @@ EstPlan plan_est(int nq, int k) {
     f.off_qstats = o;  o = up(o + 16);
     f.off_tables = o;  o = up(o + (size_t)MAX_TAB * 4);
     f.off_cand = o;    o = up(o + (size_t)nq * f.cap * 4);
+    f.off_cand_lb = o; o = up(o + (size_t)nq * f.cap * 4);
+    f.off_cand_ub = o; o = up(o + (size_t)nq * f.cap * 4);
+    f.off_pool = o;    o = up(o + (size_t)nq * POOL_CAP * 4 * 6);     // rows, lb, ub: two generations
+    f.off_pool_cnt = o; o = up(o + (size_t)nq * 4);
     f.total = o;
     return f;
 }
@@ -751,12 +858,18 @@ extern "C" int b200vq_est_scan_topk(int nseg, const int* seg_len, const int* seg
                                         count, fp.cap, running, thr, flags, LAST, out_vals, out_ids, st, SEED, GATE))
     if (n < MIN_SCREEN_ROWS) return EST_FINISH(1, n, nullptr);   // n == 0: empty lists -> +inf / 0xffffffff
 
+    float* cand_lb = reinterpret_cast<float*>(sb + fp.off_cand_lb);
+    float* cand_ub = reinterpret_cast<float*>(sb + fp.off_cand_ub);
+    uint32_t* pool_cnt = reinterpret_cast<uint32_t*>(sb + fp.off_pool_cnt);
+    const size_t pstride = (size_t)nq * POOL_CAP;
+    uint32_t* prow[2] = {reinterpret_cast<uint32_t*>(sb + fp.off_pool), reinterpret_cast<uint32_t*>(sb + fp.off_pool) + pstride};
+    float* plb[2] = {reinterpret_cast<float*>(sb + fp.off_pool) + 2 * pstride, reinterpret_cast<float*>(sb + fp.off_pool) + 3 * pstride};
+    float* pub[2] = {reinterpret_cast<float*>(sb + fp.off_pool) + 4 * pstride, reinterpret_cast<float*>(sb + fp.off_pool) + 5 * pstride};
     VQ_CUDA(cudaMemsetAsync(qstats, 0, 16, st));
-    est_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qconst, qstats);
-    VQ_LAUNCH_CHECK();
     VQ_CUDA(cudaMemsetAsync(thr, 0xFF, (size_t)fp.ntq * TILE_Q * 4, st));   // NaN: padding queries never pass
-    rc = EST_FINISH(0, SEED_ROWS, nullptr);
-    if (rc != B200VQ_OK) return rc;
+    VQ_CUDA(cudaMemsetAsync(pool_cnt, 0, (size_t)nq * 4, st));
+    est_qstats_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(queries, nq, ldq, D, qconst, qstats, thr);
+    VQ_LAUNCH_CHECK();
 
     CUtensorMap map_q;
     if ((rc = encode_2d(&map_q, queries, (uint64_t)nq, (uint64_t)D, (uint64_t)ldq, TILE_Q, CH, CU_TENSOR_MAP_SWIZZLE_128B)))
@@ -771,23 +884,40 @@ extern "C" int b200vq_est_scan_topk(int nseg, const int* seg_len, const int* seg
         screen = fixed[segs.s[0].bits];
     }
     VQ_CUDA(cudaFuncSetAttribute(screen, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t pool_smem_bytes = (size_t)POOL_MAX_ENTRIES * 8;
+    VQ_CUDA(cudaFuncSetAttribute(est_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pool_smem_bytes));
     Params p;
     p.norm2 = row_norm2; p.bias = row_bias; p.thr = thr; p.qstats = qstats; p.tables = tables; p.cand = cand;
+    p.cand_lb = cand_lb;
     p.count = count; p.cap = fp.cap; p.nq = nq; p.nchunk = D / CH; p.ntq = fp.ntq; p.ntab = ntab; p.metric = metric;
     p.ebound = 0.0009765625f * 1.02f + 3.0f * (float)D * 5.9604645e-8f;
     const int sms = device_sm_count();
-    for (int64_t r = SEED_ROWS; r < n;) {
-        int64_t r1 = r * STAGE_GROWTH;
-        if (r1 > n || n - r1 < r / 2) r1 = n;  // fold a short tail into the last stage
+    int gen = 0;
+    for (int64_t r = 0; r < n;) {
+        int64_t r1 = r == 0 ? FIRST_ROWS : r * STAGE_GROWTH;
+        if (r1 > n || n - r1 < r1 / 4) r1 = n;  // fold a short tail into the last stage
         p.r0 = r; p.r1 = r1;
+        p.dense = r == 0;
         p.ntr = (r1 - r + TILE_ROWS - 1) / TILE_ROWS;
         const int64_t units = p.ntr * p.ntq;
         screen<<<(unsigned)(units < sms ? units : sms), THREADS, smem, st>>>(map_q, segs, p);
         VQ_LAUNCH_CHECK();
-        rc = EST_FINISH(r1 == n, 0, nullptr);
-        if (rc != B200VQ_OK) return rc;
+        est_pool_kernel<<<nq, 256, pool_smem_bytes, st>>>(row_norm2, row_bias, qstats, p.ebound, metric, k, cand, cand_lb,
+                                                          cand_ub, count, fp.cap, prow[gen], plb[gen], pub[gen],
+                                                          prow[gen ^ 1], plb[gen ^ 1], pub[gen ^ 1], pool_cnt, thr, flags,
+                                                          p.dense ? (uint32_t)(r1 - r) : 0u);
+        VQ_LAUNCH_CHECK();
+        gen ^= 1;
         r = r1;
     }
+    // canonical keys of the pool rows, top-k in (key, id) order
+    rc = (k <= 32) ? est_finish_launch<64>(segs, tables, ntab, D, row_bias, queries, nq, ldq, qconst, metric, k, prow[gen],
+                                           pool_cnt, (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st, 0,
+                                           nullptr)
+                   : est_finish_launch<256>(segs, tables, ntab, D, row_bias, queries, nq, ldq, qconst, metric, k, prow[gen],
+                                            pool_cnt, (uint32_t)POOL_CAP, running, thr, flags, 1, out_vals, out_ids, st, 0,
+                                            nullptr);
+    if (rc != B200VQ_OK) return rc;
     // queries whose survivor list overflowed in some stage: exact scan of all rows, gated per query
     return EST_FINISH(1, n, flags);
 #undef EST_FINISH
