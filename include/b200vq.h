@@ -330,6 +330,17 @@ int b200vq_erabitq_pack_tc(const float* y, int64_t ldy, const void* x, int x_is_
                            const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
                            const double* levels, const double* bounds, double err_rel, double err_abs,
                            uint8_t* codes, unsigned long long* stats, void* stream);
+
+/* The same encoder, same codes and trailers, with the exact re-evaluations deferred to a second kernel that visits them
+ * coordinate by coordinate (bucket per coordinate d: row d of P^T and the centre sit in shared memory and are read
+ * once for all the rows flagged at d, instead of 12 KB of P^T per flagged coordinate); a third kernel writes the
+ * rescale factors from the corrected sums. y (the fp32 rotated residuals) and scratch are required. */
+size_t b200vq_erabitq_pack_tc2_scratch_bytes(int64_t n, int D);
+int b200vq_erabitq_pack_tc2(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                            const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
+                            const double* levels, const double* bounds, double err_rel, double err_abs,
+                            uint8_t* codes, unsigned long long* stats, void* scratch, size_t scratch_bytes,
+                            void* stream);
 /* a_i = nrm_i t_i / sqrt(D) read from the code trailers: the row scale of the code-domain estimator. */
 int b200vq_erabitq_rowscale(const uint8_t* codes, int64_t n, int D, int B, float* a, void* stream);
 /* Unpack: shat (n, D) fp64 = levels[idx]/sqrt(D)*t ; nrm_out (n) fp64. The caller

@@ -75,6 +75,9 @@ SIGNATURES = {
     "b200vq_resid_norms_f64": (_i, [_p, _i, _i64, _i64, _i, _p, _p, _p]),
     "b200vq_erabitq_pack_tc": (_i, [_p, _i64, _p, _i, _i64, _p, _p, _p, _i64, _i, _i, _p, _p, C.c_double, C.c_double,
                                     _p, _p, _p]),
+    "b200vq_erabitq_pack_tc2_scratch_bytes": (_sz, [_i64, _i]),
+    "b200vq_erabitq_pack_tc2": (_i, [_p, _i64, _p, _i, _i64, _p, _p, _p, _i64, _i, _i, _p, _p, C.c_double, C.c_double,
+                                     _p, _p, _p, _sz, _p]),
     "b200vq_erabitq_rowscale": (_i, [_p, _i64, _i, _i, _p, _p]),
     "b200vq_erabitq_unpack": (_i, [_p, _i64, _i, _i, _p, _p, _p, _p]),
     "b200vq_erabitq_scan_scratch_bytes": (_sz, [_i64, _i, _i]),

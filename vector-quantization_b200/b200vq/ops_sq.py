@@ -138,7 +138,8 @@ def erabitq_rotation_error_bound(D: int, c_norm: float) -> tuple:
 
 def erabitq_pack_tc(y: torch.Tensor | None, x: torch.Tensor, c: torch.Tensor, PT: torch.Tensor, nrm: torch.Tensor,
                     B: int, levels: torch.Tensor, bounds: torch.Tensor, err_rel: float, err_abs: float,
-                    out: torch.Tensor | None = None, stats: torch.Tensor | None = None) -> torch.Tensor:
+                    out: torch.Tensor | None = None, stats: torch.Tensor | None = None,
+                    deferred: bool = True) -> torch.Tensor:
     """Extended-RaBitQ codes from the fp32 rotated residuals y (or, y None, all-exact fp64) with exact fp64
     re-evaluation of the coordinates inside the rotation's error bound of a level mid-point."""
     for t, name in ((c, "c"), (PT, "PT"), (nrm, "nrm"), (levels, "levels"), (bounds, "bounds")):
@@ -154,9 +155,18 @@ def erabitq_pack_tc(y: torch.Tensor | None, x: torch.Tensor, c: torch.Tensor, PT
             raise B200VQError("erabitq_pack_tc: y and x disagree")
     if out is None:
         out = torch.empty((n, (D * B + 7) // 8 + 8), dtype=torch.uint8, device=x.device)
-    check(_lib.load().b200vq_erabitq_pack_tc(yptr, ldy, ptr, int(x.dtype == torch.float64), ldx, c.data_ptr(),
-                                             PT.data_ptr(), nrm.data_ptr(), n, D, B, levels.data_ptr(), bounds.data_ptr(),
-                                             err_rel, err_abs, out.data_ptr(), _p(stats), _stream()), "erabitq_pack_tc")
+    lib = _lib.load()
+    if yptr is not None and n > 0 and deferred:
+        # fix-ups visited coordinate by coordinate in a second kernel (same codes; see b200vq_erabitq_pack_tc2)
+        sc = scratch(lib.b200vq_erabitq_pack_tc2_scratch_bytes(n, D), x.device, "erq_pack")
+        check(lib.b200vq_erabitq_pack_tc2(yptr, ldy, ptr, int(x.dtype == torch.float64), ldx, c.data_ptr(), PT.data_ptr(),
+                                          nrm.data_ptr(), n, D, B, levels.data_ptr(), bounds.data_ptr(), err_rel, err_abs,
+                                          out.data_ptr(), _p(stats), sc.data_ptr(), sc.numel(), _stream()),
+              "erabitq_pack_tc2")
+        return out
+    check(lib.b200vq_erabitq_pack_tc(yptr, ldy, ptr, int(x.dtype == torch.float64), ldx, c.data_ptr(),
+                                     PT.data_ptr(), nrm.data_ptr(), n, D, B, levels.data_ptr(), bounds.data_ptr(),
+                                     err_rel, err_abs, out.data_ptr(), _p(stats), _stream()), "erabitq_pack_tc")
     return out
 
 

@@ -529,7 +529,9 @@ __global__ void __launch_bounds__(256, 4)
 erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
                        const double* __restrict__ c, const double* __restrict__ PT, const double* __restrict__ nrm,
                        int64_t n, int D, int B, const double* __restrict__ levels, const double* __restrict__ bounds,
-                       double err_rel, double err_abs, uint8_t* __restrict__ codes, unsigned long long* __restrict__ stats) {
+                       double err_rel, double err_abs, uint8_t* __restrict__ codes, unsigned long long* __restrict__ stats,
+                       unsigned* __restrict__ bcnt, unsigned long long* __restrict__ bucket, unsigned bcap,
+                       double* __restrict__ numden) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* lv = reinterpret_cast<double*>(smem_raw);        // [2^B]
     double* bd = lv + (1 << B);                              // [2^B - 1] (padded to 2^B)
@@ -573,7 +575,7 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int d = db + e;
-                bool flag = false;
+                bool flag = false, deferred = false;
                 if (d < D) {
                     if (yr) {
                         const double sv = (double)yv[e] * sc;
@@ -583,6 +585,17 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
                         const double sh = lv[lo];
                         num = fma(sv, sh, num);
                         den = fma(sh, sh, den);
+                        if (flag && bcnt) {
+                            // deferred: erabitq_fixup_kernel re-evaluates the coordinate (bucket per coordinate, so
+                            // that a row of P^T is read once for all rows that need it); a full bucket falls back
+                            // to the in-kernel fix-up below
+                            const unsigned pos = atomicAdd(bcnt + d, 1u);
+                            if (pos < bcap) {
+                                bucket[(size_t)d * bcap + pos] = ((unsigned long long)row << 8) | (unsigned long long)lo;
+                                flag = false;
+                                deferred = true;
+                            }
+                        }
                     } else {
                         flag = true;
                     }
@@ -590,6 +603,7 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
                 const unsigned m = __ballot_sync(FULL_MASK, flag);
                 if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
                 nflag += __popc(m);
+                if (bcnt) nfix_total += (unsigned long long)__popc(__ballot_sync(FULL_MASK, deferred));
             }
         }
         __syncwarp();
@@ -657,6 +671,10 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
             code[byte] = (uint8_t)acc;
         }
         if (lane == 0) {
+            if (numden) {
+                numden[2 * row] = num;
+                numden[2 * row + 1] = den;
+            }
             const double t = (den > 1e-12) ? (num / den) : 1.0;
             const uint32_t u0 = __float_as_uint((float)nr);
             const uint32_t u1 = __float_as_uint((float)t);
@@ -835,6 +853,89 @@ static RPlan rplan(int64_t n, int nq) {
     return p;
 }
 
+
+// Deferred fix-ups of erabitq_pack_tc_kernel, one CTA per coordinate d: row d of P^T and the centre sit in shared
+// memory (fp64) and every warp walks its share of the bucket: exact fp64 <x_i - c, P[:, d]>, exact level, the code
+// field is patched in place (atomic and / or on the containing 32-bit words: neighbouring fields belong to other
+// CTAs) and the row's (num, den) sums move from the approximate to the exact contribution.
+template <typename T>
+__global__ void __launch_bounds__(256)
+erabitq_fixup_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
+                     const double* __restrict__ c, const double* __restrict__ PT, const double* __restrict__ nrm, int D,
+                     int B, const double* __restrict__ levels, const double* __restrict__ bounds, uint8_t* __restrict__ codes,
+                     const unsigned* __restrict__ bcnt, const unsigned long long* __restrict__ bucket, unsigned bcap,
+                     double* __restrict__ numden) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* pt = reinterpret_cast<double*>(smem_raw);     // [D]
+    double* cs = pt + D;                                  // [D]
+    double* lv = cs + D;                                  // [2^B]
+    double* bd = lv + (1 << B);                           // [2^B]
+    const int d = blockIdx.x, L = 1 << B;
+    unsigned cnt = bcnt[d];
+    if (cnt == 0) return;
+    if (cnt > bcap) cnt = bcap;
+    for (int k = threadIdx.x; k < D; k += blockDim.x) {
+        pt[k] = PT[(int64_t)d * D + k];
+        cs[k] = c[k];
+    }
+    for (int i = threadIdx.x; i < L; i += blockDim.x) lv[i] = levels[i];
+    for (int i = threadIdx.x; i < L - 1; i += blockDim.x) bd[i] = bounds[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int ibytes = (D * B + 7) >> 3, code_size = ibytes + 8;
+    const double sqrt_d = sqrt((double)D);
+    for (unsigned e = w; e < cnt; e += nw) {
+        const unsigned long long ent = bucket[(size_t)d * bcap + e];
+        const int64_t row = (int64_t)(ent >> 8);
+        const int lo_old = (int)(ent & 255ull);
+        const T* xr = x + row * ldx;
+        double a0 = 0.0, a1 = 0.0;
+        int k = lane;
+        for (; k + 32 < D; k += 64) {
+            a0 = fma((double)xr[k] - cs[k], pt[k], a0);
+            a1 = fma((double)xr[k + 32] - cs[k + 32], pt[k + 32], a1);
+        }
+        if (k < D) a0 = fma((double)xr[k] - cs[k], pt[k], a0);
+        a0 += a1;
+        for (int o = 16; o > 0; o >>= 1) a0 += __shfl_xor_sync(FULL_MASK, a0, o);
+        if (lane == 0) {
+            const double nr = nrm[row], nsafe = fmax(nr, 1e-12);
+            const double sv = (a0 / nsafe) * sqrt_d;
+            const int lo = erabitq_level_of(bd, L, sv);
+            const double so = (double)y[row * ldy + d] * (sqrt_d / nsafe);
+            const double sho = lv[lo_old], sh = lv[lo];
+            atomicAdd(numden + 2 * row, sv * sh - so * sho);
+            atomicAdd(numden + 2 * row + 1, sh * sh - sho * sho);
+            if (lo != lo_old) {
+                // MSB-first B-bit field at bit d B of the row's code: at most two bytes
+                uint8_t* code = codes + row * (int64_t)code_size;
+                const int bit0 = d * B;
+                for (int byte = bit0 >> 3; byte * 8 < bit0 + B; ++byte) {
+                    const int shift = (byte * 8 + 8) - (bit0 + B);       // > 0: left shift inside this byte
+                    const uint32_t mask = ((shift >= 0) ? (((1u << B) - 1u) << shift) : (((1u << B) - 1u) >> (-shift))) & 0xffu;
+                    const uint32_t val = ((shift >= 0) ? ((uint32_t)lo << shift) : ((uint32_t)lo >> (-shift))) & 0xffu;
+                    const uintptr_t addr = reinterpret_cast<uintptr_t>(code + byte);
+                    unsigned* word = reinterpret_cast<unsigned*>(addr & ~(uintptr_t)3);
+                    const int sh8 = 8 * (int)(addr & 3);
+                    atomicAnd(word, ~(mask << sh8));
+                    atomicOr(word, val << sh8);
+                }
+            }
+        }
+    }
+}
+// t = <s, l> / <l, l> of every row from its final sums
+__global__ void erabitq_finalize_kernel(const double* __restrict__ numden, int64_t n, int code_size, int ibytes,
+                                        uint8_t* __restrict__ codes) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    const double num = numden[2 * row], den = numden[2 * row + 1];
+    const uint32_t u1 = __float_as_uint((float)((den > 1e-12) ? (num / den) : 1.0));
+    uint8_t* f = codes + row * (int64_t)code_size + ibytes + 4;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) f[b] = (uint8_t)(u1 >> (8 * b));
+}
+
 }  // namespace b200vq
 
 using namespace b200vq;
@@ -988,32 +1089,111 @@ extern "C" int b200vq_resid_norms_f64(const void* x, int x_is_f64, int64_t n, in
     return B200VQ_OK;
 }
 
-extern "C" int b200vq_erabitq_pack_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
-                                      const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
-                                      const double* levels, const double* bounds, double err_rel, double err_abs,
-                                      uint8_t* codes, unsigned long long* stats, void* stream) {
+namespace {
+struct PackPlan {
+    unsigned bcap;
+    size_t off_cnt, off_bucket, off_numden, total;
+};
+PackPlan pack_plan(int64_t n, int D) {
+    PackPlan p;
+    // a coordinate is flagged with probability ~1.3e-3 (B = 4, D = 1536): four times the expectation, at least 256
+    int64_t cap = (n / 192 + 255) & ~(int64_t)255;
+    if (cap < 256) cap = 256;
+    p.bcap = (unsigned)cap;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t o = 0;
+    p.off_cnt = o;     o = up(o + (size_t)D * 4);
+    p.off_bucket = o;  o = up(o + (size_t)D * cap * 8);
+    p.off_numden = o;  o = up(o + (size_t)n * 16);
+    p.total = o;
+    return p;
+}
+int pack_tc_impl(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx, const double* c, const double* PT,
+                 const double* nrm, int64_t n, int D, int B, const double* levels, const double* bounds, double err_rel,
+                 double err_abs, uint8_t* codes, unsigned long long* stats, void* scratch, size_t scratch_bytes,
+                 void* stream) {
     VQ_CHECK_ARG((x || n == 0) && c && PT && (nrm || n == 0) && levels && bounds && (codes || n == 0) && n >= 0 &&
                      D > 0 && D < 65536 && ldx >= D && (!y || ldy >= D),
                  "erabitq_pack_tc: bad args");
     VQ_CHECK_ARG(B >= 1 && B <= 8, "erabitq_pack_tc: B must be in [1,8], got %d", B);
     VQ_CHECK_ARG(err_rel >= 0.0 && err_abs >= 0.0, "erabitq_pack_tc: negative error bound");
     if (n == 0) return B200VQ_OK;
+    VQ_CHECK_ARG(n < (1ll << 40), "erabitq_pack_tc: too many rows");
     const size_t smem = (size_t)(2 << B) * sizeof(double) + (size_t)8 * 3 * ((D + 15) & ~15) + 16;
     VQ_CHECK_ARG(smem <= 200 * 1024, "erabitq_pack_tc: D too large");
+    cudaStream_t st = as_stream(stream);
+    // deferred fix-ups need the approximate coordinates (y) and a scratch area; otherwise everything happens in-kernel
+    unsigned* bcnt = nullptr;
+    unsigned long long* bucket = nullptr;
+    double* numden = nullptr;
+    PackPlan pp{};
+    const size_t fsmem = (size_t)(2 * D + (2 << B)) * sizeof(double);
+    if (y && scratch && fsmem <= 200 * 1024) {
+        pp = pack_plan(n, D);
+        VQ_CHECK_ARG(scratch_bytes >= pp.total && ((uintptr_t)scratch & 255) == 0,
+                     "erabitq_pack_tc2: scratch too small or not 256-byte aligned (%zu < %zu)", scratch_bytes, pp.total);
+        uint8_t* sb = reinterpret_cast<uint8_t*>(scratch);
+        bcnt = reinterpret_cast<unsigned*>(sb + pp.off_cnt);
+        bucket = reinterpret_cast<unsigned long long*>(sb + pp.off_bucket);
+        numden = reinterpret_cast<double*>(sb + pp.off_numden);
+        VQ_CUDA(cudaMemsetAsync(bcnt, 0, (size_t)D * 4, st));
+    }
     int64_t g = (n + 7) / 8;
     const int64_t cap = (int64_t)device_sm_count() * 8;
     if (g > cap) g = cap;
     if (x_is_f64) {
         VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        erabitq_pack_tc_kernel<double><<<(int)g, 256, smem, as_stream(stream)>>>(
-            y, ldy, reinterpret_cast<const double*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats);
+        erabitq_pack_tc_kernel<double><<<(int)g, 256, smem, st>>>(
+            y, ldy, reinterpret_cast<const double*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes,
+            stats, bcnt, bucket, pp.bcap, numden);
     } else {
         VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        erabitq_pack_tc_kernel<float><<<(int)g, 256, smem, as_stream(stream)>>>(
-            y, ldy, reinterpret_cast<const float*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats);
+        erabitq_pack_tc_kernel<float><<<(int)g, 256, smem, st>>>(
+            y, ldy, reinterpret_cast<const float*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes,
+            stats, bcnt, bucket, pp.bcap, numden);
     }
     VQ_LAUNCH_CHECK();
+    if (bcnt) {
+        const int ibytes = (D * B + 7) >> 3;
+        if (x_is_f64) {
+            VQ_CUDA(cudaFuncSetAttribute(erabitq_fixup_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            erabitq_fixup_kernel<double><<<D, 256, fsmem, st>>>(y, ldy, reinterpret_cast<const double*>(x), ldx, c, PT, nrm, D,
+                                                                B, levels, bounds, codes, bcnt, bucket, pp.bcap, numden);
+        } else {
+            VQ_CUDA(cudaFuncSetAttribute(erabitq_fixup_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            erabitq_fixup_kernel<float><<<D, 256, fsmem, st>>>(y, ldy, reinterpret_cast<const float*>(x), ldx, c, PT, nrm, D, B,
+                                                               levels, bounds, codes, bcnt, bucket, pp.bcap, numden);
+        }
+        VQ_LAUNCH_CHECK();
+        erabitq_finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(numden, n, ibytes + 8, ibytes, codes);
+        VQ_LAUNCH_CHECK();
+    }
     return B200VQ_OK;
+}
+}  // namespace
+
+extern "C" int b200vq_erabitq_pack_tc(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                                      const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
+                                      const double* levels, const double* bounds, double err_rel, double err_abs,
+                                      uint8_t* codes, unsigned long long* stats, void* stream) {
+    return pack_tc_impl(y, ldy, x, x_is_f64, ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats,
+                        nullptr, 0, stream);
+}
+
+// The same encoder with the fix-ups deferred to a second kernel that visits them coordinate by coordinate (a row of
+// P^T is read once for all the rows that need it instead of once per flagged coordinate): same codes, same trailers.
+extern "C" size_t b200vq_erabitq_pack_tc2_scratch_bytes(int64_t n, int D) {
+    if (n <= 0 || D <= 0) return 0;
+    return pack_plan(n, D).total;
+}
+extern "C" int b200vq_erabitq_pack_tc2(const float* y, int64_t ldy, const void* x, int x_is_f64, int64_t ldx,
+                                       const double* c, const double* PT, const double* nrm, int64_t n, int D, int B,
+                                       const double* levels, const double* bounds, double err_rel, double err_abs,
+                                       uint8_t* codes, unsigned long long* stats, void* scratch, size_t scratch_bytes,
+                                       void* stream) {
+    VQ_CHECK_ARG(y && scratch, "erabitq_pack_tc2: needs the approximate coordinates and a scratch area");
+    return pack_tc_impl(y, ldy, x, x_is_f64, ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes, stats,
+                        scratch, scratch_bytes, stream);
 }
 
 extern "C" int b200vq_erabitq_rowscale(const uint8_t* codes, int64_t n, int D, int B, float* a, void* stream) {
