@@ -446,7 +446,8 @@ struct ScanPlan {
 static ScanPlan plan_scan(int64_t n, int nq_ctas) {
     const int64_t unit = 2048;
     int64_t target_ctas = (int64_t)device_sm_count() * 8;
-    int64_t want_chunks = (target_ctas + nq_ctas - 1) / (nq_ctas > 0 ? nq_ctas : 1);
+    // every CTA stages its query's tables first (tens of KB): with many query CTAs one chunk each is enough
+    int64_t want_chunks = nq_ctas * 2 >= target_ctas ? 1 : (target_ctas + nq_ctas - 1) / (nq_ctas > 0 ? nq_ctas : 1);
     if (want_chunks < 1) want_chunks = 1;
     int64_t max_chunks = (n + unit - 1) / unit;
     if (max_chunks < 1) max_chunks = 1;
@@ -475,7 +476,15 @@ template <int TILE>
 static int launch_merge(const uint64_t* part, int nq, int nparts, int k, int negate,
                         float* out_vals, uint32_t* out_ids, cudaStream_t st, const uint32_t* gate = nullptr,
                         uint32_t gate_cap = 0) {
-    merge_partials_kernel<TILE><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids, gate, gate_cap);
+    // the kernel sorts TILE keys per pass whatever the number of partial entries: a few partial lists (small n) take
+    // the 256-key instantiation (an order of magnitude fewer compare-exchange steps)
+    const int64_t total = (int64_t)nparts * k;
+    if (TILE > 256 && k <= 64 && total + k <= 256)
+        merge_partials_kernel<256><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids, gate, gate_cap);
+    else if (TILE > 512 && k <= 128 && total + k <= 512)
+        merge_partials_kernel<512><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids, gate, gate_cap);
+    else
+        merge_partials_kernel<TILE><<<nq, 256, 0, st>>>(part, nparts, k, negate, out_vals, out_ids, gate, gate_cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
