@@ -553,7 +553,7 @@ def run_e2e(args, ctx):
 
 
 def run_configs(ctx):
-    """C1-C4 + SAQ-engine kernel table (tools/config_bench.py), CUDA-event timed on this box, outside the timed
+    """C1-C4 + SAQ-engine + IVF kernel table (tools/config_bench.py), CUDA-event timed on this box, outside the timed
     region of the headline: one row per kernel with its algorithmic bytes / FLOP and fraction of the measured peak."""
     torch = ctx["torch"]
     for key in ("codes", "codes_rot", "xbuf"):
@@ -565,7 +565,7 @@ def run_configs(ctx):
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     try:
         import config_bench
-        rows = config_bench.run(("c1", "c2", "c3", "c4", "saq"), device=ctx["dev"], quick=True)
+        rows = config_bench.run(("c1", "c2", "c3", "c4", "saq", "ivf"), device=ctx["dev"], quick=True)
         for r in rows:
             for k, v in list(r.items()):
                 if isinstance(v, float):

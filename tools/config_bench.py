@@ -262,10 +262,12 @@ def ivf_group():
                  "ms": round(t_fit * 1e3, 1), "units_per_s": n / t_fit, "unit": "vectors"})
     d = idx._dev
     probe = idx._probe(qd)
-    ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2", impl="simt"))
     frac = nprobe / K
-    add("IVF", f"ivf_search simt nprobe={nprobe}/{K} k={k} (cluster-major exact scan of reconstructions)", ms, nq, "queries",
-        flops=2.0 * nq * n * frac * D, note=f"{frac:.3f} of the rows per query")
+    if not QUICK:
+        ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2",
+                                           impl="simt"))
+        add("IVF", f"ivf_search simt nprobe={nprobe}/{K} k={k} (cluster-major exact scan of reconstructions)", ms, nq,
+            "queries", flops=2.0 * nq * n * frac * D, note=f"{frac:.3f} of the rows per query")
     ms = timed(lambda: divf.ivf_search(d["recon"], d["rnorm"], d["gid"], d["row_off"], K, qd, probe, k, "l2",
                                        rowcluster=d["rowcluster"], impl="tc"))
     add("IVF", f"ivf_search tc nprobe={nprobe}/{K} k={k} (tcgen05 screen of all rows, probe lists as a mask; default)", ms,
@@ -280,7 +282,7 @@ def ivf_group():
     print(f"IVF recall@{k} {rec:.4f}", file=sys.stderr, flush=True)
 
 
-def run(which=("c1", "c2", "c3", "c4", "saq"), device=None, quick=False):
+def run(which=("c1", "c2", "c3", "c4", "saq", "ivf"), device=None, quick=False):
     """Run the named config groups; returns the list of rows (and leaves it in `rows`)."""
     global dev, QUICK
     QUICK = bool(quick)
@@ -295,7 +297,7 @@ def run(which=("c1", "c2", "c3", "c4", "saq"), device=None, quick=False):
 
 
 if __name__ == "__main__":
-    which = sys.argv[1].split(",") if len(sys.argv) > 1 else ["c1", "c2", "c3", "c4", "saq"]
+    which = sys.argv[1].split(",") if len(sys.argv) > 1 else ["c1", "c2", "c3", "c4", "saq", "ivf"]
     out_path = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "r2_configs.json")
     run(which)
     os.makedirs(os.path.dirname(out_path), exist_ok=True)
