@@ -157,12 +157,41 @@ def _load_oracle_adc():
     return lib
 
 
+def _load_oracle_pq():
+    path = os.path.join(ROOT, "oracle", "_ref", "liboracle_pq.so")
+    if not os.path.exists(path):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "_ref/liboracle_pq.so"], check=True)
+    lib = ctypes.CDLL(path)
+    lib.oracle_pq_assign_dec.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                     ctypes.c_int, ctypes.c_void_p]
+    lib.oracle_pq_assign_dec.restype = ctypes.c_int
+    return lib
+
+
+_PQ_LIB = None
+
+
+def cpu_assign(X, C):
+    """Nearest-centroid codes on the host cores: oracle/pq_assign.c (C / OpenMP, all threads), the compiled form of
+    oracle.pq.pq_assign (same arithmetic, same codes; tests/test_oracle.py) - an order of magnitude faster than the
+    numpy form, so that the CPU arm is not an under-estimate of what faiss' compute_codes does on the same cores."""
+    global _PQ_LIB
+    if _PQ_LIB is None:
+        _PQ_LIB = _load_oracle_pq()
+    codes = np.empty((X.shape[0], M), dtype=np.uint8)
+    Cc = np.ascontiguousarray(C, dtype=np.float32)
+    rc = _PQ_LIB.oracle_pq_assign_dec(X.ctypes.data, X.shape[0], D, Cc.ctypes.data, M, KSUB, codes.ctypes.data)
+    if rc != 0:
+        raise RuntimeError(f"oracle_pq_assign_dec failed: {rc}")
+    return codes
+
+
 def cpu_step(X, C, codes_db, Q, adc_lib, scores_buf):
-    """One pass of the reference CPU path on a bounded sample: numpy/BLAS nearest-centroid
-    assign (oracle.pq.pq_assign) + ADC scores (C loop, OpenMP) + argpartition top-k."""
+    """One pass of the reference CPU path on a bounded sample: nearest-centroid assign (C / OpenMP restatement of
+    faiss compute_codes) + ADC scores (C loop, OpenMP) + argpartition top-k."""
     from oracle import pq as opq
     t0 = time.perf_counter()
-    opq.pq_assign(X, C)
+    cpu_assign(X, C)
     t1 = time.perf_counter()
     lut = opq.adc_lut(Q, C, opq.L2)
     n = codes_db.shape[0]
@@ -187,7 +216,7 @@ def cpu_setup(enc_rows: int, db_rows: int, nq: int):
     return X, C, codes_db, Q, _load_oracle_adc(), scores
 
 
-CPU_SAMPLE = dict(enc_rows=131_072, db_rows=1_000_000, nq=64)
+CPU_SAMPLE = dict(enc_rows=524_288, db_rows=1_000_000, nq=64)
 
 
 def cpu_baseline_leg(reps: int = 2):
@@ -201,7 +230,7 @@ def cpu_baseline_leg(reps: int = 2):
         ts += b
     return {"value": CPU_SAMPLE["enc_rows"] * reps / te, "unit": "vectors/s", "cores": cores, "kind": "port",
             "adc": {"value": CPU_SAMPLE["db_rows"] * CPU_SAMPLE["nq"] * reps / ts, "unit": "codes/s"},
-            "sample": (f"oracle port (faiss is not vendored in the reference): numpy/BLAS pq_assign of "
+            "sample": (f"oracle port (faiss is not vendored in the reference): C/OpenMP pq_assign of "
                        f"{CPU_SAMPLE['enc_rows']}x{D} rows + C/OpenMP ADC scan of {CPU_SAMPLE['db_rows']} codes x "
                        f"{CPU_SAMPLE['nq']} queries with argpartition top-{K}, {reps} reps")}
 
@@ -222,7 +251,7 @@ def run_reference(args):
         ts += b
     enc = CPU_SAMPLE["enc_rows"] * args.steps / te
     adc = CPU_SAMPLE["db_rows"] * CPU_SAMPLE["nq"] * args.steps / ts
-    sample = (f"per step: pq_assign of {CPU_SAMPLE['enc_rows']}x{D} rows (numpy/BLAS, faiss semantics) + ADC scan of "
+    sample = (f"per step: pq_assign of {CPU_SAMPLE['enc_rows']}x{D} rows (C/OpenMP, faiss semantics) + ADC scan of "
               f"{CPU_SAMPLE['db_rows']} codes x {CPU_SAMPLE['nq']} queries (C/OpenMP restatement of bench/ffd_speed.cpp)")
     line = {"impl": "reference", "metric": METRIC, "value": enc, "unit": "vectors/s",
             "adc": {"value": adc, "unit": "codes/s"}, "n_gpus": args.gpus, "steps": args.steps,

@@ -94,6 +94,30 @@ def test_pq_assign_ties_pick_first_index_and_matches_c_port():
     assert np.all((out == codes) | near)
 
 
+@pytest.mark.parametrize("n,D,M,ksub", [(700, 64, 8, 256), (333, 24, 4, 16), (1, 96, 2, 256), (0, 32, 4, 256)])
+def test_openmp_assign_port_equals_the_numpy_oracle(n, D, M, ksub):
+    """oracle/pq_assign.c (the compiled form bench.py times as the CPU arm) gives the numpy oracle's codes:
+    same decomposition |x|^2 + |c|^2 - 2 x.c, first index on ties; only near-ties may differ (summation order)."""
+    rng = np.random.default_rng(n + D)
+    X = rng.standard_normal((n, D)).astype(np.float32)
+    C = opq.pq_init_centroids(rng.standard_normal((4096, D)).astype(np.float32), M, ksub, seed=2)
+    if ksub >= 6:
+        C[0, 5] = C[0, 2]
+    lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "liboracle_pq.so"))
+    out = np.full((n, M), 255, dtype=np.uint8)
+    rc = lib.oracle_pq_assign_dec(X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(n), D,
+                                  C.ctypes.data_as(ctypes.c_void_p), M, ksub, out.ctypes.data_as(ctypes.c_void_p))
+    assert rc == 0
+    if n == 0:
+        return
+    codes, d1, d2 = opq.pq_assign(X, C, return_gap=True)
+    near = (d2 - d1) <= 1e-5 * np.maximum(d1, 1e-30)
+    assert np.all((out == codes) | near)
+    assert (out == codes).mean() > 0.999
+    assert not np.any(out[:, 0] == 5) or ksub < 6
+    assert lib.oracle_pq_assign_dec(None, ctypes.c_int64(0), 30, None, 4, 16, None) == -1     # D % M != 0
+
+
 def test_adc_equals_distance_to_reconstruction_and_c_port():
     rng = np.random.default_rng(1)
     X = rng.standard_normal((1000, 32)).astype(np.float32)
