@@ -216,6 +216,15 @@ int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const float* rnorm
                       const uint32_t* probe, int nprobe, int metric, int k, float* out_vals, uint32_t* out_ids,
                       void* scratch, size_t scratch_bytes, void* stream);
 
+/* Continuation of b200vq_ivf_search: the best k probed rows AFTER (after_vals[q], after_ids[q]) in (distance, id)
+ * order, so that any k (the reference's loop takes any k, ivf_quantized_index.py:133-146) is served in pages of at
+ * most 128. Scratch as b200vq_ivf_search. */
+int b200vq_ivf_search_after(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
+                            const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
+                            const uint32_t* probe, int nprobe, int metric, int k, const float* after_vals,
+                            const uint32_t* after_ids, float* out_vals, uint32_t* out_ids, void* scratch,
+                            size_t scratch_bytes, void* stream);
+
 /* The same search on the tensor cores: the screen / candidate-pool machinery of b200vq_flat_topk_tc over the
  * cluster-sorted reconstructions, where a row only counts for the queries whose probe list holds its cluster
  * (rowcluster (N): cluster of every row; the probe lists become one K-bit mask per query). Same values and ids as
@@ -499,6 +508,12 @@ int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D, const uint3
                              const float* qfac, int nq, int qb, int metric, int k,
                              float* out_vals, uint32_t* out_ids, void* scratch,
                              size_t scratch_bytes, void* stream);
+/* Continuation: the best k rows AFTER (after_vals[q], after_ids[q]) in (estimate, id) order; chained calls serve the
+ * k > 128 of faiss IndexRaBitQ.search (src/haag_vq/methods/search/rabitq_index.py:63-75). Same scratch. */
+int b200vq_rabitq1_scan_topk_after(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
+                                   const float* qfac, int nq, int qb, int metric, int k,
+                                   const float* after_vals, const uint32_t* after_ids, float* out_vals,
+                                   uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream);
 
 /* Same scan, same results, with the integer part of the estimator on the tensor cores: the
  * (row, query) term sum_d bit_d * qv_d is an exact FP8 (E4M3) GEMM of the sign bits with the quantised

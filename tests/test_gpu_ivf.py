@@ -101,8 +101,8 @@ def test_ivf_with_device_quantizers_given_centroids_empty_clusters_and_save_load
     small.fit(X[:60], "l2", centroids=C)
     ids_s, d_s = small.search_with_scores(Q[:5], 128)
     assert (ids_s == np.iinfo(np.uint32).max).any() and (d_s[ids_s == np.iinfo(np.uint32).max] == np.finfo(np.float32).max).all()
-    with pytest.raises(NotImplementedError):
-        idx.search(Q, 200)
+    # any k: pages of 128 chained on the device equal the oracle's loop
+    _check_search(idx, X, Q, 300, factory, "l2", 20)
     assert idx.search_with_scores(Q, 0)[0].shape == (40, 0)
     # save -> load -> identical results (the reference's pickle layout)
     path = os.path.join(tmp_path, "ivf.pkl")
@@ -178,3 +178,24 @@ def test_ivf_tensor_core_search_equals_the_simt_kernel(metric):
     for q in range(0, 300, 17):
         got = ids[q][ids[q] != np.iinfo(np.uint32).max]
         assert np.isin(assign[got], pr[q]).all()
+
+
+@pytest.mark.parametrize("metric", ["l2", "ip"])
+def test_ivf_any_k_by_chained_pages(metric):
+    """k > 128 = pages chained by b200vq_ivf_search_after: equal to the oracle, continuing the (distance, id) order
+    across identical rows, and sentinels once the probed rows run out."""
+    from haag_vq.methods.search.ivf_quantized_index import IvfQuantizedIndex
+    X, Q = _data(5000, 32, 33, 11)
+    X[1000:1200] = X[999]                             # 201 identical rows straddle a page boundary
+    idx = IvfQuantizedIndex(RoundQuantizer, K=12, nprobe=3)
+    idx.fit(X, metric)
+    _check_search(idx, X, Q, 400, RoundQuantizer, metric, 3)
+    ids, d = idx.search_with_scores(Q, 400)
+    for r in range(Q.shape[0]):
+        valid = ids[r] != np.iinfo(np.uint32).max
+        assert len(set(ids[r][valid])) == valid.sum()
+        assert np.array_equal(np.lexsort((ids[r][valid], d[r][valid])), np.arange(valid.sum()))
+    tiny = IvfQuantizedIndex(RoundQuantizer, K=4, nprobe=1)
+    tiny.fit(X[:300], metric)
+    ids, d = tiny.search_with_scores(Q[:4], 290)
+    assert (ids == np.iinfo(np.uint32).max).any()

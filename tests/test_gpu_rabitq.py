@@ -185,3 +185,39 @@ def test_rabitq_index_contract(T, tmp_path):
     gt = np.argsort(true, axis=1)[:, :10]
     rec = np.mean([len(set(gt[i]) & set(ids[i])) / 10 for i in range(11)])
     assert rec > 0.3
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_rabitq1_scan_any_k_by_chained_pages(T, metric):
+    """k > 128 (faiss IndexRaBitQ.search takes any k): pages chained by b200vq_rabitq1_scan_topk_after equal the
+    oracle's full ranking; beyond ntotal the ids are 0xffffffff."""
+    from haag_vq.methods.search import RaBitQIndex
+    n, nq, D, qb, k = 700, 7, 96, 4, 300
+    X = make_data(n, D, 31)
+    X[100:140] = X[50]                      # 41 identical rows: ties are ordered by id across a page boundary
+    Q = make_data(nq, D, 32)
+    c = X.mean(0).astype(np.float32)
+    codes = orq.rabitq1_encode(X, c, metric)
+    est = orq.rabitq1_estimate(codes, D, Q, c, qb, metric)
+    planes, qfac = T.ops_sq.rabitq1_prepare_queries(T.dev(Q), T.dev(c), qb)
+    vals, ids = T.ops_sq.rabitq1_scan_topk(T.dev(codes), D, planes, qfac, qb, k, metric)
+    v, i = vals.cpu().numpy(), ids.cpu().numpy().view(np.uint32)
+    assert_topk_parity(v, i, est, k, metric, "rabitq1_scan_pages", gap_rel=1e-4)
+    assert all(len(set(r)) == k for r in i)
+    key = -v if metric == 1 else v
+    for r in range(nq):
+        order = np.lexsort((i[r], key[r]))
+        assert np.array_equal(order, np.arange(k)), "pages must continue the (estimate, id) order"
+    # the first page is the single-launch result, bit for bit
+    v0, i0 = T.ops_sq.rabitq1_scan_topk(T.dev(codes), D, planes, qfac, qb, 128, metric)
+    assert np.array_equal(i[:, :128], i0.cpu().numpy().view(np.uint32)) and np.array_equal(v[:, :128], v0.cpu().numpy())
+    # k above ntotal through the index: all rows once, then sentinels
+    idx = RaBitQIndex(qb=qb)
+    idx.fit(X[:200], metric='l2' if metric == 0 else 'ip')
+    ids2, d2 = idx.search_with_scores(Q, 260)
+    assert ids2.shape == (nq, 260)
+    for r in range(nq):
+        assert sorted(ids2[r, :200].tolist()) == list(range(200))
+        assert (ids2[r, 200:] == np.iinfo(np.uint32).max).all() and np.isinf(d2[r, 200:]).all()
+    with pytest.raises(ValueError):
+        idx.search(Q, 0)

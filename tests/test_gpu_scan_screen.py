@@ -89,8 +89,8 @@ def test_screen_overflow_goes_through_the_exact_fallback(T):
 
 @pytest.mark.parametrize("M,n", [(16, 100_000), (80, 70_000), (48, 66_000), (16, 5_000), (16, 1_000_000)])
 def test_padded_scan_layout_matches_row_layout(M, n):
-    """M not a multiple of 32 (BASELINE config 1: M = 16): codes padded to the scan layout's group width
-    with all-zero tables give the row-layout exact kernel's ids and value bits; n >= 65536 takes the
+    """M not a multiple of 32: M = 16 (BASELINE config 1) in its own half-group layout, other M padded to the scan
+    layout's group width with all-zero tables, give the row-layout exact kernel's ids and value bits; n >= 65536 takes the
     screened path (threshold sample = n / 8 rows), smaller n the exact scan-layout kernel."""
     import torch
     from b200vq import ops, ops_sq, pq as dpq
@@ -102,7 +102,8 @@ def test_padded_scan_layout_matches_row_layout(M, n):
     codec = dpq.PQCodec(C)
     codes = codec.encode(x)
     crot = ops.pq_codes_to_scan_layout(codec.pad_codes_for_scan(codes))
-    mp = (M + 31) // 32 * 32
+    mp = dpq.scan_layout_width(M)        # 16 -> the half-group layout (no padding), else the next multiple of 32
+    assert mp == (16 if M == 16 else (M + 31) // 32 * 32) and crot.numel() == (n + 31) // 32 * 32 * mp
     for metric in ("l2", "ip"):
         v0, i0 = codec.search(codes, q, 10, metric)
         v1, i1 = codec.search(crot, q, 10, metric, n=n, rot=True, m_pad=mp)
@@ -111,3 +112,29 @@ def test_padded_scan_layout_matches_row_layout(M, n):
             assert torch.equal(v0.view(torch.int32), v1.view(torch.int32))
         else:            # exact scan-layout kernel: rotated summation order, last-bit differences
             assert torch.allclose(v0, v1, rtol=1e-6, atol=0)
+
+
+def test_half_group_layout_m16_overflow_and_small_k(T):
+    """M = 16 half-group kernels: the exact scan-layout kernel, the screen, its finish and the gated fallback."""
+    torch = T.torch
+    n, M, nq = 300_000, 16, 9
+    codes, lut = _case(T, n, M, nq, seed=11)
+    rot = T.ops.pq_codes_to_scan_layout(codes)
+    assert rot.numel() == (n + 31) // 32 * 32 * 16
+    for k in (1, 10, 64):
+        v0, i0 = T.ops.adc_scan_topk(codes, lut, k, "l2")
+        v1, i1 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True)
+        v2, i2 = T.ops.adc_scan_topk(rot, lut, k, "l2", n=n, rot=True, screen=True)
+        assert torch.equal(i0, i1) and torch.allclose(v0, v1, rtol=1e-6, atol=0)
+        assert torch.equal(i0, i2) and torch.equal(v0.view(torch.int32), v2.view(torch.int32))
+    # every row identical but for one column: all rows survive, the lists overflow, the gated exact kernels answer
+    same = torch.full((n, M), 3, dtype=torch.uint8, device="cuda")
+    same[::5, 2] = 200
+    rot = T.ops.pq_codes_to_scan_layout(same)
+    # (reference = the exact scan-layout kernel: its lane-rotated summation order splits exact ties of identical
+    # rows by an ulp, so the row-layout kernel's tie order is not comparable here; values are)
+    v0, i0 = T.ops.adc_scan_topk(rot, lut, 10, "ip", n=n, rot=True)
+    v1, i1 = T.ops.adc_scan_topk(rot, lut, 10, "ip", n=n, rot=True, screen=True)
+    assert torch.equal(i0, i1) and torch.equal(v0, v1)
+    vr, _ = T.ops.adc_scan_topk(same, lut, 10, "ip")
+    assert torch.allclose(vr, v1, rtol=2e-6)

@@ -76,8 +76,8 @@ def c1():
     add("C1", "adc_scan_topk row layout M=16 k=10", timed(lambda: ops.adc_scan_topk(codes, lut, 10, "l2")), n * nq,
         "codes", bytes_=float(n) * M * nq, note="query tile 1")
     crot = ops.pq_codes_to_scan_layout(codec.pad_codes_for_scan(codes))
-    add("C1", "ADC search M=16 padded to the scan layout (LUT + screened scan, k=10)",
-        timed(lambda: codec.search(crot, q, 10, "l2", n=n, rot=True, m_pad=32)), n * nq, "codes",
+    add("C1", "ADC search M=16 half-group scan layout (LUT + screened scan, k=10)",
+        timed(lambda: codec.search(crot, q, 10, "l2", n=n, rot=True, m_pad=dpq.scan_layout_width(M))), n * nq, "codes",
         bytes_=float(n) * M * nq / 4, note="query tile 4; default FlatQuantizedIndex path")
     xn = ops.row_sqnorms(x)
     add("C1", "flat_topk_tc k=100 (ground truth)", timed(lambda: ops.flat_topk(x, q, 100, "l2", xnorm=xn)), n * nq,

@@ -30,6 +30,26 @@ if mode == "scan":
     lut = codec.luts(Q, "l2")
     for _ in range(2):
         v, i = ops.adc_scan_topk(rot, lut, 10, "l2", n=n, rot=True, screen=True)
+elif mode == "c1adc":
+    # C1 search: 100 000 codes, M = 16 padded to the scan layout, 1000 queries
+    n, D, M, nq = 100_000, 1536, 16, 1000
+    x = data(n, D)
+    C = dpq.pq_train(x[:65536], M, 8, niter=4, seed=1234)
+    codec = dpq.PQCodec(C)
+    crot = ops.pq_codes_to_scan_layout(codec.pad_codes_for_scan(codec.encode(x)))
+    Q = data(nq, D, seed=1235)
+    mp = dpq.scan_layout_width(M)
+    for _ in range(3):
+        v, i = codec.search(crot, Q, 10, "l2", n=n, rot=True, m_pad=mp)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(20):
+        v, i = codec.search(crot, Q, 10, "l2", n=n, rot=True, m_pad=mp)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 20
+    print(f"c1adc search {ms:.3f} ms  {n * nq / ms / 1e6:.1f} G codes/s  tune={os.environ.get('B200VQ_TUNE_SAMPLE_DIV')},"
+          f"{os.environ.get('B200VQ_TUNE_SAMPLE_MIN')}")
 elif mode == "rotate":
     n, D = 262_144, 1536
     x = data(n, D)

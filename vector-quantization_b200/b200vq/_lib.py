@@ -57,6 +57,8 @@ SIGNATURES = {
     "b200vq_ivf_search_tc": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _p, _i, _i64, _p, _i, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "b200vq_ivf_search_scratch_bytes": (_sz, [_i, _i, _i, _i]),
     "b200vq_ivf_search": (_i, [_p, _i64, _i, _p, _p, _p, _i, _p, _i, _i64, _p, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_ivf_search_after": (_i, [_p, _i64, _i, _p, _p, _p, _i, _p, _i, _i64, _p, _i, _i, _i, _p, _p, _p, _p, _p, _sz,
+                                     _p]),
     "b200vq_flat_topk_tc_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_flat_topk_tc": (_i, [_p, _i64, _i64, _i, _p, _p, _p, _i, _i64, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_rotate_tc_applies": (_i, [_i64, _i64, _i64, _i64, _i64]),
@@ -106,6 +108,7 @@ SIGNATURES = {
     "b200vq_rabitq1_prepare_queries": (_i, [_p, _i, _i64, _i, _p, _i, _p, _p, _p]),
     "b200vq_rabitq1_scan_scratch_bytes": (_sz, [_i64, _i, _i]),
     "b200vq_rabitq1_scan_topk": (_i, [_p, _i64, _i, _p, _p, _i, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "b200vq_rabitq1_scan_topk_after": (_i, [_p, _i64, _i, _p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
     "b200vq_rabitq1_scan_tc_scratch_bytes": (_sz, [_i64, _i, _i, _i]),
     "b200vq_rabitq1_scan_topk_tc": (_i, [_p, _i64, _i, _p, _p, _i, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "b200vq_saq_plan_dp": (_i, [_p, _i, C.c_float, _p, _p, _p]),

@@ -122,6 +122,28 @@ def ivf_search(recon: torch.Tensor, rnorm: torch.Tensor | None, gid: torch.Tenso
     nprobe = probe.shape[1]
     mid = metric_id(metric)
     lib = _lib.load()
+    if k > 128:
+        # pages of 128: each continues after the last (distance, id) of the previous one (b200vq_ivf_search_after)
+        vals = torch.empty((nq, k), dtype=torch.float32, device=recon.device)
+        ids = torch.empty((nq, k), dtype=torch.int32, device=recon.device)
+        vals[:, :128], ids[:, :128] = ivf_search(recon, rnorm, gid, row_off, K, queries, probe, 128, metric, rowcluster,
+                                                 impl)
+        if mid == ops.METRIC_L2 and rnorm is None:
+            rnorm = ops.row_sqnorms(recon)
+        sc = scratch(lib.b200vq_ivf_search_scratch_bytes(nq, nprobe, K, 128), recon.device, "ivf")
+        done = 128
+        while done < k:
+            kk = min(128, k - done)
+            av, ai = vals[:, done - 1].contiguous(), ids[:, done - 1].contiguous()
+            v1 = torch.empty((nq, kk), dtype=torch.float32, device=recon.device)
+            i1 = torch.empty((nq, kk), dtype=torch.int32, device=recon.device)
+            check(lib.b200vq_ivf_search_after(rptr, ldr, D, _p(rnorm), gid.data_ptr(), row_off.data_ptr(), K, qptr, nq,
+                                              ldq, probe.data_ptr(), nprobe, mid, kk, av.data_ptr(), ai.data_ptr(),
+                                              v1.data_ptr(), i1.data_ptr(), sc.data_ptr(), sc.numel(), _stream()),
+                  "ivf_search_after")
+            vals[:, done:done + kk], ids[:, done:done + kk] = v1, i1
+            done += kk
+        return vals, ids
     vals = torch.empty((nq, k), dtype=torch.float32, device=recon.device)
     ids = torch.empty((nq, k), dtype=torch.int32, device=recon.device)
     tc_ok = (rowcluster is not None and N >= 1024 and D % 32 == 0 and ldr % 4 == 0 and ldq % 4 == 0 and

@@ -302,6 +302,24 @@ def rabitq1_scan_topk(codes: torch.Tensor, D: int, planes: torch.Tensor, qfac: t
     vals, ids = _topk_out(nq, k, codes.device)
     if impl not in ("auto", "tc", "simt"):
         raise ValueError(f"rabitq1_scan_topk: unknown impl {impl!r}")
+    if k > 128:
+        # one launch ranks at most 128 rows per query: pages, each starting after the last entry of the previous one
+        # in the same (estimate, id) order -- the concatenation is the exact top-k
+        v0, i0 = rabitq1_scan_topk(codes, D, planes, qfac, qb, 128, metric, impl)
+        vals[:, :128], ids[:, :128] = v0, i0
+        sc = scratch(lib.b200vq_rabitq1_scan_scratch_bytes(n, nq, 128), codes.device, "scan")
+        done = 128
+        while done < k:
+            kk = min(128, k - done)
+            av, ai = vals[:, done - 1].contiguous(), ids[:, done - 1].contiguous()
+            v1, i1 = _topk_out(nq, kk, codes.device)
+            check(lib.b200vq_rabitq1_scan_topk_after(codes.data_ptr(), n, D, planes.data_ptr(), qfac.data_ptr(), nq, qb,
+                                                     metric_id(metric), kk, av.data_ptr(), ai.data_ptr(),
+                                                     v1.data_ptr(), i1.data_ptr(), sc.data_ptr(), sc.numel(),
+                                                     _stream()), "rabitq1_scan_topk_after")
+            vals[:, done:done + kk], ids[:, done:done + kk] = v1, i1
+            done += kk
+        return vals, ids
     if impl != "simt":
         sc = scratch(lib.b200vq_rabitq1_scan_tc_scratch_bytes(n, D, nq, k), codes.device, "scan")
         check(lib.b200vq_rabitq1_scan_topk_tc(codes.data_ptr(), n, D, planes.data_ptr(), qfac.data_ptr(), nq, qb,

@@ -135,6 +135,11 @@ def opq_train(x: torch.Tensor, M: int, nbits: int = 8, niter: int = 50, niter_pq
     return A
 
 
+def scan_layout_width(M: int) -> int:
+    """Sub-quantizers per row in the scan layout: 16 (half group), else the next multiple of 32."""
+    return 16 if M == 16 else (M + 31) // 32 * 32
+
+
 class PQCodec:
     """Trained PQ state on one device + encode/decode/search helpers."""
 
@@ -162,11 +167,12 @@ class PQCodec:
         return ops.adc_lut(queries, self.centroids, metric)
 
     def pad_codes_for_scan(self, codes: torch.Tensor) -> torch.Tensor:
-        """(n, M) codes -> (n, M_pad) with M_pad the next multiple of 32 (the scan layout's group width);
-        the extra sub-quantizers hold code 0 and their tables are all zero (search(m_pad=...)), so every score
-        keeps its bits: x + 0.0 is exact and the real sub-quantizers are still summed first, in order."""
+        """(n, M) codes -> (n, M_pad) with M_pad the next multiple of 32 (the scan layout's group width; M = 16 has
+        its own half-group layout and is not padded); the extra sub-quantizers hold code 0 and their tables are all
+        zero (search(m_pad=...)), so every score keeps its bits: x + 0.0 is exact and the real sub-quantizers are
+        still summed first, in order."""
         n, M = codes.shape
-        mp = (M + 31) // 32 * 32
+        mp = scan_layout_width(M)
         if mp == M:
             return codes
         out = torch.zeros((n, mp), dtype=torch.uint8, device=codes.device)

@@ -83,7 +83,8 @@ __global__ void __launch_bounds__(THREADS)
 scan_kernel(const float* __restrict__ R, int64_t ldr, int D, const float* __restrict__ rnorm,
             const uint32_t* __restrict__ gid, const int64_t* __restrict__ row_off, const float* __restrict__ queries,
             int64_t ldq, const uint32_t* __restrict__ qoff, const uint32_t* __restrict__ qlist, int nprobe, int metric,
-            int k, uint64_t* __restrict__ part) {
+            int k, uint64_t* __restrict__ part, const float* __restrict__ after_vals = nullptr,
+            const uint32_t* __restrict__ after_ids = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int c = blockIdx.x;
     const uint32_t e0 = qoff[c] + (uint32_t)blockIdx.y * Q_TILE, e1 = qoff[c + 1];
@@ -181,10 +182,20 @@ scan_kernel(const float* __restrict__ R, int64_t ldr, int D, const float* __rest
             tk.k = k;
             tk.count = s_cnt[ql];
             tk.thr = s_thr[ql];
+            uint64_t floor_key = 0;      // continuation (b200vq_ivf_search_after): only keys after the previous page's last
+            if (after_vals) {
+                const uint32_t qg = s_ent[ql] / (uint32_t)nprobe;
+                const float av = after_vals[qg];
+                floor_key = make_key(metric == B200VQ_METRIC_IP ? -av : av, after_ids[qg]);
+            }
             for (int cc = 0; cc < N_TILE / 32; ++cc) {
                 const int rl = cc * 32 + lane;
                 const int64_t row = t0 + rl;
-                tk.offer(row < r1, ds[ql * (N_TILE + 1) + rl], row < r1 ? gid[row] : 0u);
+                const float dv = ds[ql * (N_TILE + 1) + rl];
+                const uint32_t id = row < r1 ? gid[row] : 0u;
+                bool ok = row < r1;
+                if (after_vals) ok = ok && make_key(dv, id) > floor_key;
+                tk.offer(ok, dv, id);
             }
             if (lane == 0) {
                 s_cnt[ql] = tk.count;
@@ -265,14 +276,15 @@ static Plan plan(int nq, int nprobe, int K, int k) {
 template <int CAP>
 static int launch_scan(const float* R, int64_t ldr, int D, const float* rnorm, const uint32_t* gid, const int64_t* row_off,
                        int K, const float* queries, int nq, int64_t ldq, const uint32_t* qoff, const uint32_t* qlist,
-                       int nprobe, int metric, int k, uint64_t* part, cudaStream_t st) {
+                       int nprobe, int metric, int k, uint64_t* part, cudaStream_t st, const float* after_vals,
+                       const uint32_t* after_ids) {
     const size_t smem = (size_t)(K_STEP * (Q_TILE + 4) + K_STEP * (N_TILE + 4) + Q_TILE * (N_TILE + 1) + 4 * Q_TILE) * 4 +
                         16 + (size_t)Q_TILE * CAP * sizeof(uint64_t);
     VQ_CUDA(cudaFuncSetAttribute(scan_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // a cluster is probed by at most nq queries: ceil(nq / 64) tiles, the surplus CTAs exit at once
     dim3 grid((unsigned)K, (unsigned)((nq + Q_TILE - 1) / Q_TILE));
     scan_kernel<CAP><<<grid, THREADS, smem, st>>>(R, ldr, D, rnorm, gid, row_off, queries, ldq, qoff, qlist, nprobe, metric,
-                                                  k, part);
+                                                  k, part, after_vals, after_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -287,10 +299,11 @@ extern "C" size_t b200vq_ivf_search_scratch_bytes(int nq, int nprobe, int K, int
     return ivf::plan(nq, nprobe, K, k).total;
 }
 
-extern "C" int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
-                                 const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
-                                 const uint32_t* probe, int nprobe, int metric, int k, float* out_vals, uint32_t* out_ids,
-                                 void* scratch, size_t scratch_bytes, void* stream) {
+static int ivf_search_impl(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
+                           const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
+                           const uint32_t* probe, int nprobe, int metric, int k, const float* after_vals,
+                           const uint32_t* after_ids, float* out_vals, uint32_t* out_ids,
+                           void* scratch, size_t scratch_bytes, void* stream) {
     VQ_CHECK_ARG(recon && gid && row_off && queries && probe && out_vals && out_ids, "ivf_search: null pointer");
     VQ_CHECK_ARG(D > 0 && ldr >= D && ldq >= D && nq >= 0 && K > 0 && K <= (1 << 20) && nprobe > 0,
                  "ivf_search: bad shape");
@@ -322,13 +335,33 @@ extern "C" int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const f
     ivf::fill_kernel<<<g, 256, 0, st>>>(probe, total, K, cursor, qlist);
     VQ_LAUNCH_CHECK();
     int rc = (k <= 32) ? ivf::launch_scan<64>(recon, ldr, D, rnorm, gid, row_off, K, queries, nq, ldq, off, qlist, nprobe,
-                                              metric, k, part, st)
+                                              metric, k, part, st, after_vals, after_ids)
                        : ivf::launch_scan<256>(recon, ldr, D, rnorm, gid, row_off, K, queries, nq, ldq, off, qlist, nprobe,
-                                               metric, k, part, st);
+                                               metric, k, part, st, after_vals, after_ids);
     if (rc != B200VQ_OK) return rc;
     merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, nprobe, k, metric == B200VQ_METRIC_IP, out_vals, out_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
+}
+
+extern "C" int b200vq_ivf_search(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
+                                 const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
+                                 const uint32_t* probe, int nprobe, int metric, int k, float* out_vals, uint32_t* out_ids,
+                                 void* scratch, size_t scratch_bytes, void* stream) {
+    return ivf_search_impl(recon, ldr, D, rnorm, gid, row_off, K, queries, nq, ldq, probe, nprobe, metric, k, nullptr,
+                           nullptr, out_vals, out_ids, scratch, scratch_bytes, stream);
+}
+
+// Continuation: the best k probed rows AFTER (after_vals[q], after_ids[q]) in (distance, id) order - the next page of
+// a search whose previous page ended there (any k = pages of at most 128). Same scratch as b200vq_ivf_search.
+extern "C" int b200vq_ivf_search_after(const float* recon, int64_t ldr, int D, const float* rnorm, const uint32_t* gid,
+                                       const int64_t* row_off, int K, const float* queries, int nq, int64_t ldq,
+                                       const uint32_t* probe, int nprobe, int metric, int k, const float* after_vals,
+                                       const uint32_t* after_ids, float* out_vals, uint32_t* out_ids, void* scratch,
+                                       size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(after_vals && after_ids, "ivf_search_after: null pointer");
+    return ivf_search_impl(recon, ldr, D, rnorm, gid, row_off, K, queries, nq, ldq, probe, nprobe, metric, k, after_vals,
+                           after_ids, out_vals, out_ids, scratch, scratch_bytes, stream);
 }
 
 extern "C" int b200vq_row_argmin(const float* y, int64_t n, int64_t ld, int K, uint32_t* idx, float* val, void* stream) {

@@ -333,7 +333,8 @@ __global__ void __launch_bounds__(256)
     rabitq1_scan_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
                         const uint32_t* __restrict__ planes, const float* __restrict__ qfac, int qb,
                         int metric, int k, int64_t chunk_rows, uint64_t* __restrict__ part,
-                        const uint32_t* __restrict__ gate = nullptr) {
+                        const uint32_t* __restrict__ gate = nullptr, const float* __restrict__ after_vals = nullptr,
+                        const uint32_t* __restrict__ after_ids = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
     if (gate && gate[q] == 0) return;   // gated launch: only flagged queries (rabitq_tc.cu fallback)
@@ -357,6 +358,8 @@ __global__ void __launch_bounds__(256)
 
     WarpTopK<CAP> tk;
     tk.init(wbuf + w * CAP, k);
+    uint64_t floor_key = 0;   // continuation (b200vq_rabitq1_scan_topk_after): only keys after the previous page's last
+    if (after_vals) floor_key = make_key(metric == B200VQ_METRIC_IP ? -after_vals[q] : after_vals[q], after_ids[q]);
     uint32_t* st = stage + (size_t)w * 32 * pitch_w;
     uint8_t* st8 = reinterpret_cast<uint8_t*>(st);
 
@@ -399,7 +402,8 @@ __global__ void __launch_bounds__(256)
             float f1 = load_f32_unaligned(cb + nbytes + 4);
             est = rabitq1_estimate((float)dot, (float)sumq, f0, -2.f * f1, c1, c2, c34, qc2, qn2, metric);
         }
-        tk.offer(valid, est, (uint32_t)(base + lane));
+        tk.offer(valid && (!after_vals || make_key(est, (uint32_t)(base + lane)) > floor_key), est,
+                 (uint32_t)(base + lane));
     }
     // emit
     tk.finish();
@@ -996,7 +1000,8 @@ extern "C" size_t b200vq_rabitq1_scan_scratch_bytes(int64_t n, int nq, int k) {
 template <int CAP>
 static int rabitq1_scan_launch(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
                                const float* qfac, int nq, int qb, int metric, int k, uint64_t* part,
-                               const RPlan& p, cudaStream_t st, const uint32_t* gate = nullptr) {
+                               const RPlan& p, cudaStream_t st, const uint32_t* gate = nullptr,
+                               const float* after_vals = nullptr, const uint32_t* after_ids = nullptr) {
     const int W = (D + 31) >> 5;
     const int code_size = ((D + 7) >> 3) + 8;
     const int pitch_w = ((code_size + 3) >> 2) | 1;
@@ -1008,7 +1013,7 @@ static int rabitq1_scan_launch(const uint8_t* codes, int64_t n, int D, const uin
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)nq, (unsigned)p.nchunks);
     rabitq1_scan_kernel<CAP><<<grid, 256, smem, st>>>(codes, n, D, planes, qfac, qb, metric, k,
-                                                      p.chunk_rows, part, gate);
+                                                      p.chunk_rows, part, gate, after_vals, after_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -1050,6 +1055,34 @@ extern "C" int b200vq_rabitq1_scan_topk(const uint8_t* codes, int64_t n, int D,
     if (rc != B200VQ_OK) return rc;
     merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, p.nchunks, k, metric == B200VQ_METRIC_IP,
                                                     out_vals, out_ids);
+    VQ_LAUNCH_CHECK();
+    return B200VQ_OK;
+}
+
+// Continuation: the best k rows AFTER (after_vals[q], after_ids[q]) in (estimate, id) order, so that any k is served
+// in pages of at most 128 (RaBitQIndex.search with k > 128). Exact SIMT scan; scratch as b200vq_rabitq1_scan_topk.
+extern "C" int b200vq_rabitq1_scan_topk_after(const uint8_t* codes, int64_t n, int D, const uint32_t* planes,
+                                              const float* qfac, int nq, int qb, int metric, int k,
+                                              const float* after_vals, const uint32_t* after_ids, float* out_vals,
+                                              uint32_t* out_ids, void* scratch, size_t scratch_bytes, void* stream) {
+    VQ_CHECK_ARG(codes && planes && qfac && out_vals && out_ids && after_vals && after_ids,
+                 "rabitq1_scan_topk_after: null pointer");
+    VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && D > 0 && nq >= 0, "rabitq1_scan_topk_after: bad shape");
+    VQ_CHECK_ARG(qb >= 1 && qb <= 8, "rabitq1_scan_topk_after: qb must be in [1,8]");
+    VQ_CHECK_ARG(k > 0 && k <= 128, "rabitq1_scan_topk_after: k must be in [1,128], got %d", k);
+    VQ_CHECK_ARG(metric == B200VQ_METRIC_L2 || metric == B200VQ_METRIC_IP, "rabitq1_scan_topk_after: bad metric");
+    if (nq == 0) return B200VQ_OK;
+    RPlan p = rplan(n, nq);
+    size_t need = (size_t)nq * p.nchunks * k * sizeof(uint64_t);
+    VQ_CHECK_ARG(scratch && scratch_bytes >= need, "rabitq1_scan_topk_after: scratch too small");
+    cudaStream_t st = as_stream(stream);
+    uint64_t* part = reinterpret_cast<uint64_t*>(scratch);
+    int rc = (k <= 32) ? rabitq1_scan_launch<128>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st, nullptr,
+                                                  after_vals, after_ids)
+                       : rabitq1_scan_launch<256>(codes, n, D, planes, qfac, nq, qb, metric, k, part, p, st, nullptr,
+                                                  after_vals, after_ids);
+    if (rc != B200VQ_OK) return rc;
+    merge_partials_kernel<2048><<<nq, 256, 0, st>>>(part, p.nchunks, k, metric == B200VQ_METRIC_IP, out_vals, out_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }

@@ -93,31 +93,34 @@ __global__ void __launch_bounds__(SCAN_THREADS)
 // lives at (b*G + g)*1024 + (s/16)*512 + i*16 + s%16. In the scan, lane i reads
 // LUT column (i+s) at step s, so the 32 lanes of a warp always hit 32 distinct
 // banks, and each of its two 128-bit code loads is a contiguous 512-byte request.
-__global__ void codes_to_scan_layout_kernel(const uint8_t* __restrict__ codes, int64_t n, int M,
+__global__ void codes_to_scan_layout_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int GW,
                                             uint8_t* __restrict__ out) {
-    const int G = M >> 5;
+    // GW = group width: 32, or 16 for the half group of M = 16 (one 16-byte run per lane, 512-byte blocks;
+    // step s of lane i holds sub-quantizer (i + s) % 16)
+    const int G = M / GW;
     const int64_t nblk = (n + 31) >> 5;
-    const int64_t total = nblk * G * 32 * 32;
+    const int64_t total = nblk * G * 32 * GW;
+    const int sh = GW == 32 ? 5 : 4;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
          e += (int64_t)gridDim.x * blockDim.x) {
-        int s = (int)(e & 31);
-        int i = (int)((e >> 5) & 31);
-        int64_t bg = e >> 10;
+        int s = (int)(e & (GW - 1));
+        int i = (int)((e >> sh) & 31);
+        int64_t bg = e >> (sh + 5);
         int g = (int)(bg % G);
         int64_t b = bg / G;
         int64_t row = b * 32 + i;
         uint8_t v = 0;
-        if (row < n) v = codes[row * M + g * 32 + ((i + s) & 31)];
+        if (row < n) v = codes[row * M + g * GW + ((i + s) & (GW - 1))];
         // the 32 bytes of a lane are stored as two 16-byte halves, each half contiguous across the
         // 32 lanes (512 B), so that one 128-bit load per lane is one fully used 512-byte request
-        out[(bg << 10) + ((s >> 4) << 9) + (i << 4) + (s & 15)] = v;
+        out[(bg << (sh + 5)) + ((s >> 4) << 9) + (i << 4) + (s & 15)] = v;
     }
 }
 
 // LUT in shared memory as [g][k][64] floats: entry (k, j) = lut[g*32 + (j&31)][k],
 // i.e. every 32-column row is stored twice so that lane i can address column
 // i+s with the step s as a static immediate offset.
-template <int CAP, int G>
+template <int CAP, int G, int GW = 32>
 __global__ void __launch_bounds__(SCAN_THREADS)
     adc_scan_rot_kernel(const uint8_t* __restrict__ codes_rot, int64_t n,
                         const float* __restrict__ lut, int k, int64_t chunk_rows, int negate,
@@ -125,7 +128,10 @@ __global__ void __launch_bounds__(SCAN_THREADS)
                         uint32_t gate_cap = 0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int KSUB = 256;
-    constexpr int M = G * 32;
+    constexpr int M = G * GW;
+    constexpr int NQW = GW / 4;          // column quads (= code words) of a group
+    constexpr int NV = GW / 16;          // 128-bit code loads of a group
+    static_assert(GW == 32 || (GW == 16 && G == 1), "group width 32, or one half group of 16");
     const int q = blockIdx.x, chunk = blockIdx.y, nchunks = gridDim.y;
     // gated launch (fallback of the screened scan): only queries whose candidate list overflowed
     if (gate && gate[q] <= gate_cap) return;
@@ -137,15 +143,15 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     uint64_t* mbuf = wbuf + SCAN_WARPS * CAP;
 
     // LUT fill: a thread gathers entry kk of four consecutive sub-quantizers and stores them as one
-    // float4 (twice: columns j and j+32); the 8 lanes of a quarter warp write 128 contiguous bytes.
+    // float4 (again at columns j + GW, ... up to column 31 + GW); a quarter warp writes 128 contiguous bytes.
     const float* lut_q = lut + (size_t)q * M * KSUB;
-    for (int idx = threadIdx.x; idx < G * KSUB * 8; idx += SCAN_THREADS) {
-        const int jq = idx & 7, kk = (idx >> 3) & (KSUB - 1), g = idx >> 11;
-        const float* src = lut_q + (size_t)(g * 32 + 4 * jq) * KSUB + kk;
+    for (int idx = threadIdx.x; idx < G * KSUB * NQW; idx += SCAN_THREADS) {
+        const int jq = idx % NQW, kk = (idx / NQW) & (KSUB - 1), g = idx / (NQW * KSUB);
+        const float* src = lut_q + (size_t)(g * GW + 4 * jq) * KSUB + kk;
         float4 v = make_float4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
         float4* dst = reinterpret_cast<float4*>(lut_s + ((size_t)g * KSUB + kk) * 64 + 4 * jq);
-        dst[0] = v;
-        dst[8] = v;
+#pragma unroll
+        for (int rep = 0; rep * GW < 32 + GW; ++rep) dst[rep * NQW] = v;
     }
     __syncthreads();
 
@@ -160,18 +166,17 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     // two 32-row blocks per iteration: both blocks' code loads are issued before the first lookup
     constexpr int UNR = 2;
     for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += UNR * SCAN_THREADS) {
-        uint4 cv[UNR][2 * G];
+        uint4 cv[UNR][NV * G];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             // blocks past the chunk end are clamped to a valid block and masked out below
             int64_t bb = base + (int64_t)u * SCAN_THREADS;
             if (bb >= r1) bb = base;
-            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * 1024);
+            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * (32 * GW));
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                cv[u][2 * g] = ld_stream_u4(cb + g * 64 + lane);
-                cv[u][2 * g + 1] = ld_stream_u4(cb + g * 64 + 32 + lane);
-            }
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int h = 0; h < NV; ++h) cv[u][NV * g + h] = ld_stream_u4(cb + g * 64 + h * 32 + lane);
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
@@ -179,11 +184,14 @@ __global__ void __launch_bounds__(SCAN_THREADS)
             float acc = 0.f;
 #pragma unroll
             for (int g = 0; g < G; ++g) {
-                const uint32_t wds[8] = {cv[u][2 * g].x, cv[u][2 * g].y, cv[u][2 * g].z, cv[u][2 * g].w,
-                                         cv[u][2 * g + 1].x, cv[u][2 * g + 1].y, cv[u][2 * g + 1].z,
-                                         cv[u][2 * g + 1].w};
+                uint32_t wds[NQW];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
+                for (int h = 0; h < NV; ++h) {
+                    wds[4 * h + 0] = cv[u][NV * g + h].x; wds[4 * h + 1] = cv[u][NV * g + h].y;
+                    wds[4 * h + 2] = cv[u][NV * g + h].z; wds[4 * h + 3] = cv[u][NV * g + h].w;
+                }
+#pragma unroll
+                for (int j = 0; j < NQW; ++j) {
 #pragma unroll
                     for (int b = 0; b < 4; ++b) {
                         // address = (code << 8) | (lane << 2), built with one PRMT; the group and step
@@ -557,30 +565,30 @@ extern "C" int b200vq_adc_scan_topk(const uint8_t* codes, int64_t n, int M, int 
 
 extern "C" int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, int M, uint8_t* out,
                                               void* stream) {
-    VQ_CHECK_ARG((codes || n == 0) && (out || n == 0) && n >= 0 && M > 0 && M % 32 == 0,
-                 "pq_codes_to_scan_layout: need M %% 32 == 0 (M=%d)", M);
+    VQ_CHECK_ARG((codes || n == 0) && (out || n == 0) && n >= 0 && M > 0 && (M % 32 == 0 || M == 16),
+                 "pq_codes_to_scan_layout: need M %% 32 == 0 or M == 16 (M=%d)", M);
     if (n == 0) return B200VQ_OK;
     int64_t total = ((n + 31) / 32) * 32 * (int64_t)M;
     int64_t g = (total + 255) / 256;
     int64_t cap = (int64_t)device_sm_count() * 16;
     if (g > cap) g = cap;
-    codes_to_scan_layout_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, M, out);
+    codes_to_scan_layout_kernel<<<(int)g, 256, 0, as_stream(stream)>>>(codes, n, M, M == 16 ? 16 : 32, out);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
 
-template <int CAP, int G>
+template <int CAP, int G, int GW = 32>
 static int adc_scan_rot_launch_g(const uint8_t* codes_rot, int64_t n, const float* lut, int nq, int k,
                                  int negate, uint64_t* part, const ScanPlan& p, cudaStream_t st,
                                  const uint32_t* gate = nullptr, uint32_t gate_cap = 0) {
     const int n2 = next_pow2(SCAN_WARPS * k);
     size_t smem = (size_t)G * 256 * 64 * 4 + (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
-    VQ_CHECK_ARG(smem <= 227 * 1024, "adc_scan_topk_rot: M=%d needs %zu B of shared memory", G * 32, smem);
-    VQ_CUDA(cudaFuncSetAttribute(adc_scan_rot_kernel<CAP, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VQ_CHECK_ARG(smem <= 227 * 1024, "adc_scan_topk_rot: M=%d needs %zu B of shared memory", G * GW, smem);
+    VQ_CUDA(cudaFuncSetAttribute(adc_scan_rot_kernel<CAP, G, GW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem));
     dim3 grid((unsigned)nq, (unsigned)p.nchunks);
-    adc_scan_rot_kernel<CAP, G><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, lut, k, p.chunk_rows, negate,
-                                                                  part, gate, gate_cap);
+    adc_scan_rot_kernel<CAP, G, GW><<<grid, SCAN_THREADS, smem, st>>>(codes_rot, n, lut, k, p.chunk_rows, negate,
+                                                                      part, gate, gate_cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
 }
@@ -589,6 +597,7 @@ template <int CAP>
 static int adc_scan_rot_launch(const uint8_t* codes_rot, int64_t n, int M, const float* lut, int nq,
                                int k, int negate, uint64_t* part, const ScanPlan& p,
                                cudaStream_t st, const uint32_t* gate = nullptr, uint32_t gate_cap = 0) {
+    if (M == 16) return adc_scan_rot_launch_g<CAP, 1, 16>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
     switch (M / 32) {
         case 1: return adc_scan_rot_launch_g<CAP, 1>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
         case 2: return adc_scan_rot_launch_g<CAP, 2>(codes_rot, n, lut, nq, k, negate, part, p, st, gate, gate_cap);
@@ -601,8 +610,8 @@ extern "C" int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int
                                         float* out_vals, uint32_t* out_ids, void* scratch,
                                         size_t scratch_bytes, void* stream) {
     VQ_CHECK_ARG(codes_rot && lut && out_vals && out_ids, "adc_scan_topk_rot: null pointer");
-    VQ_CHECK_ARG(ksub == 256 && M > 0 && M % 32 == 0 && M <= 96,
-                 "adc_scan_topk_rot: needs ksub == 256 and M in {32,64,96} (M=%d ksub=%d)", M, ksub);
+    VQ_CHECK_ARG(ksub == 256 && M > 0 && (M % 32 == 0 || M == 16) && M <= 96,
+                 "adc_scan_topk_rot: needs ksub == 256 and M in {16,32,64,96} (M=%d ksub=%d)", M, ksub);
     VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && nq >= 0, "adc_scan_topk_rot: bad n/nq");
     VQ_CHECK_ARG(k > 0 && k <= 128, "adc_scan_topk_rot: k must be in [1,128], got %d", k);
     VQ_CHECK_ARG(((uintptr_t)codes_rot & 15) == 0, "adc_scan_topk_rot: codes must be 16B aligned");
@@ -630,9 +639,18 @@ static ScreenPlan plan_screen(int64_t n, int M, int nq, int k) {
     ScreenPlan s;
     // threshold sample: an eighth of the rows, between 8192 and SCREEN_SAMPLE (a smaller sample only loosens
     // the thresholds; the result stays exact)
-    int64_t ns = (n / 8) & ~(int64_t)31;
-    if (ns < 8192) ns = 8192;
-    if (ns > SCREEN_SAMPLE) ns = SCREEN_SAMPLE;
+    // (shards of at most 262 144 rows: a sixteenth, at most SAMPLE_KTH_MAX rows, scored and radix-selected by
+    // adc_sample_kth_kernel - the general path's fixed costs would dominate the whole search)
+    int64_t ns;
+    if (n <= (1 << 18) && (M == 16 || M == 32)) {
+        ns = (n / 16) & ~(int64_t)31;
+        if (ns < 4096) ns = 4096;
+        if (ns > SAMPLE_KTH_MAX) ns = SAMPLE_KTH_MAX;
+    } else {
+        ns = (n / 8) & ~(int64_t)31;
+        if (ns < 8192) ns = 8192;
+        if (ns > SCREEN_SAMPLE) ns = SCREEN_SAMPLE;
+    }
     s.n_sample = ns;
     s.ngroups = (nq + 3) / 4;
     int64_t cap = n / 256;
@@ -661,15 +679,15 @@ extern "C" size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq,
     return plan_screen(n, M, nq, k).total;
 }
 
-template <int G, bool ABS>
+template <int G, bool ABS, int GW = 32>
 static int screen_launch_g(const uint8_t* codes_rot, int64_t n, const uint32_t* qlut4, const int* thr,
                            const ScanPlan& p, int ngroups, uint32_t* cand, uint32_t* count, uint32_t cap,
                            cudaStream_t st) {
     // ABS: up to 64 KiB of padding in front of the table (it starts at a multiple of 64 KiB of the shared window)
     const size_t smem = (size_t)G * 256 * 64 * 4 + (ABS ? 65536 : 0);
-    VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G, ABS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G, ABS, GW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ngroups, (unsigned)p.nchunks);
-    adc_screen_kernel<G, ABS><<<grid, ABS ? 1024 : SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows,
+    adc_screen_kernel<G, ABS, GW><<<grid, ABS ? 1024 : SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows,
                                                                             cand, count, cap);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
@@ -680,7 +698,8 @@ static int screen_finish_launch(const uint8_t* codes_rot, int M, const float* lu
                                 const uint32_t* count, uint32_t cap, int nq, int k, int negate, float* out_vals,
                                 uint32_t* out_ids, cudaStream_t st) {
     const int n2 = next_pow2(SCAN_WARPS * k);
-    const size_t smem = (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
+    size_t smem = (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
+    if (smem < (size_t)FINISH_SORT_MAX * sizeof(uint64_t)) smem = (size_t)FINISH_SORT_MAX * sizeof(uint64_t);
     VQ_CUDA(cudaFuncSetAttribute(screen_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     screen_finish_kernel<CAP><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, M, lut, cand, count, cap, k, negate,
                                                              out_vals, out_ids);
@@ -692,8 +711,8 @@ extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, 
                                            int nq, int metric, int k, float* out_vals, uint32_t* out_ids,
                                            void* scratch, size_t scratch_bytes, void* stream) {
     VQ_CHECK_ARG(codes_rot && lut && out_vals && out_ids, "adc_scan_topk_screen: null pointer");
-    VQ_CHECK_ARG(ksub == 256 && M > 0 && M % 32 == 0 && M <= 96,
-                 "adc_scan_topk_screen: needs ksub == 256 and M in {32,64,96} (M=%d ksub=%d)", M, ksub);
+    VQ_CHECK_ARG(ksub == 256 && M > 0 && (M % 32 == 0 || M == 16) && M <= 96,
+                 "adc_scan_topk_screen: needs ksub == 256 and M in {16,32,64,96} (M=%d ksub=%d)", M, ksub);
     VQ_CHECK_ARG(n >= 0 && n < (1ll << 32) && nq >= 0, "adc_scan_topk_screen: bad n/nq");
     VQ_CHECK_ARG(k > 0 && k <= 128, "adc_scan_topk_screen: k must be in [1,128], got %d", k);
     if (nq == 0) return B200VQ_OK;
@@ -712,8 +731,18 @@ extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, 
     uint32_t* count = reinterpret_cast<uint32_t*>(base + sp.off_count);
     uint32_t* cand = reinterpret_cast<uint32_t*>(base + sp.off_cand);
     const int negate = metric == B200VQ_METRIC_IP;
-    // 1. threshold sample: exact top-k of the first n_sample rows
-    {
+    // 1. threshold sample: exact k-th best score of the first n_sample rows
+    if (sp.n_sample <= SAMPLE_KTH_MAX && (M == 16 || M == 32)) {
+        const size_t smem = (size_t)256 * 64 * 4 + (size_t)sp.n_sample * 4;
+        if (M == 16) {
+            VQ_CUDA(cudaFuncSetAttribute(adc_sample_kth_kernel<1, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            adc_sample_kth_kernel<1, 16><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
+        } else {
+            VQ_CUDA(cudaFuncSetAttribute(adc_sample_kth_kernel<1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            adc_sample_kth_kernel<1, 32><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
+        }
+        VQ_LAUNCH_CHECK();
+    } else {
         ScanPlan p = plan_scan(sp.n_sample, nq);
         int rc = (k <= 32) ? adc_scan_rot_launch<128>(codes_rot, sp.n_sample, M, lut, nq, k, negate, part, p, st)
                            : adc_scan_rot_launch<256>(codes_rot, sp.n_sample, M, lut, nq, k, negate, part, p, st);
@@ -731,7 +760,8 @@ extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, 
     {
         ScanPlan p = plan_scan(n, sp.ngroups);
         int rc;
-        switch (M / 32) {
+        if (M == 16) rc = screen_launch_g<1, true, 16>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st);
+        else switch (M / 32) {
             case 1: rc = screen_launch_g<1, true>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
             case 2: rc = screen_launch_g<2, true>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;
             default: rc = screen_launch_g<3, false>(codes_rot, n, qlut4, thr, p, sp.ngroups, cand, count, sp.cap, st); break;

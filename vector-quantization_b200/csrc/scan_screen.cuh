@@ -29,7 +29,6 @@ constexpr int SCREEN_SAMPLE = 65536;     // rows of the threshold sample
 __global__ void __launch_bounds__(256)
 screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float* __restrict__ sample_vals, int k,
                       int negate, uint8_t* __restrict__ qlut4, int* __restrict__ thr) {
-    __shared__ float red[8], redx[8];
     __shared__ float lo_s[96];
     __shared__ float amax_s[96];
     __shared__ int active_s;
@@ -38,31 +37,29 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
     const float* T = lut + (size_t)q * M * 256;
     const float sgn = negate ? -1.f : 1.f;
     if (t == 0) active_s = 0;
-    for (int m = 0; m < M; ++m) {
-        float v = sgn * T[m * 256 + t], vx = v;
+    __syncthreads();
+    // warp w reduces the tables of sub-quantizers w, w + 8, ...: eight entries per lane, min / max by shuffles
+    for (int m = w; m < M; m += 8) {
+        float v = sgn * T[m * 256 + lane], vx = v;
+#pragma unroll
+        for (int j = 1; j < 8; ++j) {
+            const float e = sgn * T[m * 256 + j * 32 + lane];
+            v = fminf(v, e);
+            vx = fmaxf(vx, e);
+        }
         for (int s = 16; s > 0; s >>= 1) {
             v = fminf(v, __shfl_xor_sync(FULL_MASK, v, s));
             vx = fmaxf(vx, __shfl_xor_sync(FULL_MASK, vx, s));
         }
         if (lane == 0) {
-            red[w] = v;
-            redx[w] = vx;
-        }
-        __syncthreads();
-        if (t == 0) {
-            float mn = red[0], mx = redx[0];
-            for (int i = 1; i < 8; ++i) {
-                mn = fminf(mn, red[i]);
-                mx = fmaxf(mx, redx[i]);
-            }
-            lo_s[m] = mn;
-            amax_s[m] = fmaxf(fabsf(mn), fabsf(mx));
+            lo_s[m] = v;
+            amax_s[m] = fmaxf(fabsf(v), fabsf(vx));
             // constant tables (the all-zero tables of sub-quantizers added by padding M to the scan layout's
             // group width) always contribute exactly lo: they take no share of the budget
-            if (mx > mn) ++active_s;
+            if (vx > v) atomicAdd(&active_s, 1);
         }
-        __syncthreads();
     }
+    __syncthreads();
     if (t == 0) {
         double sum_lo = 0.0, sum_abs = 0.0, sum_amax = 0.0;
         for (int m = 0; m < M; ++m) { sum_lo += lo_s[m]; sum_abs += fabs((double)lo_s[m]); sum_amax += (double)amax_s[m]; }
@@ -105,6 +102,128 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
     }
 }
 
+// Threshold sample of a SMALL shard (n_sample <= SAMPLE_KTH_MAX rows): one CTA per query scores the first n_sample rows
+// exactly (same tables in shared memory and the same lookups as adc_scan_rot_kernel), keeps the scores in shared memory
+// and radix-selects the k-th smallest (four 8-bit passes over the order-preserving integer image of the floats).
+// Only that value is needed (screen_prepare_kernel reads sample_vals[q * k + k - 1]); the running top-k lists, their
+// bitonic compactions and the merge launch of the general path were 60 % of a 100 000-row search (ncu, r2).
+constexpr int SAMPLE_KTH_MAX = 8192;
+template <int G, int GW>
+__global__ void __launch_bounds__(SCAN_THREADS)
+adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const float* __restrict__ lut, int k,
+                      int negate, float* __restrict__ sample_vals) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int KSUB = 256;
+    constexpr int M = G * GW;
+    constexpr int NQW = GW / 4;
+    constexpr int NV = GW / 16;
+    const int q = blockIdx.x;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* lut_s = reinterpret_cast<float*>(smem_raw);
+    constexpr size_t lut_bytes = (size_t)G * KSUB * 64 * 4;
+    uint32_t* keys = reinterpret_cast<uint32_t*>(smem_raw + lut_bytes);     // [n_sample] ordered-integer scores
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t sel_prefix, sel_k;
+
+    const float* lut_q = lut + (size_t)q * M * KSUB;
+    for (int idx = threadIdx.x; idx < G * KSUB * NQW; idx += SCAN_THREADS) {
+        const int jq = idx % NQW, kk = (idx / NQW) & (KSUB - 1), g = idx / (NQW * KSUB);
+        const float* src = lut_q + (size_t)(g * GW + 4 * jq) * KSUB + kk;
+        float4 v = make_float4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
+        float4* dst = reinterpret_cast<float4*>(lut_s + ((size_t)g * KSUB + kk) * 64 + 4 * jq);
+#pragma unroll
+        for (int rep = 0; rep * GW < 32 + GW; ++rep) dst[rep * NQW] = v;
+    }
+    __syncthreads();
+
+    const unsigned char* lbase = smem_raw;
+    const uint32_t lane4 = (uint32_t)lane << 2;
+    constexpr int UNR = 4;
+    for (int base = w * 32; base < n_sample; base += UNR * SCAN_THREADS) {
+        uint4 cv[UNR][NV * G];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            int bb = base + u * SCAN_THREADS;
+            if (bb >= n_sample) bb = base;
+            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (size_t)(bb >> 5) * G * (32 * GW));
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int h = 0; h < NV; ++h) cv[u][NV * g + h] = ld_stream_u4(cb + g * 64 + h * 32 + lane);
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const int row = base + u * SCAN_THREADS + lane;
+            float acc = 0.f;
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                uint32_t wds[NQW];
+#pragma unroll
+                for (int h = 0; h < NV; ++h) {
+                    wds[4 * h + 0] = cv[u][NV * g + h].x; wds[4 * h + 1] = cv[u][NV * g + h].y;
+                    wds[4 * h + 2] = cv[u][NV * g + h].z; wds[4 * h + 3] = cv[u][NV * g + h].w;
+                }
+#pragma unroll
+                for (int j = 0; j < NQW; ++j)
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
+                        acc += *reinterpret_cast<const float*>(lbase + off + g * (KSUB * 64 * 4) + (4 * j + b) * 4);
+                    }
+            }
+            if (row < n_sample) keys[row] = float_to_ordered(negate ? -acc : acc);
+        }
+    }
+    if (threadIdx.x == 0) {
+        sel_prefix = 0;
+        sel_k = (uint32_t)k;
+    }
+    __syncthreads();
+    // radix select: after pass p the top 8 (p + 1) bits of the k-th smallest key are known
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        hist[threadIdx.x] = 0;
+        __syncthreads();
+        const uint32_t prefix = sel_prefix, kk = sel_k;
+        for (int i = threadIdx.x; i < n_sample; i += SCAN_THREADS) {
+            const uint32_t key = keys[i];
+            if (pass == 0 || ((key ^ prefix) >> (shift + 8)) == 0) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (w == 0) {
+            uint32_t c[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                c[j] = hist[lane * 8 + j];
+                tot += c[j];
+            }
+            uint32_t incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const uint32_t excl = incl - tot;
+            if (excl < kk && kk <= incl) {           // exactly one lane: its 8 bins hold the k-th key
+                uint32_t run = excl;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (run < kk && kk <= run + c[j]) {
+                        sel_prefix = prefix | ((uint32_t)(lane * 8 + j) << shift);
+                        sel_k = kk - run;
+                    }
+                    run += c[j];
+                }
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const float v = ordered_to_float(sel_prefix);
+        sample_vals[(size_t)q * k + (k - 1)] = negate ? -v : v;
+    }
+}
+
 // ld.shared with a compile-time immediate offset from a 32-bit shared-window address
 template <int IMM>
 __device__ __forceinline__ uint32_t lds_abs(uint32_t addr) {
@@ -114,9 +233,9 @@ __device__ __forceinline__ uint32_t lds_abs(uint32_t addr) {
 }
 // Lookups of code word W (4 code bytes = 4 consecutive steps) of the 8*G words of a lane, unrolled at
 // compile time so that the group / step offsets are LDS immediates.
-template <int G, int W>
+template <int NW, int W>
 struct ScreenWords {
-    static __device__ __forceinline__ void run(const uint32_t (&wds)[8 * G], uint32_t lane4, uint32_t& lo16,
+    static __device__ __forceinline__ void run(const uint32_t (&wds)[NW], uint32_t lane4, uint32_t& lo16,
                                                uint32_t& hi16) {
         constexpr int g = W / 8, j = W % 8;
         constexpr int imm = g * (256 * 64 * 4) + (4 * j) * 4;
@@ -126,12 +245,12 @@ struct ScreenWords {
         t4 += lds_abs<imm + 12>(__byte_perm(wds[W], lane4, 0x7634u));
         lo16 += t4 & 0x00FF00FFu;
         hi16 += (t4 >> 8) & 0x00FF00FFu;
-        ScreenWords<G, W + 1>::run(wds, lane4, lo16, hi16);
+        ScreenWords<NW, W + 1>::run(wds, lane4, lo16, hi16);
     }
 };
-template <int G>
-struct ScreenWords<G, 8 * G> {
-    static __device__ __forceinline__ void run(const uint32_t (&)[8 * G], uint32_t, uint32_t&, uint32_t&) {}
+template <int NW>
+struct ScreenWords<NW, NW> {
+    static __device__ __forceinline__ void run(const uint32_t (&)[NW], uint32_t, uint32_t&, uint32_t&) {}
 };
 
 // grid (query groups of 4, row chunks). Table in shared memory as [g][code][64] uint32 (columns
@@ -140,14 +259,18 @@ struct ScreenWords<G, 8 * G> {
 // so the PRMT that merges (code << 8) with (lane << 2) also supplies the upper address bytes and
 // its result IS the LDS address (no per-lookup base add). That costs up to 64 KiB of padding, so
 // the CTA is 1024 threads (one per SM) instead of three CTAs of 256.
-template <int G, bool ABS>
+// GW = 16: the half group of M = 16 (one 128-bit code load and 16 lookups per row; table columns j = m, m + 16, m + 32).
+template <int G, bool ABS, int GW = 32>
 __global__ void __launch_bounds__(ABS ? 1024 : SCAN_THREADS)
 adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32_t* __restrict__ qlut4,
                   const int* __restrict__ thr, int64_t chunk_rows, uint32_t* __restrict__ cand,
                   uint32_t* __restrict__ count, uint32_t cap) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int KSUB = 256;
-    constexpr int M = G * 32;
+    constexpr int M = G * GW;
+    constexpr int NQW = GW / 4;          // column quads (= code words) of a group
+    constexpr int NV = GW / 16;          // 128-bit code loads of a group
+    static_assert(GW == 32 || (GW == 16 && G == 1), "group width 32, or one half group of 16");
     constexpr int THREADS = ABS ? 1024 : SCAN_THREADS;
     const int grp = blockIdx.x, chunk = blockIdx.y;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -155,13 +278,13 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
     const uint32_t tab32 = ABS ? ((base32 + 0xFFFFu) & ~0xFFFFu) : base32;
     uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw + (tab32 - base32));
     const uint32_t* src_q = qlut4 + (size_t)grp * M * KSUB;
-    for (int idx = threadIdx.x; idx < G * KSUB * 8; idx += THREADS) {
-        const int jq = idx & 7, kk = (idx >> 3) & (KSUB - 1), g = idx >> 11;
-        const uint32_t* src = src_q + (size_t)(g * 32 + 4 * jq) * KSUB + kk;
+    for (int idx = threadIdx.x; idx < G * KSUB * NQW; idx += THREADS) {
+        const int jq = idx % NQW, kk = (idx / NQW) & (KSUB - 1), g = idx / (NQW * KSUB);
+        const uint32_t* src = src_q + (size_t)(g * GW + 4 * jq) * KSUB + kk;
         uint4 v = make_uint4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
         uint4* dst = reinterpret_cast<uint4*>(tab + ((size_t)g * KSUB + kk) * 64 + 4 * jq);
-        dst[0] = v;
-        dst[8] = v;
+#pragma unroll
+        for (int rep = 0; rep * GW < 32 + GW; ++rep) dst[rep * NQW] = v;
     }
     const int t0 = thr[grp * 4 + 0], t1 = thr[grp * 4 + 1], t2 = thr[grp * 4 + 2], t3 = thr[grp * 4 + 3];
     __syncthreads();
@@ -171,42 +294,44 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
     const int64_t r0 = (int64_t)chunk * chunk_rows;  // multiple of 32
     int64_t r1 = r0 + chunk_rows;
     if (r1 > n) r1 = n;
-    constexpr int UNR = 2;
+    constexpr int UNR = GW == 32 ? 2 : 4;
     for (int64_t base = r0 + (int64_t)w * 32; base < r1; base += UNR * THREADS) {
-        uint4 cv[UNR][2 * G];
+        uint4 cv[UNR][NV * G];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             int64_t bb = base + (int64_t)u * THREADS;
             if (bb >= r1) bb = base;
-            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * 1024);
+            const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (bb >> 5) * (int64_t)G * (32 * GW));
 #pragma unroll
-            for (int g = 0; g < G; ++g) {
-                cv[u][2 * g] = ld_stream_u4(cb + g * 64 + lane);
-                cv[u][2 * g + 1] = ld_stream_u4(cb + g * 64 + 32 + lane);
-            }
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+                for (int h = 0; h < NV; ++h) cv[u][NV * g + h] = ld_stream_u4(cb + g * 64 + h * 32 + lane);
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             const int64_t row = base + (int64_t)u * THREADS + lane;
             uint32_t lo16 = 0, hi16 = 0;   // 16-bit fields: (query 0, query 2) and (query 1, query 3)
             if (ABS) {
-                uint32_t wds[8 * G];
+                uint32_t wds[NQW * G];
 #pragma unroll
-                for (int g = 0; g < G; ++g) {
-                    wds[8 * g + 0] = cv[u][2 * g].x; wds[8 * g + 1] = cv[u][2 * g].y;
-                    wds[8 * g + 2] = cv[u][2 * g].z; wds[8 * g + 3] = cv[u][2 * g].w;
-                    wds[8 * g + 4] = cv[u][2 * g + 1].x; wds[8 * g + 5] = cv[u][2 * g + 1].y;
-                    wds[8 * g + 6] = cv[u][2 * g + 1].z; wds[8 * g + 7] = cv[u][2 * g + 1].w;
-                }
-                ScreenWords<G, 0>::run(wds, lane4, lo16, hi16);
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int h = 0; h < NV; ++h) {
+                        wds[NQW * g + 4 * h + 0] = cv[u][NV * g + h].x; wds[NQW * g + 4 * h + 1] = cv[u][NV * g + h].y;
+                        wds[NQW * g + 4 * h + 2] = cv[u][NV * g + h].z; wds[NQW * g + 4 * h + 3] = cv[u][NV * g + h].w;
+                    }
+                ScreenWords<NQW * G, 0>::run(wds, lane4, lo16, hi16);
             } else {
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    const uint32_t wds[8] = {cv[u][2 * g].x, cv[u][2 * g].y, cv[u][2 * g].z, cv[u][2 * g].w,
-                                             cv[u][2 * g + 1].x, cv[u][2 * g + 1].y, cv[u][2 * g + 1].z,
-                                             cv[u][2 * g + 1].w};
+                    uint32_t wds[NQW];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
+                    for (int h = 0; h < NV; ++h) {
+                        wds[4 * h + 0] = cv[u][NV * g + h].x; wds[4 * h + 1] = cv[u][NV * g + h].y;
+                        wds[4 * h + 2] = cv[u][NV * g + h].z; wds[4 * h + 3] = cv[u][NV * g + h].w;
+                    }
+#pragma unroll
+                    for (int j = 0; j < NQW; ++j) {
                         uint32_t t4 = 0;
 #pragma unroll
                         for (int b = 0; b < 4; ++b) {
@@ -240,8 +365,48 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
     }
 }
 
-// One CTA per query: exact fp32 score of every listed row (sub-quantizers in increasing order,
-// codes read back from the scan layout), running top-k, final (value, id)-ordered k results.
+// Exact fp32 score of one row from the scan layout: code bytes, then table entries, all loads in flight together
+// (a serial loop pays two dependent L2 latencies per sub-quantizer); summed in increasing m, as the row kernel does.
+__device__ __forceinline__ float screen_exact_score(const uint8_t* __restrict__ codes_rot, int M, const float* __restrict__ T,
+                                                    uint32_t row) {
+    const uint32_t i = row & 31u;
+    float acc = 0.f;
+    if (M == 16) {      // half group: 512-byte blocks, step s of lane i = sub-quantizer (i + s) % 16
+        const uint8_t* bg = codes_rot + (size_t)(row >> 5) * 512 + (i << 4);
+        uint32_t c[16];
+#pragma unroll
+        for (int m = 0; m < 16; ++m) c[m] = __ldg(bg + (((uint32_t)m - i) & 15u));
+        float tv[16];
+#pragma unroll
+        for (int m = 0; m < 16; ++m) tv[m] = __ldg(T + m * 256 + c[m]);
+#pragma unroll
+        for (int m = 0; m < 16; ++m) acc += tv[m];
+        return acc;
+    }
+    const int G = M >> 5;
+    const uint8_t* blk = codes_rot + (size_t)(row >> 5) * G * 1024 + (i << 4);
+    for (int g = 0; g < G; ++g) {
+        const uint8_t* bg = blk + (size_t)g * 1024;
+        const float* Tg = T + (size_t)g * 32 * 256;
+        uint32_t c[32];
+#pragma unroll
+        for (int m = 0; m < 32; ++m) {
+            const uint32_t s = ((uint32_t)m - i) & 31u;
+            c[m] = __ldg(bg + ((s >> 4) << 9) + (s & 15u));
+        }
+        float tv[32];
+#pragma unroll
+        for (int m = 0; m < 32; ++m) tv[m] = __ldg(Tg + m * 256 + c[m]);
+#pragma unroll
+        for (int m = 0; m < 32; ++m) acc += tv[m];
+    }
+    return acc;
+}
+
+// One CTA per query: exact fp32 score of every listed row, final (value, id)-ordered k results. Lists of at most
+// FINISH_SORT_MAX rows (the usual case) are scored into shared memory and sorted once by the whole CTA; longer lists
+// go through the warps' running top-k.
+constexpr int FINISH_SORT_MAX = 2048;
 template <int CAP>
 __global__ void __launch_bounds__(SCAN_THREADS)
 screen_finish_kernel(const uint8_t* __restrict__ codes_rot, int M, const float* __restrict__ lut,
@@ -252,35 +417,46 @@ screen_finish_kernel(const uint8_t* __restrict__ codes_rot, int M, const float* 
     const uint32_t cnt = count[q];
     if (cnt > cap) return;     // overflow: the gated exact kernels produce this query's result
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int G = M >> 5;
-    uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_raw);
-    const int n2 = next_pow2(SCAN_WARPS * k);
-    uint64_t* mbuf = wbuf + SCAN_WARPS * CAP;
-    __shared__ uint64_t best[128];
-    WarpTopK<CAP> tk;
-    tk.init(wbuf + w * CAP, k);
     const float* T = lut + (size_t)q * M * 256;
     const uint32_t* list = cand + (size_t)q * cap;
-    const uint32_t rounds = (cnt + SCAN_THREADS - 1) / SCAN_THREADS;
-    for (uint32_t it = 0; it < rounds; ++it) {
-        const uint32_t e = it * SCAN_THREADS + threadIdx.x;
-        const bool valid = e < cnt;
-        float acc = 0.f;
-        uint32_t row = 0;
-        if (valid) {
-            row = list[e];
-            const uint32_t i = row & 31u;
-            const uint8_t* blk = codes_rot + (size_t)(row >> 5) * G * 1024 + (i << 4);
-            for (int m = 0; m < M; ++m) {
-                const uint32_t s = ((uint32_t)m - i) & 31u;
-                const uint8_t c = blk[(size_t)(m >> 5) * 1024 + ((s >> 4) << 9) + (s & 15u)];
-                acc += __ldg(T + m * 256 + c);
+    const uint64_t* best;
+    if (cnt <= (uint32_t)FINISH_SORT_MAX) {
+        uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
+        const int n2 = next_pow2((int)(cnt > (uint32_t)k ? cnt : (uint32_t)k));
+        for (int e = threadIdx.x; e < n2; e += SCAN_THREADS) {
+            uint64_t key = KEY_INF;
+            if ((uint32_t)e < cnt) {
+                const uint32_t row = list[e];
+                const float acc = screen_exact_score(codes_rot, M, T, row);
+                key = make_key(negate ? -acc : acc, row);
             }
+            keys[e] = key;
         }
-        tk.offer(valid, negate ? -acc : acc, row);
+        block_bitonic_sort(keys, n2);
+        best = keys;
+    } else {
+        uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_raw);
+        const int n2 = next_pow2(SCAN_WARPS * k);
+        uint64_t* mbuf = wbuf + SCAN_WARPS * CAP;
+        __shared__ uint64_t best_s[128];
+        WarpTopK<CAP> tk;
+        tk.init(wbuf + w * CAP, k);
+        const uint32_t rounds = (cnt + SCAN_THREADS - 1) / SCAN_THREADS;
+        for (uint32_t it = 0; it < rounds; ++it) {
+            const uint32_t e = it * SCAN_THREADS + threadIdx.x;
+            const bool valid = e < cnt;
+            float acc = 0.f;
+            uint32_t row = 0;
+            if (valid) {
+                row = list[e];
+                acc = screen_exact_score(codes_rot, M, T, row);
+            }
+            tk.offer(valid, negate ? -acc : acc, row);
+        }
+        block_emit_topk<CAP>(tk, mbuf, n2, k, best_s);
+        __syncthreads();
+        best = best_s;
     }
-    block_emit_topk<CAP>(tk, mbuf, n2, k, best);
-    __syncthreads();
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
         const uint64_t key = best[j];
         float v;

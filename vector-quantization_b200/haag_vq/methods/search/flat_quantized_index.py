@@ -22,6 +22,7 @@ import numpy as np
 import torch
 
 from b200vq import host, ops
+from b200vq.pq import scan_layout_width
 
 from haag_vq.methods.base_quantizer import BaseQuantizer
 from haag_vq.methods.base_search_index import BaseSearchIndex
@@ -108,11 +109,11 @@ class FlatQuantizedIndex(BaseSearchIndex):
                 self._codes_dev = self._quantizer.pq.unpack_codes(
                     host.to_device(np.ascontiguousarray(self._codes, dtype=np.uint8)))
             if codec.ksub == 256 and codec.M <= 96 and (codec.M % 32 == 0 or (codec.M % 16 == 0 and self._N >= 65536)):
-                # conflict-free scan layout (b200vq_pq_codes_to_scan_layout), built once per fit/load; M is
-                # padded to the layout's group width of 32 with all-zero tables (same scores bit for bit; M % 16 keeps
-                # the row-layout kernel's summation order; below 65536 rows the screen does not apply and the
-                # row layout is as fast)
-                m_pad = (codec.M + 31) // 32 * 32
+                # conflict-free scan layout (b200vq_pq_codes_to_scan_layout), built once per fit/load; M = 16 has its
+                # own half-group layout, other M are padded to the group width of 32 with all-zero tables (same
+                # scores bit for bit; M % 16 keeps the row-layout kernel's summation order; below 65536 rows the
+                # screen does not apply and the row layout is as fast)
+                m_pad = scan_layout_width(codec.M)
                 if self._codes_rot is None:
                     self._codes_rot = ops.pq_codes_to_scan_layout(codec.pad_codes_for_scan(self._codes_dev))
                 vals, ids = codec.search(self._codes_rot, q_dev, k, self._metric, n=self._N, rot=True, m_pad=m_pad)

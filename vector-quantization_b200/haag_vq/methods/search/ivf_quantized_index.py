@@ -120,14 +120,13 @@ class IvfQuantizedIndex(BaseSearchIndex):
         return ids
 
     def search_with_scores(self, Q: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray]:
+        """Any k: one device pass ranks 128 rows per query, larger k are pages chained by b200vq_ivf_search_after."""
         Q = np.ascontiguousarray(Q, dtype=np.float32)
         nq = Q.shape[0]
         if k <= 0:
             return np.empty((nq, 0), dtype=np.uint32), np.empty((nq, 0), dtype=np.float32)
         if self._dev is None:
             raise RuntimeError("IvfQuantizedIndex must be fitted or loaded before search().")
-        if k > 128:
-            raise NotImplementedError("IvfQuantizedIndex on the B200 kernels supports k <= 128")
         fmax = np.finfo(np.float32).max
         dist_sentinel = -fmax if self._metric == 'ip' else fmax
         if nq == 0 or self._dev['recon'].shape[0] == 0:

@@ -76,8 +76,10 @@ class RaBitQIndex(BaseSearchIndex):
     def search_with_scores(self, Q: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray]:
         codes = self._require_fit()
         Q = np.ascontiguousarray(Q, dtype=np.float32)
-        if k <= 0 or k > MAX_K:
-            raise ValueError(f"k must be in [1, {MAX_K}], got {k}")
+        if k <= 0:
+            raise ValueError(f"k must be positive, got {k}")
+        # k > MAX_K: pages of MAX_K chained on the device (b200vq_rabitq1_scan_topk_after); beyond ntotal the ids are
+        # 0xffffffff (faiss' -1) and the distances +-inf, as IndexRaBitQ.search returns them
         q_dev = host.to_device(Q)
         planes, qfac = ops_sq.rabitq1_prepare_queries(q_dev, self._centroid_dev, self._qb)
         vals, ids = ops_sq.rabitq1_scan_topk(codes, self._D, planes, qfac, self._qb, k, self._metric)
