@@ -48,6 +48,15 @@ elif mode == "c1adc":
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / 20
+    # survivors per query: the screen's counters inside the scratch block (layout of plan_screen, csrc/scan.cu)
+    up = lambda v: (v + 255) & ~255
+    k_ = 10
+    o = up(nq * k_ * 4); o = up(o + nq * k_ * 4); o = up(o + nq * 1 * k_ * 8)
+    ng = (nq + 3) // 4
+    o = up(o + ng * mp * 256 * 4); o = up(o + ng * 16)
+    sc = ops.scratch(0, crot.device, "scan_screen")
+    cnt = sc[o:o + nq * 4].view(torch.int32)
+    print("survivors per query: mean %.0f  median %.0f  max %d" % (cnt.float().mean().item(), cnt.float().median().item(), cnt.max().item()))
     print(f"c1adc search {ms:.3f} ms  {n * nq / ms / 1e6:.1f} G codes/s  tune={os.environ.get('B200VQ_TUNE_SAMPLE_DIV')},"
           f"{os.environ.get('B200VQ_TUNE_SAMPLE_MIN')}")
 elif mode == "rotate":

@@ -293,54 +293,83 @@ __global__ void adc_lut_kernel(const float* __restrict__ queries, int64_t ldq,
     }
 }
 
-// Batched LUT build: grid (M, ceil(nq / 32)), 256 threads. The CTA stages the 256 centroids of its
-// sub-quantizer dimension-major ([i][k]: thread k reads consecutive words) and 32 query sub-vectors
-// dimension-major ([i][32]) once, then thread k runs the same sequential fp32 chain as adc_lut_kernel
-// for four queries at a time (one centroid load per dimension serves four chains).
+// Batched LUT build: grid (M, ceil(nq / 32)), 512 threads. The CTA stages the 256 centroids of its sub-quantizer
+// dimension-major ([i][256]) and 32 query sub-vectors dimension-major ([i][32]) once; thread (kq, gq) then owns a
+// 4 x 4 register tile (centroids 4 kq .. 4 kq + 3, queries 4 gq .. 4 gq + 3) and runs, for each of its 16 entries,
+// the same sequential fp32 chain as adc_lut_kernel. Per dimension a thread issues two 128-bit shared loads for 32
+// FP instructions: the one-centroid-per-thread form (1 + 1 loads for 8 FP) was bound by shared-memory wavefronts
+// (ncu r2: 77 us at 1000 x 1536, the same with 256 or 512 threads).
 constexpr int LUT_QB = 32;
-__global__ void __launch_bounds__(256)
+constexpr int LUT_THREADS = 512;
+__global__ void __launch_bounds__(LUT_THREADS)
 adc_lut_batched_kernel(const float* __restrict__ queries, int nq, int64_t ldq, const float* __restrict__ centroids,
                        int M, int dsub, int metric, float* __restrict__ lut) {
     extern __shared__ __align__(16) float lsm[];
-    float* cs = lsm + (size_t)dsub * LUT_QB;      // [dsub][257] (padded: conflict-free transposed staging)
     float* qs = lsm;                              // [dsub][LUT_QB]
-    const int m = blockIdx.x, q0 = blockIdx.y * LUT_QB, k = threadIdx.x;
+    float* cs = lsm + (size_t)dsub * LUT_QB;      // [dsub][256]
+    const int m = blockIdx.x, q0 = blockIdx.y * LUT_QB;
     const float* cm = centroids + (size_t)m * 256 * dsub;
-    for (int idx = threadIdx.x; idx < 256 * dsub; idx += 256) {
-        const int j = idx / dsub, i = idx - j * dsub;     // coalesced global read
-        cs[i * 257 + j] = cm[idx];
+    {
+        const int k = threadIdx.x & 255, half = threadIdx.x >> 8;
+        if ((dsub & 3) == 0 && ((uintptr_t)cm & 15) == 0) {
+            // thread (k, h) copies every other quad of centroid k with 128-bit loads (independent, several in
+            // flight); the transposed stores of a warp are 32 consecutive words
+            const float4* row = reinterpret_cast<const float4*>(cm + (size_t)k * dsub);
+#pragma unroll 8
+            for (int i4 = half; i4 < (dsub >> 2); i4 += 2) {
+                const float4 v = __ldg(row + i4);
+                cs[(4 * i4 + 0) * 256 + k] = v.x;
+                cs[(4 * i4 + 1) * 256 + k] = v.y;
+                cs[(4 * i4 + 2) * 256 + k] = v.z;
+                cs[(4 * i4 + 3) * 256 + k] = v.w;
+            }
+        } else {
+            for (int i = half; i < dsub; i += 2) cs[i * 256 + k] = cm[(size_t)k * dsub + i];
+        }
     }
-    for (int idx = threadIdx.x; idx < LUT_QB * dsub; idx += 256) {
+    for (int idx = threadIdx.x; idx < LUT_QB * dsub; idx += LUT_THREADS) {
         const int qq = idx / dsub, i = idx - qq * dsub;
         qs[i * LUT_QB + qq] = (q0 + qq < nq) ? queries[(int64_t)(q0 + qq) * ldq + (int64_t)m * dsub + i] : 0.f;
     }
     __syncthreads();
-    for (int g = 0; g < LUT_QB && q0 + g < nq; g += 4) {
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        if (metric == B200VQ_METRIC_L2) {
-            for (int i = 0; i < dsub; ++i) {
-                const float c = cs[i * 257 + k];
-                const float4 qv = *reinterpret_cast<const float4*>(qs + i * LUT_QB + g);
-                const float d0 = __fsub_rn(qv.x, c), d1 = __fsub_rn(qv.y, c), d2 = __fsub_rn(qv.z, c), d3 = __fsub_rn(qv.w, c);
-                a0 = __fmaf_rn(d0, d0, a0);
-                a1 = __fmaf_rn(d1, d1, a1);
-                a2 = __fmaf_rn(d2, d2, a2);
-                a3 = __fmaf_rn(d3, d3, a3);
-            }
-        } else {
-            for (int i = 0; i < dsub; ++i) {
-                const float c = cs[i * 257 + k];
-                const float4 qv = *reinterpret_cast<const float4*>(qs + i * LUT_QB + g);
-                a0 = __fmaf_rn(qv.x, c, a0);
-                a1 = __fmaf_rn(qv.y, c, a1);
-                a2 = __fmaf_rn(qv.z, c, a2);
-                a3 = __fmaf_rn(qv.w, c, a3);
-            }
-        }
-        const float av[4] = {a0, a1, a2, a3};
+    const int kq = threadIdx.x & 63, gq = threadIdx.x >> 6;
+    float acc[4][4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-            if (q0 + g + e < nq) lut[((size_t)(q0 + g + e) * M + m) * 256 + k] = av[e];
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    const float4* cs4 = reinterpret_cast<const float4*>(cs) + kq;
+    const float4* qs4 = reinterpret_cast<const float4*>(qs) + gq;
+    if (metric == B200VQ_METRIC_L2) {
+#pragma unroll 2
+        for (int i = 0; i < dsub; ++i) {
+            const float4 c4 = cs4[i * 64], q4 = qs4[i * (LUT_QB / 4)];
+            const float cv[4] = {c4.x, c4.y, c4.z, c4.w}, qv[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const float d = __fsub_rn(qv[a], cv[b]);
+                    acc[a][b] = __fmaf_rn(d, d, acc[a][b]);
+                }
+        }
+    } else {
+#pragma unroll 2
+        for (int i = 0; i < dsub; ++i) {
+            const float4 c4 = cs4[i * 64], q4 = qs4[i * (LUT_QB / 4)];
+            const float cv[4] = {c4.x, c4.y, c4.z, c4.w}, qv[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = __fmaf_rn(qv[a], cv[b], acc[a][b]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int q = q0 + 4 * gq + a;
+        if (q < nq)
+            *reinterpret_cast<float4*>(lut + ((size_t)q * M + m) * 256 + 4 * kq) =
+                make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
     }
 }
 
@@ -536,10 +565,13 @@ extern "C" int b200vq_adc_lut(const float* queries, int nq, int64_t ldq, const f
     VQ_CHECK_ARG(M <= 65535, "adc_lut: M > 65535");
     VQ_CHECK_ARG((size_t)dsub * sizeof(float) <= 48 * 1024, "adc_lut: dsub too large");
     if (nq == 0) return B200VQ_OK;
-    const size_t bsm = ((size_t)dsub * 257 + (size_t)dsub * LUT_QB) * sizeof(float);
-    if (ksub == 256 && nq >= 8 && bsm <= 200 * 1024) {
+    const size_t bsm = ((size_t)dsub * 256 + (size_t)dsub * LUT_QB) * sizeof(float);
+    if (ksub == 256 && nq >= 8 && bsm <= 200 * 1024 && ((uintptr_t)lut & 15) == 0) {
         VQ_CUDA(cudaFuncSetAttribute(adc_lut_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsm));
-        adc_lut_batched_kernel<<<dim3((unsigned)M, (unsigned)((nq + LUT_QB - 1) / LUT_QB)), 256, bsm, as_stream(stream)>>>(
+        // two CTAs per SM need the largest shared-memory carve-out (dsub = 96: 2 x 111 KB)
+        VQ_CUDA(cudaFuncSetAttribute(adc_lut_batched_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     (int)cudaSharedmemCarveoutMaxShared));
+        adc_lut_batched_kernel<<<dim3((unsigned)M, (unsigned)((nq + LUT_QB - 1) / LUT_QB)), LUT_THREADS, bsm, as_stream(stream)>>>(
             queries, nq, ldq, centroids, M, dsub, metric, lut);
         VQ_LAUNCH_CHECK();
         return B200VQ_OK;

@@ -700,6 +700,7 @@ static int screen_finish_launch(const uint8_t* codes_rot, int M, const float* lu
     const int n2 = next_pow2(SCAN_WARPS * k);
     size_t smem = (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
     if (smem < (size_t)FINISH_SORT_MAX * sizeof(uint64_t)) smem = (size_t)FINISH_SORT_MAX * sizeof(uint64_t);
+    smem += (size_t)M * 1024;      // the query's table
     VQ_CUDA(cudaFuncSetAttribute(screen_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     screen_finish_kernel<CAP><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, M, lut, cand, count, cap, k, negate,
                                                              out_vals, out_ids);
@@ -736,10 +737,10 @@ extern "C" int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, 
         const size_t smem = (size_t)256 * 64 * 4 + (size_t)sp.n_sample * 4;
         if (M == 16) {
             VQ_CUDA(cudaFuncSetAttribute(adc_sample_kth_kernel<1, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            adc_sample_kth_kernel<1, 16><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
+            adc_sample_kth_kernel<1, 16><<<nq, SAMPLE_KTH_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
         } else {
             VQ_CUDA(cudaFuncSetAttribute(adc_sample_kth_kernel<1, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            adc_sample_kth_kernel<1, 32><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
+            adc_sample_kth_kernel<1, 32><<<nq, SAMPLE_KTH_THREADS, smem, st>>>(codes_rot, (int)sp.n_sample, lut, k, negate, s_vals);
         }
         VQ_LAUNCH_CHECK();
     } else {

@@ -108,8 +108,9 @@ screen_prepare_kernel(const float* __restrict__ lut, int nq, int M, const float*
 // Only that value is needed (screen_prepare_kernel reads sample_vals[q * k + k - 1]); the running top-k lists, their
 // bitonic compactions and the merge launch of the general path were 60 % of a 100 000-row search (ncu, r2).
 constexpr int SAMPLE_KTH_MAX = 8192;
+constexpr int SAMPLE_KTH_THREADS = 512;
 template <int G, int GW>
-__global__ void __launch_bounds__(SCAN_THREADS)
+__global__ void __launch_bounds__(SAMPLE_KTH_THREADS)
 adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const float* __restrict__ lut, int k,
                       int negate, float* __restrict__ sample_vals) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -126,7 +127,7 @@ adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const
     __shared__ uint32_t sel_prefix, sel_k;
 
     const float* lut_q = lut + (size_t)q * M * KSUB;
-    for (int idx = threadIdx.x; idx < G * KSUB * NQW; idx += SCAN_THREADS) {
+    for (int idx = threadIdx.x; idx < G * KSUB * NQW; idx += SAMPLE_KTH_THREADS) {
         const int jq = idx % NQW, kk = (idx / NQW) & (KSUB - 1), g = idx / (NQW * KSUB);
         const float* src = lut_q + (size_t)(g * GW + 4 * jq) * KSUB + kk;
         float4 v = make_float4(src[0], src[KSUB], src[2 * KSUB], src[3 * KSUB]);
@@ -139,11 +140,11 @@ adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const
     const unsigned char* lbase = smem_raw;
     const uint32_t lane4 = (uint32_t)lane << 2;
     constexpr int UNR = 4;
-    for (int base = w * 32; base < n_sample; base += UNR * SCAN_THREADS) {
+    for (int base = w * 32; base < n_sample; base += UNR * SAMPLE_KTH_THREADS) {
         uint4 cv[UNR][NV * G];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
-            int bb = base + u * SCAN_THREADS;
+            int bb = base + u * SAMPLE_KTH_THREADS;
             if (bb >= n_sample) bb = base;
             const uint4* cb = reinterpret_cast<const uint4*>(codes_rot + (size_t)(bb >> 5) * G * (32 * GW));
 #pragma unroll
@@ -153,7 +154,7 @@ adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
-            const int row = base + u * SCAN_THREADS + lane;
+            const int row = base + u * SAMPLE_KTH_THREADS + lane;
             float acc = 0.f;
 #pragma unroll
             for (int g = 0; g < G; ++g) {
@@ -182,10 +183,10 @@ adc_sample_kth_kernel(const uint8_t* __restrict__ codes_rot, int n_sample, const
     // radix select: after pass p the top 8 (p + 1) bits of the k-th smallest key are known
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
-        hist[threadIdx.x] = 0;
+        if (threadIdx.x < 256) hist[threadIdx.x] = 0;
         __syncthreads();
         const uint32_t prefix = sel_prefix, kk = sel_k;
-        for (int i = threadIdx.x; i < n_sample; i += SCAN_THREADS) {
+        for (int i = threadIdx.x; i < n_sample; i += SAMPLE_KTH_THREADS) {
             const uint32_t key = keys[i];
             if (pass == 0 || ((key ^ prefix) >> (shift + 8)) == 0) atomicAdd(&hist[(key >> shift) & 255u], 1u);
         }
@@ -365,40 +366,52 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
     }
 }
 
-// Exact fp32 score of one row from the scan layout: code bytes, then table entries, all loads in flight together
-// (a serial loop pays two dependent L2 latencies per sub-quantizer); summed in increasing m, as the row kernel does.
-__device__ __forceinline__ float screen_exact_score(const uint8_t* __restrict__ codes_rot, int M, const float* __restrict__ T,
+// Rotate the 4 * NW bytes held in w[0 .. NW) left by r byte positions towards lower indices: byte j of the result is
+// byte (j + r) % (4 NW) of the input (a barrel shifter: funnel shifts for r % 4, conditional word moves for r / 4).
+template <int NW>
+__device__ __forceinline__ void rotate_bytes_down(uint32_t (&w)[NW], uint32_t r) {
+    const uint32_t bits = (r & 3u) * 8u;
+    uint32_t t[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) t[j] = __funnelshift_r(w[j], w[(j + 1) % NW], bits);
+#pragma unroll
+    for (int sh = 1; sh < NW; sh <<= 1) {
+        const bool on = ((r >> 2) & (uint32_t)sh) != 0;
+        uint32_t u[NW];
+#pragma unroll
+        for (int j = 0; j < NW; ++j) u[j] = on ? t[(j + sh) % NW] : t[j];
+#pragma unroll
+        for (int j = 0; j < NW; ++j) t[j] = u[j];
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) w[j] = t[j];
+}
+
+// Exact fp32 score of one row from the scan layout: the row's codes are one (M = 16) or two 128-bit loads per group,
+// rotated so that byte m is sub-quantizer m (lane i stores sub-quantizer (i + s) % GW at step s); the table entries
+// come from the query's table T (shared memory) and are summed in increasing m, as the row kernel does.
+__device__ __forceinline__ float screen_exact_score(const uint8_t* __restrict__ codes_rot, int M, const float* T,
                                                     uint32_t row) {
     const uint32_t i = row & 31u;
     float acc = 0.f;
-    if (M == 16) {      // half group: 512-byte blocks, step s of lane i = sub-quantizer (i + s) % 16
-        const uint8_t* bg = codes_rot + (size_t)(row >> 5) * 512 + (i << 4);
-        uint32_t c[16];
+    if (M == 16) {      // half group: 512-byte blocks
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(codes_rot + (size_t)(row >> 5) * 512 + (i << 4)));
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        rotate_bytes_down<4>(w, (16u - (i & 15u)) & 15u);     // byte m <- step (m - i) % 16
 #pragma unroll
-        for (int m = 0; m < 16; ++m) c[m] = __ldg(bg + (((uint32_t)m - i) & 15u));
-        float tv[16];
-#pragma unroll
-        for (int m = 0; m < 16; ++m) tv[m] = __ldg(T + m * 256 + c[m]);
-#pragma unroll
-        for (int m = 0; m < 16; ++m) acc += tv[m];
+        for (int m = 0; m < 16; ++m) acc += T[m * 256 + ((w[m >> 2] >> ((m & 3) * 8)) & 0xFFu)];
         return acc;
     }
     const int G = M >> 5;
     const uint8_t* blk = codes_rot + (size_t)(row >> 5) * G * 1024 + (i << 4);
     for (int g = 0; g < G; ++g) {
-        const uint8_t* bg = blk + (size_t)g * 1024;
+        const uint4 v0 = __ldg(reinterpret_cast<const uint4*>(blk + (size_t)g * 1024));
+        const uint4 v1 = __ldg(reinterpret_cast<const uint4*>(blk + (size_t)g * 1024 + 512));
+        uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        rotate_bytes_down<8>(w, (32u - i) & 31u);             // byte m <- step (m - i) % 32
         const float* Tg = T + (size_t)g * 32 * 256;
-        uint32_t c[32];
 #pragma unroll
-        for (int m = 0; m < 32; ++m) {
-            const uint32_t s = ((uint32_t)m - i) & 31u;
-            c[m] = __ldg(bg + ((s >> 4) << 9) + (s & 15u));
-        }
-        float tv[32];
-#pragma unroll
-        for (int m = 0; m < 32; ++m) tv[m] = __ldg(Tg + m * 256 + c[m]);
-#pragma unroll
-        for (int m = 0; m < 32; ++m) acc += tv[m];
+        for (int m = 0; m < 32; ++m) acc += Tg[m * 256 + ((w[m >> 2] >> ((m & 3) * 8)) & 0xFFu)];
     }
     return acc;
 }
@@ -417,25 +430,36 @@ screen_finish_kernel(const uint8_t* __restrict__ codes_rot, int M, const float* 
     const uint32_t cnt = count[q];
     if (cnt > cap) return;     // overflow: the gated exact kernels produce this query's result
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const float* T = lut + (size_t)q * M * 256;
+    // the query's table in shared memory: M KB read once, coalesced (gathering it from L2 entry by entry cost a
+    // 32-byte sector per look-up: 13x the bytes at 400 rows per query)
+    float* T = reinterpret_cast<float*>(smem_raw);
+    {
+        const float4* src = reinterpret_cast<const float4*>(lut + (size_t)q * M * 256);
+        float4* dst = reinterpret_cast<float4*>(T);
+        for (int idx = threadIdx.x; idx < M * 64; idx += SCAN_THREADS) dst[idx] = __ldg(src + idx);
+    }
+    __syncthreads();
+    unsigned char* smem_top = smem_raw + (size_t)M * 1024;
     const uint32_t* list = cand + (size_t)q * cap;
     const uint64_t* best;
     if (cnt <= (uint32_t)FINISH_SORT_MAX) {
-        uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
+        uint64_t* keys = reinterpret_cast<uint64_t*>(smem_top);
         const int n2 = next_pow2((int)(cnt > (uint32_t)k ? cnt : (uint32_t)k));
-        for (int e = threadIdx.x; e < n2; e += SCAN_THREADS) {
-            uint64_t key = KEY_INF;
-            if ((uint32_t)e < cnt) {
-                const uint32_t row = list[e];
-                const float acc = screen_exact_score(codes_rot, M, T, row);
-                key = make_key(negate ? -acc : acc, row);
-            }
-            keys[e] = key;
+        // two list entries per thread and pass: the gathers of both rows are in flight together
+        for (int e = threadIdx.x; e < n2; e += 2 * SCAN_THREADS) {
+            const int e1 = e + SCAN_THREADS;
+            const bool v0 = (uint32_t)e < cnt, v1 = (uint32_t)e1 < cnt;
+            const uint32_t row0 = v0 ? list[e] : 0u, row1 = v1 ? list[e1] : 0u;
+            float acc0 = 0.f, acc1 = 0.f;
+            if (v0) acc0 = screen_exact_score(codes_rot, M, T, row0);
+            if (v1) acc1 = screen_exact_score(codes_rot, M, T, row1);
+            keys[e] = v0 ? make_key(negate ? -acc0 : acc0, row0) : KEY_INF;
+            if (e1 < n2) keys[e1] = v1 ? make_key(negate ? -acc1 : acc1, row1) : KEY_INF;
         }
         block_bitonic_sort(keys, n2);
         best = keys;
     } else {
-        uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_raw);
+        uint64_t* wbuf = reinterpret_cast<uint64_t*>(smem_top);
         const int n2 = next_pow2(SCAN_WARPS * k);
         uint64_t* mbuf = wbuf + SCAN_WARPS * CAP;
         __shared__ uint64_t best_s[128];

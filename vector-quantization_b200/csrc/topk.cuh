@@ -16,10 +16,17 @@ __host__ __device__ __forceinline__ int next_pow2(int v) {
 
 // Sort keys[0..n2) ascending with the whole CTA. n2 must be a power of two.
 // Ends with a __syncthreads().
+// A warp's 32 consecutive compare-exchange slots t touch one aligned block of 64 keys whenever stride <= 32, and the
+// slot -> thread map is the same in every stage: consecutive stages with stride <= 32 only need a warp barrier
+// (10 CTA barriers instead of 45 for 512 keys; the CTA barrier per stage was 65 % of the screened scan's finish).
 __device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, int n2) {
+    bool wide_prev = true;      // the keys were written by arbitrary threads
     for (int size = 2; size <= n2; size <<= 1) {
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            __syncthreads();
+            const bool wide = stride >= 64;
+            if (wide || wide_prev) __syncthreads();
+            else __syncwarp();
+            wide_prev = wide;
             for (int t = threadIdx.x; t < (n2 >> 1); t += blockDim.x) {
                 int lo = 2 * t - (t & (stride - 1));
                 int hi = lo + stride;
