@@ -33,7 +33,7 @@ def timed(fn, reps=5):
     return a.elapsed_time(b) / reps, r
 
 t0, (v0, i0) = timed(lambda: codec.search(codes, q, 10, "l2"))
-t1, (v1, i1) = timed(lambda: codec.search(crot, q, 10, "l2", n=n, rot=True, m_pad=32))
+t1, (v1, i1) = timed(lambda: codec.search(crot, q, 10, "l2", n=n, rot=True))
 print(f"n={n} nq={nq} M=16: row layout {t0:.3f} ms ({n*nq/t0/1e6:.1f} G codes/s)  padded scan layout {t1:.3f} ms "
       f"({n*nq/t1/1e6:.1f} G codes/s)  identical={bool(torch.equal(i0, i1) and torch.equal(v0.view(torch.int32), v1.view(torch.int32)))}")
 if not torch.equal(i0, i1) or not torch.equal(v0.view(torch.int32), v1.view(torch.int32)):

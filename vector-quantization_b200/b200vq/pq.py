@@ -186,6 +186,8 @@ class PQCodec:
         m_pad: the codes were padded to m_pad sub-quantizers (pad_codes_for_scan); the tables are padded with zeros."""
         if screen is None:
             screen = rot
+        if rot and m_pad is None:
+            m_pad = scan_layout_width(self.M)
         nq = queries.shape[0]
         vals = torch.empty((nq, k), dtype=torch.float32, device=queries.device)
         ids = torch.empty((nq, k), dtype=torch.int32, device=queries.device)
