@@ -684,7 +684,7 @@ static int screen_launch_g(const uint8_t* codes_rot, int64_t n, const uint32_t* 
                            const ScanPlan& p, int ngroups, uint32_t* cand, uint32_t* count, uint32_t cap,
                            cudaStream_t st) {
     // ABS: up to 64 KiB of padding in front of the table (it starts at a multiple of 64 KiB of the shared window)
-    const size_t smem = (size_t)G * 256 * 64 * 4 + (ABS ? 65536 : 0);
+    const size_t smem = (size_t)G * 256 * 64 * 4 + (ABS ? 65536 : 0) + (size_t)4 * SCREEN_LCAP * 4;
     VQ_CUDA(cudaFuncSetAttribute(adc_screen_kernel<G, ABS, GW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)ngroups, (unsigned)p.nchunks);
     adc_screen_kernel<G, ABS, GW><<<grid, ABS ? 1024 : SCAN_THREADS, smem, st>>>(codes_rot, n, qlut4, thr, p.chunk_rows,

@@ -22,6 +22,7 @@ namespace b200vq {
 
 constexpr int SCREEN_QMAX = 63;          // 6-bit entries
 constexpr int SCREEN_SAMPLE = 65536;     // rows of the threshold sample
+constexpr int SCREEN_LCAP = 512;         // survivors per (CTA, query) buffered in shared memory
 
 // One CTA (256 threads) per query: lo[m] = min_c T'[m][c] (T' = -T for inner product), the step
 // from the threshold budget, the integer threshold, and this query's byte lane of the packed
@@ -288,6 +289,12 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
         for (int rep = 0; rep * GW < 32 + GW; ++rep) dst[rep * NQW] = v;
     }
     const int t0 = thr[grp * 4 + 0], t1 = thr[grp * 4 + 1], t2 = thr[grp * 4 + 2], t3 = thr[grp * 4 + 3];
+    // survivors are collected per CTA in shared memory (SCREEN_LCAP per query) and appended to the global lists with
+    // one atomic per query at the end: a global atomicAdd with a return value inside the scan loop stalled the warp
+    // for a memory round trip whenever one of its 128 (row, query) pairs survived (40 % of the iterations at C1)
+    __shared__ uint32_t s_cnt[4], s_base[4];
+    uint32_t* lbuf = tab + (size_t)G * KSUB * 64;          // [4][SCREEN_LCAP]
+    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0u;
     __syncthreads();
 
     // second PRMT operand: byte 0 = lane * 4, bytes 2..3 = upper bytes of the table address (ABS)
@@ -356,13 +363,32 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
                     const unsigned mk = __ballot_sync(FULL_MASK, ps[qq]);
                     if (mk) {
                         uint32_t pos = 0;
-                        if (lane == 0) pos = atomicAdd(count + grp * 4 + qq, (uint32_t)__popc(mk));
+                        if (lane == 0) pos = atomicAdd(&s_cnt[qq], (uint32_t)__popc(mk));
                         pos = __shfl_sync(FULL_MASK, pos, 0) + __popc(mk & ((1u << lane) - 1u));
-                        if (ps[qq] && pos < cap) cand[(size_t)(grp * 4 + qq) * cap + pos] = (uint32_t)row;
+                        if (ps[qq]) {
+                            if (pos < (uint32_t)SCREEN_LCAP) {
+                                lbuf[qq * SCREEN_LCAP + pos] = (uint32_t)row;
+                            } else {        // local buffer full (dense survivors): straight to the global list
+                                const uint32_t gp = atomicAdd(count + grp * 4 + qq, 1u);
+                                if (gp < cap) cand[(size_t)(grp * 4 + qq) * cap + gp] = (uint32_t)row;
+                            }
+                        }
                     }
                 }
             }
         }
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        const uint32_t nloc = min(s_cnt[threadIdx.x], (uint32_t)SCREEN_LCAP);
+        s_base[threadIdx.x] = nloc ? atomicAdd(count + grp * 4 + threadIdx.x, nloc) : 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int qq = 0; qq < 4; ++qq) {
+        const uint32_t nloc = min(s_cnt[qq], (uint32_t)SCREEN_LCAP), gb = s_base[qq];
+        for (uint32_t i2 = threadIdx.x; i2 < nloc; i2 += THREADS)
+            if (gb + i2 < cap) cand[(size_t)(grp * 4 + qq) * cap + gb + i2] = lbuf[qq * SCREEN_LCAP + i2];
     }
 }
 
