@@ -165,6 +165,9 @@ def _load_oracle_pq():
     lib.oracle_pq_assign_dec.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
                                      ctypes.c_int, ctypes.c_void_p]
     lib.oracle_pq_assign_dec.restype = ctypes.c_int
+    # all host cores, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for its workers); liboracle_adc.so shares
+    # the same OpenMP runtime
+    lib.oracle_pq_set_threads(ctypes.c_int(os.cpu_count() or 1))
     return lib
 
 

@@ -8,6 +8,11 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include <omp.h>
+
+/* torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU arm asks for its threads explicitly. */
+void oracle_pq_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int oracle_pq_max_threads(void) { return omp_get_max_threads(); }
 
 int oracle_pq_assign_dec(const float* x, int64_t n, int D, const float* cent, int M, int ksub, uint8_t* codes) {
     const int dsub = D / M;

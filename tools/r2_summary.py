@@ -25,6 +25,11 @@ w("TF32 = 678 TF/s).\n")
 
 for name in sorted(glob.glob(os.path.join(P, "r2_bench_*.json"))):
     d = last_json(name)
+    if d.get("impl") == "reference":
+        c = d["cpu_baseline"]
+        w(f"## `{os.path.basename(name)}` — bench.py --impl reference (CPU arm, {c['cores']} host cores)\n")
+        w(f"* {d['value']:.0f} vectors/s encoded, {d['adc']['value']/1e6:.0f} M codes/s scanned; {c['sample']}\n")
+        continue
     w(f"## `{os.path.basename(name)}` — bench.py, N={d['n_gpus']}\n")
     w(f"* workload: {d['config']['workload']}")
     w(f"* value: **{d['value']/1e6:.1f} M vectors/s** encoded, **{d['adc']['value']/1e9:.1f} G codes/s** ADC "
@@ -80,7 +85,9 @@ w("|---|---:|---:|---:|---:|---:|---:|---:|---:|---|---:|")
 for name in sorted(glob.glob(os.path.join(P, "r2_ncu_*.csv"))):
     for r in csv.DictReader(open(name)):
         g = lambda key: next((float(v) for kk, v in r.items() if kk.startswith(key) and v not in ("", None)), 0.0)
-        w(f"| {r['kernel']} ({os.path.basename(name)[7:-4]}) | {g('gpu__time_duration'):.3f} | "
+        tkey = next(kk for kk in r if kk.startswith('gpu__time_duration'))
+        scale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(tkey[tkey.index('[') + 1:tkey.index(']')], 1.0)
+        w(f"| {r['kernel']} ({os.path.basename(name)[7:-4]}) | {g('gpu__time_duration') * scale:.3f} | "
           f"{float(r.get('dram_bytes_total') or 0)/1e6:.0f} | {g('sm__pipe_tensor_cycles_active'):.0f} | "
           f"{g('sm__inst_executed_pipe_tmem'):.1f} | {g('smsp__issue_active'):.0f} | "
           f"{g('l1tex__data_pipe_lsu_wavefronts_mem_shared'):.0f} | {g('lts__throughput'):.0f} | "
