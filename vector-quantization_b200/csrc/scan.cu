@@ -699,10 +699,12 @@ static int screen_finish_launch(const uint8_t* codes_rot, int M, const float* lu
                                 uint32_t* out_ids, cudaStream_t st) {
     const int n2 = next_pow2(SCAN_WARPS * k);
     size_t smem = (size_t)(SCAN_WARPS * CAP + n2) * sizeof(uint64_t);
-    if (smem < (size_t)FINISH_SORT_MAX * sizeof(uint64_t)) smem = (size_t)FINISH_SORT_MAX * sizeof(uint64_t);
+    // lists up to half the capacity (at most FINISH_SEL_MAX rows) take the select path: keys in shared memory
+    uint32_t sel_max = cap / 2 < (uint32_t)FINISH_SEL_MAX ? cap / 2 : (uint32_t)FINISH_SEL_MAX;
+    if (smem < (size_t)sel_max * sizeof(uint64_t)) smem = (size_t)sel_max * sizeof(uint64_t);
     smem += (size_t)M * 1024;      // the query's table
     VQ_CUDA(cudaFuncSetAttribute(screen_finish_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    screen_finish_kernel<CAP><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, M, lut, cand, count, cap, k, negate,
+    screen_finish_kernel<CAP><<<nq, SCAN_THREADS, smem, st>>>(codes_rot, M, lut, cand, count, cap, k, negate, sel_max,
                                                              out_vals, out_ids);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
