@@ -42,6 +42,59 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, int n2) {
     __syncthreads();
 }
 
+// k-th smallest (1 <= k <= n) of n order-preserving integer images of floats (float_to_ordered) in shared memory,
+// found by a radix select: four passes over 8-bit digits, most significant first (histogram with shared atomics,
+// warp 0 locates the digit). Whole CTA, any multiple of 32 threads; `hist` = 256 words and `sel` = 2 words of shared
+// memory. Duplicates count with their multiplicity. A sort is only needed where the ORDER of the k keys matters.
+__device__ __forceinline__ uint32_t block_kth_smallest(const uint32_t* keys, int n, uint32_t k, uint32_t* hist,
+                                                       uint32_t* sel) {
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        sel[0] = 0u;
+        sel[1] = k;
+    }
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        __syncthreads();
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0u;
+        __syncthreads();
+        const uint32_t prefix = sel[0], kk = sel[1];
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const uint32_t key = keys[i];
+            if (pass == 0 || ((key ^ prefix) >> (shift + 8)) == 0u) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t c[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                c[j] = hist[lane * 8 + j];
+                tot += c[j];
+            }
+            uint32_t incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL_MASK, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const uint32_t excl = incl - tot;
+            if (excl < kk && kk <= incl) {           // exactly one lane: its 8 bins hold the k-th key
+                uint32_t run = excl;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (run < kk && kk <= run + c[j]) {
+                        sel[0] = prefix | ((uint32_t)(lane * 8 + j) << shift);
+                        sel[1] = kk - run;
+                    }
+                    run += c[j];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    return sel[0];
+}
+
 // Emit the CTA's best k: gather every warp's sorted list into `mbuf`
 // (n2 = pow2 >= SCAN_WARPS*k), sort, write k keys to dst.
 template <int CAP>
