@@ -75,6 +75,15 @@ __device__ __forceinline__ void flag_chunk(const float (&v)[64], float thr, uint
 #undef B200VQ_FA8
 #undef B200VQ_FA
 }
+template <int CB>   // 32-column form (J = CB * 32 + i): halves the live accumulator values
+__device__ __forceinline__ void flag_chunk32(const float (&v)[32], float thr, uint32_t one, uint32_t (&ia)[4]) {
+#define B200VQ_FA(i) flag_accumulate<CB * 32 + (i)>(v[i], thr, one, ia[(i) & 3]);
+#define B200VQ_FA8(b) B200VQ_FA(b) B200VQ_FA(b + 1) B200VQ_FA(b + 2) B200VQ_FA(b + 3) \
+                      B200VQ_FA(b + 4) B200VQ_FA(b + 5) B200VQ_FA(b + 6) B200VQ_FA(b + 7)
+    B200VQ_FA8(0) B200VQ_FA8(8) B200VQ_FA8(16) B200VQ_FA8(24)
+#undef B200VQ_FA8
+#undef B200VQ_FA
+}
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
     float m;
     asm("min.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(a), "f"(b), "f"(c));
@@ -575,14 +584,18 @@ __global__ void __launch_bounds__(THREADS, 1)
             xoff[u] = off ^ (((off >> 7) & swz) << 4);
         }
         uint32_t st = 0, a_phase = 0, t_phase = 0, unit = 0;
-        for (int64_t item = blockIdx.x; item < p.nitems; item += gridDim.x) {
-            const int g = (int)(item % p.groups);
-            const int64_t rc = item / p.groups;
-            const int64_t t0 = rc * p.tiles_per_item;
-            int64_t t1 = t0 + p.tiles_per_item;
-            if (t1 > p.ntiles) t1 = p.ntiles;
-            for (int64_t t = t0; t < t1; ++t) {
-                const int64_t row = t * TILE_ROWS + r;
+        // 32-bit loop state (n < 2^32 rows: tile and item counts fit): the 64-bit form spilled four loop variables
+        // to local memory, whose reloads sat on the critical path of every slice
+        const uint32_t nitems32 = (uint32_t)p.nitems, ntiles32 = (uint32_t)p.ntiles, tpi32 = (uint32_t)p.tiles_per_item;
+        for (uint32_t item = blockIdx.x; item < nitems32; item += gridDim.x) {
+            const int g = (int)(item % (uint32_t)p.groups);
+            const uint32_t rc = item / (uint32_t)p.groups;
+            const uint32_t t0 = rc * tpi32;
+            uint32_t t1 = t0 + tpi32;
+            if (t1 > ntiles32) t1 = ntiles32;
+            for (uint32_t t = t0; t < t1; ++t) {
+                const uint32_t row32 = t * (uint32_t)TILE_ROWS + (uint32_t)r;
+                const int64_t row = (int64_t)row32;
                 const bool live = row < p.n;
                 mbar_wait(bar(BAR_A_FULL + st), a_phase);
                 // units alternate between the two accumulator stages: this warp takes every second one
@@ -613,22 +626,20 @@ __global__ void __launch_bounds__(THREADS, 1)
                     mbar_wait(bar(BAR_T_FULL + acc), t_phase);
                     tc_fence_after();
                     const uint32_t taddr = lane_addr + acc * 256u + hf * 128u;
-                    float v[64];
-                    // pass 1: minimum of this warp's 128 columns (two 64-column TMEM loads)
+                    float v[32];
+                    // pass 1: minimum of this warp's 128 columns (four 32-column TMEM loads: 64-column loads kept
+                    // 64 values live next to the loop state and ptxas spilled that state to local memory)
                     float mn = __int_as_float(0x7f800000);
 #pragma unroll
-                    for (int cb = 0; cb < 2; ++cb) {
+                    for (int cb = 0; cb < 4; ++cb) {
                         if (dbg & 8) break;
-                        tmem_ld64(taddr + cb * 64, v);
-                        float t[22];
+                        tmem_ld32(taddr + cb * 32, v);
+                        float t[10];
 #pragma unroll
-                        for (int k = 0; k < 21; ++k) t[k] = fmin3(v[3 * k], v[3 * k + 1], v[3 * k + 2]);
-                        t[21] = v[63];
-                        float u0 = fmin3(t[0], t[1], t[2]), u1 = fmin3(t[3], t[4], t[5]), u2 = fmin3(t[6], t[7], t[8]);
-                        float u3 = fmin3(t[9], t[10], t[11]), u4 = fmin3(t[12], t[13], t[14]);
-                        float u5 = fmin3(t[15], t[16], t[17]), u6 = fmin3(t[18], t[19], t[20]);
-                        float w0 = fmin3(u0, u1, u2), w1 = fmin3(u3, u4, u5), w2 = fmin3(u6, t[21], mn);
-                        mn = fmin3(w0, w1, w2);
+                        for (int k = 0; k < 10; ++k) t[k] = fmin3(v[3 * k], v[3 * k + 1], v[3 * k + 2]);
+                        const float u0 = fmin3(t[0], t[1], t[2]), u1 = fmin3(t[3], t[4], t[5]), u2 = fmin3(t[6], t[7], t[8]);
+                        const float u3 = fmin3(t[9], v[30], v[31]);
+                        mn = fmin3(fmin3(u0, u1, u2), u3, mn);
                     }
                     xch[hf * 32 + lane] = mn;
                     if (hf == 1) {
@@ -646,10 +657,14 @@ __global__ void __launch_bounds__(THREADS, 1)
                     //   the upper fields are exact whenever the count is <= 2, which is all that reads them)
                     uint32_t ia[4] = {0, 0, 0, 0};
                     if (dbg & 1) { ia[0] = 1; } else {
-                    tmem_ld64(taddr, v);
-                    flag_chunk<0>(v, thr, one, ia);
-                    tmem_ld64(taddr + 64, v);
-                    flag_chunk<1>(v, thr, one, ia);
+                    tmem_ld32(taddr, v);
+                    flag_chunk32<0>(v, thr, one, ia);
+                    tmem_ld32(taddr + 32, v);
+                    flag_chunk32<1>(v, thr, one, ia);
+                    tmem_ld32(taddr + 64, v);
+                    flag_chunk32<2>(v, thr, one, ia);
+                    tmem_ld32(taddr + 96, v);
+                    flag_chunk32<3>(v, thr, one, ia);
                     }
                     const uint32_t isum = (ia[0] + ia[1]) + (ia[2] + ia[3]);
                     tc_fence_before();
