@@ -59,6 +59,16 @@ elif mode == "c1adc":
     print("survivors per query: mean %.0f  median %.0f  max %d" % (cnt.float().mean().item(), cnt.float().median().item(), cnt.max().item()))
     print(f"c1adc search {ms:.3f} ms  {n * nq / ms / 1e6:.1f} G codes/s  tune={os.environ.get('B200VQ_TUNE_SAMPLE_DIV')},"
           f"{os.environ.get('B200VQ_TUNE_SAMPLE_MIN')}")
+elif mode == "c1enc":
+    # C1 encode: 100 000 x 1536, M = 16 (dsub = 96)
+    n, D, M = 100_000, 1536, 16
+    x = data(n, D)
+    C = dpq.pq_train(x[:65536], M, 8, niter=4, seed=1234)
+    codec = dpq.PQCodec(C)
+    codes = codec.encode(x)
+    for _ in range(3):
+        codec.encode(x, out=codes)
+    torch.cuda.synchronize()
 elif mode == "rotate":
     n, D = 262_144, 1536
     x = data(n, D)
