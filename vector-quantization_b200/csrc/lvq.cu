@@ -298,6 +298,60 @@ __global__ void __launch_bounds__(256) lvq_decode_kernel(const uint8_t* __restri
     }
 }
 
+// Decode with float4-granular lane ownership (B = 8, 4, 2; D % 4 == 0): a lane owns four consecutive dimensions =
+// B/2 code bytes, so a warp's loads are 32 B (B) consecutive bytes and its stores 512 consecutive bytes (the 8-dimension
+// form stored two float4 per lane at a 32-byte lane pitch: half of every 32-byte sector per store instruction). Two
+// rows per warp step keep twice the loads in flight. Same arithmetic: fl(lo + fl(q delta)) + mu.
+template <int B>
+__global__ void __launch_bounds__(256) lvq_decode4_kernel(const uint8_t* __restrict__ codes, int64_t n, int D,
+                                                          const float* __restrict__ mu, float* __restrict__ out,
+                                                          int64_t ldo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int index_bytes = (D * B) >> 3, code_size = index_bytes + 8;
+    auto field4 = [&](const uint8_t* code, int j, unsigned (&q)[4]) {
+        if (B == 8) {
+            const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(code + j));
+            q[0] = w & 0xFFu; q[1] = (w >> 8) & 0xFFu; q[2] = (w >> 16) & 0xFFu; q[3] = w >> 24;
+        } else if (B == 4) {
+            const uint32_t h = __ldg(reinterpret_cast<const uint16_t*>(code + (j >> 1)));
+            q[0] = (h >> 4) & 15u; q[1] = h & 15u; q[2] = (h >> 12) & 15u; q[3] = (h >> 8) & 15u;
+        } else {
+            const uint32_t b = __ldg(code + (j >> 2));
+            q[0] = (b >> 6) & 3u; q[1] = (b >> 4) & 3u; q[2] = (b >> 2) & 3u; q[3] = b & 3u;
+        }
+    };
+    for (int64_t row = 2 * wid; row < n; row += 2 * nw) {
+        const bool two = row + 1 < n;
+        const uint8_t* c0 = codes + row * (int64_t)code_size;
+        const uint8_t* c1 = two ? c0 + code_size : c0;
+        const float lo0 = lvq_load_f32(c0 + index_bytes), de0 = lvq_load_f32(c0 + index_bytes + 4);
+        const float lo1 = lvq_load_f32(c1 + index_bytes), de1 = lvq_load_f32(c1 + index_bytes + 4);
+        float* o0 = out + row * ldo;
+        float* o1 = o0 + ldo;
+#pragma unroll 2
+        for (int j = 4 * lane; j < D; j += 128) {
+            unsigned q0[4], q1[4];
+            field4(c0, j, q0);
+            field4(c1, j, q1);
+            const float4 m = __ldg(reinterpret_cast<const float4*>(mu + j));
+            const float4 r0 = make_float4(__fadd_rn(__fadd_rn(lo0, __fmul_rn((float)q0[0], de0)), m.x),
+                                          __fadd_rn(__fadd_rn(lo0, __fmul_rn((float)q0[1], de0)), m.y),
+                                          __fadd_rn(__fadd_rn(lo0, __fmul_rn((float)q0[2], de0)), m.z),
+                                          __fadd_rn(__fadd_rn(lo0, __fmul_rn((float)q0[3], de0)), m.w));
+            *reinterpret_cast<float4*>(o0 + j) = r0;
+            if (two) {
+                const float4 r1 = make_float4(__fadd_rn(__fadd_rn(lo1, __fmul_rn((float)q1[0], de1)), m.x),
+                                              __fadd_rn(__fadd_rn(lo1, __fmul_rn((float)q1[1], de1)), m.y),
+                                              __fadd_rn(__fadd_rn(lo1, __fmul_rn((float)q1[2], de1)), m.z),
+                                              __fadd_rn(__fadd_rn(lo1, __fmul_rn((float)q1[3], de1)), m.w));
+                *reinterpret_cast<float4*>(o1 + j) = r1;
+            }
+        }
+    }
+}
+
 // Column means in numpy's order: X.mean(axis=0) of a C-contiguous float32 matrix adds row after row
 // into an fp32 accumulator per column, then divides by n in fp32. One thread per column; 16 rows of
 // loads in flight before their (sequential) adds.
@@ -359,6 +413,18 @@ extern "C" int b200vq_lvq_decode(const uint8_t* codes, int64_t n, int D, const f
     VQ_CHECK_ARG(num_bits >= 1 && num_bits <= 8, "lvq_decode: num_bits must be in [1, 8], got %d", num_bits);
     if (n == 0) return B200VQ_OK;
     VQ_CHECK_ARG(codes && mu && out, "lvq_decode: null pointer");
+    const int code_size = ((D * num_bits + 7) >> 3) + 8;
+    const bool fast = (num_bits == 8 || num_bits == 4 || num_bits == 2) && D % 4 == 0 && ldo % 4 == 0 &&
+                      ((uintptr_t)out & 15) == 0 && ((uintptr_t)mu & 15) == 0 &&
+                      (num_bits == 2 || (((uintptr_t)codes % (num_bits / 2)) == 0 && code_size % (num_bits / 2) == 0));
+    if (fast) {
+        const int g = lvq_grid((n + 1) / 2);
+        if (num_bits == 8) lvq_decode4_kernel<8><<<g, 256, 0, as_stream(stream)>>>(codes, n, D, mu, out, ldo);
+        else if (num_bits == 4) lvq_decode4_kernel<4><<<g, 256, 0, as_stream(stream)>>>(codes, n, D, mu, out, ldo);
+        else lvq_decode4_kernel<2><<<g, 256, 0, as_stream(stream)>>>(codes, n, D, mu, out, ldo);
+        VQ_LAUNCH_CHECK();
+        return B200VQ_OK;
+    }
     lvq_decode_kernel<<<lvq_grid(n), 256, 0, as_stream(stream)>>>(codes, n, D, mu, num_bits, out, ldo);
     VQ_LAUNCH_CHECK();
     return B200VQ_OK;
