@@ -34,7 +34,8 @@ def test_lvq_matches_reference_golden(golden_dir, D):
         LVQQuantizer(num_bits=9)
 
 
-@pytest.mark.parametrize("D,B", [(1536, 8), (1536, 4), (1024, 2), (387, 5), (7, 3), (3072, 1)])
+@pytest.mark.parametrize("D,B", [(1536, 8), (1536, 4), (1024, 2), (387, 5), (7, 3), (3072, 1), (3072, 8), (2048, 2), (1540, 6),
+                                 (512, 6)])
 def test_lvq_matches_oracle_larger(D, B):
     from haag_vq.methods.lvq_quantization import LVQQuantizer
     rng = np.random.default_rng(D + B)
