@@ -26,7 +26,8 @@ P est_screen est_screen_kernel 4 4 python tools/r2_prof_est.py
 P est_pool est_pool_kernel 3 3 python tools/r2_prof_est.py
 P erq_pack erabitq_pack_tc 1 1 python tools/r2_prof_est.py
 P erq_fixup erabitq_fixup_kernel 1 1 python tools/r2_prof_est.py
-P lvq_encode lvq_encode_reg_kernel 3 1 python tools/config_bench.py c3 gpurun_out/_c3.json
+P lvq_encode lvq_encode2p_kernel 3 1 python tools/config_bench.py c3 gpurun_out/_c3.json
+P lvq_decode lvq_decode4_kernel 3 1 python tools/config_bench.py c3 gpurun_out/_c3.json
 P saq_encode saq_encode_vec_kernel 3 1 python tools/config_bench.py c3 gpurun_out/_c3.json
 P rq1_encode rabitq1_encode_vec_kernel 3 1 python tools/config_bench.py c4 gpurun_out/_c4.json
 P c1_lut adc_lut_batched_kernel 3 1 python tools/r2_prof.py c1adc
