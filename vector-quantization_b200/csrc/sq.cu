@@ -520,12 +520,12 @@ saq_decode_vec_kernel(const uint8_t* __restrict__ codes, int64_t n, int D, const
             for (int j = 0; j < 4; ++j) v[j] = dequant(j, (uint32_t)(win >> (wsh[j] & 63)) & ((1u << nb[j]) - 1u));
             reinterpret_cast<float4*>(out + r * ldo)[c4] = make_float4(v[0], v[1], v[2], v[3]);
         };
-        for (; row + 3 * step < n; row += 4 * step) {
-            uint64_t win[4];
+        for (; row + 7 * step < n; row += 8 * step) {
+            uint64_t win[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) win[u] = fetch(row + u * step);
+            for (int u = 0; u < 8; ++u) win[u] = fetch(row + u * step);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) emit(row + u * step, win[u]);
+            for (int u = 0; u < 8; ++u) emit(row + u * step, win[u]);
         }
         for (; row < n; row += step) emit(row, fetch(row));
         return;
