@@ -138,3 +138,46 @@ def test_half_group_layout_m16_overflow_and_small_k(T):
     assert torch.equal(i0, i1) and torch.equal(v0, v1)
     vr, _ = T.ops.adc_scan_topk(same, lut, 10, "ip")
     assert torch.allclose(vr, v1, rtol=2e-6)
+
+
+@pytest.mark.parametrize("n,M,k,metric,kind", [
+    (100_000, 32, 10, "l2", "uniform"),       # small shard: radix-select threshold sample (adc_sample_kth_kernel<1, 32>)
+    (262_144, 32, 64, "ip", "signed"),        # large k: k n / sample would crowd the lists - general sample path
+    (262_144, 32, 10, "ip", "signed"),        # 320 expected survivors: general sample path
+    (200_000, 32, 8, "ip", "signed"),         # the small-sample path near its limit
+    (262_145, 32, 10, "l2", "uniform"),       # one row more: the general sample path
+    (70_000, 16, 33, "ip", "signed"),         # half group, k > 32 (CAP = 256 instantiations)
+    (65_536, 64, 5, "l2", "signed"),          # M = 64 keeps the general sample at every size
+])
+def test_small_shard_threshold_sample_paths(T, n, M, k, metric, kind):
+    """Shards of at most 262 144 rows take their threshold from adc_sample_kth_kernel (M = 16 / 32); results must
+    stay those of the exact kernels on both sides of the switch."""
+    torch = T.torch
+    codes, lut = _case(T, n, M, 11, seed=n % 97 + M, lut_kind=kind)
+    rot = T.ops.pq_codes_to_scan_layout(codes)
+    v0, i0 = T.ops.adc_scan_topk(codes, lut, k, metric)
+    v1, i1 = T.ops.adc_scan_topk(rot, lut, k, metric, n=n, rot=True, screen=True)
+    assert torch.equal(i0, i1)
+    # values: the row-layout kernel and the scan-layout kernels add the M table entries in different orders (and a
+    # query whose list overflows comes from the gated exact scan-layout kernel): equal to fp32 summation accuracy
+    assert torch.allclose(v0, v1, rtol=2e-6, atol=1e-6)
+    if kind == "uniform" and k <= 33:
+        assert torch.equal(v0.view(torch.int32), v1.view(torch.int32))
+    assert (v1[:, 1:] >= v1[:, :-1]).all() if metric == "l2" else (v1[:, 1:] <= v1[:, :-1]).all()
+
+
+def test_adc_lut_unaligned_output_takes_the_scalar_kernel(T):
+    """The 4 x 4-tile LUT kernel stores 128-bit words: an output buffer that is not 16-byte aligned goes through
+    adc_lut_kernel; same bits either way."""
+    torch = T.torch
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, dsub, nq = 8, 24, 37
+    C = torch.randn((M, 256, dsub), device="cuda", generator=g)
+    Q = torch.randn((nq, M * dsub), device="cuda", generator=g)
+    ref = T.ops.adc_lut(Q, C, "l2")
+    buf = torch.empty(nq * M * 256 + 1, device="cuda")
+    out = buf[1:]                                   # 4-byte aligned only
+    from b200vq import _lib
+    rc = _lib.load().b200vq_adc_lut(Q.data_ptr(), nq, Q.stride(0), C.data_ptr(), M, 256, dsub, 0, out.data_ptr(), None)
+    assert rc == 0
+    assert torch.equal(out.view(nq, M, 256).view(torch.int32), ref.view(torch.int32))

@@ -641,12 +641,13 @@ static ScreenPlan plan_screen(int64_t n, int M, int nq, int k) {
     // the thresholds; the result stays exact)
     // (shards of at most 262 144 rows: a sixteenth, at most SAMPLE_KTH_MAX rows, scored and radix-selected by
     // adc_sample_kth_kernel - the general path's fixed costs would dominate the whole search)
-    int64_t ns;
-    if (n <= (1 << 18) && (M == 16 || M == 32)) {
-        ns = (n / 16) & ~(int64_t)31;
-        if (ns < 4096) ns = 4096;
-        if (ns > SAMPLE_KTH_MAX) ns = SAMPLE_KTH_MAX;
-    } else {
+    int64_t ns = (n / 16) & ~(int64_t)31;
+    if (ns < 4096) ns = 4096;
+    if (ns > SAMPLE_KTH_MAX) ns = SAMPLE_KTH_MAX;
+    // (about k n / ns rows survive a threshold taken from ns rows - several times more when the 6-bit bound is loose:
+    // the small sample only while that estimate stays below a sixteenth of the candidate lists,
+    // otherwise large k or wide-range tables would overflow them into the exact fallback)
+    if (!(n <= (1 << 18) && (M == 16 || M == 32) && (int64_t)k * n <= 256 * ns)) {
         ns = (n / 8) & ~(int64_t)31;
         if (ns < 8192) ns = 8192;
         if (ns > SCREEN_SAMPLE) ns = SCREEN_SAMPLE;
