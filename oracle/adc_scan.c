@@ -73,3 +73,38 @@ void oracle_pq_assign(const float* x, int64_t n, int D, const float* centroids, 
         }
     }
 }
+
+/* Top-k scan without the n-sized score matrix: queries are shared out over the threads, each keeps a sorted list of
+ * its k best (score, id) pairs (ascending score, lower id first on ties; inner product callers pass negated tables).
+ * The scores are those of oracle_adc_scores (same loop, same order). k <= 1024. */
+int oracle_adc_topk(const uint8_t* codes, int64_t n, int M, int ksub, const float* lut, int nq, int k,
+                    float* out_vals, int64_t* out_ids) {
+    if (k < 1 || k > 1024) return -1;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int q = 0; q < nq; ++q) {
+        const float* L = lut + (size_t)q * M * ksub;
+        float bv[1024];
+        int64_t bi[1024];
+        int cnt = 0;
+        for (int64_t i = 0; i < n; ++i) {
+            const uint8_t* c = codes + (size_t)i * M;
+            float a = 0.f;
+            for (int m = 0; m < M; ++m) a += L[(size_t)m * ksub + c[m]];
+            if (cnt == k && !(a < bv[k - 1])) continue;      /* ids ascend: an equal score never displaces */
+            int p = cnt < k ? cnt : k - 1;
+            while (p > 0 && bv[p - 1] > a) {
+                bv[p] = bv[p - 1];
+                bi[p] = bi[p - 1];
+                --p;
+            }
+            bv[p] = a;
+            bi[p] = i;
+            if (cnt < k) ++cnt;
+        }
+        for (int j = 0; j < k; ++j) {
+            out_vals[(size_t)q * k + j] = j < cnt ? bv[j] : FLT_MAX;
+            out_ids[(size_t)q * k + j] = j < cnt ? bi[j] : -1;
+        }
+    }
+    return 0;
+}

@@ -118,6 +118,34 @@ def test_openmp_assign_port_equals_the_numpy_oracle(n, D, M, ksub):
     assert lib.oracle_pq_assign_dec(None, ctypes.c_int64(0), 30, None, 4, 16, None) == -1     # D % M != 0
 
 
+def test_openmp_topk_scan_equals_scores_then_sorted_topk():
+    """oracle_adc_topk (the CPU arm's scan in bench.py) == oracle_adc_scores followed by the (value, id)-ordered top-k."""
+    rng = np.random.default_rng(4)
+    n, M, nq = 30000, 8, 5
+    codes = rng.integers(0, 256, (n, M), dtype=np.uint8)
+    codes[17] = codes[3]
+    codes[29999] = codes[3]              # exact ties: the lower id comes first
+    lut = rng.random((nq, M, 256), dtype=np.float32)
+    lib = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "liboracle_adc.so"))
+    for k in (1, 10, 100):
+        vals = np.empty((nq, k), np.float32)
+        ids = np.empty((nq, k), np.int64)
+        rc = lib.oracle_adc_topk(codes.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(n), M, 256,
+                                 lut.ctypes.data_as(ctypes.c_void_p), nq, k, vals.ctypes.data_as(ctypes.c_void_p),
+                                 ids.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0
+        ov, oi = opq.topk_sorted(opq.adc_scores(codes, lut), k, opq.L2)
+        assert np.array_equal(ids.astype(np.uint32), oi) and np.allclose(vals, ov, rtol=1e-6)
+    # fewer rows than k: padded with (FLT_MAX, -1)
+    vals = np.empty((nq, 8), np.float32)
+    ids = np.empty((nq, 8), np.int64)
+    lib.oracle_adc_topk(codes.ctypes.data_as(ctypes.c_void_p), ctypes.c_int64(5), M, 256,
+                        lut.ctypes.data_as(ctypes.c_void_p), nq, 8, vals.ctypes.data_as(ctypes.c_void_p),
+                        ids.ctypes.data_as(ctypes.c_void_p))
+    assert (ids[:, 5:] == -1).all() and (ids[:, :5] >= 0).all()
+    assert lib.oracle_adc_topk(None, ctypes.c_int64(0), M, 256, None, 0, 0, None, None) == -1
+
+
 def test_adc_equals_distance_to_reconstruction_and_c_port():
     rng = np.random.default_rng(1)
     X = rng.standard_normal((1000, 32)).astype(np.float32)
