@@ -548,48 +548,80 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
     const int dpad = (D + 15) & ~15;
     uint8_t* idx = reinterpret_cast<uint8_t*>(bd + L) + (size_t)w * dpad * 3;  // [warps][D] indices
     uint16_t* flist = reinterpret_cast<uint16_t*>(idx + dpad);                 // [warps][D] flagged coordinates
+    // fp32 copy of the bounds for the level search of pass 1 (the exact fp64 search is only needed for coordinates
+    // within the error bound of a mid-point, and those are re-evaluated anyway)
+    __shared__ float bd32[256];
+    __shared__ float bmax_s;
     for (int i = tid; i < L; i += blockDim.x) lv[i] = levels[i];
-    for (int i = tid; i < L - 1; i += blockDim.x) bd[i] = bounds[i];
+    for (int i = tid; i < L - 1; i += blockDim.x) {
+        bd[i] = bounds[i];
+        bd32[i] = (float)bounds[i];
+    }
+    if (tid == 0) bmax_s = fmaxf(fabsf((float)bounds[0]), fabsf((float)bounds[L - 2])) * 1.000001f;   // sorted bounds
     __syncthreads();
+    const float bmax = bmax_s;
     const int ibytes = (D * B + 7) >> 3;
     const int code_size = ibytes + 8;
     const double sqrt_d = sqrt((double)D);
-    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + tid) >> 5;
+    const int64_t wid = ((int64_t)blockIdx.x * blockDim.x >> 5) + __shfl_sync(FULL_MASK, tid >> 5, 0);
     const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    // a lane's four coordinates are B / 2 whole bytes for B = 8, 4, 2: stored straight from registers
+    const int galign = B == 8 ? 4 : (B == 4 ? 2 : 1);
+    const bool direct = (B == 8 || B == 4 || B == 2) && (D & 3) == 0 && (code_size % galign) == 0 &&
+                        (reinterpret_cast<uintptr_t>(codes) % galign) == 0;
     unsigned long long nfix_total = 0;
+    unsigned ndef_lane = 0;
     for (int64_t row = wid; row < n; row += nw) {
         const double nr = nrm[row];
         const double nsafe = fmax(nr, 1e-12);
         const double sc = sqrt_d / nsafe;
         const double eps_s = (err_rel * nr + err_abs) * sc;
+        const float sc32 = (float)sc;
+        // fp32 margin: eps_s plus the rounding of s32 = fl(y fl(sc)) (2^-23 relative) and of the fp32 bounds (2^-24)
+        const float eps32 = (float)(eps_s * 1.000001);
         const float* yr = y ? y + row * ldy : nullptr;
+        uint8_t* code = codes + row * (int64_t)code_size;
         double num = 0.0, den = 0.0;
         int nflag = 0;
         // pass 1: four consecutive coordinates per lane and step (one 128-bit load when the row allows it)
         const bool vec4 = yr && ((reinterpret_cast<uintptr_t>(yr) & 15) == 0);
-        for (int d0 = 0; d0 < D; d0 += 128) {
-            const int db = d0 + 4 * lane;
-            float yv[4] = {0.f, 0.f, 0.f, 0.f};
-            if (yr) {
-                if (vec4 && db + 3 < D) {
-                    const float4 v = __ldg(reinterpret_cast<const float4*>(yr + db));
-                    yv[0] = v.x; yv[1] = v.y; yv[2] = v.z; yv[3] = v.w;
+        // (the next step's 128-bit load is issued before this step's arithmetic: with one load in flight per lane
+        // 14 % of the samples waited on it)
+        auto load4 = [&](int dbase) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (yr && dbase < D) {
+                if (vec4 && dbase + 3 < D) {
+                    v = __ldg(reinterpret_cast<const float4*>(yr + dbase));
                 } else {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (db + e < D) yv[e] = __ldg(yr + db + e);
+                    if (dbase + 0 < D) v.x = __ldg(yr + dbase + 0);
+                    if (dbase + 1 < D) v.y = __ldg(yr + dbase + 1);
+                    if (dbase + 2 < D) v.z = __ldg(yr + dbase + 2);
+                    if (dbase + 3 < D) v.w = __ldg(yr + dbase + 3);
                 }
             }
+            return v;
+        };
+        float4 vnext = load4(4 * lane);
+        for (int d0 = 0; d0 < D; d0 += 128) {
+            const int db = d0 + 4 * lane;
+            const float4 vcur = vnext;
+            vnext = load4(db + 128);
+            const float yv[4] = {vcur.x, vcur.y, vcur.z, vcur.w};
+            unsigned fmask = 0, los = 0;      // flag bits and the four indices (8 bits each) of this lane's coordinates
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int d = db + e;
-                bool flag = false, deferred = false;
                 if (d < D) {
                     if (yr) {
-                        const double sv = (double)yv[e] * sc;
-                        const int lo = erabitq_level_of(bd, L, sv);
-                        flag = (lo > 0 && sv - bd[lo - 1] < eps_s) || (lo < L - 1 && bd[lo] - sv < eps_s);
+                        const float s32 = __fmul_rn(yv[e], sc32);
+                        int lo = 0;                      // number of bounds < s32 (branch-free: L is a power of two)
+                        for (int step = L >> 1; step > 0; step >>= 1)
+                            if (bd32[lo + step - 1] < s32) lo += step;
+                        const float margin = eps32 + 5e-7f * (fabsf(s32) + bmax);
+                        bool flag = (lo > 0 && s32 - bd32[lo - 1] < margin) || (lo < L - 1 && bd32[lo] - s32 < margin);
                         idx[d] = (uint8_t)lo;
+                        los |= (unsigned)lo << (8 * e);
+                        const double sv = (double)yv[e] * sc;
                         const double sh = lv[lo];
                         num = fma(sv, sh, num);
                         den = fma(sh, sh, den);
@@ -601,17 +633,33 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
                             if (pos < bcap) {
                                 bucket[(size_t)d * bcap + pos] = ((unsigned long long)row << 8) | (unsigned long long)lo;
                                 flag = false;
-                                deferred = true;
+                                ++ndef_lane;
                             }
                         }
+                        if (flag) fmask |= 1u << e;
                     } else {
-                        flag = true;
+                        fmask |= 1u << e;
                     }
                 }
-                const unsigned m = __ballot_sync(FULL_MASK, flag);
-                if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)d;
-                nflag += __popc(m);
-                if (bcnt) nfix_total += (unsigned long long)__popc(__ballot_sync(FULL_MASK, deferred));
+            }
+            if (direct && db < D) {
+                if (B == 8) {
+                    *reinterpret_cast<uint32_t*>(code + db) = los;
+                } else if (B == 4) {
+                    const unsigned b0 = ((los & 0xFu) << 4) | ((los >> 8) & 0xFu), b1 = (((los >> 16) & 0xFu) << 4) | (los >> 24);
+                    *reinterpret_cast<uint16_t*>(code + (db >> 1)) = (uint16_t)(b0 | (b1 << 8));
+                } else {
+                    code[db >> 2] = (uint8_t)(((los & 3u) << 6) | (((los >> 8) & 3u) << 4) | (((los >> 16) & 3u) << 2) | (los >> 24));
+                }
+            }
+            if (__any_sync(FULL_MASK, fmask != 0u)) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool flag = (fmask >> e) & 1u;
+                    const unsigned m = __ballot_sync(FULL_MASK, flag);
+                    if (flag) flist[nflag + __popc(m & ((1u << lane) - 1u))] = (uint16_t)(db + e);
+                    nflag += __popc(m);
+                }
             }
         }
         __syncwarp();
@@ -667,7 +715,7 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
             den += __shfl_xor_sync(FULL_MASK, den, o);
         }
         __syncwarp();
-        uint8_t* code = codes + row * (int64_t)code_size;
+        if (!(direct && nflag == 0))
         for (int byte = lane; byte < ibytes; byte += 32) {       // MSB-first B-bit packing, one lane per output byte
             const int b0 = byte * 8, b1 = b0 + 8;
             uint32_t acc = 0;
@@ -694,6 +742,8 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
         }
         __syncwarp();
     }
+    for (int o = 16; o > 0; o >>= 1) ndef_lane += __shfl_xor_sync(FULL_MASK, ndef_lane, o);
+    nfix_total += ndef_lane;
     if (stats && lane == 0 && nfix_total) atomicAdd(stats, nfix_total);
 }
 
