@@ -532,14 +532,16 @@ __device__ __forceinline__ int erabitq_level_of(const double* bd, int L, double 
     return lo;
 }
 
-template <typename T>
+// BT = B at compile time (4 or 8: the level search and the packing unroll), 0 = any B
+template <typename T, int BT>
 __global__ void __launch_bounds__(256, 4)
 erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __restrict__ x, int64_t ldx,
                        const double* __restrict__ c, const double* __restrict__ PT, const double* __restrict__ nrm,
-                       int64_t n, int D, int B, const double* __restrict__ levels, const double* __restrict__ bounds,
+                       int64_t n, int D, int B_rt, const double* __restrict__ levels, const double* __restrict__ bounds,
                        double err_rel, double err_abs, uint8_t* __restrict__ codes, unsigned long long* __restrict__ stats,
                        unsigned* __restrict__ bcnt, unsigned long long* __restrict__ bucket, unsigned bcap,
                        double* __restrict__ numden) {
+    const int B = BT ? BT : B_rt;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* lv = reinterpret_cast<double*>(smem_raw);        // [2^B]
     double* bd = lv + (1 << B);                              // [2^B - 1] (padded to 2^B)
@@ -615,8 +617,14 @@ erabitq_pack_tc_kernel(const float* __restrict__ y, int64_t ldy, const T* __rest
                     if (yr) {
                         const float s32 = __fmul_rn(yv[e], sc32);
                         int lo = 0;                      // number of bounds < s32 (branch-free: L is a power of two)
-                        for (int step = L >> 1; step > 0; step >>= 1)
-                            if (bd32[lo + step - 1] < s32) lo += step;
+                        if (BT) {
+#pragma unroll
+                            for (int step = (1 << (BT ? BT : 1)) >> 1; step > 0; step >>= 1)
+                                if (bd32[lo + step - 1] < s32) lo += step;
+                        } else {
+                            for (int step = L >> 1; step > 0; step >>= 1)
+                                if (bd32[lo + step - 1] < s32) lo += step;
+                        }
                         const float margin = eps32 + 5e-7f * (fabsf(s32) + bmax);
                         bool flag = (lo > 0 && s32 - bd32[lo - 1] < margin) || (lo < L - 1 && bd32[lo] - s32 < margin);
                         idx[d] = (uint8_t)lo;
@@ -1228,17 +1236,24 @@ int pack_tc_impl(const float* y, int64_t ldy, const void* x, int x_is_f64, int64
     int64_t g = (n + 7) / 8;
     const int64_t cap = (int64_t)device_sm_count() * 8;
     if (g > cap) g = cap;
+#define B200VQ_PACK_LAUNCH(TY, BTV)                                                                                  \
+    do {                                                                                                            \
+        VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<TY, BTV>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                     (int)smem));                                                                   \
+        erabitq_pack_tc_kernel<TY, BTV><<<(int)g, 256, smem, st>>>(                                                  \
+            y, ldy, reinterpret_cast<const TY*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs,      \
+            codes, stats, bcnt, bucket, pp.bcap, numden);                                                           \
+    } while (0)
     if (x_is_f64) {
-        VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        erabitq_pack_tc_kernel<double><<<(int)g, 256, smem, st>>>(
-            y, ldy, reinterpret_cast<const double*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes,
-            stats, bcnt, bucket, pp.bcap, numden);
+        if (B == 4) B200VQ_PACK_LAUNCH(double, 4);
+        else if (B == 8) B200VQ_PACK_LAUNCH(double, 8);
+        else B200VQ_PACK_LAUNCH(double, 0);
     } else {
-        VQ_CUDA(cudaFuncSetAttribute(erabitq_pack_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        erabitq_pack_tc_kernel<float><<<(int)g, 256, smem, st>>>(
-            y, ldy, reinterpret_cast<const float*>(x), ldx, c, PT, nrm, n, D, B, levels, bounds, err_rel, err_abs, codes,
-            stats, bcnt, bucket, pp.bcap, numden);
+        if (B == 4) B200VQ_PACK_LAUNCH(float, 4);
+        else if (B == 8) B200VQ_PACK_LAUNCH(float, 8);
+        else B200VQ_PACK_LAUNCH(float, 0);
     }
+#undef B200VQ_PACK_LAUNCH
     VQ_LAUNCH_CHECK();
     if (bcnt) {
         const int ibytes = (D * B + 7) >> 3;
