@@ -156,8 +156,10 @@ int b200vq_adc_scan_topk_static(const uint8_t* codes, int64_t n, int M, int ksub
  * bytes, byte s = its code for sub-quantizer (i+s) mod 32 of the group (so at step s
  * the 32 lanes address 32 distinct table columns = 32 distinct banks); the bytes are
  * stored as two 16-byte halves, each half contiguous across the 32 lanes:
- * out[block*1024 + (s/16)*512 + i*16 + s%16]. Requires M % 32 == 0, M <= 96; out has
- * ceil(n/32)*32*M bytes (rows past n are padding). */
+ * out[block*1024 + (s/16)*512 + i*16 + s%16]. Requires M % 32 == 0, M <= 96, or M == 16: the
+ * half-group layout of BASELINE config 1 - blocks of 32 rows x 16 bytes (512 B), byte s of lane i =
+ * sub-quantizer (i+s) mod 16, out[block*512 + i*16 + s]. out has ceil(n/32)*32*M bytes (rows past n
+ * are padding). */
 int b200vq_pq_codes_to_scan_layout(const uint8_t* codes, int64_t n, int M, uint8_t* out,
                                    void* stream);
 int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksub,
@@ -169,9 +171,11 @@ int b200vq_adc_scan_topk_rot(const uint8_t* codes_rot, int64_t n, int M, int ksu
  * scores, (value, id) order), obtained faster for large n. The table entries of four queries are
  * quantised to 6 bits and packed into one 32-bit word, so one shared-memory lookup serves four
  * queries; the integer sum is a rigorous lower bound of the score and only rows that can still
- * reach the top-k (threshold = exact k-th best of a 65 536-row sample) are re-evaluated exactly.
+ * reach the top-k (threshold = exact k-th best of a sample: n/8 rows up to 65 536, or n/16 rows up
+ * to 8192 for shards of at most 262 144 rows while k n / sample <= 256) are re-evaluated exactly.
  * Queries whose survivor list overflows are re-done by the exact kernel. Falls back to the exact
- * scan for n < 524 288, nq < 4 or k > 64. Scratch: b200vq_adc_scan_screen_scratch_bytes. */
+ * scan for n < 65 536, nq < 4 or k > 64. M in {16, 32, 64, 96}.
+ * Scratch: b200vq_adc_scan_screen_scratch_bytes. */
 size_t b200vq_adc_scan_screen_scratch_bytes(int64_t n, int M, int nq, int k);
 int b200vq_adc_scan_topk_screen(const uint8_t* codes_rot, int64_t n, int M, int ksub,
                                 const float* lut, int nq, int metric, int k, float* out_vals,
