@@ -358,10 +358,11 @@ adc_screen_kernel(const uint8_t* __restrict__ codes_rot, int64_t n, const uint32
                             const uint32_t off = __byte_perm(wds[j], lane4, 0x5504u | ((uint32_t)b << 4));
                             t4 += *reinterpret_cast<const uint32_t*>(smem_raw + off + g * (KSUB * 64 * 4) + (4 * j + b) * 4);
                         }
-                        lo16 += t4 & 0x00FF00FFu;
-                        hi16 += (t4 >> 8) & 0x00FF00FFu;
+                        lo16 = imad_acc(t4, one, lo16);                                    // whole words (see ScreenWords)
+                        hi16 = imad_acc(__byte_perm(t4, 0u, 0x4341u), one, hi16);
                     }
                 }
+                lo16 -= hi16 << 8;
             }
             const bool live = row < r1;
             const bool p0 = live && (int)(lo16 & 0xFFFFu) <= t0;
